@@ -1,0 +1,609 @@
+/* sumo_flatten -- REFERENCE-SIDE integration shim (not part of libsumob200.so).
+ *
+ * This is the piece a SUMO maintainer adds on their side of the drop-in boundary:
+ * it is compiled against the reference headers and linked with the reference's own loader objects (NLBuilder, NLHandler,
+ * MSRouteHandler, ...), lets the UNCHANGED loader build MSNet from net/route/sumocfg input, then walks
+ * MSEdge/MSLane/MSLink/MSJunctionLogic/MSTrafficLightLogic/MSVehicleType/MSRoute/SUMOVehicle and writes the flattened
+ * arrays of include/sumob200_flatfile.h.  The engine never sees MS* objects.
+ *
+ * It doubles as the parity harness: with --trace-out it then runs the reference's own MSNet::simulationStep and
+ * records, per step, every on-road vehicle's (numerical id, lane, pos, speed) as raw fp64 -- the ground truth the
+ * "-m gpu" parity tests compare the CUDA engine with bit for bit.
+ *
+ * usage: sumo_flatten --flat-out X.flat [--trace-out X.trace] <any sumo options: -n net -r routes / -c cfg ...>
+ *
+ * Build: oracle/build_ref.sh flatten   (objects come from the reference sources under /root/reference, outputs into
+ * oracle/_ref/, never committed).
+ */
+#include <config.h>
+#include <version.h>
+#include <microsim/MSLink.h>
+#include <microsim/MSNet.h>
+#include <microsim/MSEdge.h>
+#include <microsim/MSLane.h>
+#include <microsim/MSJunction.h>
+#include <microsim/MSJunctionLogic.h>
+#include <microsim/MSRoute.h>
+#include <microsim/MSGlobals.h>
+#include <microsim/MSVehicle.h>
+#include <microsim/MSVehicleType.h>
+#include <microsim/MSVehicleControl.h>
+#include <microsim/MSInsertionControl.h>
+#include <microsim/cfmodels/MSCFModel.h>
+#include <microsim/traffic_lights/MSTLLogicControl.h>
+#include <microsim/traffic_lights/MSTrafficLightLogic.h>
+#include <microsim/traffic_lights/MSSimpleTrafficLightLogic.h>
+#include <netload/NLBuilder.h>
+#include <utils/common/MsgHandler.h>
+#include <utils/common/RandHelper.h>
+#include <utils/common/SystemFrame.h>
+#include <utils/common/StringUtils.h>
+#include <utils/options/OptionsCont.h>
+#include <utils/options/OptionsIO.h>
+#include <utils/xml/XMLSubSys.h>
+#include <utils/iodevices/OutputDevice.h>
+#include <traci-server/TraCIServer.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../include/sumob200_flatfile.h"
+
+namespace {
+
+// MSLink::myRadius / myAmCont / myAmContOff / myHavePedestrianCrossingFoe have no getters (MSLink.h:728ff); read them through
+// the explicit-instantiation access idiom instead of patching the reference header.
+template<typename Tag, typename Tag::type M> struct Rob {
+    friend typename Tag::type get(Tag) {
+        return M;
+    }
+};
+struct RadiusTag {
+    typedef double MSLink::* type;
+    friend type get(RadiusTag);
+};
+template struct Rob<RadiusTag, &MSLink::myRadius>;
+struct AmContTag {
+    typedef bool MSLink::* type;
+    friend type get(AmContTag);
+};
+template struct Rob<AmContTag, &MSLink::myAmCont>;
+struct AmContOffTag {
+    typedef bool MSLink::* type;
+    friend type get(AmContOffTag);
+};
+template struct Rob<AmContOffTag, &MSLink::myAmContOff>;
+struct PedFoeTag {
+    typedef bool MSLink::* type;
+    friend type get(PedFoeTag);
+};
+template struct Rob<PedFoeTag, &MSLink::myHavePedestrianCrossingFoe>;
+
+struct NameTable {
+    std::vector<int32_t> begin{0};
+    std::vector<uint8_t> bytes;
+    void add(const std::string& s) {
+        bytes.insert(bytes.end(), s.begin(), s.end());
+        begin.push_back((int32_t)bytes.size());
+    }
+    void put(sb2::FlatFile& ff, const std::string& prefix) {
+        ff.put(prefix + "_name_begin", begin);
+        ff.put(prefix + "_names", bytes);
+    }
+};
+
+int edgeFlags(const MSEdge* e) {
+    return (e->isInternal() ? 1 : 0) | (e->isRoundabout() ? 2 : 0) | (e->isFringe() ? 4 : 0) | (e->hasLaneChanger() ? 8 : 0)
+           | (e->isCrossing() || e->isWalkingArea() ? 16 : 0);
+}
+
+void flatten(MSNet* net, const std::string& path) {
+    sb2::FlatFile ff;
+    OptionsCont& oc = OptionsCont::getOptions();
+    // ---------------- edges and lanes
+    const MSEdgeVector& edges = MSEdge::getAllEdges();
+    std::map<const MSLane*, int> laneIdx;
+    std::map<const MSEdge*, int> edgeIdx;
+    std::map<const MSJunction*, int> junctionIdx;
+    std::vector<const MSLane*> lanes;
+    std::vector<const MSJunction*> junctions;
+    std::vector<int32_t> edgeLaneBegin{0}, edgeFlagsV;
+    NameTable edgeNames, laneNames, junctionNames;
+    auto jIdx = [&](const MSJunction* j) -> int {
+        if (j == nullptr) {
+            return -1;
+        }
+        auto it = junctionIdx.find(j);
+        if (it != junctionIdx.end()) {
+            return it->second;
+        }
+        const int idx = (int)junctions.size();
+        junctionIdx[j] = idx;
+        junctions.push_back(j);
+        junctionNames.add(j->getID());
+        return idx;
+    };
+    for (const MSEdge* e : edges) {
+        edgeIdx[e] = (int)edgeIdx.size();
+        edgeNames.add(e->getID());
+        edgeFlagsV.push_back(edgeFlags(e));
+        for (const MSLane* l : e->getLanes()) {
+            laneIdx[l] = (int)lanes.size();
+            lanes.push_back(l);
+            laneNames.add(l->getID());
+        }
+        edgeLaneBegin.push_back((int32_t)lanes.size());
+    }
+    auto lIdx = [&](const MSLane* l) -> int {
+        if (l == nullptr) {
+            return -1;
+        }
+        auto it = laneIdx.find(l);
+        return it == laneIdx.end() ? -1 : it->second;
+    };
+    const int nL = (int)lanes.size();
+    // ---------------- links
+    std::map<const MSLink*, int> linkIdx;
+    std::vector<const MSLink*> links;
+    std::vector<int32_t> laneLinkBegin{0};
+    for (const MSLane* l : lanes) {
+        for (const MSLink* k : l->getLinkCont()) {
+            linkIdx[k] = (int)links.size();
+            links.push_back(k);
+        }
+        laneLinkBegin.push_back((int32_t)links.size());
+    }
+    auto kIdx = [&](const MSLink* k) -> int {
+        if (k == nullptr) {
+            return -1;
+        }
+        auto it = linkIdx.find(k);
+        return it == linkIdx.end() ? -1 : it->second;
+    };
+    {
+        std::vector<double> len, spd, wid, geomf, shapeXY, incLen;
+        std::vector<int32_t> ledge, lflags, lnumid, predLog, predNorm, entryLink, incLink, incBegin{0}, incLane, incViaLink, toJ, fromJ, shapeBegin{0};
+        for (const MSLane* l : lanes) {
+            len.push_back(l->getLength());
+            spd.push_back(l->getSpeedLimit());
+            wid.push_back(l->getWidth());
+            geomf.push_back(l->getLengthGeometryFactor());
+            ledge.push_back(edgeIdx[&l->getEdge()]);
+            lflags.push_back(edgeFlags(&l->getEdge()));
+            lnumid.push_back(l->getNumericalID());
+            predLog.push_back(lIdx(l->getLogicalPredecessorLane()));
+            predNorm.push_back(lIdx(l->getNormalPredecessorLane()));
+            entryLink.push_back(l->isInternal() ? kIdx(l->getEntryLink()) : -1);
+            incLink.push_back(l->isInternal() && l->getIncomingLanes().size() == 1 ? kIdx(l->getIncomingLanes()[0].viaLink) : -1);
+            for (const MSLane::IncomingLaneInfo& ili : l->getIncomingLanes()) {
+                incLane.push_back(lIdx(ili.lane));
+                incViaLink.push_back(kIdx(ili.viaLink));
+                incLen.push_back(ili.length);
+            }
+            incBegin.push_back((int32_t)incLane.size());
+            toJ.push_back(jIdx(l->getEdge().getToJunction()));
+            fromJ.push_back(jIdx(l->getEdge().getFromJunction()));
+            for (const Position& p : l->getShape()) {
+                shapeXY.push_back(p.x());
+                shapeXY.push_back(p.y());
+            }
+            shapeBegin.push_back((int32_t)(shapeXY.size() / 2));
+        }
+        ff.put("lane_length", len);
+        ff.put("lane_speed", spd);
+        ff.put("lane_width", wid);
+        ff.put("lane_geomfactor", geomf);
+        ff.put("lane_edge", ledge);
+        ff.put("lane_flags", lflags);
+        ff.put("lane_numid", lnumid);
+        ff.put("lane_link_begin", laneLinkBegin);
+        ff.put("lane_pred_logical", predLog);
+        ff.put("lane_pred_normal", predNorm);
+        ff.put("lane_entry_link", entryLink);
+        ff.put("lane_inc_link", incLink);
+        ff.put("lane_inc_begin", incBegin);
+        ff.put("inc_lane", incLane);
+        ff.put("inc_link", incViaLink);
+        ff.put("inc_length", incLen);
+        ff.put("lane_to_junction", toJ);
+        ff.put("lane_from_junction", fromJ);
+        ff.put("lane_shape_begin", shapeBegin);
+        ff.put("shape_xy", shapeXY);
+        laneNames.put(ff, "lane");
+        ff.put("edge_lane_begin", edgeLaneBegin);
+        ff.put("edge_flags", edgeFlagsV);
+        edgeNames.put(ff, "edge");
+    }
+    // ---------------- traffic lights (index table first; links refer to it)
+    std::map<const MSTrafficLightLogic*, int> tlIdx;
+    std::vector<MSTrafficLightLogic*> tls;
+    for (const std::string& id : net->getTLSControl().getAllTLIds()) {
+        MSTrafficLightLogic* logic = net->getTLSControl().getActive(id);
+        tlIdx[logic] = (int)tls.size();
+        tls.push_back(logic);
+    }
+    {
+        std::vector<int32_t> from, to, via, flags, index, tl, tlindex, intBefore, junction, entry, exitL;
+        std::vector<uint8_t> state, dir;
+        std::vector<double> length, foevis, radius, lbc, csize;
+        std::vector<int32_t> foeLinkBegin{0}, foeLink, foeLaneBegin{0}, foeLane, cflag, cfoeidx;
+        std::vector<uint64_t> response;
+        for (const MSLink* k : links) {
+            from.push_back(lIdx(k->getLaneBefore()));
+            to.push_back(lIdx(k->getLane()));
+            via.push_back(lIdx(k->getViaLane()));
+            state.push_back((uint8_t)k->getState());
+            dir.push_back((uint8_t)toString(k->getDirection())[0]);
+            length.push_back(k->getLength());
+            foevis.push_back(k->getFoeVisibilityDistance());
+            radius.push_back(k->*get(RadiusTag()));
+            int f = 0;
+            f |= k->keepClear() ? 1 : 0;
+            f |= k->hasFoes() ? 2 : 0;
+            f |= k->*get(AmContTag()) ? 4 : 0;
+            f |= k->isEntryLink() ? 8 : 0;
+            f |= k->isConflictEntryLink() ? 16 : 0;
+            f |= k->isExitLink() ? 32 : 0;
+            f |= k->isExitLinkAfterInternalJunction() ? 64 : 0;
+            f |= k->isInternalJunctionLink() ? 128 : 0;
+            f |= k->isIndirect() ? 256 : 0;
+            f |= k->*get(PedFoeTag()) ? 512 : 0;
+            f |= k->isTurnaround() ? 1024 : 0;
+            f |= k->*get(AmContOffTag()) ? 2048 : 0;
+            flags.push_back(f);
+            index.push_back(k->getIndex());
+            auto ti = tlIdx.find(k->getTLLogic());
+            tl.push_back(ti == tlIdx.end() ? -1 : ti->second);
+            tlindex.push_back(k->getTLIndex());
+            intBefore.push_back(lIdx(k->getInternalLaneBefore()));
+            junction.push_back(jIdx(k->getJunction()));
+            entry.push_back(kIdx(k->getCorrespondingEntryLink()));
+            exitL.push_back(kIdx(k->getCorrespondingExitLink()));
+            for (const MSLink* fl : k->getFoeLinks()) {
+                foeLink.push_back(kIdx(fl));
+            }
+            foeLinkBegin.push_back((int32_t)foeLink.size());
+            const std::vector<const MSLane*>& fls = k->getFoeLanes();
+            const std::vector<MSLink::ConflictInfo>& cis = k->getConflicts();
+            for (int i = 0; i < (int)fls.size(); i++) {
+                foeLane.push_back(lIdx(fls[i]));
+                if (i < (int)cis.size()) {
+                    lbc.push_back(cis[i].lengthBehindCrossing);
+                    csize.push_back(cis[i].conflictSize);
+                    cflag.push_back((int)cis[i].flag);
+                    cfoeidx.push_back(cis[i].foeConflictIndex);
+                } else {
+                    // entry links keep foe lanes without conflict geometry (MSLink.cpp:249: geometry only if internalLaneBefore)
+                    lbc.push_back(0);
+                    csize.push_back(0);
+                    cflag.push_back(-1);
+                    cfoeidx.push_back(-1);
+                }
+            }
+            foeLaneBegin.push_back((int32_t)foeLane.size());
+            uint64_t mask[4] = {0, 0, 0, 0};
+            const MSJunction* j = k->getJunction();
+            if (j != nullptr && j->getLogic() != nullptr && k->getIndex() >= 0 && k->getIndex() < j->getLogic()->getLogicSize()) {
+                const MSLogicJunction::LinkBits& bits = j->getLogic()->getResponseFor(k->getIndex());
+                for (int b = 0; b < 256 && b < (int)bits.size(); b++) {
+                    if (bits.test(b)) {
+                        mask[b / 64] |= (uint64_t)1 << (b % 64);
+                    }
+                }
+            }
+            for (int w = 0; w < 4; w++) {
+                response.push_back(mask[w]);
+            }
+        }
+        ff.put("link_from", from);
+        ff.put("link_to", to);
+        ff.put("link_via", via);
+        ff.put("link_state", state);
+        ff.put("link_dir", dir);
+        ff.put("link_length", length);
+        ff.put("link_foevis", foevis);
+        ff.put("link_radius", radius);
+        ff.put("link_flags", flags);
+        ff.put("link_index", index);
+        ff.put("link_tl", tl);
+        ff.put("link_tlindex", tlindex);
+        ff.put("link_internal_before", intBefore);
+        ff.put("link_junction", junction);
+        ff.put("link_entry", entry);
+        ff.put("link_exit", exitL);
+        ff.put("link_foelink_begin", foeLinkBegin);
+        ff.put("foelink", foeLink);
+        ff.put("link_foelane_begin", foeLaneBegin);
+        ff.put("foelane", foeLane);
+        ff.put("conf_lbc", lbc);
+        ff.put("conf_size", csize);
+        ff.put("conf_flag", cflag);
+        ff.put("conf_foeidx", cfoeidx);
+        ff.put("link_response", response);
+        junctionNames.put(ff, "junction");
+    }
+    // ---------------- static traffic light programs
+    {
+        std::vector<int32_t> phaseBegin{0}, stateBegin{0}, curPhase, tlLinkBegin{0}, tlLinkIndex, tlLinkLink, tlStatic;
+        std::vector<int64_t> dur, nextSwitch;
+        std::vector<uint8_t> states;
+        NameTable tlNames;
+        for (MSTrafficLightLogic* logic : tls) {
+            tlNames.add(logic->getID());
+            tlStatic.push_back(dynamic_cast<MSSimpleTrafficLightLogic*>(logic) != nullptr && logic->getLogicType() == TrafficLightType::STATIC ? 1 : 0);
+            for (const MSPhaseDefinition* p : logic->getPhases()) {
+                dur.push_back(p->duration);
+                states.insert(states.end(), p->getState().begin(), p->getState().end());
+                stateBegin.push_back((int32_t)states.size());
+            }
+            phaseBegin.push_back((int32_t)dur.size());
+            curPhase.push_back(logic->getCurrentPhaseIndex());
+            nextSwitch.push_back(logic->getNextSwitchTime());
+            const MSTrafficLightLogic::LinkVectorVector& lvv = logic->getLinks();
+            for (int i = 0; i < (int)lvv.size(); i++) {
+                for (const MSLink* k : lvv[i]) {
+                    tlLinkIndex.push_back(i);
+                    tlLinkLink.push_back(kIdx(k));
+                }
+            }
+            tlLinkBegin.push_back((int32_t)tlLinkIndex.size());
+        }
+        ff.put("tl_phase_begin", phaseBegin);
+        ff.put("phase_dur", dur);
+        ff.put("phase_state_begin", stateBegin);
+        ff.put("phase_states", states);
+        ff.put("tl_cur_phase", curPhase);
+        ff.put("tl_next_switch", nextSwitch);
+        ff.put("tl_link_begin", tlLinkBegin);
+        ff.put("tllink_index", tlLinkIndex);
+        ff.put("tllink_link", tlLinkLink);
+        ff.put("tl_static", tlStatic);
+        tlNames.put(ff, "tl");
+    }
+    // ---------------- vehicles, their types and routes (everything loaded: run with --route-steps 0)
+    {
+        MSVehicleControl& vc = net->getVehicleControl();
+        std::vector<const SUMOVehicle*> vehs;
+        for (auto it = vc.loadedVehBegin(); it != vc.loadedVehEnd(); ++it) {
+            vehs.push_back(it->second);
+        }
+        // insertion order: MSVehicleContainer keys by depart time, equal times keep load order (= numerical id order)
+        std::stable_sort(vehs.begin(), vehs.end(), [](const SUMOVehicle* a, const SUMOVehicle* b) {
+            if (a->getParameter().depart != b->getParameter().depart) {
+                return a->getParameter().depart < b->getParameter().depart;
+            }
+            return a->getNumericalID() < b->getNumericalID();
+        });
+        std::map<const MSVehicleType*, int> typeIdx;
+        std::vector<const MSVehicleType*> types;
+        std::map<const MSRoute*, int> routeIdx;
+        std::vector<const MSRoute*> routes;
+        std::vector<int32_t> numid, vtype, vroute, dpp, dsp, dlp, dlane, idrank(vehs.size(), 0);
+        std::vector<int64_t> depart;
+        std::vector<double> sf, arrpos, dpos, dspeed;
+        NameTable vehNames;
+        for (const SUMOVehicle* v : vehs) {
+            const MSVehicleType* t = &v->getVehicleType();
+            if (typeIdx.count(t) == 0) {
+                typeIdx[t] = (int)types.size();
+                types.push_back(t);
+            }
+            const MSRoute* r = &v->getRoute();
+            if (routeIdx.count(r) == 0) {
+                routeIdx[r] = (int)routes.size();
+                routes.push_back(r);
+            }
+            const SUMOVehicleParameter& p = v->getParameter();
+            numid.push_back((int32_t)v->getNumericalID());
+            vtype.push_back(typeIdx[t]);
+            vroute.push_back(routeIdx[r]);
+            depart.push_back(p.depart);
+            sf.push_back(v->getChosenSpeedFactor());
+            arrpos.push_back(v->getArrivalPos());
+            dpp.push_back((int)p.departPosProcedure);
+            dpos.push_back(p.departPos);
+            dsp.push_back((int)p.departSpeedProcedure);
+            dspeed.push_back(p.departSpeed);
+            dlp.push_back((int)p.departLaneProcedure);
+            dlane.push_back(p.departLane);
+            vehNames.add(v->getID());
+        }
+        {
+            // rank in std::string order (MSVehicle::isLeader tie breaker MSVehicle.cpp:7791; FCD output order MSFCDExport.cpp:98)
+            std::vector<int> order(vehs.size());
+            for (int i = 0; i < (int)order.size(); i++) {
+                order[i] = i;
+            }
+            std::sort(order.begin(), order.end(), [&](int a, int b) {
+                return vehs[a]->getID() < vehs[b]->getID();
+            });
+            for (int r = 0; r < (int)order.size(); r++) {
+                idrank[order[r]] = r;
+            }
+        }
+        ff.put("veh_numid", numid);
+        ff.put("veh_type", vtype);
+        ff.put("veh_route", vroute);
+        ff.put("veh_depart", depart);
+        ff.put("veh_speedfactor", sf);
+        ff.put("veh_arrivalpos", arrpos);
+        ff.put("veh_departpos_proc", dpp);
+        ff.put("veh_departpos", dpos);
+        ff.put("veh_departspeed_proc", dsp);
+        ff.put("veh_departspeed", dspeed);
+        ff.put("veh_departlane_proc", dlp);
+        ff.put("veh_departlane", dlane);
+        ff.put("veh_idrank", idrank);
+        vehNames.put(ff, "veh");
+        // types
+        std::vector<double> tl, tg, tms, tdms, ta, td, ted, tad, ttau, tsig, timp, tw, tcmg, idmDelta, idmStep;
+        std::vector<int32_t> tcf, tem;
+        std::vector<int64_t> tsd;
+        NameTable typeNames;
+        for (const MSVehicleType* t : types) {
+            const MSCFModel& cf = t->getCarFollowModel();
+            typeNames.add(t->getID());
+            tl.push_back(t->getLength());
+            tg.push_back(t->getMinGap());
+            tms.push_back(t->getMaxSpeed());
+            tdms.push_back(t->getDesiredMaxSpeed());
+            ta.push_back(cf.getMaxAccel());
+            td.push_back(cf.getMaxDecel());
+            ted.push_back(cf.getEmergencyDecel());
+            tad.push_back(cf.getApparentDecel());
+            ttau.push_back(cf.getHeadwayTime());
+            tsig.push_back(cf.getImperfection());
+            timp.push_back(t->getImpatience());
+            tw.push_back(t->getWidth());
+            tcmg.push_back(cf.getCollisionMinGapFactor());
+            tcf.push_back(cf.getModelID());
+            tsd.push_back(cf.getStartupDelay());
+            tem.push_back((int)t->getEmissionClass());
+            idmDelta.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_DELTA, 4.));
+            idmStep.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_STEPPING, .25));
+        }
+        ff.put("vt_length", tl);
+        ff.put("vt_mingap", tg);
+        ff.put("vt_maxspeed", tms);
+        ff.put("vt_desiredmaxspeed", tdms);
+        ff.put("vt_accel", ta);
+        ff.put("vt_decel", td);
+        ff.put("vt_emergencydecel", ted);
+        ff.put("vt_apparentdecel", tad);
+        ff.put("vt_tau", ttau);
+        ff.put("vt_sigma", tsig);
+        ff.put("vt_impatience", timp);
+        ff.put("vt_width", tw);
+        ff.put("vt_collision_mingap_factor", tcmg);
+        ff.put("vt_cfmodel", tcf);
+        ff.put("vt_startupdelay", tsd);
+        ff.put("vt_emission_class", tem);
+        ff.put("vt_idm_delta", idmDelta);
+        ff.put("vt_idm_stepping", idmStep);
+        typeNames.put(ff, "vt");
+        // routes
+        std::vector<int32_t> routeBegin{0}, routeEdges;
+        for (const MSRoute* r : routes) {
+            for (const MSEdge* e : r->getEdges()) {
+                routeEdges.push_back(edgeIdx[e]);
+            }
+            routeBegin.push_back((int32_t)routeEdges.size());
+        }
+        ff.put("route_begin", routeBegin);
+        ff.put("route_edges", routeEdges);
+    }
+    // ---------------- options the step depends on (MSFrame::setMSGlobals, MSFrame.cpp:1172-1283)
+    ff.putScalar<int64_t>("opt_delta_t", DELTA_T);
+    ff.putScalar<int64_t>("opt_begin", string2time(oc.getString("begin")));
+    ff.putScalar<int64_t>("opt_end", string2time(oc.getString("end")));
+    ff.putScalar<int64_t>("opt_seed", (int64_t)oc.getInt("seed"));
+    ff.putScalar<int64_t>("opt_time_to_teleport", MSGlobals::gTimeToGridlock);
+    ff.putScalar<int64_t>("opt_time_to_impatience", MSGlobals::gTimeToImpatience);
+    ff.putScalar<int64_t>("opt_startup_wait_threshold", MSGlobals::gStartupWaitThreshold);
+    ff.putScalar<int64_t>("opt_ignore_junction_blocker", MSGlobals::gIgnoreJunctionBlocker);
+    ff.putScalar<double>("opt_tls_yellow_min_decel", MSGlobals::gTLSYellowMinDecel);
+    ff.putScalar<double>("opt_emergency_decel_warning_threshold", MSGlobals::gEmergencyDecelWarningThreshold);
+    ff.putScalar<int32_t>("opt_default_departspeed_proc", (int)MSLane::getDefaultDepartSpeedDefinition());
+    ff.putScalar<double>("opt_default_departspeed", MSLane::getDefaultDepartSpeed());
+    ff.putScalar<int32_t>("opt_using_internal_lanes", MSGlobals::gUsingInternalLanes ? 1 : 0);
+    ff.putScalar<int32_t>("opt_semi_implicit_euler", MSGlobals::gSemiImplicitEulerUpdate ? 1 : 0);
+    ff.putScalar<int32_t>("opt_sublane", MSGlobals::gSublane ? 1 : 0);
+    ff.putScalar<int32_t>("opt_thread_rngs", oc.getInt("thread-rngs"));
+    ff.putScalar<double>("opt_lanechange_duration", STEPS2TIME(MSGlobals::gLaneChangeDuration));
+    ff.save(path);
+}
+
+}  // namespace
+
+int
+main(int argc, char** argv) {
+    std::string flatOut, traceOut;
+    std::vector<char*> args;
+    args.push_back(argv[0]);
+    for (int i = 1; i < argc; i++) {
+        const std::string a = argv[i];
+        if (a == "--flat-out" && i + 1 < argc) {
+            flatOut = argv[++i];
+        } else if (a == "--trace-out" && i + 1 < argc) {
+            traceOut = argv[++i];
+        } else {
+            args.push_back(argv[i]);
+        }
+    }
+    static char routeSteps[] = "--route-steps";
+    static char zero[] = "0";
+    args.push_back(routeSteps);
+    args.push_back(zero);
+    OptionsCont& oc = OptionsCont::getOptions();
+    oc.setApplicationName("sumo", "Eclipse SUMO sumo " VERSION_STRING);
+    gSimulation = true;
+    int ret = 0;
+    MSNet* net = nullptr;
+    try {
+        XMLSubSys::init();
+        OptionsIO::setArgs((int)args.size(), args.data());
+        net = NLBuilder::init();
+        if (net == nullptr) {
+            return 1;
+        }
+        if (!flatOut.empty()) {
+            flatten(net, flatOut);
+        }
+        if (!traceOut.empty()) {
+            // lane index as in the flat file
+            std::map<const MSLane*, int> laneIdx;
+            for (const MSEdge* e : MSEdge::getAllEdges()) {
+                for (const MSLane* l : e->getLanes()) {
+                    const int idx = (int)laneIdx.size();
+                    laneIdx[l] = idx;
+                }
+            }
+            FILE* f = fopen(traceOut.c_str(), "wb");
+            const SUMOTime begin = string2time(oc.getString("begin"));
+            const SUMOTime end = string2time(oc.getString("end"));
+            MSNet::SimulationState state = MSNet::SIMSTATE_RUNNING;
+            // mirror MSNet::simulate (MSNet.cpp:462-500) but record the state after every step
+            while (state == MSNet::SIMSTATE_RUNNING) {
+                const SUMOTime t = net->getCurrentTimeStep();
+                net->simulationStep();
+                std::vector<const MSVehicle*> on;
+                MSVehicleControl& vc = net->getVehicleControl();
+                for (auto it = vc.loadedVehBegin(); it != vc.loadedVehEnd(); ++it) {
+                    const MSVehicle* v = dynamic_cast<const MSVehicle*>(it->second);
+                    if (v != nullptr && v->isOnRoad()) {
+                        on.push_back(v);
+                    }
+                }
+                std::sort(on.begin(), on.end(), [](const MSVehicle* a, const MSVehicle* b) {
+                    return a->getNumericalID() < b->getNumericalID();
+                });
+                const int64_t hdr[2] = {(int64_t)t, (int64_t)on.size()};
+                fwrite(hdr, 8, 2, f);
+                for (const MSVehicle* v : on) {
+                    const int64_t ids[2] = {(int64_t)v->getNumericalID(), (int64_t)laneIdx[v->getLane()]};
+                    const double st[2] = {v->getPositionOnLane(), v->getSpeed()};
+                    fwrite(ids, 8, 2, f);
+                    fwrite(st, 8, 2, f);
+                }
+                state = net->simulationState(end);
+                if (state == MSNet::SIMSTATE_LOADING) {
+                    state = MSNet::SIMSTATE_RUNNING;
+                }
+            }
+            fclose(f);
+            net->closeSimulation(begin, MSNet::getStateMessage(state));
+        }
+        delete net;
+        OutputDevice::closeAll();
+        MsgHandler::cleanupOnEnd();
+    } catch (const ProcessError& e) {
+        if (std::string(e.what()) != std::string("Process Error") && std::string(e.what()) != std::string("")) {
+            WRITE_ERROR(e.what());
+        }
+        ret = 1;
+    }
+    SystemFrame::close();
+    return ret;
+}

@@ -6,7 +6,7 @@
 # Flags: -O2 -ffp-contract=off and no -march, so the oracle is strict non-FMA IEEE fp64
 # (the reference sets no FP flags itself, CMakeLists.txt:147-157).
 #
-# usage: oracle/build_ref.sh [sumo|netgenerate|duarouter|all]   (default: all)
+# usage: oracle/build_ref.sh [sumo|netgenerate|duarouter|flatten|all]   (default: all)
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${SUMO_REFERENCE:-/root/reference}"
@@ -84,10 +84,16 @@ MK="$OUT/Makefile"
     printf '\t@echo LINK $@\n\t@$(CXX) -o $@ $^ -l:libexpat.a -l:libz.a -lpthread -ldl\n'
     echo "$OUT/duarouter: \$(DUA_OBJS) \$(VEHICLE_OBJS) \$(COMMON_OBJS)"
     printf '\t@echo LINK $@\n\t@$(CXX) -o $@ $^ -l:libexpat.a -l:libz.a -lpthread -ldl\n'
+    # integration/sumo_flatten.cpp = the reference-side flattening shim + parity trace recorder; it replaces sumo_main.o
+    echo "\$(OBJ)/sumo_flatten.o: $HERE/../integration/sumo_flatten.cpp $HERE/../include/sumob200_flatfile.h"
+    printf '\t@echo CXX integration/sumo_flatten.cpp\n\t@$(CXX) $(CXXFLAGS) -c $< -o $@\n'
+    echo "$OUT/sumo_flatten: \$(OBJ)/sumo_flatten.o \$(filter-out %sumo_main.o,\$(SIM_OBJS)) \$(VEHICLE_OBJS) \$(COMMON_OBJS)"
+    printf '\t@echo LINK $@\n\t@$(CXX) -o $@ $^ -l:libexpat.a -l:libz.a -lpthread -ldl\n'
+    echo "flatten: $OUT/sumo_flatten"
     echo "sumo: $OUT/sumo"
     echo "netgenerate: $OUT/netgenerate"
     echo "duarouter: $OUT/duarouter"
-    echo "all: sumo netgenerate"
+    echo "all: sumo netgenerate flatten"
 } > "$MK"
 
 make -k -f "$MK" -j"$JOBS" "$WHAT"
