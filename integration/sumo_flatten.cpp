@@ -370,9 +370,15 @@ void flatten(MSNet* net, const std::string& path) {
             vehs.push_back(it->second);
         }
         // insertion order: MSVehicleContainer keys by depart time, equal times keep load order (= numerical id order)
-        std::stable_sort(vehs.begin(), vehs.end(), [](const SUMOVehicle* a, const SUMOVehicle* b) {
-            if (a->getParameter().depart != b->getParameter().depart) {
-                return a->getParameter().depart < b->getParameter().depart;
+        // (MSVehicleContainer::add buckets by depart rounded UP to a step boundary, MSVehicleContainer.cpp:73-89)
+        auto bucket = [](const SUMOVehicle* a) {
+            const SUMOTime d = a->getParameter().depart;
+            const SUMOTime delay = d % DELTA_T;
+            return d + (delay == 0 ? 0 : DELTA_T - delay);
+        };
+        std::stable_sort(vehs.begin(), vehs.end(), [&](const SUMOVehicle* a, const SUMOVehicle* b) {
+            if (bucket(a) != bucket(b)) {
+                return bucket(a) < bucket(b);
             }
             return a->getNumericalID() < b->getNumericalID();
         });
@@ -512,6 +518,16 @@ void flatten(MSNet* net, const std::string& path) {
     ff.putScalar<int32_t>("opt_sublane", MSGlobals::gSublane ? 1 : 0);
     ff.putScalar<int32_t>("opt_thread_rngs", oc.getInt("thread-rngs"));
     ff.putScalar<double>("opt_lanechange_duration", STEPS2TIME(MSGlobals::gLaneChangeDuration));
+    // fleet aggregates behind MSLane::getMaximumBrakeDist (MSLane.cpp:2945-2953)
+    ff.putScalar<double>("opt_max_speed_factor", net->getVehicleControl().getMaxSpeedFactor());
+    ff.putScalar<double>("opt_min_deceleration", net->getVehicleControl().getMinDeceleration());
+    ff.putScalar<double>("opt_max_mingap", net->getVehicleControl().getMaxMinGap());
+    // numeric values of the car-following model tags written to vt_cfmodel (MSCFModel::getModelID)
+    ff.putScalar<int32_t>("opt_tag_cf_krauss", (int)SUMO_TAG_CF_KRAUSS);
+    ff.putScalar<int32_t>("opt_tag_cf_krauss_orig1", (int)SUMO_TAG_CF_KRAUSS_ORIG1);
+    ff.putScalar<int32_t>("opt_tag_cf_idm", (int)SUMO_TAG_CF_IDM);
+    ff.putScalar<int32_t>("opt_default_departlane_proc", (int)MSEdge::getAllEdges().front()->getDefaultDepartLaneDefinition());
+    ff.putScalar<int32_t>("opt_default_departlane", MSEdge::getAllEdges().front()->getDefaultDepartLane());
     ff.save(path);
 }
 

@@ -1,0 +1,360 @@
+/* sb2_build.h -- host side: turns the flattened scenario arrays (include/sumob200_flatfile.h) into the engine state.
+ * Produces a list of named buffers plus a Ctx whose pointers refer to them; the CUDA engine uploads every buffer and
+ * patches the pointers (engine.cu), the host emulation (tests/host_emul) uses them in place.
+ *
+ * Refuses, with a message, every option/feature the step kernels do not implement (SURVEY.md section 5 "config / flags").
+ */
+#pragma once
+#include <cstddef>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "../../include/sumob200_flatfile.h"
+#include "sb2_types.h"
+#include "sb2_insert.h"
+
+namespace sb2 {
+
+struct Buffer {
+    std::string name;
+    size_t offset;       // offset of the pointer inside Ctx
+    std::vector<uint8_t> host;
+    bool dynamic;        // written by kernels (state); static buffers are read-only after load
+};
+
+class Model {
+public:
+    Ctx h;                         // host view
+    std::vector<Buffer*> buffers;
+    std::vector<double> vt_collision_mingap_factor;
+    std::vector<std::string> lane_names, veh_names;
+    SUMOTime begin = 0, end = 0;
+
+    Model() { memset(&h, 0, sizeof(h)); }
+    ~Model() { for (Buffer* b : buffers) { delete b; } }
+    Model(const Model&) = delete;
+    Model& operator=(const Model&) = delete;
+
+    template<class T> T* add(const char* name, size_t offset, size_t count, bool dynamic, T fill) {
+        Buffer* b = new Buffer();
+        b->name = name; b->offset = offset; b->dynamic = dynamic;
+        b->host.resize(std::max<size_t>(count, 1) * sizeof(T));
+        T* p = reinterpret_cast<T*>(b->host.data());
+        for (size_t i = 0; i < std::max<size_t>(count, 1); i++) {
+            p[i] = fill;
+        }
+        buffers.push_back(b);
+        *reinterpret_cast<void**>(reinterpret_cast<char*>(&h) + offset) = p;
+        return p;
+    }
+    template<class T> T* copy(const char* name, size_t offset, const FlatFile& ff, const char* flatName) {
+        const FlatArray& a = ff.get(flatName);
+        if (a.elemSize != sizeof(T)) {
+            throw std::runtime_error(std::string("flat array '") + flatName + "' has unexpected element size");
+        }
+        T* p = add<T>(name, offset, a.count, false, T());
+        if (a.count > 0) {
+            memcpy(p, a.bytes.data(), a.count * sizeof(T));
+        }
+        return p;
+    }
+
+#define SB2_OFF(member) offsetof(Ctx, member)
+#define SB2_COPY(T, member) copy<T>(#member, SB2_OFF(member), ff, #member)
+#define SB2_COPY2(T, member, flatName) copy<T>(#member, SB2_OFF(member), ff, flatName)
+#define SB2_DYN(T, member, count, fill) add<T>(#member, SB2_OFF(member), (count), true, (fill))
+#define SB2_DYN2(T, member, idx, count, fill) add<T>(#member, SB2_OFF(member) + (idx) * sizeof(void*), (count), true, (fill))
+
+    static std::vector<std::string> names(const FlatFile& ff, const std::string& prefix) {
+        std::vector<std::string> out;
+        const int32_t* b = ff.ptr<int32_t>(prefix + "_name_begin");
+        const uint8_t* raw = ff.ptr<uint8_t>(prefix + "_names");
+        const size_t n = ff.count(prefix + "_name_begin") - 1;
+        for (size_t i = 0; i < n; i++) {
+            out.emplace_back(reinterpret_cast<const char*>(raw) + b[i], reinterpret_cast<const char*>(raw) + b[i + 1]);
+        }
+        return out;
+    }
+
+    void build(const FlatFile& ff) {
+        // ---------------- options
+        h.DELTA_T = ff.scalar<int64_t>("opt_delta_t", 1000);
+        h.TS = (double)h.DELTA_T / 1000.;
+        begin = ff.scalar<int64_t>("opt_begin", 0);
+        end = ff.scalar<int64_t>("opt_end", -1);
+        h.t = begin;
+        h.timeToImpatience = ff.scalar<int64_t>("opt_time_to_impatience", 180000);
+        h.timeToTeleport = ff.scalar<int64_t>("opt_time_to_teleport", 300000);
+        h.startupWaitThreshold = ff.scalar<int64_t>("opt_startup_wait_threshold", 2000);
+        h.ignoreJunctionBlocker = ff.scalar<int64_t>("opt_ignore_junction_blocker", -1);
+        h.tlsYellowMinDecel = ff.scalar<double>("opt_tls_yellow_min_decel", 3.);
+        if (ff.scalar<int32_t>("opt_sublane", 0) != 0) {
+            throw std::runtime_error("sumob200: the sublane model (--lateral-resolution) is not supported");
+        }
+        if (ff.scalar<int32_t>("opt_semi_implicit_euler", 1) == 0) {
+            throw std::runtime_error("sumob200: the ballistic update (--step-method.ballistic) is not supported");
+        }
+        if (ff.scalar<int32_t>("opt_using_internal_lanes", 1) == 0) {
+            throw std::runtime_error("sumob200: --no-internal-links is not supported");
+        }
+        if (ff.scalar<double>("opt_lanechange_duration", 0.) > 0) {
+            throw std::runtime_error("sumob200: --lanechange.duration > 0 is not supported");
+        }
+        h.nL = (int)ff.count("lane_length");
+        h.nE = (int)ff.count("edge_flags");
+        h.nK = (int)ff.count("link_from");
+        h.nV = (int)ff.count("veh_type");
+        h.nT = (int)ff.count("vt_length");
+        h.nTL = (int)ff.count("tl_cur_phase");
+        const int nL = h.nL, nK = h.nK, nV = h.nV, nT = h.nT;
+        lane_names = names(ff, "lane");
+        veh_names = names(ff, "veh");
+        // ---------------- lanes
+        SB2_COPY(double, lane_length); SB2_COPY(double, lane_speed);
+        SB2_COPY(int32_t, lane_edge); SB2_COPY(int32_t, lane_flags); SB2_COPY(int32_t, lane_link_begin);
+        SB2_COPY(int32_t, lane_pred_logical); SB2_COPY(int32_t, lane_pred_normal); SB2_COPY(int32_t, lane_entry_link);
+        SB2_COPY(int32_t, lane_inc_begin); SB2_COPY(int32_t, inc_lane); SB2_COPY(int32_t, inc_link); SB2_COPY(double, inc_length);
+        SB2_COPY(int32_t, lane_to_junction); SB2_COPY(int32_t, lane_from_junction);
+        SB2_COPY(int32_t, edge_lane_begin);
+        SB2_DYN(int32_t, lane_first, nL, -1); SB2_DYN(int32_t, lane_last, nL, -1); SB2_DYN(int32_t, lane_nveh, nL, 0);
+        SB2_DYN(double, lane_brutto, nL, 0.);
+        SB2_DYN(int32_t, lane_npartial, nL, 0); SB2_DYN(int32_t, lane_partial, (size_t)nL * MAX_PARTIAL, -1);
+        SB2_DYN(int32_t, lane_incoming, nL, -1);
+        SB2_DYN(int32_t, ls_lastveh, nL, -1); SB2_DYN(double, ls_space, nL, 0.); SB2_DYN(uint8_t, ls_found_stopped, nL, (uint8_t)0);
+        for (int e = 0; e < h.nE; e++) {
+            const int nl = h.edge_lane_begin[e + 1] - h.edge_lane_begin[e];
+            const bool internal = (ff.ptr<int32_t>("edge_flags")[e] & LF_INTERNAL) != 0;
+            if (nl > 1 && !internal) {
+                throw std::runtime_error("sumob200: multi-lane edges (lane changing, LC2013) are not implemented yet");
+            }
+        }
+        // ---------------- links
+        SB2_COPY(int32_t, link_from); SB2_COPY(int32_t, link_to); SB2_COPY(int32_t, link_via);
+        {
+            const FlatArray& a = ff.get("link_state");
+            uint8_t* p = SB2_DYN(uint8_t, link_state, a.count, (uint8_t)0);
+            if (a.count > 0) {
+                memcpy(p, a.bytes.data(), a.count);
+            }
+            for (size_t k = 0; k < a.count; k++) {
+                if (p[k] == 'Z') {
+                    throw std::runtime_error("sumob200: zipper links are not supported");
+                }
+            }
+        }
+        SB2_COPY(uint8_t, link_dir);
+        SB2_COPY(double, link_length); SB2_COPY(double, link_foevis); SB2_COPY(double, link_radius);
+        SB2_COPY(int32_t, link_flags); SB2_COPY(int32_t, link_index); SB2_COPY(int32_t, link_tl);
+        SB2_COPY(int32_t, link_internal_before); SB2_COPY(int32_t, link_junction); SB2_COPY(int32_t, link_entry); SB2_COPY(int32_t, link_exit);
+        SB2_COPY(int32_t, link_foelink_begin); SB2_COPY(int32_t, foelink);
+        SB2_COPY(int32_t, link_foelane_begin); SB2_COPY(int32_t, foelane);
+        SB2_COPY(double, conf_lbc); SB2_COPY(double, conf_size); SB2_COPY(int32_t, conf_flag); SB2_COPY(int32_t, conf_foeidx);
+        SB2_COPY(uint64_t, link_response);
+        {
+            // MSLink::lastWasContMajor / lastWasContState (MSLink.cpp:1353-1397): for a link whose via lane's logical
+            // predecessor `pred` is internal, the link pred2 -> pred (pred2 = logical predecessor of pred)
+            int32_t* cp = add<int32_t>("link_contpred", SB2_OFF(link_contpred), nK, false, -1);
+            for (int k = 0; k < nK; k++) {
+                const int via = h.link_via[k];
+                if (via < 0) {
+                    continue;
+                }
+                const int pred = h.lane_pred_logical[via];
+                if (pred < 0 || !(h.lane_flags[pred] & LF_INTERNAL)) {
+                    continue;
+                }
+                const int pred2 = h.lane_pred_logical[pred];
+                if (pred2 < 0) {
+                    continue;
+                }
+                for (int q = h.lane_link_begin[pred2]; q < h.lane_link_begin[pred2 + 1]; q++) {
+                    // MSLane::getLinkTo(pred): pred is internal -> match the via lane
+                    if (h.link_via[q] == pred) {
+                        cp[k] = q;
+                        break;
+                    }
+                }
+            }
+        }
+        SB2_DYN(int64_t, link_last_change, nK, (int64_t)(INT64_MIN / 2));
+        {
+            uint8_t* lg = SB2_DYN(uint8_t, link_last_green, nK, (uint8_t)'g');
+            (void)lg;
+        }
+        SB2_DYN2(int32_t, link_app_head, 0, nK, -1); SB2_DYN2(int32_t, link_app_head, 1, nK, -1);
+        // ---------------- traffic lights
+        SB2_COPY(int32_t, tl_phase_begin); SB2_COPY2(int64_t, phase_dur, "phase_dur"); SB2_COPY(int32_t, phase_state_begin); SB2_COPY(uint8_t, phase_states);
+        {
+            const FlatArray& a = ff.get("tl_cur_phase");
+            int32_t* p = SB2_DYN(int32_t, tl_cur_phase, a.count, 0);
+            if (a.count > 0) {
+                memcpy(p, a.bytes.data(), a.count * 4);
+            }
+            const FlatArray& b = ff.get("tl_next_switch");
+            int64_t* q = SB2_DYN(int64_t, tl_next_switch, b.count, (int64_t)0);
+            if (b.count > 0) {
+                memcpy(q, b.bytes.data(), b.count * 8);
+            }
+            if (ff.has("tl_static")) {
+                const int32_t* st = ff.ptr<int32_t>("tl_static");
+                for (size_t i = 0; i < ff.count("tl_static"); i++) {
+                    if (!st[i]) {
+                        throw std::runtime_error("sumob200: only static traffic light programs are supported");
+                    }
+                }
+            }
+        }
+        SB2_COPY(int32_t, tl_link_begin); SB2_COPY(int32_t, tllink_index); SB2_COPY(int32_t, tllink_link);
+        // ---------------- vTypes
+        SB2_COPY(double, vt_length); SB2_COPY(double, vt_mingap); SB2_COPY(double, vt_maxspeed); SB2_COPY(double, vt_desiredmaxspeed);
+        SB2_COPY(double, vt_accel); SB2_COPY(double, vt_decel); SB2_COPY(double, vt_emergencydecel); SB2_COPY(double, vt_apparentdecel);
+        SB2_COPY(double, vt_tau); SB2_COPY(double, vt_sigma); SB2_COPY(double, vt_impatience);
+        SB2_COPY2(int64_t, vt_startupdelay, "vt_startupdelay");
+        SB2_COPY(double, vt_idm_delta); SB2_COPY(double, vt_idm_stepping);
+        {
+            const int32_t* tag = ff.ptr<int32_t>("vt_cfmodel");
+            int32_t* m = add<int32_t>("vt_cfmodel", SB2_OFF(vt_cfmodel), nT, false, 0);
+            const int tagKrauss = ff.scalar<int32_t>("opt_tag_cf_krauss", -1);
+            const int tagOrig = ff.scalar<int32_t>("opt_tag_cf_krauss_orig1", -1);
+            const int tagIDM = ff.scalar<int32_t>("opt_tag_cf_idm", -1);
+            for (int i = 0; i < nT; i++) {
+                if (tag[i] == tagKrauss) {
+                    m[i] = CF_KRAUSS;
+                } else if (tag[i] == tagOrig) {
+                    m[i] = CF_KRAUSS_ORIG1;
+                } else if (tag[i] == tagIDM) {
+                    m[i] = CF_IDM;
+                } else {
+                    throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss)");
+                }
+                if (m[i] != CF_KRAUSS) {
+                    throw std::runtime_error("sumob200: only the Krauss car-following model is implemented yet");
+                }
+            }
+            const double* f = ff.ptr<double>("vt_collision_mingap_factor");
+            vt_collision_mingap_factor.assign(f, f + nT);
+        }
+        // ---------------- routes, vehicles
+        SB2_COPY(int32_t, route_begin); SB2_COPY(int32_t, route_edges);
+        SB2_COPY(int32_t, veh_type); SB2_COPY(int32_t, veh_route); SB2_COPY(int32_t, veh_numid); SB2_COPY(int32_t, veh_idrank);
+        SB2_COPY(double, veh_speedfactor); SB2_COPY(double, veh_arrivalpos);
+        SB2_COPY(double, veh_departpos); SB2_COPY(int32_t, veh_departpos_proc);
+        {
+            // depart time = MSVehicleContainer bucket (rounded up to the step grid, MSVehicleContainer.cpp:80-81)
+            const int64_t* d = ff.ptr<int64_t>("veh_depart");
+            int64_t* o = add<int64_t>("veh_depart", SB2_OFF(veh_depart), nV, false, (int64_t)0);
+            for (int v = 0; v < nV; v++) {
+                const int64_t delay = d[v] % h.DELTA_T;
+                o[v] = d[v] + (delay == 0 ? 0 : h.DELTA_T - delay);
+                if (v > 0 && o[v] < o[v - 1]) {
+                    throw std::runtime_error("sumob200: vehicles must be sorted by departure time");
+                }
+            }
+            // depart speed: resolve DEFAULT (MSLane::getDepartSpeed, MSLane.cpp:609-614)
+            const int32_t* sp = ff.ptr<int32_t>("veh_departspeed_proc");
+            const double* sv = ff.ptr<double>("veh_departspeed");
+            int32_t* op = add<int32_t>("veh_departspeed_proc", SB2_OFF(veh_departspeed_proc), nV, false, 0);
+            double* ov = add<double>("veh_departspeed", SB2_OFF(veh_departspeed), nV, false, 0.);
+            const int defProc = ff.scalar<int32_t>("opt_default_departspeed_proc", DSD_DEFAULT);
+            const double defSpeed = ff.scalar<double>("opt_default_departspeed", 0.);
+            for (int v = 0; v < nV; v++) {
+                op[v] = sp[v];
+                ov[v] = sv[v];
+                if (op[v] == DSD_DEFAULT) {
+                    op[v] = defProc;
+                    ov[v] = defProc == DSD_GIVEN ? defSpeed : 0.;
+                }
+                if (op[v] == DSD_RANDOM || op[v] == DSD_GIVEN_VEHROUTE) {
+                    throw std::runtime_error("sumob200: departSpeed random is not supported");
+                }
+                const int pp = h.veh_departpos_proc[v];
+                if (pp != DPD_DEFAULT && pp != DPD_GIVEN && pp != DPD_BASE) {
+                    throw std::runtime_error("sumob200: departPos must be 'base' or a number");
+                }
+            }
+            // depart lane (MSEdge::getDepartLane, MSEdge.cpp:677-751): first lane / given index
+            const int32_t* lp = ff.ptr<int32_t>("veh_departlane_proc");
+            const int32_t* lv = ff.ptr<int32_t>("veh_departlane");
+            int32_t* dl = add<int32_t>("veh_departlane", SB2_OFF(veh_departlane), nV, false, 0);
+            const int defLaneProc = ff.scalar<int32_t>("opt_default_departlane_proc", DLD_DEFAULT);
+            const int defLane = ff.scalar<int32_t>("opt_default_departlane", 0);
+            for (int v = 0; v < nV; v++) {
+                int proc = lp[v], idx = lv[v];
+                if (proc == DLD_DEFAULT) {
+                    proc = defLaneProc;
+                    idx = defLane;
+                }
+                const int r = h.veh_route[v];
+                const int e0 = h.route_edges[h.route_begin[r]];
+                const int nl = h.edge_lane_begin[e0 + 1] - h.edge_lane_begin[e0];
+                if (proc == DLD_DEFAULT || proc == DLD_FIRST_ALLOWED) {
+                    idx = 0;
+                } else if (proc != DLD_GIVEN) {
+                    // free / allowed / best: every choice is the only lane of a single-lane edge; "random" draws from the RNG
+                    if (nl != 1 || proc == 2) {
+                        throw std::runtime_error("sumob200: departLane must be 'first' or an index on multi-lane edges");
+                    }
+                    idx = 0;
+                }
+                if (idx >= nl) {
+                    throw std::runtime_error("sumob200: departLane index out of range");
+                }
+                dl[v] = h.edge_lane_begin[e0] + idx;
+            }
+            // departure queues per lane, in load order
+            int32_t* qb = add<int32_t>("dq_begin", SB2_OFF(dq_begin), (size_t)nL + 1, false, 0);
+            int32_t* qv = add<int32_t>("dq_veh", SB2_OFF(dq_veh), nV, false, 0);
+            int32_t* qh = SB2_DYN(int32_t, dq_head, nL, 0);
+            for (int v = 0; v < nV; v++) {
+                qb[dl[v] + 1]++;
+            }
+            for (int l = 0; l < nL; l++) {
+                qb[l + 1] += qb[l];
+                qh[l] = qb[l];
+            }
+            std::vector<int32_t> fill(qb, qb + nL);
+            for (int v = 0; v < nV; v++) {
+                qv[fill[dl[v]]++] = v;
+            }
+        }
+        // ---------------- vehicle state
+        SB2_DYN(int32_t, veh_lane, nV, -1); SB2_DYN(int32_t, veh_routepos, nV, 0);
+        SB2_DYN(double, veh_pos, nV, 0.); SB2_DYN(double, veh_speed, nV, 0.); SB2_DYN(double, veh_prevspeed, nV, 0.);
+        SB2_DYN(double, veh_accel, nV, 0.); SB2_DYN(double, veh_backpos, nV, 0.); SB2_DYN(double, veh_lastdist, nV, 0.);
+        SB2_DYN(int64_t, veh_waiting, nV, (int64_t)0); SB2_DYN(int64_t, veh_since_startup, nV, (int64_t)86400000);
+        SB2_DYN(int64_t, veh_jentry, nV, (int64_t)SB2_TIME_MAX); SB2_DYN(int64_t, veh_jentry_ny, nV, (int64_t)SB2_TIME_MAX);
+        SB2_DYN(int64_t, veh_jconflict, nV, (int64_t)SB2_TIME_MAX);
+        SB2_DYN(uint8_t, veh_havetowait, nV, (uint8_t)0); SB2_DYN(uint8_t, veh_moved, nV, (uint8_t)0);
+        SB2_DYN(int64_t, veh_depart_time, nV, (int64_t)-1);
+        SB2_DYN(double, veh_odometer, nV, 0.); SB2_DYN(double, veh_timeloss, nV, 0.); SB2_DYN(double, veh_stopspeed, nV, SB2_DBL_MAX);
+        SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
+        SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
+        SB2_DYN(double, veh_len_in_front, nV, 0.);
+        const size_t nDI = (size_t)nV * MAX_DRIVE_ITEMS;
+        for (int b = 0; b < 2; b++) {
+            SB2_DYN2(int32_t, veh_ndi, b, nV, 0);
+            SB2_DYN2(int32_t, di_link, b, nDI, -1); SB2_DYN2(uint8_t, di_request, b, nDI, (uint8_t)0); SB2_DYN2(uint8_t, di_hadstopped, b, nDI, (uint8_t)0);
+            SB2_DYN2(double, di_vpass, b, nDI, 0.); SB2_DYN2(double, di_vwait, b, nDI, 0.); SB2_DYN2(double, di_arrspeed, b, nDI, 0.);
+            SB2_DYN2(double, di_arrspeedbraking, b, nDI, 0.); SB2_DYN2(double, di_dist, b, nDI, 0.); SB2_DYN2(double, di_accelv, b, nDI, 0.);
+            SB2_DYN2(double, di_avail, b, nDI, 0.);
+            SB2_DYN2(int64_t, di_arrtime, b, nDI, (int64_t)0); SB2_DYN2(int64_t, di_leavetime, b, nDI, (int64_t)0);
+            SB2_DYN2(double, di_regspeed, b, nDI, 0.); SB2_DYN2(int64_t, di_regwaiting, b, nDI, (int64_t)0);
+            SB2_DYN2(int32_t, di_next, b, nDI, -1);
+        }
+        h.cur = 0;
+        {
+            double* f = SB2_DYN(double, fleet, 3, 0.);
+            double* g = SB2_DYN(double, fleet_next, 3, 0.);
+            f[0] = g[0] = ff.scalar<double>("opt_max_speed_factor", 1.);
+            f[1] = g[1] = ff.scalar<double>("opt_min_deceleration", 4.5);
+            f[2] = g[2] = ff.scalar<double>("opt_max_mingap", 0.);
+        }
+        SB2_DYN(int32_t, err_flags, 1, 0);
+        SB2_DYN(int32_t, counters, 8, 0);
+    }
+};
+
+}  // namespace sb2

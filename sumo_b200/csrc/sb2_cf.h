@@ -1,0 +1,239 @@
+/* sb2_cf.h -- car-following algebra (semi-implicit Euler update only; MSGlobals::gSemiImplicitEulerUpdate == true).
+ *
+ * Restates, expression for expression (fp64, no FMA contraction: nvcc -fmad=false / g++ -ffp-contract=off):
+ *   MSCFModel            src/microsim/cfmodels/MSCFModel.cpp:87-108 (brakeGap), 112-132 (freeSpeed), 178-195 (getSecureGap),
+ *                        324-348 (max/minNextSpeed), 461-479 (getMinimalArrivalTime), 578-591 (getMinimalArrivalSpeedEuler),
+ *                        798-802 (estimateSpeedAfterDistance), 807-884 (maximumSafeStopSpeed[Euler]), 958-1034
+ *                        (maximumSafeFollowSpeed), 1038-1086 (calculateEmergencyDeceleration)
+ *   MSCFModel_Krauss     src/microsim/cfmodels/MSCFModel_Krauss.cpp:127-176 (stopSpeed, followSpeed, dawdle2)
+ *   MSCFModel_IDM        src/microsim/cfmodels/MSCFModel_IDM.cpp:80-134,178-269
+ */
+#pragma once
+#include "sb2_types.h"
+
+namespace sb2 {
+
+struct CF {
+    double TS;
+    double accel, decel, emergencyDecel, apparentDecel, tau, maxSpeed /* vType maxSpeed */, sigma;
+    int model;
+    double idmDelta, idmStepping;
+    double minGap, length;
+    SUMOTime startupDelay;
+};
+
+SB2_HD CF make_cf(const Ctx& c, int vt) {
+    CF m;
+    m.TS = c.TS;
+    m.accel = c.vt_accel[vt]; m.decel = c.vt_decel[vt]; m.emergencyDecel = c.vt_emergencydecel[vt];
+    m.apparentDecel = c.vt_apparentdecel[vt]; m.tau = c.vt_tau[vt]; m.maxSpeed = c.vt_maxspeed[vt]; m.sigma = c.vt_sigma[vt];
+    m.model = c.vt_cfmodel[vt]; m.idmDelta = c.vt_idm_delta[vt]; m.idmStepping = c.vt_idm_stepping[vt];
+    m.minGap = c.vt_mingap[vt]; m.length = c.vt_length[vt]; m.startupDelay = c.vt_startupdelay[vt];
+    return m;
+}
+
+// MSCFModel.cpp:101-108
+SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) {
+    const double speedReduction = decel * m.TS;
+    const int steps = int(speed / speedReduction);
+    return (steps * speed - speedReduction * steps * (steps + 1) / 2) * m.TS + speed * headwayTime;
+}
+SB2_HD double cf_brakeGap(const CF& m, double speed, double decel, double headwayTime) { return cf_brakeGapEuler(m, speed, decel, headwayTime); }
+// MSCFModel.h: brakeGap(speed) = brakeGap(speed, myDecel, myHeadwayTime)
+SB2_HD double cf_brakeGap(const CF& m, double speed) { return cf_brakeGapEuler(m, speed, m.decel, m.tau); }
+
+// MSCFModel.cpp:324-326 (no accel profiles)
+SB2_HD double cf_maxNextSpeed(const CF& m, double speed) { return MIN2(speed + m.accel * m.TS, m.maxSpeed); }
+// MSCFModel.cpp:330-333
+SB2_HD double cf_minNextSpeed(const CF& m, double speed) { return MAX2(speed - m.decel * m.TS, 0.); }
+// MSCFModel.cpp:341-343
+SB2_HD double cf_minNextSpeedEmergency(const CF& m, double speed) { return MAX2(speed - m.emergencyDecel * m.TS, 0.); }
+
+// MSCFModel.cpp:112-132 (Euler branch); freeSpeed(veh, speed, seen, maxSpeed, onInsertion) at :353-360
+SB2_HD double cf_freeSpeed(const CF& m, double /*currentSpeed*/, double dist, double targetSpeed, bool onInsertion) {
+    if (targetSpeed < 0.) {
+        return targetSpeed;
+    }
+    const double decel = m.decel;
+    const double v = targetSpeed * m.TS;
+    if (dist < v) {
+        return targetSpeed;
+    }
+    const double b = decel * m.TS * m.TS;
+    const double y = MAX2(0.0, ((sqrt((b + 2.0 * v) * (b + 2.0 * v) + 8.0 * b * dist) - b) * 0.5 - v) / b);
+    const double yFull = floor(y);
+    const double exactGap = (yFull * yFull + yFull) * 0.5 * b + yFull * v + (y > yFull ? v : 0.0);
+    const double fullSpeedGain = (yFull + (onInsertion ? 1. : 0.)) * (decel * m.TS);
+    return (MAX2(0.0, dist - exactGap) / (yFull + 1)) / m.TS + fullSpeedGain + targetSpeed;
+}
+
+// MSCFModel.cpp:798-802
+SB2_HD double cf_estimateSpeedAfterDistance(const CF& m, double dist, double v, double accel) {
+    return MIN2(m.maxSpeed, (double)sqrt(MAX2(0., 2 * dist * accel + v * v)));
+}
+
+// MSCFModel.cpp:461-479
+SB2_HD SUMOTime cf_getMinimalArrivalTime(const CF& m, double dist, double currentSpeed, double arrivalSpeed) {
+    if (dist <= 0.) {
+        return 0;
+    }
+    arrivalSpeed = MAX2(0.0, arrivalSpeed);
+    const double accel = (arrivalSpeed >= currentSpeed) ? m.accel : -m.decel;
+    const double accelTime = accel == 0. ? 0. : (arrivalSpeed - currentSpeed) / accel;
+    const double accelWay = accelTime * (arrivalSpeed + currentSpeed) * 0.5;
+    if (dist >= accelWay) {
+        const double nonAccelWay = dist - accelWay;
+        const double nonAccelSpeed = MAX3(currentSpeed, arrivalSpeed, SB2_HALTING_SPEED);
+        return TIME2STEPS(accelTime + nonAccelWay / nonAccelSpeed);
+    }
+    return TIME2STEPS(-(currentSpeed - sqrt(currentSpeed * currentSpeed + 2 * accel * dist)) / accel);
+}
+
+// MSCFModel.cpp:578-591
+SB2_HD double cf_getMinimalArrivalSpeedEuler(const CF& m, double dist, double currentSpeed) {
+    double arrivalSpeedBraking;
+    if (dist < currentSpeed) {
+        arrivalSpeedBraking = SB2_INVALID_SPEED;
+    } else if (2 * (dist - currentSpeed * m.tau) * -m.decel + currentSpeed * currentSpeed >= 0) {
+        arrivalSpeedBraking = cf_estimateSpeedAfterDistance(m, dist - currentSpeed * m.tau, currentSpeed, -m.decel);
+    } else {
+        arrivalSpeedBraking = m.decel;
+    }
+    return arrivalSpeedBraking;
+}
+
+// MSCFModel.cpp:1038-1086
+SB2_HD double cf_calculateEmergencyDeceleration(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel) {
+    if (gap <= 0.) {
+        return m.emergencyDecel;
+    }
+    const double predBrakeDist = 0.5 * predSpeed * predSpeed / predMaxDecel;
+    const double b1 = 0.5 * egoSpeed * egoSpeed / (gap + predBrakeDist);
+    if (b1 <= predMaxDecel) {
+        return b1;
+    }
+    const double b2 = 0.5 * (egoSpeed * egoSpeed - predSpeed * predSpeed) / gap;
+    return b2;
+}
+
+// MSCFModel.cpp:860-884
+SB2_HD double cf_maximumSafeStopSpeedEuler(const CF& m, double gap, double decel, double headway) {
+    const double g = gap - SB2_NUMERICAL_EPS;
+    if (g < 0.) {
+        return 0.;
+    }
+    const double b = decel * m.TS;
+    const double t = headway >= 0 ? headway : m.tau;
+    const double s = m.TS;
+    const double n = floor(.5 - ((t + (sqrt(((s * s) + (4.0 * ((s * (2.0 * g / b - t)) + (t * t))))) * -0.5)) / s));
+    const double h = 0.5 * n * (n - 1) * b * s + n * b * t;
+    const double r = (g - h) / (n * s + t);
+    const double x = n * b + r;
+    return x;
+}
+
+// MSCFModel.cpp:807-856
+SB2_HD double cf_maximumSafeStopSpeed(const CF& m, double gap, double decel, double currentSpeed, bool /*onInsertion*/, double headway, bool relaxEmergency) {
+    double vsafe = cf_maximumSafeStopSpeedEuler(m, gap, decel, headway);
+    if (relaxEmergency && m.decel != m.emergencyDecel) {
+        double origSafeDecel = (currentSpeed - vsafe) / m.TS;
+        if (origSafeDecel > m.decel + SB2_NUMERICAL_EPS) {
+            double safeDecel = SB2_EMERGENCY_DECEL_AMPLIFIER * cf_calculateEmergencyDeceleration(m, gap, currentSpeed, 0., 1);
+            safeDecel = MAX2(safeDecel, m.decel);
+            safeDecel = MIN2(safeDecel, origSafeDecel);
+            vsafe = currentSpeed - safeDecel * m.TS;
+            vsafe = MAX2(vsafe, 0.);
+        }
+    }
+    return vsafe;
+}
+
+// MSCFModel.cpp:958-1034 (gComputeLC false outside the lane changer)
+SB2_HD double cf_maximumSafeFollowSpeed(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel, bool onInsertion, bool computeLC) {
+    const double headway = m.tau;
+    double x;
+    if (gap >= 0 || computeLC) {
+        x = cf_maximumSafeStopSpeed(m, gap + cf_brakeGap(m, predSpeed, MAX2(m.decel, predMaxDecel), 0), m.decel, egoSpeed, onInsertion, headway, false);
+    } else {
+        x = egoSpeed - m.emergencyDecel * m.TS;
+        x = MAX2(x, 0.);
+    }
+    if (m.decel != m.emergencyDecel && !onInsertion && !computeLC) {
+        double origSafeDecel = (egoSpeed - x) / m.TS;
+        if (origSafeDecel > m.decel + SB2_NUMERICAL_EPS) {
+            double safeDecel = SB2_EMERGENCY_DECEL_AMPLIFIER * cf_calculateEmergencyDeceleration(m, gap, egoSpeed, predSpeed, predMaxDecel);
+            safeDecel = MAX2(safeDecel, m.decel);
+            safeDecel = MIN2(safeDecel, origSafeDecel);
+            x = egoSpeed - safeDecel * m.TS;
+            x = MAX2(x, 0.);
+        }
+    }
+    return x;
+}
+
+// ---- IDM (MSCFModel_IDM.cpp) -------------------------------------------------------------------
+// pow(x, delta): delta is 4 by default -> exact repeated squaring is NOT what glibc pow returns in general, but for
+// integer delta in {1,2,4} glibc's correctly rounded pow equals the correctly rounded product only approximately; the
+// IDM path is therefore tolerance-checked, not bit-exact (DESIGN.md "libm").
+SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
+    // MSCFModel_IDM.cpp:236-269
+    const double twoSqrtAccelDecel = 2 * sqrt(m.accel * m.decel);
+    const int iterations = MAX2(1, int(m.TS / m.idmStepping + .5));
+    const double headwayTime = m.tau;
+    double newSpeed = egoSpeed;
+    double gap = gap2pred;
+    if (respectMinGap) {
+        gap += m.minGap;
+    }
+    for (int i = 0; i < iterations; i++) {
+        const double delta_v = newSpeed - predSpeed;
+        double s = MAX2(0., newSpeed * headwayTime + newSpeed * delta_v / twoSqrtAccelDecel);
+        if (respectMinGap) {
+            s += m.minGap;
+        }
+        gap = MAX2(SB2_NUMERICAL_EPS, gap);
+        const double acc = m.accel * (1. - pow(newSpeed / MAX2(SB2_NUMERICAL_EPS, desSpeed), m.idmDelta) - (s * s) / (gap * gap));
+        newSpeed = MAX2(0.0, newSpeed + m.TS * acc / iterations);
+        gap -= MAX2(0., (m.TS / iterations) * (newSpeed - predSpeed));
+    }
+    return MAX2(0., newSpeed);
+}
+
+// ---- model dispatch -----------------------------------------------------------------------------
+// stopSpeed(veh, speed, gap, decel, usage): MSCFModel_Krauss.cpp:127-134 ; relaxEmergency = (usage != FUTURE)
+SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap, double decel, bool future) {
+    return MIN2(cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS /* actionStepLengthSecs */, !future), cf_maxNextSpeed(m, speed));
+}
+SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel, false); }
+
+// followSpeed: MSCFModel_Krauss.cpp:138-152 (Euler branch)
+SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predSpeed, double predMaxDecel, bool computeLC = false) {
+    const double vsafe = cf_maximumSafeFollowSpeed(m, gap, speed, predSpeed, predMaxDecel, false, computeLC);
+    const double vmax = cf_maxNextSpeed(m, speed);
+    return MIN2(vsafe, vmax);
+}
+// MSCFModel.cpp:364-366
+SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred, double predSpeed, double predMaxDecel) {
+    return cf_maximumSafeFollowSpeed(m, gap2pred, speed, predSpeed, predMaxDecel, true, false);
+}
+// MSCFModel.cpp:375-377
+SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel, true); }
+
+// MSCFModel.cpp:178-195 with gComputeLC == false
+SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, double leaderMaxDecel) {
+    const double maxDecel = MAX2(m.decel, leaderMaxDecel);
+    const double bgLeader = cf_brakeGap(m, leaderSpeed, maxDecel, 0);
+    return MAX2(0.0, cf_brakeGap(m, speed, m.decel, m.tau) - bgLeader);
+}
+
+// MSCFModel_Krauss.cpp:155-176 ; random in [0,1)
+SB2_HD double cf_dawdle2(const CF& m, double speed, double sigma, double random) {
+    if (speed < m.accel) {
+        speed -= (sigma * speed * random) * m.TS;
+    } else {
+        speed -= (sigma * m.accel * random) * m.TS;
+    }
+    return MAX2(0., speed);
+}
+
+}  // namespace sb2

@@ -1,0 +1,218 @@
+/* sb2_lane.h -- per-lane work (one GPU thread per lane): pre-plan summary, post-execute hand-off, collision check; and
+ * the static traffic-light phase clock (one thread per program).
+ *
+ * Restates src/microsim/MSLane.cpp:1588-1624 (planMovements: cumulatedVehLength), 4734-4754 (getSpaceTillLastStanding),
+ * 2311-2401 + 2470-2487 (executeMovements removal bookkeeping, updateLengthSum), 2598-2621 + 3539-3548
+ * (integrateNewVehicles, vehicle_position_sorter), 2625-2629 (sortPartialVehicles), 1826-1835 + 1971-2030
+ * (detectCollisions / detectCollisionBetween, non-sublane); src/microsim/traffic_lights/MSTrafficLightLogic.cpp:68-92,
+ * 402-414 (SwitchCommand::execute, setTrafficLightSignals), MSSimpleTrafficLightLogic.cpp:80-110 (trySwitch),
+ * src/microsim/MSLink.cpp:1325-1336 (setTLState).
+ */
+#pragma once
+#include "sb2_types.h"
+#include "sb2_cf.h"
+#include "sb2_veh.h"
+
+namespace sb2 {
+
+// before planMove: cumulated lengths in front of every vehicle, space till last standing vehicle
+SB2_HDN void lane_summary(const Ctx& c, int l) {
+    // front -> back (MSLane.cpp:1608-1623)
+    double cum = 0.;
+    for (int v = c.lane_first[l]; v >= 0; v = c.veh_behind[v]) {
+        c.veh_len_in_front[v] = cum;
+        cum += veh_length_with_gap(c, v);
+    }
+    // back -> front (MSLane.cpp:4734-4754); `last != ego` never excludes anything for the lanes ahead of ego
+    double lengths = 0;
+    bool found = false;
+    double ret = 0;
+    for (int last = c.lane_last[l]; last >= 0; last = c.veh_ahead[last]) {
+        if (c.veh_speed[last] < SB2_HALTING_SPEED && !(c.lane_flags[l] & LF_ROUNDABOUT)) {
+            found = true;
+            const CF cf = make_cf(c, c.veh_type[last]);
+            const double lastBrakeGap = cf_brakeGap(cf, c.veh_speed[last]);
+            ret = (c.veh_pos[last] - cf.length) + lastBrakeGap - lengths;
+            break;
+        }
+        lengths += veh_length_with_gap(c, last);
+    }
+    if (!found) {
+        ret = c.lane_length[l] - lengths;
+    }
+    c.ls_space[l] = ret;
+    c.ls_found_stopped[l] = found;
+}
+
+// after executeMove: pop the vehicles that left at the front, append the arrivals at the rear, sort partial occupators
+SB2_HDN void lane_handoff(const Ctx& c, int l) {
+    // ---- MSLane::executeMovements erase + updateLengthSum
+    double toRemove = 0;
+    int f = c.lane_first[l];
+    int removed = 0;
+    while (f >= 0 && c.veh_lane[f] != l) {
+        toRemove += veh_length_with_gap(c, f);
+        f = c.veh_behind[f];
+        removed++;
+    }
+    if (removed > 0) {
+        c.lane_first[l] = f;
+        if (f >= 0) {
+            c.veh_ahead[f] = -1;
+        } else {
+            c.lane_last[l] = -1;
+        }
+        c.lane_nveh[l] -= removed;
+    }
+    double brutto = c.lane_brutto[l] - toRemove;
+    if (c.lane_nveh[l] == 0) {
+        brutto = 0;
+    }
+    // ---- MSLane::integrateNewVehicles
+    int inc[16];
+    int ni = 0;
+    for (int v = c.lane_incoming[l]; v >= 0; v = c.veh_next_incoming[v]) {
+        if (ni < 16) {
+            inc[ni++] = v;
+        } else {
+            raise(c, ERR_LANE_ORDER);
+        }
+    }
+    c.lane_incoming[l] = -1;
+    // sort by (back position descending, numerical id descending) -- vehicle_position_sorter
+    for (int i = 1; i < ni; i++) {
+        const int x = inc[i];
+        const double px = c.veh_pos[x] - veh_length(c, x);
+        int j = i - 1;
+        while (j >= 0) {
+            const int y = inc[j];
+            const double py = c.veh_pos[y] - veh_length(c, y);
+            const bool xBeforeY = (px != py) ? (px > py) : (c.veh_numid[x] > c.veh_numid[y]);
+            if (!xBeforeY) {
+                break;
+            }
+            inc[j + 1] = y;
+            j--;
+        }
+        inc[j + 1] = x;
+    }
+    for (int i = 0; i < ni; i++) {
+        const int v = inc[i];
+        const int oldLast = c.lane_last[l];
+        c.veh_ahead[v] = oldLast;
+        c.veh_behind[v] = -1;
+        if (oldLast >= 0) {
+            c.veh_behind[oldLast] = v;
+        } else {
+            c.lane_first[l] = v;
+        }
+        c.lane_last[l] = v;
+        brutto += veh_length_with_gap(c, v);
+    }
+    c.lane_nveh[l] += ni;
+    c.lane_brutto[l] = brutto;
+    // ---- partial occupators were appended by executeMove; keep them sorted by back position (sortPartialVehicles)
+    int np = c.lane_npartial[l];
+    if (np > MAX_PARTIAL) {
+        raise(c, ERR_PARTIAL_OVERFLOW);
+        np = MAX_PARTIAL;
+        c.lane_npartial[l] = np;
+    }
+    int32_t* p = c.lane_partial + (size_t)l * MAX_PARTIAL;
+    for (int i = 1; i < np; i++) {
+        const int x = p[i];
+        const double px = veh_back_pos_on_lane(c, x, l);
+        int j = i - 1;
+        while (j >= 0) {
+            const double py = veh_back_pos_on_lane(c, p[j], l);
+            // equal back positions: lower vehicle index first (the reference order is then the push order)
+            if (py < px || (py == px && p[j] < x)) {
+                break;
+            }
+            p[j + 1] = p[j];
+            j--;
+        }
+        p[j + 1] = x;
+    }
+}
+
+// executeMove appends the vehicle to the partial list of every lane its back still covers
+SB2_HD void veh_register_partials(const Ctx& c, int v) {
+    if (c.veh_lane[v] < 0) {
+        return;
+    }
+    const int nf = c.veh_nfurther[v];
+    for (int i = 0; i < nf; i++) {
+        const int l = c.veh_further[(size_t)v * MAX_FURTHER + i];
+#if defined(__CUDA_ARCH__)
+        const int slot = atomicAdd(&c.lane_npartial[l], 1);
+#else
+        const int slot = c.lane_npartial[l]++;
+#endif
+        if (slot < MAX_PARTIAL) {
+            c.lane_partial[(size_t)l * MAX_PARTIAL + slot] = v;
+        }
+    }
+}
+
+// MSLane::detectCollisions (non-sublane): adjacent pairs + rear-most partial occupator.  The engine does not implement
+// the teleport that follows a collision: it raises ERR_COLLISION and counts it.
+SB2_HDN void lane_detect_collisions(const Ctx& c, int l, const double* vt_collision_mingap_factor) {
+    int pred = c.lane_first[l];
+    if (pred < 0) {
+        return;
+    }
+    if (c.lane_npartial[l] > 0) {
+        const int victim = c.lane_partial[(size_t)l * MAX_PARTIAL];
+        const int collider = pred;
+        const double gap = veh_back_pos_on_lane(c, victim, l) - c.veh_pos[collider] - vt_collision_mingap_factor[c.veh_type[collider]] * veh_mingap(c, collider);
+        if (gap < -SB2_NUMERICAL_EPS) {
+            raise(c, ERR_COLLISION);
+            atomic_inc(&c.counters[4]);
+        }
+    }
+    for (int veh = c.veh_behind[pred]; veh >= 0; pred = veh, veh = c.veh_behind[veh]) {
+        const double gap = (c.veh_pos[pred] - veh_length(c, pred)) - c.veh_pos[veh] - vt_collision_mingap_factor[c.veh_type[veh]] * veh_mingap(c, veh);
+        if (gap < -SB2_NUMERICAL_EPS) {
+            raise(c, ERR_COLLISION);
+            atomic_inc(&c.counters[4]);
+        }
+    }
+}
+
+// static program phase clock: fires like MSTrafficLightLogic::SwitchCommand at the begin of the step
+SB2_HDN void tls_advance(const Ctx& c, int tl) {
+    const int p0 = c.tl_phase_begin[tl];
+    const int nPhases = c.tl_phase_begin[tl + 1] - p0;
+    if (nPhases == 0) {
+        return;
+    }
+    // a phase of duration 0 would re-fire within the same step in the reference's event queue
+    int guard = 0;
+    while (c.tl_next_switch[tl] <= c.t && guard++ < 16) {
+        // MSSimpleTrafficLightLogic::trySwitch: step = (step + 1) % phases ; return duration
+        int step = c.tl_cur_phase[tl] + 1;
+        if (step >= nPhases) {
+            step = 0;
+        }
+        c.tl_cur_phase[tl] = step;
+        const SUMOTime switchTime = c.tl_next_switch[tl];
+        c.tl_next_switch[tl] = switchTime + c.phase_dur[p0 + step];
+        // setTrafficLightSignals(t)
+        const uint8_t* st = c.phase_states + c.phase_state_begin[p0 + step];
+        for (int i = c.tl_link_begin[tl]; i < c.tl_link_begin[tl + 1]; i++) {
+            const int k = c.tllink_link[i];
+            const uint8_t s = st[c.tllink_index[i]];
+            // MSLink::setTLState (MSLink.cpp:1325-1336)
+            if (c.link_state[k] != s) {
+                c.link_last_change[k] = switchTime;
+            }
+            c.link_state[k] = s;
+            if (state_green(s)) {
+                c.link_last_green[k] = s;
+            }
+        }
+    }
+}
+
+}  // namespace sb2

@@ -1,0 +1,239 @@
+/* sb2_types.h -- state layout of the step engine.
+ *
+ * One `Ctx` of raw pointers describes the whole simulation state: the flattened network (read-only after load), the
+ * per-vehicle structure-of-arrays (indexed by the vehicle's load-order index, which is stable for its whole life, so a
+ * grid of one thread per vehicle touches every state array fully coalesced), the per-vehicle drive items (double
+ * buffered: the items written by planMove of step t stay readable as the "approach table" while planMove of step t+1
+ * writes the other buffer), and per-lane queues (doubly linked through veh_ahead/veh_behind; lanes are FIFOs in the
+ * non-sublane model, so hand-off is pop-front / push-back).
+ *
+ * All functions over a Ctx are SB2_HD: they are compiled by nvcc into the sm_100a kernels of libsumob200.so (the
+ * product) and, for debugging in a container without a GPU, by g++ into tests/host_emul (test infrastructure only;
+ * libsumob200.so has no CPU path).
+ *
+ * Reference types mirrored here: MSVehicle::State / DriveProcessItem (MSVehicle.h:1985), MSLink::ApproachingVehicleInformation
+ * (MSLink.h:118), MSLink::ConflictInfo (MSLink.h:196), MSLane vehicle containers (MSLane.h myVehicles/myPartialVehicles).
+ */
+#pragma once
+#include <stdint.h>
+#include <math.h>
+#include <float.h>
+
+#if defined(__CUDACC__)
+#define SB2_HD __host__ __device__ __forceinline__
+#define SB2_HDN __host__ __device__ __noinline__
+#else
+#define SB2_HD inline
+#define SB2_HDN inline
+#endif
+
+namespace sb2 {
+
+typedef int64_t SUMOTime;
+
+// src/config.h.cmake:236-243, utils/common/StdDefs.h:52, MSVehicle.cpp:118-127, SUMOTime.h:34
+#define SB2_NUMERICAL_EPS 0.001
+#define SB2_POSITION_EPS 0.1
+#define SB2_SPEED_EPS 0.01
+#define SB2_HALTING_SPEED 0.1
+#define SB2_NUMERICAL_EPS_SPEED (0.1 * SB2_NUMERICAL_EPS * c.TS)
+#define SB2_CRLL_LOOK_AHEAD 5
+#define SB2_JUNCTION_BLOCKAGE_TIME 5
+#define SB2_DIST_TO_STOPLINE_EXPECT_PRIORITY 1.0
+#define SB2_DBL_MAX 1.7976931348623157e308
+#define SB2_TIME_MAX (INT64_MAX - 1000)          /* SUMOTime_MAX */
+#define SB2_TIME_MIN INT64_MIN                   /* SUMOTime_MIN */
+#define SB2_INVALID_TIME INT64_MIN               /* MSLink.h INVALID_TIME = SUMOTime_MIN */
+#define SB2_INVALID_SPEED 299792459.0            /* MSCFModel.h:33 */
+#define SB2_NO_INTERSECTION 10000.0              /* MSLink.cpp:76 */
+#define SB2_EMERGENCY_DECEL_AMPLIFIER 1.2        /* MSCFModel.h:35 */
+
+enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4 };
+
+// lane_flags / edge_flags bits (include/sumob200_flatfile.h)
+enum { LF_INTERNAL = 1, LF_ROUNDABOUT = 2, LF_FRINGE = 4, LF_LANECHANGER = 8 };
+// link_flags bits
+enum {
+    KF_KEEPCLEAR = 1, KF_HASFOES = 2, KF_AMCONT = 4, KF_ENTRY = 8, KF_CONFLICT_ENTRY = 16, KF_EXIT = 32,
+    KF_EXIT_AFTER_IJ = 64, KF_INTERNAL_JUNCTION = 128, KF_INDIRECT = 256, KF_PEDFOE = 512, KF_TURNAROUND = 1024, KF_AMCONT_OFF = 2048
+};
+// MSLink::ConflictFlag (MSLink.h:187-193)
+enum { CONFLICT_DEFAULT = 0, CONFLICT_DUMMY_MERGE = 1, CONFLICT_NO_INTERSECTION = 2, CONFLICT_STOP_AT_INTERNAL_JUNCTION = 3, CONFLICT_SIBLING_CONTINUATION = 4 };
+// LinkLeader flags (MSLink.h:75-83)
+enum { LL_IN_THE_WAY = 1, LL_FROM_LEFT = 2, LL_SAME_SOURCE = 4, LL_SAME_TARGET = 8 };
+// error / event flags raised by kernels (never silently ignored: sumob200_step returns them)
+enum {
+    ERR_DRIVE_ITEM_OVERFLOW = 1, ERR_FURTHER_OVERFLOW = 2, ERR_PARTIAL_OVERFLOW = 4, ERR_COLLISION = 8, ERR_TELEPORT = 16,
+    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512
+};
+// car-following model ids = SUMO_TAG_CF_* values are remapped at load time
+enum { CF_KRAUSS = 0, CF_KRAUSS_ORIG1 = 1, CF_IDM = 2 };
+
+struct Ctx {
+    // ---- options (MSGlobals) -------------------------------------------------------------
+    double TS;                 // step length [s]
+    SUMOTime DELTA_T;          // step length [ms]
+    SUMOTime t;                // current time step (SIMSTEP)
+    SUMOTime timeToImpatience, timeToTeleport, startupWaitThreshold, ignoreJunctionBlocker;
+    double tlsYellowMinDecel;
+    // fleet aggregates used by MSLane::getMaximumBrakeDist, running max/min over departed vehicles (MSVehicleControl.cpp:199-216):
+    // [0] maxSpeedFactor [1] minDeceleration [2] maxMinGap.  `fleet` is the snapshot read during a step, `fleet_next` is updated
+    // at departure and copied over at the begin of the next step.
+    double* fleet; double* fleet_next;
+    int nL, nE, nK, nV, nT, nTL;
+
+    // ---- lanes (static) ------------------------------------------------------------------
+    const double* lane_length; const double* lane_speed;
+    const int32_t* lane_edge; const int32_t* lane_flags; const int32_t* lane_link_begin;
+    const int32_t* lane_pred_logical; const int32_t* lane_pred_normal; const int32_t* lane_entry_link;
+    const int32_t* lane_inc_begin; const int32_t* inc_lane; const int32_t* inc_link; const double* inc_length;
+    const int32_t* lane_to_junction; const int32_t* lane_from_junction;
+    const int32_t* edge_lane_begin;
+    // ---- lanes (dynamic) -----------------------------------------------------------------
+    int32_t* lane_first;       // front-most vehicle (largest pos) or -1        (MSLane::myVehicles.back())
+    int32_t* lane_last;        // rear-most vehicle or -1                        (MSLane::myVehicles.front())
+    int32_t* lane_nveh;
+    double* lane_brutto;       // myBruttoVehicleLengthSum
+    int32_t* lane_npartial; int32_t* lane_partial;   // [nL*MAX_PARTIAL] partial occupators, sorted by back position
+    int32_t* lane_incoming;    // head of the list of vehicles that entered this lane in executeMove (myVehBuffer)
+    // per-step lane summary (k_lane_summary)
+    int32_t* ls_lastveh;       // getLastVehicleInformation(nullptr,0): rear-most of vehicles+partials, -1 if none
+    double* ls_space;          // getSpaceTillLastStanding(...)
+    uint8_t* ls_found_stopped;
+    // ---- links ---------------------------------------------------------------------------
+    const int32_t* link_from; const int32_t* link_to; const int32_t* link_via;
+    uint8_t* link_state;       // dynamic for TLS controlled links
+    const uint8_t* link_dir;
+    const double* link_length; const double* link_foevis; const double* link_radius;
+    const int32_t* link_flags; const int32_t* link_index; const int32_t* link_tl;
+    const int32_t* link_internal_before; const int32_t* link_junction; const int32_t* link_entry; const int32_t* link_exit;
+    const int32_t* link_foelink_begin; const int32_t* foelink;
+    const int32_t* link_foelane_begin; const int32_t* foelane;
+    const double* conf_lbc; const double* conf_size; const int32_t* conf_flag; const int32_t* conf_foeidx;
+    const uint64_t* link_response;                   // [4*nK]
+    const int32_t* link_contpred;                    // derived: the entry link consulted by lastWasContMajor/State, or -1
+    SUMOTime* link_last_change;                      // myLastStateChange
+    uint8_t* link_last_green;                        // myLastGreenState
+    int32_t* link_app_head[2];                       // approach table heads (record = veh*MAX_DRIVE_ITEMS+item), per buffer
+    // ---- traffic lights ------------------------------------------------------------------
+    const int32_t* tl_phase_begin; const SUMOTime* phase_dur; const int32_t* phase_state_begin; const uint8_t* phase_states;
+    int32_t* tl_cur_phase; SUMOTime* tl_next_switch;
+    const int32_t* tl_link_begin; const int32_t* tllink_index; const int32_t* tllink_link;
+    // ---- vTypes --------------------------------------------------------------------------
+    const double* vt_length; const double* vt_mingap; const double* vt_maxspeed; const double* vt_desiredmaxspeed;
+    const double* vt_accel; const double* vt_decel; const double* vt_emergencydecel; const double* vt_apparentdecel;
+    const double* vt_tau; const double* vt_sigma; const double* vt_impatience;
+    const int32_t* vt_cfmodel; const SUMOTime* vt_startupdelay;
+    const double* vt_idm_delta; const double* vt_idm_stepping;
+    // ---- routes --------------------------------------------------------------------------
+    const int32_t* route_begin; const int32_t* route_edges;
+    // ---- vehicles (static) ---------------------------------------------------------------
+    const int32_t* veh_type; const int32_t* veh_route; const int32_t* veh_numid; const int32_t* veh_idrank;
+    const SUMOTime* veh_depart; const double* veh_speedfactor; const double* veh_arrivalpos;
+    const int32_t* veh_departlane;                   // resolved departure lane index
+    const double* veh_departpos; const int32_t* veh_departpos_proc;
+    const double* veh_departspeed; const int32_t* veh_departspeed_proc;
+    // ---- vehicles (dynamic) --------------------------------------------------------------
+    int32_t* veh_lane;         // -1 pending, -2 arrived, else lane index
+    int32_t* veh_routepos;     // myCurrEdge - myRoute->begin()
+    double* veh_pos; double* veh_speed; double* veh_prevspeed; double* veh_accel; double* veh_backpos;
+    double* veh_lastdist;      // myLastCoveredDist
+    SUMOTime* veh_waiting; SUMOTime* veh_since_startup;
+    SUMOTime* veh_jentry; SUMOTime* veh_jentry_ny; SUMOTime* veh_jconflict;   // myJunctionEntryTime, ..NeverYield, ..ConflictEntryTime
+    uint8_t* veh_havetowait;   // myHaveToWaitOnNextLink
+    uint8_t* veh_moved;        // set by executeMove: 1 = entered a new lane, 2 = arrived
+    SUMOTime* veh_depart_time; // myDeparture
+    double* veh_odometer; double* veh_timeloss; double* veh_stopspeed;
+    int32_t* veh_ahead; int32_t* veh_behind;   // lane queue links (towards larger / smaller position)
+    int32_t* veh_next_incoming;
+    int32_t* veh_nfurther; int32_t* veh_further;     // [nV*MAX_FURTHER] lanes the back still covers, nearest first
+    double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)
+    // drive items, double buffered [2][MAX_DRIVE_ITEMS*nV], item-major (item i of vehicle v at i*nV+v)
+    int32_t* veh_ndi[2];
+    int32_t* di_link[2]; uint8_t* di_request[2]; uint8_t* di_hadstopped[2];
+    double* di_vpass[2]; double* di_vwait[2]; double* di_arrspeed[2]; double* di_arrspeedbraking[2];
+    double* di_dist[2]; double* di_accelv[2]; double* di_avail[2];
+    SUMOTime* di_arrtime[2];
+    SUMOTime* di_leavetime[2];           // approach record: MSLink::getLeaveTime at registration
+    double* di_regspeed[2];              // approach record: approaching->getSpeed() at registration
+    SUMOTime* di_regwaiting[2];          // approach record: waiting time at registration
+    int32_t* di_next[2];                 // next record in the link's approach list
+    int cur;                             // buffer written by this step's planMove
+    // ---- departure queues (per departure lane, in load order) ----------------------------
+    const int32_t* dq_begin; const int32_t* dq_veh; int32_t* dq_head;   // [nL+1], [nV], [nL]
+    // ---- step results --------------------------------------------------------------------
+    int32_t* err_flags;        // [1] OR of ERR_*
+    int32_t* counters;         // [8]: 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports
+};
+
+SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }
+SB2_HD double MAX2(double a, double b) { return a > b ? a : b; }
+SB2_HD double MIN3(double a, double b, double c) { return MIN2(c, a < b ? a : b); }
+SB2_HD double MAX3(double a, double b, double c) { return MAX2(c, a > b ? a : b); }
+SB2_HD SUMOTime MAX2T(SUMOTime a, SUMOTime b) { return a > b ? a : b; }
+SB2_HD SUMOTime MIN2T(SUMOTime a, SUMOTime b) { return a < b ? a : b; }
+
+// SUMOTime.h:58 -- static_cast<SUMOTime> of a double truncates towards zero
+SB2_HD SUMOTime TIME2STEPS(double x) { return (SUMOTime)(x * 1000. + (x >= 0 ? 0.5 : -0.5)); }
+SB2_HD double STEPS2TIME(SUMOTime x) { return (double)x / 1000.; }
+
+SB2_HD void raise(const Ctx& c, int flag) {
+#if defined(__CUDA_ARCH__)
+    atomicOr(c.err_flags, flag);
+#else
+    *c.err_flags |= flag;
+#endif
+}
+SB2_HD int32_t atomic_exch(int32_t* p, int32_t v) {
+#if defined(__CUDA_ARCH__)
+    return atomicExch(p, v);
+#else
+    const int32_t old = *p; *p = v; return old;
+#endif
+}
+SB2_HD void atomic_inc(int32_t* p) {
+#if defined(__CUDA_ARCH__)
+    atomicAdd(p, 1);
+#else
+    (*p)++;
+#endif
+}
+
+SB2_HD void atomic_max_double(double* p, double v) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long* a = (unsigned long long*)p;
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) >= v) {
+            break;
+        }
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    } while (assumed != old);
+#else
+    if (*p < v) { *p = v; }
+#endif
+}
+SB2_HD void atomic_min_double(double* p, double v) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long* a = (unsigned long long*)p;
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) <= v) {
+            break;
+        }
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    } while (assumed != old);
+#else
+    if (*p > v) { *p = v; }
+#endif
+}
+
+SB2_HD bool lane_internal(const Ctx& c, int l) { return (c.lane_flags[l] & LF_INTERNAL) != 0; }
+SB2_HD bool state_priority(uint8_t s) { return s >= 'A' && s <= 'Z'; }               // MSLink.h:473
+SB2_HD bool state_red(uint8_t s) { return s == 'r' || s == 'u'; }                     // MSLink.h:484
+SB2_HD bool state_yellow(uint8_t s) { return s == 'y' || s == 'Y'; }                  // MSLink.h:488
+SB2_HD bool state_green(uint8_t s) { return s == 'G' || s == 'g'; }                   // MSLink.h:492
+
+}  // namespace sb2

@@ -1,0 +1,130 @@
+/* host_emul -- TEST INFRASTRUCTURE, not a product path.
+ *
+ * Compiles the device functions of sumo_b200/csrc (sb2_*.h, the same source nvcc turns into the sm_100a kernels of
+ * libsumob200.so) for the host with g++ -ffp-contract=off and runs the step phases as plain loops.  It exists because the
+ * build container has no GPU: parity of the step logic against traces of the UNMODIFIED reference (oracle/_ref/sumo_flatten
+ * --trace-out) is debugged here, then confirmed on the B200 through the C ABI (tests -m gpu).  libsumob200.so never links
+ * or calls this.
+ *
+ * usage: host_emul X.flat [--trace-out X.trace] [--steps N] [--dump-veh ID]
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "../../sumo_b200/csrc/sb2_build.h"
+#include "../../sumo_b200/csrc/sb2_plan2.h"
+#include "../../sumo_b200/csrc/sb2_exec.h"
+#include "../../sumo_b200/csrc/sb2_lane.h"
+#include "../../sumo_b200/csrc/sb2_insert.h"
+
+using namespace sb2;
+
+static void step(Model& m) {
+    Ctx& c = m.h;
+    for (int tl = 0; tl < c.nTL; tl++) {
+        tls_advance(c, tl);
+    }
+    for (int l = 0; l < c.nL; l++) {
+        lane_summary(c, l);
+    }
+    c.cur ^= 1;
+    std::fill(c.link_app_head[c.cur], c.link_app_head[c.cur] + c.nK, -1);
+    for (int v = 0; v < c.nV; v++) {
+        veh_planMove(c, v);
+    }
+    std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
+    for (int v = 0; v < c.nV; v++) {
+        veh_executeMove(c, v, 0.);
+        veh_register_partials(c, v);
+    }
+    for (int l = 0; l < c.nL; l++) {
+        lane_handoff(c, l);
+    }
+    for (int l = 0; l < c.nL; l++) {
+        lane_detect_collisions(c, l, m.vt_collision_mingap_factor.data());
+    }
+    for (int i = 0; i < 3; i++) {
+        c.fleet[i] = c.fleet_next[i];
+    }
+    for (int l = 0; l < c.nL; l++) {
+        if (c.dq_head[l] < c.dq_begin[l + 1]) {
+            lane_insertVehicles(c, l);
+        }
+    }
+    c.t += c.DELTA_T;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 2) {
+        fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
+        return 2;
+    }
+    std::string traceOut;
+    long maxSteps = -1;
+    for (int i = 2; i < argc; i++) {
+        const std::string a = argv[i];
+        if (a == "--trace-out" && i + 1 < argc) {
+            traceOut = argv[++i];
+        } else if (a == "--steps" && i + 1 < argc) {
+            maxSteps = atol(argv[++i]);
+        }
+    }
+    FlatFile ff;
+    Model m;
+    try {
+        ff.load(argv[1]);
+        m.build(ff);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "%s\n", e.what());
+        return 1;
+    }
+    Ctx& c = m.h;
+    FILE* f = traceOut.empty() ? nullptr : fopen(traceOut.c_str(), "wb");
+    std::vector<int> order(c.nV);
+    for (int v = 0; v < c.nV; v++) {
+        order[v] = v;
+    }
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
+    long steps = 0;
+    long long updates = 0;
+    int lastErr = 0;
+    while ((m.end < 0 || c.t < m.end) && (maxSteps < 0 || steps < maxSteps)) {
+        const SUMOTime t = c.t;
+        step(m);
+        steps++;
+        int n = 0;
+        for (int v = 0; v < c.nV; v++) {
+            n += c.veh_lane[v] >= 0;
+        }
+        updates += n;
+        if (f != nullptr) {
+            const int64_t hdr[2] = {(int64_t)t, (int64_t)n};
+            fwrite(hdr, 8, 2, f);
+            for (int v : order) {
+                if (c.veh_lane[v] >= 0) {
+                    const int64_t ids[2] = {(int64_t)c.veh_numid[v], (int64_t)c.veh_lane[v]};
+                    const double st[2] = {c.veh_pos[v], c.veh_speed[v]};
+                    fwrite(ids, 8, 2, f);
+                    fwrite(st, 8, 2, f);
+                }
+            }
+        }
+        if (*c.err_flags != lastErr) {
+            fprintf(stderr, "t=%lld: error flags now 0x%x\n", (long long)t, *c.err_flags);
+            lastErr = *c.err_flags;
+        }
+        // termination like MSNet::simulationState: no vehicles left and none pending
+        if (m.end < 0 && n == 0 && c.counters[2] == c.nV) {
+            break;
+        }
+    }
+    if (f != nullptr) {
+        fclose(f);
+    }
+    fprintf(stderr, "steps=%ld vehicle-updates=%lld inserted=%d arrived=%d collisions=%d emergencyStops=%d err=0x%x\n", steps, updates,
+            c.counters[2], c.counters[1], c.counters[4], c.counters[5], *c.err_flags);
+    return 0;
+}
