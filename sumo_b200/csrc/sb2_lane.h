@@ -44,8 +44,9 @@ SB2_HDN void lane_summary(const Ctx& c, int l) {
     c.ls_found_stopped[l] = found;
 }
 
-// after executeMove: pop the vehicles that left at the front, append the arrivals at the rear, sort partial occupators
-SB2_HDN void lane_handoff(const Ctx& c, int l) {
+// after executeMove, pass 1: pop the vehicles that left at the front (reads veh_behind of the leavers, which pass 2
+// overwrites when it links them into their new lane -- hence two passes with a grid-wide barrier in between)
+SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
     // ---- MSLane::executeMovements erase + updateLengthSum
     double toRemove = 0;
     int f = c.lane_first[l];
@@ -68,6 +69,12 @@ SB2_HDN void lane_handoff(const Ctx& c, int l) {
     if (c.lane_nveh[l] == 0) {
         brutto = 0;
     }
+    c.lane_brutto[l] = brutto;
+}
+
+// pass 2: append the arrivals at the rear, sort partial occupators
+SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
+    double brutto = c.lane_brutto[l];
     // ---- MSLane::integrateNewVehicles
     int inc[16];
     int ni = 0;

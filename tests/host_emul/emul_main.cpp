@@ -22,6 +22,29 @@
 
 using namespace sb2;
 
+static int gDebugVeh = -1;
+static void dumpItems(const Model& m, int v, const char* tag) {
+    const Ctx& c = m.h;
+    const int cur = c.cur;
+    fprintf(stderr, "%s t=%lld veh=%s lane=%s pos=%.6f speed=%.6f wait=%lld ndi=%d htw=%d\n", tag, (long long)c.t, m.veh_names[v].c_str(),
+            c.veh_lane[v] >= 0 ? m.lane_names[c.veh_lane[v]].c_str() : "-", c.veh_pos[v], c.veh_speed[v], (long long)c.veh_waiting[v], c.veh_ndi[cur][v], c.veh_havetowait[v]);
+    if (c.veh_lane[v] >= 0) {
+        fprintf(stderr, "   queue(front->back):");
+        for (int x = c.lane_first[c.veh_lane[v]]; x >= 0; x = c.veh_behind[x]) {
+            fprintf(stderr, " %s@%.2f", m.veh_names[x].c_str(), c.veh_pos[x]);
+        }
+        fprintf(stderr, " | lenInFront=%.2f brutto=%.2f npartial=%d\n", c.veh_len_in_front[v], c.lane_brutto[c.veh_lane[v]], c.lane_npartial[c.veh_lane[v]]);
+    }
+    for (int i = 0; i < c.veh_ndi[cur][v]; i++) {
+        const size_t r = (size_t)i * c.nV + v;
+        const int k = c.di_link[cur][r];
+        fprintf(stderr, "   item %d link=%d(%s->%s state=%c) vPass=%.6f vWait=%.6f req=%d arrT=%lld arrV=%.4f arrVB=%.4f dist=%.4f accelV=%.4f avail=%.4f hadStopped=%d\n", i, k,
+                k >= 0 ? m.lane_names[c.link_from[k]].c_str() : "-", k >= 0 ? m.lane_names[c.link_via[k] >= 0 ? c.link_via[k] : c.link_to[k]].c_str() : "-",
+                k >= 0 ? c.link_state[k] : '-', c.di_vpass[cur][r], c.di_vwait[cur][r], c.di_request[cur][r], (long long)c.di_arrtime[cur][r], c.di_arrspeed[cur][r],
+                c.di_arrspeedbraking[cur][r], c.di_dist[cur][r], c.di_accelv[cur][r], c.di_avail[cur][r], c.di_hadstopped[cur][r]);
+    }
+}
+
 static void step(Model& m) {
     Ctx& c = m.h;
     for (int tl = 0; tl < c.nTL; tl++) {
@@ -35,13 +58,19 @@ static void step(Model& m) {
     for (int v = 0; v < c.nV; v++) {
         veh_planMove(c, v);
     }
+    if (gDebugVeh >= 0 && c.veh_lane[gDebugVeh] >= 0) {
+        dumpItems(m, gDebugVeh, "plan");
+    }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
     for (int v = 0; v < c.nV; v++) {
         veh_executeMove(c, v, 0.);
         veh_register_partials(c, v);
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_handoff(c, l);
+        lane_handoff_remove(c, l);
+    }
+    for (int l = 0; l < c.nL; l++) {
+        lane_handoff_integrate(c, l);
     }
     for (int l = 0; l < c.nL; l++) {
         lane_detect_collisions(c, l, m.vt_collision_mingap_factor.data());
@@ -64,12 +93,15 @@ int main(int argc, char** argv) {
     }
     std::string traceOut;
     long maxSteps = -1;
+    std::string debugName;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
         } else if (a == "--steps" && i + 1 < argc) {
             maxSteps = atol(argv[++i]);
+        } else if (a == "--debug-veh" && i + 1 < argc) {
+            debugName = argv[++i];
         }
     }
     FlatFile ff;
@@ -82,6 +114,11 @@ int main(int argc, char** argv) {
         return 1;
     }
     Ctx& c = m.h;
+    for (int v = 0; v < c.nV; v++) {
+        if (m.veh_names[v] == debugName) {
+            gDebugVeh = v;
+        }
+    }
     FILE* f = traceOut.empty() ? nullptr : fopen(traceOut.c_str(), "wb");
     std::vector<int> order(c.nV);
     for (int v = 0; v < c.nV; v++) {
