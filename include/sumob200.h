@@ -1,0 +1,120 @@
+/* sumob200.h -- C ABI of libsumob200.so, the B200-native replacement of SUMO's per-step vehicle update.
+ *
+ * The boundary sits where the reference's MSNet::simulationStep calls MSEdgeControl
+ * (src/microsim/MSNet.cpp:854-919): one sumob200_step() does what these reference calls do for one simulation step
+ *   myBeginOfTimestepEvents->execute (static TLS SwitchCommand)      MSNet.cpp:854, traffic_lights/MSTrafficLightLogic.cpp:68
+ *   MSEdgeControl::planMovements / setJunctionApproaches              MSNet.cpp:875,878  (src/microsim/MSEdgeControl.cpp:142,188)
+ *   MSEdgeControl::executeMovements                                   MSNet.cpp:881      (MSEdgeControl.cpp:196)
+ *   MSEdgeControl::detectCollisions                                   MSNet.cpp:883      (MSEdgeControl.cpp:339)
+ *   MSInsertionControl::emitVehicles                                  MSNet.cpp:915      (src/microsim/MSInsertionControl.cpp:127)
+ * The scenario crosses the boundary as plain named arrays (the flattened network / vTypes / routes / vehicles described
+ * in sumob200_flatfile.h), produced on the reference side by integration/sumo_flatten.cpp from the objects the unchanged
+ * NLBuilder built.  No SUMO type, no C++ type and no torch type appears in any signature.
+ *
+ * All functions return 0 on success and a negative SUMOB200_E* code on failure; sumob200_last_error() gives the text.
+ * One engine must be driven by one host thread at a time.  There is no CPU fallback: without a CUDA device every
+ * call that computes fails with SUMOB200_ENODEVICE.
+ */
+#ifndef SUMOB200_H
+#define SUMOB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SUMOB200_EINVAL (-1)      /* bad argument / malformed arrays */
+#define SUMOB200_EUNSUPPORTED (-2) /* scenario uses a feature the engine refuses (sublanes, ballistic, multi-lane edges, ...) */
+#define SUMOB200_ENODEVICE (-3)   /* no usable CUDA device */
+#define SUMOB200_ECUDA (-4)       /* CUDA runtime error */
+
+/* bits of sumob200_step_result.flags: events the engine detects but does not resolve itself (the reference resolves them
+ * on the host: teleporting MSVehicleTransfer, collision handling MSLane.cpp:2078, emergency stop warnings) or capacity
+ * overflows of its fixed-size per-vehicle tables.  A non-zero value means the run diverges from the reference from that
+ * step on; the caller must treat it as an error, it is never silently ignored. */
+#define SUMOB200_F_DRIVE_ITEM_OVERFLOW 1
+#define SUMOB200_F_FURTHER_OVERFLOW 2
+#define SUMOB200_F_PARTIAL_OVERFLOW 4
+#define SUMOB200_F_COLLISION 8
+#define SUMOB200_F_TELEPORT 16
+#define SUMOB200_F_EMERGENCY_STOP 32
+#define SUMOB200_F_NO_CONNECTION 64
+#define SUMOB200_F_UNSUPPORTED_LINKSTATE 128
+#define SUMOB200_F_LANE_ORDER 256
+#define SUMOB200_F_SEARCH_OVERFLOW 512
+
+typedef struct sumob200_engine sumob200_engine;
+
+/* one named array of the flattened scenario; dtype: 0=u8 1=i32 2=i64 3=f64 4=u64 (sumob200_flatfile.h) */
+typedef struct sumob200_array {
+    const char* name;
+    uint32_t dtype;
+    uint32_t elem_size;
+    uint64_t count;
+    const void* data;     /* host memory, borrowed for the duration of the call */
+} sumob200_array;
+
+typedef struct sumob200_step_result {
+    int64_t time_ms;          /* simulation time after the last executed step (MSNet::getCurrentTimeStep) */
+    int32_t running;          /* vehicles on the road                  (MSVehicleControl::getRunningVehicleNo) */
+    int32_t departed_total;   /* vehicles inserted so far              (getDepartedVehicleNo) */
+    int32_t arrived_total;    /* vehicles that reached their arrival   (getArrivedVehicleNo) */
+    int32_t collisions;       /* collisions detected so far */
+    int32_t emergency_stops;  /* emergency stops at lane ends so far */
+    int32_t teleports;        /* teleport conditions detected so far (not executed) */
+    int32_t flags;            /* OR of SUMOB200_F_* raised so far */
+    int32_t reserved;
+    int64_t vehicle_updates;  /* sum over the executed steps of vehicles on the road (numerator of SUMO's UPS, MSNet.cpp:959) */
+} sumob200_step_result;
+
+/* state mirror of one vehicle slot (slot = index in the veh_* arrays = load order); what libsumo::Vehicle getters read
+ * from MSVehicle (src/libsumo/Vehicle.cpp getLaneID/getLanePosition/getSpeed) and what MSFCDExport writes */
+typedef struct sumob200_vehicle_state {
+    int32_t lane;             /* lane index, -1 not yet departed, -2 arrived */
+    int32_t route_pos;        /* index of the current route edge */
+    double pos;               /* MSVehicle::getPositionOnLane */
+    double speed;             /* MSVehicle::getSpeed */
+} sumob200_vehicle_state;
+
+/* build an engine on CUDA device `device` from the flattened scenario arrays */
+int sumob200_create(const sumob200_array* arrays, int n_arrays, int device, sumob200_engine** out);
+/* same, reading a .flat container (sumob200_flatfile.h) */
+int sumob200_create_from_file(const char* flat_path, int device, sumob200_engine** out);
+void sumob200_destroy(sumob200_engine* e);
+
+/* run n_steps simulation steps; *out (may be NULL) receives the counters after the last one */
+int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out);
+
+/* copy the state of all vehicle slots to host memory (n = number of loaded vehicles, see sumob200_num_vehicles) */
+int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int capacity);
+/* FCD rows of the vehicles currently on the road, ordered by slot: writes up to `capacity` rows, *n = rows available */
+typedef struct sumob200_fcd_row {
+    int32_t slot;             /* vehicle slot (index into the veh_* arrays; veh_names gives the id) */
+    int32_t lane;
+    double pos, speed;
+    double x, y, angle;       /* MSVehicle::getPosition / computeAngle as navi degrees (MSFCDExport.cpp:119-180) */
+} sumob200_fcd_row;
+int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capacity, int* n);
+
+int sumob200_num_vehicles(const sumob200_engine* e);
+int sumob200_num_lanes(const sumob200_engine* e);
+int64_t sumob200_time_ms(const sumob200_engine* e);
+/* supply the [0,1) dawdle draws of the next step (one per vehicle slot), e.g. draws recorded from the reference; n must
+ * equal sumob200_num_vehicles.  After the call every step consumes draws[] until sumob200_set_random_mode resets it. */
+int sumob200_set_random_draws(sumob200_engine* e, const double* draws, int n);
+/* 0 = no draws (only valid if all sigma == 0), 1 = counter-based generator seeded by --seed */
+int sumob200_set_random_mode(sumob200_engine* e, int mode);
+/* number of kernel launches issued by the engine so far (bench.py reports it as gpu_launches) */
+int64_t sumob200_kernel_launches(const sumob200_engine* e);
+/* time spent in the kernels of the step pipeline, measured with CUDA events on the engine's stream: per phase sums in ms
+ * since the last call with reset != 0.  phases: 0 pre (tls, lane summary) 1 plan 2 execute 3 hand-off 4 insert */
+int sumob200_phase_times(sumob200_engine* e, double* ms, int n_phases, int reset);
+int sumob200_set_profiling(sumob200_engine* e, int enabled);
+
+const char* sumob200_last_error(void);
+const char* sumob200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,449 @@
+/* engine.cu -- libsumob200.so: the sm_100a kernels of the step pipeline and the C ABI of include/sumob200.h.
+ *
+ * Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -prec-div=true -prec-sqrt=true -lineinfo (see build.py).
+ * -fmad=false keeps every fp64 expression in the reference's evaluation order without FMA contraction, so Krauss sigma=0
+ * trajectories are bit-identical to the reference built with g++ -ffp-contract=off.
+ *
+ * One simulation step = 8 launches on one stream (no host synchronisation in between):
+ *   k_pre       max(nL,nK,nTL) threads   TLS phase clock, per-lane summary (lengths in front, space till last standing),
+ *                                        reset of this step's approach-table heads, fleet aggregate snapshot
+ *   k_plan      nV threads               MSVehicle::planMove + approach registration           (sb2_plan2.h)
+ *   (memset)    lane_npartial
+ *   k_execute   nV threads               MSVehicle::executeMove, partial occupator registration (sb2_exec.h)
+ *   k_remove    nL threads               pop vehicles that left each lane                       (sb2_lane.h)
+ *   k_integrate nL threads               append arrivals, sort partial occupators, collisions
+ *   k_insert    nL threads               MSInsertionControl::emitVehicles per departure lane    (sb2_insert.h)
+ *   k_count     nV threads               running-vehicle count (summary / UPS numerator)
+ *   k_advance   1 thread                 clock += DELTA_T, flip drive-item buffer (state lives on the device: graph-replayable)
+ * There is no CPU path in this library.
+ */
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/sumob200.h"
+#include "sb2_build.h"
+#include "sb2_plan2.h"
+#include "sb2_exec.h"
+#include "sb2_lane.h"
+#include "sb2_insert.h"
+
+using namespace sb2;
+
+namespace {
+
+thread_local std::string gLastError;
+
+#define CUDA_TRY(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
+        gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
+
+constexpr int BLOCK = 128;
+
+__global__ void __launch_bounds__(BLOCK) k_pre(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.nTL) {
+        tls_advance(c, i);
+    }
+    if (i < c.nL) {
+        lane_summary(c, i);
+    }
+    if (i < c.nK) {
+        c.link_app_head[c.cur][i] = -1;
+    }
+    if (i < 3) {
+        c.fleet[i] = c.fleet_next[i];
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_plan(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV) {
+        veh_planMove(c, v);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_execute(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV) {
+        veh_executeMove(c, v, veh_random(c, v));
+        veh_register_partials(c, v);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_remove(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        lane_handoff_remove(c, l);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_integrate(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        lane_handoff_integrate(c, l);
+        lane_detect_collisions(c, l);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_insert(const Ctx* __restrict__ dc) {
+    const Ctx& c = *dc;
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1]) {
+        lane_insertVehicles(c, l);
+    }
+}
+
+// running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
+__global__ void __launch_bounds__(BLOCK) k_count(const Ctx* __restrict__ dc, unsigned long long* updates) {
+    const Ctx& c = *dc;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const unsigned mask = __ballot_sync(0xffffffffu, on);
+    if ((threadIdx.x & 31) == 0 && mask != 0) {
+        const int n = __popc(mask);
+        atomicAdd(&c.counters[0], n);
+        atomicAdd(updates, (unsigned long long)n);
+    }
+}
+
+// end of step: advance the clock and flip the drive-item buffer (device-resident so that a step needs no host-side
+// parameter change and can be replayed from a CUDA graph)
+__global__ void k_advance(Ctx* dc) {
+    dc->t += dc->DELTA_T;
+    dc->cur ^= 1;
+}
+
+__global__ void k_mirror(const Ctx* __restrict__ dc, sumob200_vehicle_state* out) {
+    const Ctx& c = *dc;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV) {
+        sumob200_vehicle_state s;
+        s.lane = c.veh_lane[v];
+        s.route_pos = c.veh_routepos[v];
+        s.pos = c.veh_pos[v];
+        s.speed = c.veh_speed[v];
+        out[v] = s;
+    }
+}
+
+}  // namespace
+
+struct sumob200_engine {
+    Model model;
+    Ctx d;                                  // host shadow of the device-resident Ctx (pointers into device memory)
+    Ctx* dCtx = nullptr;                    // the device-resident copy every kernel reads
+    std::vector<void*> dev;                 // device allocation of model.buffers[i]
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    unsigned long long* dUpdates = nullptr;
+    sumob200_vehicle_state* dMirror = nullptr;
+    double* dReplay = nullptr;
+    int64_t launches = 0;
+    bool profiling = false;
+    cudaEvent_t ev[6];
+    double phaseMs[5] = {0, 0, 0, 0, 0};
+    long long stepsDone = 0;
+};
+
+namespace {
+
+int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_engine** out) {
+    int nDev = 0;
+    if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev <= 0) {
+        gLastError = "sumob200: no CUDA device available (this library has no CPU path)";
+        delete e;
+        return SUMOB200_ENODEVICE;
+    }
+    if (device < 0 || device >= nDev) {
+        gLastError = "sumob200: invalid device index";
+        delete e;
+        return SUMOB200_EINVAL;
+    }
+    try {
+        e->model.build(ff);
+    } catch (const std::exception& ex) {
+        gLastError = ex.what();
+        delete e;
+        return SUMOB200_EUNSUPPORTED;
+    }
+    e->device = device;
+    cudaError_t err = cudaSetDevice(device);
+    if (err == cudaSuccess) {
+        err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    }
+    e->d = e->model.h;
+    for (Buffer* b : e->model.buffers) {
+        void* p = nullptr;
+        if (err == cudaSuccess) {
+            err = cudaMalloc(&p, b->host.size());
+        }
+        if (err == cudaSuccess) {
+            err = cudaMemcpyAsync(p, b->host.data(), b->host.size(), cudaMemcpyHostToDevice, e->stream);
+        }
+        e->dev.push_back(p);
+        *reinterpret_cast<void**>(reinterpret_cast<char*>(&e->d) + b->offset) = p;
+    }
+    e->d.cur = 1;   // the first step writes buffer 1 (the host emulation flips 0 -> 1 at the start of its first step)
+    if (err == cudaSuccess) {
+        err = cudaMalloc(&e->dCtx, sizeof(Ctx));
+    }
+    if (err == cudaSuccess) {
+        err = cudaMemcpyAsync(e->dCtx, &e->d, sizeof(Ctx), cudaMemcpyHostToDevice, e->stream);
+    }
+    if (err == cudaSuccess) {
+        err = cudaMalloc(&e->dUpdates, sizeof(unsigned long long));
+    }
+    if (err == cudaSuccess) {
+        err = cudaMemsetAsync(e->dUpdates, 0, sizeof(unsigned long long), e->stream);
+    }
+    for (int i = 0; i < 6 && err == cudaSuccess; i++) {
+        err = cudaEventCreate(&e->ev[i]);
+    }
+    if (err == cudaSuccess) {
+        err = cudaStreamSynchronize(e->stream);
+    }
+    if (err != cudaSuccess) {
+        gLastError = std::string("sumob200_create: ") + cudaGetErrorString(err);
+        sumob200_destroy(e);
+        return SUMOB200_ECUDA;
+    }
+    // the host copies of the big dynamic buffers are not needed any more
+    for (Buffer* b : e->model.buffers) {
+        if (b->dynamic) {
+            std::vector<uint8_t>().swap(b->host);
+        }
+    }
+    *out = e;
+    return 0;
+}
+
+inline int grid(int n) { return n > 0 ? (n + BLOCK - 1) / BLOCK : 1; }
+
+}  // namespace
+
+extern "C" {
+
+const char* sumob200_last_error(void) { return gLastError.c_str(); }
+const char* sumob200_version(void) { return "sumob200 0.1 (sm_100a; Krauss, single-lane edges, static TLS)"; }
+
+int sumob200_create(const sumob200_array* arrays, int n_arrays, int device, sumob200_engine** out) {
+    if (arrays == nullptr || out == nullptr || n_arrays <= 0) {
+        gLastError = "sumob200_create: null argument";
+        return SUMOB200_EINVAL;
+    }
+    FlatFile ff;
+    for (int i = 0; i < n_arrays; i++) {
+        const sumob200_array& a = arrays[i];
+        if (a.name == nullptr || (a.count > 0 && a.data == nullptr) || a.elem_size == 0) {
+            gLastError = "sumob200_create: malformed array descriptor";
+            return SUMOB200_EINVAL;
+        }
+        FlatArray fa;
+        fa.dtype = a.dtype;
+        fa.elemSize = a.elem_size;
+        fa.count = a.count;
+        fa.bytes.resize(a.count * a.elem_size);
+        if (!fa.bytes.empty()) {
+            memcpy(fa.bytes.data(), a.data, fa.bytes.size());
+        }
+        ff.arrays[a.name] = std::move(fa);
+    }
+    return finishCreate(new sumob200_engine(), ff, device, out);
+}
+
+int sumob200_create_from_file(const char* flat_path, int device, sumob200_engine** out) {
+    if (flat_path == nullptr || out == nullptr) {
+        gLastError = "sumob200_create_from_file: null argument";
+        return SUMOB200_EINVAL;
+    }
+    FlatFile ff;
+    try {
+        ff.load(flat_path);
+    } catch (const std::exception& ex) {
+        gLastError = ex.what();
+        return SUMOB200_EINVAL;
+    }
+    return finishCreate(new sumob200_engine(), ff, device, out);
+}
+
+void sumob200_destroy(sumob200_engine* e) {
+    if (e == nullptr) {
+        return;
+    }
+    cudaSetDevice(e->device);
+    for (void* p : e->dev) {
+        if (p != nullptr) {
+            cudaFree(p);
+        }
+    }
+    if (e->dUpdates != nullptr) {
+        cudaFree(e->dUpdates);
+    }
+    if (e->dCtx != nullptr) {
+        cudaFree(e->dCtx);
+    }
+    if (e->dMirror != nullptr) {
+        cudaFree(e->dMirror);
+    }
+    if (e->dReplay != nullptr) {
+        cudaFree(e->dReplay);
+    }
+    if (e->stream != nullptr) {
+        cudaStreamDestroy(e->stream);
+    }
+    delete e;
+}
+
+int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
+    if (e == nullptr || n_steps < 0) {
+        gLastError = "sumob200_step: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    Ctx& c = e->d;
+    const int nPre = c.nL > c.nK ? (c.nL > c.nTL ? c.nL : c.nTL) : (c.nK > c.nTL ? c.nK : c.nTL);
+    cudaStream_t s = e->stream;
+    for (int i = 0; i < n_steps; i++) {
+        const bool prof = e->profiling;
+        if (prof) { cudaEventRecord(e->ev[0], s); }
+        CUDA_TRY(cudaMemsetAsync(c.counters, 0, sizeof(int32_t), s));   // counters[0] = running vehicles of this step
+        k_pre<<<grid(nPre < 3 ? 3 : nPre), BLOCK, 0, s>>>(e->dCtx);
+        if (prof) { cudaEventRecord(e->ev[1], s); }
+        k_plan<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx);
+        if (prof) { cudaEventRecord(e->ev[2], s); }
+        CUDA_TRY(cudaMemsetAsync(c.lane_npartial, 0, sizeof(int32_t) * (size_t)c.nL, s));
+        k_execute<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx);
+        if (prof) { cudaEventRecord(e->ev[3], s); }
+        k_remove<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
+        k_integrate<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
+        if (prof) { cudaEventRecord(e->ev[4], s); }
+        k_insert<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
+        k_count<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx, e->dUpdates);
+        k_advance<<<1, 1, 0, s>>>(e->dCtx);
+        if (prof) {
+            cudaEventRecord(e->ev[5], s);
+            CUDA_TRY(cudaEventSynchronize(e->ev[5]));
+            for (int p = 0; p < 5; p++) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, e->ev[p], e->ev[p + 1]);
+                e->phaseMs[p] += ms;
+            }
+        }
+        e->launches += 8;
+        c.t += c.DELTA_T;
+        c.cur ^= 1;
+        e->stepsDone++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    if (out != nullptr) {
+        int32_t counters[8];
+        int32_t flags = 0;
+        unsigned long long updates = 0;
+        CUDA_TRY(cudaMemcpyAsync(counters, c.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaMemcpyAsync(&flags, c.err_flags, sizeof(flags), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaMemcpyAsync(&updates, e->dUpdates, sizeof(updates), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        out->time_ms = c.t;
+        out->running = counters[0];
+        out->arrived_total = counters[1];
+        out->departed_total = counters[2];
+        out->collisions = counters[4];
+        out->emergency_stops = counters[5];
+        out->teleports = counters[6];
+        out->flags = flags;
+        out->reserved = 0;
+        out->vehicle_updates = (int64_t)updates;
+    }
+    return 0;
+}
+
+int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int capacity) {
+    if (e == nullptr || out == nullptr || capacity < e->d.nV) {
+        gLastError = "sumob200_mirror_all: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int nV = e->d.nV;
+    if (e->dMirror == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)(nV > 0 ? nV : 1)));
+    }
+    k_mirror<<<grid(nV), BLOCK, 0, e->stream>>>(e->dCtx, e->dMirror);
+    e->launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(out, e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)nV, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int sumob200_num_vehicles(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nV; }
+int sumob200_num_lanes(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nL; }
+int64_t sumob200_time_ms(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.t; }
+int64_t sumob200_kernel_launches(const sumob200_engine* e) { return e == nullptr ? 0 : e->launches; }
+
+int sumob200_set_random_draws(sumob200_engine* e, const double* draws, int n) {
+    if (e == nullptr || draws == nullptr || n != e->d.nV) {
+        gLastError = "sumob200_set_random_draws: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    if (e->dReplay == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->dReplay, sizeof(double) * (size_t)(n > 0 ? n : 1)));
+    }
+    CUDA_TRY(cudaMemcpyAsync(e->dReplay, draws, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->d.rng_replay = e->dReplay;
+    e->d.rng_mode = 2;
+    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_replay, &e->d.rng_replay, sizeof(e->d.rng_replay), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_mode, &e->d.rng_mode, sizeof(e->d.rng_mode), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int sumob200_set_random_mode(sumob200_engine* e, int mode) {
+    if (e == nullptr || mode < 0 || mode > 1) {
+        gLastError = "sumob200_set_random_mode: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    e->d.rng_mode = mode;
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_mode, &e->d.rng_mode, sizeof(e->d.rng_mode), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int sumob200_set_profiling(sumob200_engine* e, int enabled) {
+    if (e == nullptr) {
+        return SUMOB200_EINVAL;
+    }
+    e->profiling = enabled != 0;
+    return 0;
+}
+
+int sumob200_phase_times(sumob200_engine* e, double* ms, int n_phases, int reset) {
+    if (e == nullptr || ms == nullptr) {
+        return SUMOB200_EINVAL;
+    }
+    for (int i = 0; i < n_phases && i < 5; i++) {
+        ms[i] = e->phaseMs[i];
+    }
+    if (reset) {
+        for (double& x : e->phaseMs) {
+            x = 0;
+        }
+    }
+    return 0;
+}
+
+int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capacity, int* n) {
+    (void)e; (void)rows; (void)capacity; (void)n;
+    gLastError = "sumob200_fcd_snapshot: not implemented yet";
+    return SUMOB200_EUNSUPPORTED;
+}
+
+}  // extern "C"

@@ -29,7 +29,6 @@ class Model {
 public:
     Ctx h;                         // host view
     std::vector<Buffer*> buffers;
-    std::vector<double> vt_collision_mingap_factor;
     std::vector<std::string> lane_names, veh_names;
     SUMOTime begin = 0, end = 0;
 
@@ -234,8 +233,14 @@ public:
                     throw std::runtime_error("sumob200: only the Krauss car-following model is implemented yet");
                 }
             }
-            const double* f = ff.ptr<double>("vt_collision_mingap_factor");
-            vt_collision_mingap_factor.assign(f, f + nT);
+            SB2_COPY(double, vt_collision_mingap_factor);
+            bool anySigma = false;
+            for (int i = 0; i < nT; i++) {
+                anySigma = anySigma || h.vt_sigma[i] != 0.;
+            }
+            h.rng_mode = anySigma ? 1 : 0;
+            h.rng_seed = (uint64_t)ff.scalar<int64_t>("opt_seed", 23423);
+            h.rng_replay = nullptr;
         }
         // ---------------- routes, vehicles
         SB2_COPY(int32_t, route_begin); SB2_COPY(int32_t, route_edges);

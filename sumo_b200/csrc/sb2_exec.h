@@ -143,6 +143,23 @@ SB2_HD double cf_finalizeSpeed(const Ctx& c, const CF& cf, int v, int lane, doub
     return vNext;
 }
 
+// the [0,1) draw of the dawdle step.  The reference draws from one of 64 per-lane-bucket mt19937 streams in active-lane order
+// (RandHelper.cpp:102-106, MSLane.cpp:296); the engine uses a counter-based generator (splitmix64 of seed, vehicle, step), so
+// sigma > 0 runs are statistically, not bitwise, equivalent unless the draws are replayed (rng_mode 2).
+SB2_HD double veh_random(const Ctx& c, int v) {
+    if (c.rng_mode == 0) {
+        return 0.;
+    }
+    if (c.rng_mode == 2) {
+        return c.rng_replay[v];
+    }
+    uint64_t z = c.rng_seed + 0x9E3779B97F4A7C15ull * ((uint64_t)v + 1) + 0xD1B54A32D192ED03ull * (uint64_t)(c.t / c.DELTA_T + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (double)(z >> 32) / 4294967296.0;   // 32 random bits like rng() / 4294967296.0
+}
+
 // MSVehicle::executeMove; `random` = RandHelper::rand(getRNG()) for the dawdle step
 SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
     int myLane = c.veh_lane[v];

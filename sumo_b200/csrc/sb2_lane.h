@@ -70,6 +70,12 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         brutto = 0;
     }
     c.lane_brutto[l] = brutto;
+    // MSLane.cpp:2402-2456: the front-most remaining vehicle is teleported after waiting longer than time-to-teleport.
+    // Teleporting (MSVehicleTransfer) is host-side logic the engine does not implement: report it, never ignore it.
+    if (f >= 0 && c.timeToTeleport > 0 && c.veh_waiting[f] > c.timeToTeleport) {
+        raise(c, ERR_TELEPORT);
+        atomic_inc(&c.counters[6]);
+    }
 }
 
 // pass 2: append the arrivals at the rear, sort partial occupators
@@ -164,7 +170,8 @@ SB2_HD void veh_register_partials(const Ctx& c, int v) {
 
 // MSLane::detectCollisions (non-sublane): adjacent pairs + rear-most partial occupator.  The engine does not implement
 // the teleport that follows a collision: it raises ERR_COLLISION and counts it.
-SB2_HDN void lane_detect_collisions(const Ctx& c, int l, const double* vt_collision_mingap_factor) {
+SB2_HDN void lane_detect_collisions(const Ctx& c, int l) {
+    const double* vt_collision_mingap_factor = c.vt_collision_mingap_factor;
     int pred = c.lane_first[l];
     if (pred < 0) {
         return;

@@ -124,6 +124,7 @@ struct Ctx {
     const double* vt_accel; const double* vt_decel; const double* vt_emergencydecel; const double* vt_apparentdecel;
     const double* vt_tau; const double* vt_sigma; const double* vt_impatience;
     const int32_t* vt_cfmodel; const SUMOTime* vt_startupdelay;
+    const double* vt_collision_mingap_factor;
     const double* vt_idm_delta; const double* vt_idm_stepping;
     // ---- routes --------------------------------------------------------------------------
     const int32_t* route_begin; const int32_t* route_edges;
@@ -161,6 +162,9 @@ struct Ctx {
     int cur;                             // buffer written by this step's planMove
     // ---- departure queues (per departure lane, in load order) ----------------------------
     const int32_t* dq_begin; const int32_t* dq_veh; int32_t* dq_head;   // [nL+1], [nV], [nL]
+    // ---- random numbers for the dawdle step (MSCFModel_Krauss::dawdle2): 0 = none needed (all sigma == 0),
+    // 1 = counter-based generator keyed by (seed, vehicle, step), 2 = replay of host-supplied draws (rng_replay[v])
+    int rng_mode; uint64_t rng_seed; const double* rng_replay;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
     int32_t* counters;         // [8]: 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports

@@ -1,0 +1,175 @@
+"""ctypes binding of libsumob200.so (include/sumob200.h) -- the host-side mirror of the reference's step-and-query surface.
+
+`Engine.step()` is what `libsumo.simulationStep()` / `MSNet::simulationStep` do for the vehicle update
+(src/libsumo/Simulation.cpp:168-188, src/microsim/MSNet.cpp:800-936); `Engine.vehicles()` is the state the
+`libsumo.vehicle.get*` getters read (src/libsumo/Vehicle.cpp).  There is no CPU fallback: importing works anywhere, but
+creating an engine without the built library or without a CUDA device raises.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsumob200.so")
+
+FLAGS = {
+    1: "drive item overflow", 2: "further-lane overflow", 4: "partial occupator overflow", 8: "collision", 16: "teleport",
+    32: "emergency stop", 64: "no connection", 128: "unsupported link state", 256: "lane order", 512: "search overflow",
+}
+
+
+class SumoB200Error(RuntimeError):
+    pass
+
+
+class _Array(ctypes.Structure):
+    _fields_ = [("name", ctypes.c_char_p), ("dtype", ctypes.c_uint32), ("elem_size", ctypes.c_uint32),
+                ("count", ctypes.c_uint64), ("data", ctypes.c_void_p)]
+
+
+class StepResult(ctypes.Structure):
+    _fields_ = [("time_ms", ctypes.c_int64), ("running", ctypes.c_int32), ("departed_total", ctypes.c_int32),
+                ("arrived_total", ctypes.c_int32), ("collisions", ctypes.c_int32), ("emergency_stops", ctypes.c_int32),
+                ("teleports", ctypes.c_int32), ("flags", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("vehicle_updates", ctypes.c_int64)]
+
+
+VEHICLE_STATE = np.dtype([("lane", np.int32), ("route_pos", np.int32), ("pos", np.float64), ("speed", np.float64)])
+FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
+                    ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
+
+_DTYPE_CODES = {np.dtype(np.uint8): 0, np.dtype(np.int32): 1, np.dtype(np.int64): 2, np.dtype(np.float64): 3, np.dtype(np.uint64): 4}
+
+_lib = None
+
+
+def load_library(path=None):
+    """dlopen libsumob200.so and declare the prototypes of include/sumob200.h"""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise SumoB200Error("%s is missing: run `python -m sumo_b200.build` (needs nvcc); there is no CPU fallback" % path)
+    lib = ctypes.CDLL(path)
+    P = ctypes.POINTER
+    lib.sumob200_create.argtypes = [P(_Array), ctypes.c_int, ctypes.c_int, P(ctypes.c_void_p)]
+    lib.sumob200_create_from_file.argtypes = [ctypes.c_char_p, ctypes.c_int, P(ctypes.c_void_p)]
+    lib.sumob200_destroy.argtypes = [ctypes.c_void_p]
+    lib.sumob200_destroy.restype = None
+    lib.sumob200_step.argtypes = [ctypes.c_void_p, ctypes.c_int, P(StepResult)]
+    lib.sumob200_mirror_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_fcd_snapshot.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int)]
+    lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
+    lib.sumob200_num_lanes.argtypes = [ctypes.c_void_p]
+    lib.sumob200_time_ms.argtypes = [ctypes.c_void_p]
+    lib.sumob200_time_ms.restype = ctypes.c_int64
+    lib.sumob200_kernel_launches.argtypes = [ctypes.c_void_p]
+    lib.sumob200_kernel_launches.restype = ctypes.c_int64
+    lib.sumob200_set_random_draws.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_set_random_mode.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_set_profiling.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_phase_times.argtypes = [ctypes.c_void_p, P(ctypes.c_double), ctypes.c_int, ctypes.c_int]
+    lib.sumob200_last_error.restype = ctypes.c_char_p
+    lib.sumob200_version.restype = ctypes.c_char_p
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+def _check(lib, rc, what):
+    if rc != 0:
+        raise SumoB200Error("%s failed (%d): %s" % (what, rc, lib.sumob200_last_error().decode()))
+
+
+class Engine:
+    """one simulation on one GPU"""
+
+    def __init__(self, scenario, device=0):
+        """scenario: path of a .flat file, or {name: np.ndarray} as returned by flatfile.load_flat / tiler.tile"""
+        self._lib = load_library()
+        self._h = ctypes.c_void_p()
+        if isinstance(scenario, (str, bytes, os.PathLike)):
+            rc = self._lib.sumob200_create_from_file(os.fsencode(scenario), device, ctypes.byref(self._h))
+        else:
+            keep = []
+            arr = (_Array * len(scenario))()
+            for i, (name, a) in enumerate(scenario.items()):
+                a = np.ascontiguousarray(a)
+                keep.append(a)
+                arr[i].name = name.encode()
+                arr[i].dtype = _DTYPE_CODES[a.dtype]
+                arr[i].elem_size = a.dtype.itemsize
+                arr[i].count = a.size
+                arr[i].data = a.ctypes.data
+            rc = self._lib.sumob200_create(arr, len(scenario), device, ctypes.byref(self._h))
+        _check(self._lib, rc, "sumob200_create")
+        self.num_vehicles = self._lib.sumob200_num_vehicles(self._h)
+        self.num_lanes = self._lib.sumob200_num_lanes(self._h)
+        self._state = np.zeros(max(self.num_vehicles, 1), dtype=VEHICLE_STATE)
+
+    def close(self):
+        if self._h:
+            self._lib.sumob200_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def time_ms(self):
+        return self._lib.sumob200_time_ms(self._h)
+
+    @property
+    def kernel_launches(self):
+        return self._lib.sumob200_kernel_launches(self._h)
+
+    def step(self, n=1, result=True):
+        """run n simulation steps; returns the StepResult after the last one (None if result is False: no host sync)"""
+        if result:
+            r = StepResult()
+            _check(self._lib, self._lib.sumob200_step(self._h, n, ctypes.byref(r)), "sumob200_step")
+            return r
+        _check(self._lib, self._lib.sumob200_step(self._h, n, None), "sumob200_step")
+        return None
+
+    def vehicles(self, out=None):
+        """state of all vehicle slots as a structured array (lane, route_pos, pos, speed); lane < 0 = not on the road"""
+        buf = self._state if out is None else out
+        _check(self._lib, self._lib.sumob200_mirror_all(self._h, buf.ctypes.data, buf.shape[0]), "sumob200_mirror_all")
+        return buf[:self.num_vehicles]
+
+    def set_random_draws(self, draws):
+        d = np.ascontiguousarray(draws, dtype=np.float64)
+        _check(self._lib, self._lib.sumob200_set_random_draws(self._h, d.ctypes.data, d.size), "sumob200_set_random_draws")
+
+    def set_random_mode(self, mode):
+        _check(self._lib, self._lib.sumob200_set_random_mode(self._h, mode), "sumob200_set_random_mode")
+
+    def set_profiling(self, enabled):
+        _check(self._lib, self._lib.sumob200_set_profiling(self._h, 1 if enabled else 0), "sumob200_set_profiling")
+
+    def phase_times(self, reset=True):
+        ms = (ctypes.c_double * 5)()
+        _check(self._lib, self._lib.sumob200_phase_times(self._h, ms, 5, 1 if reset else 0), "sumob200_phase_times")
+        return dict(zip(("pre", "plan", "execute", "handoff", "insert"), list(ms)))
+
+
+def describe_flags(flags):
+    return [name for bit, name in FLAGS.items() if flags & bit]
+
+
+def ensure_built():
+    return _build.build()

@@ -54,6 +54,8 @@ def load_trace(path):
     while off < raw.size:
         t, n = int(raw[off]), int(raw[off + 1])
         off += 2
+        if off + 4 * n > raw.size:
+            break  # truncated last record (writer was interrupted)
         rec = raw[off:off + 4 * n].reshape(n, 4)
         off += 4 * n
         steps.append((t, rec[:, 0].copy(), rec[:, 1].copy(), rec[:, 2].copy().view(np.float64), rec[:, 3].copy().view(np.float64)))

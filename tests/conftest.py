@@ -1,0 +1,67 @@
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+REF = os.path.join(ROOT, "oracle", "_ref")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+CACHE = os.path.join(ROOT, "tests", "_cache")
+
+# (fixture, extra reference options): every case is run through the UNMODIFIED reference (oracle/_ref/sumo_flatten) to get
+# the flattened scenario and the ground-truth trace.  --default.speeddev 0 like tests/sumo/options.sumo of the reference.
+CASES = {
+    "grid3_small": ["--default.speeddev", "0"],
+    "grid3_small_depart0": ["--default.speeddev", "0", "--default.departspeed", "0", "--default.departlane", "first"],
+    "c1_grid10": ["--default.speeddev", "0", "--end", "3700"],
+    "c1_grid10_depart0": ["--default.speeddev", "0", "--default.departspeed", "0", "--default.departlane", "first", "--end", "3700"],
+    "grid4_tls": ["--default.speeddev", "0", "--end", "1200"],
+    "grid5_dense": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    # vehicles with individual speed factors (normc(1,0.1,0.2,2), sampled by the reference's loader)
+    "grid4_tls_speeddev": ["--end", "1000"],
+}
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def ensure_reference():
+    """oracle/_ref/sumo_flatten: prebuilt on the GPU box, built from /root/reference in the build container"""
+    exe = os.path.join(REF, "sumo_flatten")
+    if not os.path.exists(exe):
+        if not os.path.isdir(os.environ.get("SUMO_REFERENCE", "/root/reference")):
+            pytest.skip("oracle/_ref/sumo_flatten missing and no reference sources to build it from")
+        subprocess.check_call([os.path.join(ROOT, "oracle", "build_ref.sh"), "flatten"])
+    return exe
+
+
+def reference_case(name):
+    """returns (flat path, trace path) for a case, generating them with the reference binary on first use"""
+    exe = ensure_reference()
+    os.makedirs(CACHE, exist_ok=True)
+    flat = os.path.join(CACHE, name + ".flat")
+    trace = os.path.join(CACHE, name + ".trace")
+    if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
+        base = name
+        for suffix in ("_depart0", "_speeddev", "_teleport"):
+            base = base.replace(suffix, "")
+        cmd = [exe, "--flat-out", flat, "--trace-out", trace + ".tmp", "-n", os.path.join(GOLDEN, base + ".net.xml"),
+               "-r", os.path.join(GOLDEN, base + ".rou.xml"), "--no-step-log", "--no-warnings"] + CASES[name]
+        subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        os.replace(trace + ".tmp", trace)
+    return flat, trace
+
+
+@pytest.fixture(scope="session")
+def host_emul():
+    """tests/host_emul: the device functions compiled for the host (test infrastructure, see its header)"""
+    os.makedirs(CACHE, exist_ok=True)
+    exe = os.path.join(CACHE, "host_emul")
+    src = os.path.join(ROOT, "tests", "host_emul", "emul_main.cpp")
+    deps = [src] + [os.path.join(ROOT, "sumo_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "sumo_b200", "csrc"))]
+    if not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-o", exe, src])
+    return exe

@@ -63,7 +63,7 @@ static void step(Model& m) {
     }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
     for (int v = 0; v < c.nV; v++) {
-        veh_executeMove(c, v, 0.);
+        veh_executeMove(c, v, veh_random(c, v));
         veh_register_partials(c, v);
     }
     for (int l = 0; l < c.nL; l++) {
@@ -73,7 +73,7 @@ static void step(Model& m) {
         lane_handoff_integrate(c, l);
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_detect_collisions(c, l, m.vt_collision_mingap_factor.data());
+        lane_detect_collisions(c, l);
     }
     for (int i = 0; i < 3; i++) {
         c.fleet[i] = c.fleet_next[i];

@@ -1,0 +1,48 @@
+"""GPU suite: libsumob200.so through its C ABI (ctypes) against traces of the UNMODIFIED reference `sumo`.  Bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import reference_case
+from sumo_b200.flatfile import load_flat, load_trace
+
+pytestmark = pytest.mark.gpu
+
+GPU_CASES = ["grid3_small", "grid3_small_depart0", "c1_grid10", "c1_grid10_depart0", "grid4_tls", "grid5_dense", "grid4_tls_speeddev"]
+
+
+@pytest.mark.parametrize("case", GPU_CASES)
+def test_engine_matches_reference(case):
+    from sumo_b200.engine import Engine
+    flat, trace = reference_case(case)
+    ref = load_trace(trace)
+    numid = load_flat(flat)["veh_numid"]
+    order = np.argsort(numid, kind="stable")
+    compared = 0
+    with Engine(flat) as eng:
+        for (t, ids, lanes, pos, speed) in ref:
+            assert eng.time_ms == t
+            r = eng.step(1)
+            st = eng.vehicles()[order]
+            on = st["lane"] >= 0
+            assert r.flags == 0, "t=%d: engine raised flags 0x%x" % (t, r.flags)
+            assert r.running == int(on.sum()) == len(ids), "t=%d: running vehicles differ" % t
+            assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
+            assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
+            assert np.array_equal(st["pos"][on].view(np.int64), pos.view(np.int64)), "t=%d: positions differ (bitwise)" % t
+            assert np.array_equal(st["speed"][on].view(np.int64), speed.view(np.int64)), "t=%d: speeds differ (bitwise)" % t
+            compared += len(ids)
+        assert r.vehicle_updates == compared
+    assert compared > 1000
+
+
+def test_teleport_condition_is_reported():
+    """the reference teleports a vehicle of grid5_dense at t=425 s; the engine must flag that step, not silently diverge"""
+    from sumo_b200.engine import Engine
+    from conftest import CASES
+    CASES.setdefault("grid5_dense_teleport", ["--default.speeddev", "0", "--default.departspeed", "0", "--default.departlane", "first", "--end", "430"])
+    flat, trace = reference_case("grid5_dense_teleport".replace("_teleport", "") if False else "grid5_dense_teleport")
+    with Engine(flat) as eng:
+        r = eng.step(424)
+        assert r.flags == 0
+        r = eng.step(2)
+        assert r.flags & 16 and r.teleports >= 1
