@@ -85,6 +85,10 @@ void sumob200_destroy(sumob200_engine* e);
 /* run n_steps simulation steps; *out (may be NULL) receives the counters after the last one */
 int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out);
 
+/* like sumob200_step, and *elapsed_ms receives the device time of the n_steps steps measured with CUDA events recorded
+ * on the engine's own stream (the stream the kernels are launched on) */
+int sumob200_step_timed(sumob200_engine* e, int n_steps, sumob200_step_result* out, double* elapsed_ms);
+
 /* copy the state of all vehicle slots to host memory (n = number of loaded vehicles, see sumob200_num_vehicles) */
 int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int capacity);
 /* FCD rows of the vehicles currently on the road, ordered by slot: writes up to `capacity` rows, *n = rows available */

@@ -364,6 +364,31 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     return 0;
 }
 
+int sumob200_step_timed(sumob200_engine* e, int n_steps, sumob200_step_result* out, double* elapsed_ms) {
+    if (e == nullptr || elapsed_ms == nullptr) {
+        gLastError = "sumob200_step_timed: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    cudaEvent_t a, b;
+    CUDA_TRY(cudaEventCreate(&a));
+    CUDA_TRY(cudaEventCreate(&b));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    CUDA_TRY(cudaEventRecord(a, e->stream));
+    const int rc = sumob200_step(e, n_steps, nullptr);
+    if (rc != 0) {
+        return rc;
+    }
+    CUDA_TRY(cudaEventRecord(b, e->stream));
+    CUDA_TRY(cudaEventSynchronize(b));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, a, b));
+    *elapsed_ms = ms;
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    return sumob200_step(e, 0, out);
+}
+
 int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int capacity) {
     if (e == nullptr || out == nullptr || capacity < e->d.nV) {
         gLastError = "sumob200_mirror_all: bad argument / capacity too small";

@@ -109,8 +109,10 @@ public:
         h.nT = (int)ff.count("vt_length");
         h.nTL = (int)ff.count("tl_cur_phase");
         const int nL = h.nL, nK = h.nK, nV = h.nV, nT = h.nT;
-        lane_names = names(ff, "lane");
-        veh_names = names(ff, "veh");
+        if (ff.has("lane_names") && ff.has("veh_names")) {   // ids are only needed for diagnostics and output writers
+            lane_names = names(ff, "lane");
+            veh_names = names(ff, "veh");
+        }
         // ---------------- lanes
         SB2_COPY(double, lane_length); SB2_COPY(double, lane_speed);
         SB2_COPY(int32_t, lane_edge); SB2_COPY(int32_t, lane_flags); SB2_COPY(int32_t, lane_link_begin);
@@ -254,9 +256,6 @@ public:
             for (int v = 0; v < nV; v++) {
                 const int64_t delay = d[v] % h.DELTA_T;
                 o[v] = d[v] + (delay == 0 ? 0 : h.DELTA_T - delay);
-                if (v > 0 && o[v] < o[v - 1]) {
-                    throw std::runtime_error("sumob200: vehicles must be sorted by departure time");
-                }
             }
             // depart speed: resolve DEFAULT (MSLane::getDepartSpeed, MSLane.cpp:609-614)
             const int32_t* sp = ff.ptr<int32_t>("veh_departspeed_proc");
@@ -322,7 +321,12 @@ public:
             }
             std::vector<int32_t> fill(qb, qb + nL);
             for (int v = 0; v < nV; v++) {
-                qv[fill[dl[v]]++] = v;
+                const int slot = fill[dl[v]]++;
+                qv[slot] = v;
+                // MSInsertionControl tries vehicles in departure order: within a departure lane the slots must be sorted
+                if (slot > qb[dl[v]] && h.veh_depart[qv[slot - 1]] > h.veh_depart[v]) {
+                    throw std::runtime_error("sumob200: vehicles must be sorted by departure time");
+                }
             }
         }
         // ---------------- vehicle state

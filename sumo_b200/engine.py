@@ -61,6 +61,7 @@ def load_library(path=None):
     lib.sumob200_destroy.argtypes = [ctypes.c_void_p]
     lib.sumob200_destroy.restype = None
     lib.sumob200_step.argtypes = [ctypes.c_void_p, ctypes.c_int, P(StepResult)]
+    lib.sumob200_step_timed.argtypes = [ctypes.c_void_p, ctypes.c_int, P(StepResult), P(ctypes.c_double)]
     lib.sumob200_mirror_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_fcd_snapshot.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int)]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
@@ -144,6 +145,13 @@ class Engine:
             return r
         _check(self._lib, self._lib.sumob200_step(self._h, n, None), "sumob200_step")
         return None
+
+    def step_timed(self, n):
+        """run n steps; returns (StepResult, device milliseconds measured with CUDA events on the engine's stream)"""
+        r = StepResult()
+        ms = ctypes.c_double()
+        _check(self._lib, self._lib.sumob200_step_timed(self._h, n, ctypes.byref(r), ctypes.byref(ms)), "sumob200_step_timed")
+        return r, ms.value
 
     def vehicles(self, out=None):
         """state of all vehicle slots as a structured array (lane, route_pos, pos, speed); lane < 0 = not on the road"""

@@ -114,7 +114,7 @@ int main(int argc, char** argv) {
         return 1;
     }
     Ctx& c = m.h;
-    for (int v = 0; v < c.nV; v++) {
+    for (int v = 0; v < c.nV && !m.veh_names.empty(); v++) {
         if (m.veh_names[v] == debugName) {
             gDebugVeh = v;
         }
