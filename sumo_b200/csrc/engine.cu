@@ -4,7 +4,8 @@
  * -fmad=false keeps every fp64 expression in the reference's evaluation order without FMA contraction, so Krauss sigma=0
  * trajectories are bit-identical to the reference built with g++ -ffp-contract=off.
  *
- * One simulation step = 8 launches on one stream (no host synchronisation in between):
+ * One simulation step = 7 launches on one stream (no host synchronisation in between).  Every kernel takes the Ctx by value
+ * as a __grid_constant__ parameter, so the ~150 array base pointers are read from the constant bank, not from HBM:
  *   k_pre       max(nL,nK,nTL) threads   TLS phase clock, per-lane summary (lengths in front, space till last standing),
  *                                        reset of this step's approach-table heads, fleet aggregate snapshot
  *   k_plan      nV threads               MSVehicle::planMove + approach registration           (sb2_plan2.h)
@@ -14,7 +15,6 @@
  *   k_integrate nL threads               append arrivals, sort partial occupators, collisions
  *   k_insert    nL threads               MSInsertionControl::emitVehicles per departure lane    (sb2_insert.h)
  *   k_count     nV threads               running-vehicle count (summary / UPS numerator)
- *   k_advance   1 thread                 clock += DELTA_T, flip drive-item buffer (state lives on the device: graph-replayable)
  * There is no CPU path in this library.
  */
 #include <cuda_runtime.h>
@@ -40,15 +40,54 @@ thread_local std::string gLastError;
         gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
 
 constexpr int BLOCK = 128;
+// resident CTAs per SM the register allocation of the two per-vehicle kernels is bounded for (profiles/r01_*: both are
+// latency bound -- long scoreboard on dependent gathers -- so occupancy is worth more than a spill-free allocation)
+#ifndef SB2_PLAN_MINB
+#define SB2_PLAN_MINB 4
+#endif
+#ifndef SB2_EXEC_MINB
+#define SB2_EXEC_MINB 4
+#endif
 
-__global__ void __launch_bounds__(BLOCK) k_pre(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
+__global__ void k_reset(const __grid_constant__ Ctx c) {
+    if (threadIdx.x == 0) {
+        c.counters[0] = 0;
+        c.counters[7] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < c.nTL) {
         tls_advance(c, i);
     }
+    // lane-ordered work list: block-wide exclusive scan of the lanes' vehicle counts, one atomic per block for the base
+    __shared__ int warpSum[BLOCK / 32];
+    __shared__ int blockBase;
+    const int n = i < c.nL ? c.lane_nveh[i] : 0;
+    int incl = n;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((threadIdx.x & 31) >= d) {
+            incl += o;
+        }
+    }
+    if ((threadIdx.x & 31) == 31) {
+        warpSum[threadIdx.x >> 5] = incl;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int w = 0; w < BLOCK / 32; w++) {
+            const int x = warpSum[w];
+            warpSum[w] = tot;
+            tot += x;
+        }
+        blockBase = tot > 0 ? atomicAdd(&c.counters[7], tot) : 0;
+    }
+    __syncthreads();
     if (i < c.nL) {
-        lane_summary(c, i);
+        lane_summary(c, i, blockBase + warpSum[threadIdx.x >> 5] + incl - n);
     }
     if (i < c.nK) {
         c.link_app_head[c.cur][i] = -1;
@@ -58,33 +97,30 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const Ctx* __restrict__ dc) {
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) k_plan(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < c.nV) {
-        veh_planMove(c, v);
+__global__ void __launch_bounds__(BLOCK, SB2_PLAN_MINB) k_plan(const __grid_constant__ Ctx c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.counters[7]) {
+        veh_planMove(c, c.veh_order[i]);
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) k_execute(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < c.nV) {
+__global__ void __launch_bounds__(BLOCK, SB2_EXEC_MINB) k_execute(const __grid_constant__ Ctx c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.counters[7]) {
+        const int v = c.veh_order[i];
         veh_executeMove(c, v, veh_random(c, v));
         veh_register_partials(c, v);
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) k_remove(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
+__global__ void __launch_bounds__(BLOCK) k_remove(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l < c.nL) {
         lane_handoff_remove(c, l);
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) k_integrate(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
+__global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l < c.nL) {
         lane_handoff_integrate(c, l);
@@ -92,8 +128,7 @@ __global__ void __launch_bounds__(BLOCK) k_integrate(const Ctx* __restrict__ dc)
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) k_insert(const Ctx* __restrict__ dc) {
-    const Ctx& c = *dc;
+__global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1]) {
         lane_insertVehicles(c, l);
@@ -101,8 +136,7 @@ __global__ void __launch_bounds__(BLOCK) k_insert(const Ctx* __restrict__ dc) {
 }
 
 // running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
-__global__ void __launch_bounds__(BLOCK) k_count(const Ctx* __restrict__ dc, unsigned long long* updates) {
-    const Ctx& c = *dc;
+__global__ void __launch_bounds__(BLOCK) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     const bool on = v < c.nV && c.veh_lane[v] >= 0;
     const unsigned mask = __ballot_sync(0xffffffffu, on);
@@ -113,15 +147,7 @@ __global__ void __launch_bounds__(BLOCK) k_count(const Ctx* __restrict__ dc, uns
     }
 }
 
-// end of step: advance the clock and flip the drive-item buffer (device-resident so that a step needs no host-side
-// parameter change and can be replayed from a CUDA graph)
-__global__ void k_advance(Ctx* dc) {
-    dc->t += dc->DELTA_T;
-    dc->cur ^= 1;
-}
-
-__global__ void k_mirror(const Ctx* __restrict__ dc, sumob200_vehicle_state* out) {
-    const Ctx& c = *dc;
+__global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
         sumob200_vehicle_state s;
@@ -137,8 +163,7 @@ __global__ void k_mirror(const Ctx* __restrict__ dc, sumob200_vehicle_state* out
 
 struct sumob200_engine {
     Model model;
-    Ctx d;                                  // host shadow of the device-resident Ctx (pointers into device memory)
-    Ctx* dCtx = nullptr;                    // the device-resident copy every kernel reads
+    Ctx d;                                  // the Ctx passed by value to every kernel (pointers into device memory)
     std::vector<void*> dev;                 // device allocation of model.buffers[i]
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -191,12 +216,6 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
         *reinterpret_cast<void**>(reinterpret_cast<char*>(&e->d) + b->offset) = p;
     }
     e->d.cur = 1;   // the first step writes buffer 1 (the host emulation flips 0 -> 1 at the start of its first step)
-    if (err == cudaSuccess) {
-        err = cudaMalloc(&e->dCtx, sizeof(Ctx));
-    }
-    if (err == cudaSuccess) {
-        err = cudaMemcpyAsync(e->dCtx, &e->d, sizeof(Ctx), cudaMemcpyHostToDevice, e->stream);
-    }
     if (err == cudaSuccess) {
         err = cudaMalloc(&e->dUpdates, sizeof(unsigned long long));
     }
@@ -286,9 +305,6 @@ void sumob200_destroy(sumob200_engine* e) {
     if (e->dUpdates != nullptr) {
         cudaFree(e->dUpdates);
     }
-    if (e->dCtx != nullptr) {
-        cudaFree(e->dCtx);
-    }
     if (e->dMirror != nullptr) {
         cudaFree(e->dMirror);
     }
@@ -313,20 +329,19 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     for (int i = 0; i < n_steps; i++) {
         const bool prof = e->profiling;
         if (prof) { cudaEventRecord(e->ev[0], s); }
-        CUDA_TRY(cudaMemsetAsync(c.counters, 0, sizeof(int32_t), s));   // counters[0] = running vehicles of this step
-        k_pre<<<grid(nPre < 3 ? 3 : nPre), BLOCK, 0, s>>>(e->dCtx);
+        k_reset<<<1, 32, 0, s>>>(e->d);   // counters[0] = running vehicles of this step, counters[7] = length of the work list
+        k_pre<<<grid(nPre < 3 ? 3 : nPre), BLOCK, 0, s>>>(e->d);
         if (prof) { cudaEventRecord(e->ev[1], s); }
-        k_plan<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx);
+        k_plan<<<grid(c.nV), BLOCK, 0, s>>>(e->d);
         if (prof) { cudaEventRecord(e->ev[2], s); }
         CUDA_TRY(cudaMemsetAsync(c.lane_npartial, 0, sizeof(int32_t) * (size_t)c.nL, s));
-        k_execute<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx);
+        k_execute<<<grid(c.nV), BLOCK, 0, s>>>(e->d);
         if (prof) { cudaEventRecord(e->ev[3], s); }
-        k_remove<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
-        k_integrate<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
+        k_remove<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
+        k_integrate<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
         if (prof) { cudaEventRecord(e->ev[4], s); }
-        k_insert<<<grid(c.nL), BLOCK, 0, s>>>(e->dCtx);
-        k_count<<<grid(c.nV), BLOCK, 0, s>>>(e->dCtx, e->dUpdates);
-        k_advance<<<1, 1, 0, s>>>(e->dCtx);
+        k_insert<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
+        k_count<<<grid(c.nV), BLOCK, 0, s>>>(e->d, e->dUpdates);
         if (prof) {
             cudaEventRecord(e->ev[5], s);
             CUDA_TRY(cudaEventSynchronize(e->ev[5]));
@@ -399,7 +414,7 @@ int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int cap
     if (e->dMirror == nullptr) {
         CUDA_TRY(cudaMalloc(&e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)(nV > 0 ? nV : 1)));
     }
-    k_mirror<<<grid(nV), BLOCK, 0, e->stream>>>(e->dCtx, e->dMirror);
+    k_mirror<<<grid(nV), BLOCK, 0, e->stream>>>(e->d, e->dMirror);
     e->launches += 1;
     CUDA_TRY(cudaMemcpyAsync(out, e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)nV, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
@@ -424,9 +439,6 @@ int sumob200_set_random_draws(sumob200_engine* e, const double* draws, int n) {
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->d.rng_replay = e->dReplay;
     e->d.rng_mode = 2;
-    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_replay, &e->d.rng_replay, sizeof(e->d.rng_replay), cudaMemcpyHostToDevice, e->stream));
-    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_mode, &e->d.rng_mode, sizeof(e->d.rng_mode), cudaMemcpyHostToDevice, e->stream));
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
     return 0;
 }
 
@@ -436,9 +448,6 @@ int sumob200_set_random_mode(sumob200_engine* e, int mode) {
         return SUMOB200_EINVAL;
     }
     e->d.rng_mode = mode;
-    CUDA_TRY(cudaSetDevice(e->device));
-    CUDA_TRY(cudaMemcpyAsync(&e->dCtx->rng_mode, &e->d.rng_mode, sizeof(e->d.rng_mode), cudaMemcpyHostToDevice, e->stream));
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
     return 0;
 }
 

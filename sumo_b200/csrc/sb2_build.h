@@ -342,6 +342,7 @@ public:
         SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
         SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
         SB2_DYN(double, veh_len_in_front, nV, 0.);
+        SB2_DYN(int32_t, veh_order, nV, -1);
         const size_t nDI = (size_t)nV * MAX_DRIVE_ITEMS;
         for (int b = 0; b < 2; b++) {
             SB2_DYN2(int32_t, veh_ndi, b, nV, 0);

@@ -149,6 +149,10 @@ struct Ctx {
     int32_t* veh_next_incoming;
     int32_t* veh_nfurther; int32_t* veh_further;     // [nV*MAX_FURTHER] lanes the back still covers, nearest first
     double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)
+    // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
+    // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
+    // neighbouring lanes, see the same links and foes and take the same branches.  counters[7] = its length.
+    int32_t* veh_order;
     // drive items, double buffered [2][MAX_DRIVE_ITEMS*nV], item-major (item i of vehicle v at i*nV+v)
     int32_t* veh_ndi[2];
     int32_t* di_link[2]; uint8_t* di_request[2]; uint8_t* di_hadstopped[2];

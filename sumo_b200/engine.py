@@ -13,7 +13,7 @@ import numpy as np
 from . import build as _build
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsumob200.so")
+LIB_PATH = os.environ.get("SUMOB200_LIB") or os.path.join(_HERE, "libsumob200.so")   # override: tuning variants only
 
 FLAGS = {
     1: "drive item overflow", 2: "further-lane overflow", 4: "partial occupator overflow", 8: "collision", 16: "teleport",

@@ -50,19 +50,23 @@ static void step(Model& m) {
     for (int tl = 0; tl < c.nTL; tl++) {
         tls_advance(c, tl);
     }
+    int nOrder = 0;
     for (int l = 0; l < c.nL; l++) {
-        lane_summary(c, l);
+        lane_summary(c, l, nOrder);
+        nOrder += c.lane_nveh[l];
     }
+    c.counters[7] = nOrder;
     c.cur ^= 1;
     std::fill(c.link_app_head[c.cur], c.link_app_head[c.cur] + c.nK, -1);
-    for (int v = 0; v < c.nV; v++) {
-        veh_planMove(c, v);
+    for (int i = 0; i < nOrder; i++) {
+        veh_planMove(c, c.veh_order[i]);
     }
     if (gDebugVeh >= 0 && c.veh_lane[gDebugVeh] >= 0) {
         dumpItems(m, gDebugVeh, "plan");
     }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
-    for (int v = 0; v < c.nV; v++) {
+    for (int i = 0; i < nOrder; i++) {
+        const int v = c.veh_order[i];
         veh_executeMove(c, v, veh_random(c, v));
         veh_register_partials(c, v);
     }
