@@ -1,0 +1,46 @@
+"""CPU suite: libsumob200.so loads without a GPU and exports every symbol include/sumob200.h declares; without a CUDA
+device every computing entry point fails loudly (there is no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "sumob200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(sumob200_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from sumo_b200 import build
+    from sumo_b200.engine import load_library
+    build.build()
+    lib = load_library()
+    names = declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), "include/sumob200.h declares %s but libsumob200.so does not export it" % n
+
+
+def test_no_cpu_fallback():
+    import shutil
+    if shutil.which("nvidia-smi") and os.system("nvidia-smi -L >/dev/null 2>&1") == 0:
+        pytest.skip("a GPU is present")
+    from sumo_b200.engine import Engine, SumoB200Error
+    flat = os.path.join(ROOT, "tests", "golden", "bench_grid10_tls.flat")
+    with pytest.raises(SumoB200Error) as ei:
+        Engine(flat)
+    assert "no CUDA device" in str(ei.value) or "CUDA" in str(ei.value)
+
+
+def test_bad_arguments_are_rejected():
+    from sumo_b200.engine import load_library
+    lib = load_library()
+    out = ctypes.c_void_p()
+    assert lib.sumob200_create_from_file(b"/nonexistent.flat", 0, ctypes.byref(out)) < 0
+    assert lib.sumob200_step(None, 1, None) < 0
+    assert lib.sumob200_num_vehicles(None) == 0
