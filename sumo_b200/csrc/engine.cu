@@ -43,10 +43,10 @@ constexpr int BLOCK = 128;
 // resident CTAs per SM the register allocation of the two per-vehicle kernels is bounded for (profiles/r01_*: both are
 // latency bound -- long scoreboard on dependent gathers -- so occupancy is worth more than a spill-free allocation)
 #ifndef SB2_PLAN_MINB
-#define SB2_PLAN_MINB 4
+#define SB2_PLAN_MINB 8
 #endif
 #ifndef SB2_EXEC_MINB
-#define SB2_EXEC_MINB 4
+#define SB2_EXEC_MINB 8
 #endif
 
 __global__ void k_reset(const __grid_constant__ Ctx c) {

@@ -239,16 +239,18 @@ SB2_HDN void veh_planMove(const Ctx& c, int v) {
         double stopSpeed = cf_stopSpeed(cf, e.speed, stopDist, stopDecel, false);
         double vLinkWait = MIN2(vv, stopSpeed);
 
-        if (yellowOrRed && canBrakeBeforeStopLine /* && !ignoreRed && seen >= mustSeeBeforeReversal(0) */) {
-            if (lane_internal(c, lane)) {
-                veh_checkLinkLeader(c, e, link, lane, seen, lastLink, vv, vLinkPass, vLinkWait, setRequest, prev);
-            }
+        // MSVehicle.cpp:2920-2945: a vehicle that can stop at yellow/red only looks for link leaders when it is already on the
+        // intersection; everybody else always does (one call site for both cases keeps the kernel's code small)
+        const bool stopAtRed = yellowOrRed && canBrakeBeforeStopLine /* && !ignoreRed && seen >= mustSeeBeforeReversal(0) */;
+        if (!stopAtRed || lane_internal(c, lane)) {
+            veh_checkLinkLeader(c, e, link, lane, seen, lastLink, vv, vLinkPass, vLinkWait, setRequest, prev);
+        }
+        if (stopAtRed) {
             const SUMOTime arrivalTime = veh_getArrivalTime(c, e, t, seen, vv, vLinkPass);
             SB2_PUSH(di_make(link, vv, vLinkWait, false, arrivalTime, vLinkWait, 0, seen, -1));
             break;
         }
         // (ignoreRed is always false for jmDriveAfterRedTime = -1: the restrict-speed-at-red branch :2948 is dead)
-        veh_checkLinkLeader(c, e, link, lane, seen, lastLink, vv, vLinkPass, vLinkWait, setRequest, prev);
 
         if (lastLink != nullptr) {
             di_adaptLeaveSpeed(*lastLink, laneMaxV);

@@ -21,7 +21,9 @@
 
 #if defined(__CUDACC__)
 #define SB2_HD __host__ __device__ __forceinline__
-#define SB2_HDN __host__ __device__ __noinline__
+/* entry functions called once per kernel: inlined, so that the members of the __grid_constant__ Ctx are read as
+ * constant-bank operands (a noinline callee would get a generic pointer to the parameter space instead) */
+#define SB2_HDN __host__ __device__ __forceinline__
 #else
 #define SB2_HD inline
 #define SB2_HDN inline
