@@ -33,11 +33,12 @@ SB2_HD CF make_cf(const Ctx& c, int vt) {
 }
 
 // MSCFModel.cpp:101-108
-SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) {
-    const double speedReduction = decel * m.TS;
+SB2_CORE double cfk_brakeGapEuler(double TS, double speed, double decel, double headwayTime) {
+    const double speedReduction = decel * TS;
     const int steps = int(speed / speedReduction);
-    return (steps * speed - speedReduction * steps * (steps + 1) / 2) * m.TS + speed * headwayTime;
+    return (steps * speed - speedReduction * steps * (steps + 1) / 2) * TS + speed * headwayTime;
 }
+SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) { return cfk_brakeGapEuler(m.TS, speed, decel, headwayTime); }
 SB2_HD double cf_brakeGap(const CF& m, double speed, double decel, double headwayTime) { return cf_brakeGapEuler(m, speed, decel, headwayTime); }
 // MSCFModel.h: brakeGap(speed) = brakeGap(speed, myDecel, myHeadwayTime)
 SB2_HD double cf_brakeGap(const CF& m, double speed) { return cf_brakeGapEuler(m, speed, m.decel, m.tau); }
@@ -50,35 +51,38 @@ SB2_HD double cf_minNextSpeed(const CF& m, double speed) { return MAX2(speed - m
 SB2_HD double cf_minNextSpeedEmergency(const CF& m, double speed) { return MAX2(speed - m.emergencyDecel * m.TS, 0.); }
 
 // MSCFModel.cpp:112-132 (Euler branch); freeSpeed(veh, speed, seen, maxSpeed, onInsertion) at :353-360
-SB2_HD double cf_freeSpeed(const CF& m, double /*currentSpeed*/, double dist, double targetSpeed, bool onInsertion) {
+SB2_CORE double cfk_freeSpeed(double TS, double decel, double dist, double targetSpeed, bool onInsertion) {
     if (targetSpeed < 0.) {
         return targetSpeed;
     }
-    const double decel = m.decel;
-    const double v = targetSpeed * m.TS;
+    const double v = targetSpeed * TS;
     if (dist < v) {
         return targetSpeed;
     }
-    const double b = decel * m.TS * m.TS;
+    const double b = decel * TS * TS;
     const double y = MAX2(0.0, ((sqrt((b + 2.0 * v) * (b + 2.0 * v) + 8.0 * b * dist) - b) * 0.5 - v) / b);
     const double yFull = floor(y);
     const double exactGap = (yFull * yFull + yFull) * 0.5 * b + yFull * v + (y > yFull ? v : 0.0);
-    const double fullSpeedGain = (yFull + (onInsertion ? 1. : 0.)) * (decel * m.TS);
-    return (MAX2(0.0, dist - exactGap) / (yFull + 1)) / m.TS + fullSpeedGain + targetSpeed;
+    const double fullSpeedGain = (yFull + (onInsertion ? 1. : 0.)) * (decel * TS);
+    return (MAX2(0.0, dist - exactGap) / (yFull + 1)) / TS + fullSpeedGain + targetSpeed;
+}
+SB2_HD double cf_freeSpeed(const CF& m, double /*currentSpeed*/, double dist, double targetSpeed, bool onInsertion) {
+    return cfk_freeSpeed(m.TS, m.decel, dist, targetSpeed, onInsertion);
 }
 
 // MSCFModel.cpp:798-802
-SB2_HD double cf_estimateSpeedAfterDistance(const CF& m, double dist, double v, double accel) {
-    return MIN2(m.maxSpeed, (double)sqrt(MAX2(0., 2 * dist * accel + v * v)));
+SB2_CORE double cfk_estimateSpeedAfterDistance(double maxSpeed, double dist, double v, double accel) {
+    return MIN2(maxSpeed, (double)sqrt(MAX2(0., 2 * dist * accel + v * v)));
 }
+SB2_HD double cf_estimateSpeedAfterDistance(const CF& m, double dist, double v, double accel) { return cfk_estimateSpeedAfterDistance(m.maxSpeed, dist, v, accel); }
 
 // MSCFModel.cpp:461-479
-SB2_HD SUMOTime cf_getMinimalArrivalTime(const CF& m, double dist, double currentSpeed, double arrivalSpeed) {
+SB2_CORE SUMOTime cfk_getMinimalArrivalTime(double mAccel, double mDecel, double dist, double currentSpeed, double arrivalSpeed) {
     if (dist <= 0.) {
         return 0;
     }
     arrivalSpeed = MAX2(0.0, arrivalSpeed);
-    const double accel = (arrivalSpeed >= currentSpeed) ? m.accel : -m.decel;
+    const double accel = (arrivalSpeed >= currentSpeed) ? mAccel : -mDecel;
     const double accelTime = accel == 0. ? 0. : (arrivalSpeed - currentSpeed) / accel;
     const double accelWay = accelTime * (arrivalSpeed + currentSpeed) * 0.5;
     if (dist >= accelWay) {
@@ -87,6 +91,9 @@ SB2_HD SUMOTime cf_getMinimalArrivalTime(const CF& m, double dist, double curren
         return TIME2STEPS(accelTime + nonAccelWay / nonAccelSpeed);
     }
     return TIME2STEPS(-(currentSpeed - sqrt(currentSpeed * currentSpeed + 2 * accel * dist)) / accel);
+}
+SB2_HD SUMOTime cf_getMinimalArrivalTime(const CF& m, double dist, double currentSpeed, double arrivalSpeed) {
+    return cfk_getMinimalArrivalTime(m.accel, m.decel, dist, currentSpeed, arrivalSpeed);
 }
 
 // MSCFModel.cpp:578-591
@@ -103,9 +110,9 @@ SB2_HD double cf_getMinimalArrivalSpeedEuler(const CF& m, double dist, double cu
 }
 
 // MSCFModel.cpp:1038-1086
-SB2_HD double cf_calculateEmergencyDeceleration(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel) {
+SB2_CORE double cfk_calculateEmergencyDeceleration(double emergencyDecel, double gap, double egoSpeed, double predSpeed, double predMaxDecel) {
     if (gap <= 0.) {
-        return m.emergencyDecel;
+        return emergencyDecel;
     }
     const double predBrakeDist = 0.5 * predSpeed * predSpeed / predMaxDecel;
     const double b1 = 0.5 * egoSpeed * egoSpeed / (gap + predBrakeDist);
@@ -115,21 +122,27 @@ SB2_HD double cf_calculateEmergencyDeceleration(const CF& m, double gap, double 
     const double b2 = 0.5 * (egoSpeed * egoSpeed - predSpeed * predSpeed) / gap;
     return b2;
 }
+SB2_HD double cf_calculateEmergencyDeceleration(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel) {
+    return cfk_calculateEmergencyDeceleration(m.emergencyDecel, gap, egoSpeed, predSpeed, predMaxDecel);
+}
 
 // MSCFModel.cpp:860-884
-SB2_HD double cf_maximumSafeStopSpeedEuler(const CF& m, double gap, double decel, double headway) {
+SB2_CORE double cfk_maximumSafeStopSpeedEuler(double TS, double tau, double gap, double decel, double headway) {
     const double g = gap - SB2_NUMERICAL_EPS;
     if (g < 0.) {
         return 0.;
     }
-    const double b = decel * m.TS;
-    const double t = headway >= 0 ? headway : m.tau;
-    const double s = m.TS;
+    const double b = decel * TS;
+    const double t = headway >= 0 ? headway : tau;
+    const double s = TS;
     const double n = floor(.5 - ((t + (sqrt(((s * s) + (4.0 * ((s * (2.0 * g / b - t)) + (t * t))))) * -0.5)) / s));
     const double h = 0.5 * n * (n - 1) * b * s + n * b * t;
     const double r = (g - h) / (n * s + t);
     const double x = n * b + r;
     return x;
+}
+SB2_HD double cf_maximumSafeStopSpeedEuler(const CF& m, double gap, double decel, double headway) {
+    return cfk_maximumSafeStopSpeedEuler(m.TS, m.tau, gap, decel, headway);
 }
 
 // MSCFModel.cpp:807-856

@@ -24,9 +24,18 @@
 /* entry functions called once per kernel: inlined, so that the members of the __grid_constant__ Ctx are read as
  * constant-bank operands (a noinline callee would get a generic pointer to the parameter space instead) */
 #define SB2_HDN __host__ __device__ __forceinline__
+/* pure scalar arithmetic cores that are used from dozens of call sites (fp64 division / sqrt expand to long instruction
+ * sequences): real calls, arguments in registers.  profiles/r01b: with everything inlined k_plan is ~8 k instructions and
+ * its divergent warps stall on instruction fetch as often as on memory. */
+#if defined(SB2_CORE_INLINE)
+#define SB2_CORE __host__ __device__ __forceinline__
+#else
+#define SB2_CORE __host__ __device__ __noinline__
+#endif
 #else
 #define SB2_HD inline
 #define SB2_HDN inline
+#define SB2_CORE inline
 #endif
 
 namespace sb2 {
