@@ -42,6 +42,12 @@
 #include <utils/options/OptionsIO.h>
 #include <utils/xml/XMLSubSys.h>
 #include <utils/iodevices/OutputDevice.h>
+#include <utils/iodevices/OutputDevice_String.h>
+#include <utils/common/StringTokenizer.h>
+#include <microsim/MSEdgeControl.h>
+#include <random>
+#include <list>
+#include <set>
 #include <traci-server/TraCIServer.h>
 
 #include <algorithm>
@@ -531,11 +537,96 @@ void flatten(MSNet* net, const std::string& path) {
     ff.save(path);
 }
 
+// ---- per-vehicle dawdle draws of the coming step (sigma > 0 parity, BASELINE north_star "replaying the reference's
+// per-vehicle RNG draws").  Nothing in the reference is patched: the draws are PREDICTED from public state before the step
+// and the prediction is verified against the streams' public call counters after the step.
+//   * MSCFModel_Krauss::patchSpeedBeforeLC draws once per executeMove from veh->getRNG() = the RNG of the vehicle's lane
+//     (MSCFModel_Krauss.cpp:117,165; MSBaseVehicle::getRNG; MSLane.h:246), value = rng() / 2^32 (RandHelper.cpp:105)
+//   * executeMove order = MSEdgeControl::myActiveLanes order (written by MSEdgeControl::saveState, MSEdgeControl.cpp:389),
+//     within a lane front to back (MSLane.cpp:2321)
+struct DrawPrediction {
+    std::vector<std::pair<int64_t, double> > draws;                 // (vehicle numerical id, draw)
+    std::map<SumoRNG*, std::pair<unsigned long long, int> > streams;   // stream -> (count before, predicted calls)
+    void checkAndWrite(SUMOTime t, FILE* fd) {
+        int64_t ok = 1;
+        for (const auto& it : streams) {
+            if (it.first->count != it.second.first + (unsigned long long)it.second.second) {
+                ok = 0;
+                if (getenv("SB2_DRAW_DEBUG") != nullptr) {
+                    fprintf(stderr, "draws t=%lld stream %s: predicted %d calls, saw %lld\n", (long long)t, it.first->id.c_str(), it.second.second,
+                            (long long)(it.first->count - it.second.first));
+                }
+            }
+        }
+        const int64_t hdr[3] = {(int64_t)t, (int64_t)draws.size(), ok};
+        fwrite(hdr, 8, 3, fd);
+        for (const auto& d : draws) {
+            fwrite(&d.first, 8, 1, fd);
+            fwrite(&d.second, 8, 1, fd);
+        }
+    }
+};
+
+DrawPrediction
+predictDraws(MSNet* net) {
+    DrawPrediction p;
+    OutputDevice_String od(0);
+    net->getEdgeControl().saveState(od);
+    const std::string xml = od.getString();
+    const size_t a = xml.find("lanes=\"");
+    if (a == std::string::npos) {
+        return p;
+    }
+    const size_t b = xml.find('"', a + 7);
+    std::map<SumoRNG*, std::mt19937> clones;
+    std::list<MSLane*> active;
+    std::set<const MSLane*> isActive;
+    for (const std::string& id : StringTokenizer(xml.substr(a + 7, b - a - 7)).getVector()) {
+        MSLane* lane = MSLane::dictionary(id);
+        if (lane != nullptr) {
+            active.push_back(lane);
+            isActive.insert(lane);
+        }
+    }
+    // MSEdgeControl::patchActiveLanes (MSEdgeControl.cpp:118-133) runs at the begin of the coming step: lanes that got their
+    // first vehicle since the last step join in numerical-id order (lanes of multi-lane edges at the front)
+    std::map<int, MSLane*> byNumId;
+    for (const MSEdge* e : MSEdge::getAllEdges()) {
+        for (MSLane* l : e->getLanes()) {
+            if (l->getVehicleNumber() > 0 && isActive.count(l) == 0) {
+                byNumId[l->getNumericalID()] = l;
+            }
+        }
+    }
+    for (const auto& it : byNumId) {
+        if (it.second->getEdge().getLanes().size() > 1) {
+            active.push_front(it.second);
+        } else {
+            active.push_back(it.second);
+        }
+    }
+    for (MSLane* lane : active) {
+        SumoRNG* rng = lane->getRNG();
+        if (clones.count(rng) == 0) {
+            clones[rng] = *static_cast<std::mt19937*>(rng);
+            p.streams[rng] = std::make_pair(rng->count, 0);
+        }
+        const MSLane::VehCont& vehs = lane->getVehiclesSecure();
+        for (auto it = vehs.rbegin(); it != vehs.rend(); ++it) {
+            const double draw = double(clones[rng]() / 4294967296.0);
+            p.draws.push_back(std::make_pair((int64_t)(*it)->getNumericalID(), draw));
+            p.streams[rng].second++;
+        }
+        lane->releaseVehicles();
+    }
+    return p;
+}
+
 }  // namespace
 
 int
 main(int argc, char** argv) {
-    std::string flatOut, traceOut;
+    std::string flatOut, traceOut, drawsOut;
     std::vector<char*> args;
     args.push_back(argv[0]);
     for (int i = 1; i < argc; i++) {
@@ -544,6 +635,8 @@ main(int argc, char** argv) {
             flatOut = argv[++i];
         } else if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--draws-out" && i + 1 < argc) {
+            drawsOut = argv[++i];
         } else {
             args.push_back(argv[i]);
         }
@@ -577,13 +670,21 @@ main(int argc, char** argv) {
                 }
             }
             FILE* f = fopen(traceOut.c_str(), "wb");
+            FILE* fd = drawsOut.empty() ? nullptr : fopen(drawsOut.c_str(), "wb");
             const SUMOTime begin = string2time(oc.getString("begin"));
             const SUMOTime end = string2time(oc.getString("end"));
             MSNet::SimulationState state = MSNet::SIMSTATE_RUNNING;
             // mirror MSNet::simulate (MSNet.cpp:462-500) but record the state after every step
             while (state == MSNet::SIMSTATE_RUNNING) {
                 const SUMOTime t = net->getCurrentTimeStep();
+                DrawPrediction pred;
+                if (fd != nullptr) {
+                    pred = predictDraws(net);
+                }
                 net->simulationStep();
+                if (fd != nullptr) {
+                    pred.checkAndWrite(t, fd);
+                }
                 std::vector<const MSVehicle*> on;
                 MSVehicleControl& vc = net->getVehicleControl();
                 for (auto it = vc.loadedVehBegin(); it != vc.loadedVehEnd(); ++it) {
@@ -609,6 +710,9 @@ main(int argc, char** argv) {
                 }
             }
             fclose(f);
+            if (fd != nullptr) {
+                fclose(fd);
+            }
             net->closeSimulation(begin, MSNet::getStateMessage(state));
         }
         delete net;

@@ -21,6 +21,10 @@ CASES = {
     "grid5_dense": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
     # vehicles with individual speed factors (normc(1,0.1,0.2,2), sampled by the reference's loader)
     "grid4_tls_speeddev": ["--end", "1000"],
+    # Krauss sigma = 0.5 (the vType default): the reference's per-vehicle dawdle draws are recorded (--draws-out) and replayed
+    "grid4_tls_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
+    "grid5_dense_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "700"],
+    "c1_grid10_sigma": ["--time-to-teleport", "-1", "--end", "2000"],
 }
 
 
@@ -38,6 +42,23 @@ def ensure_reference():
     return exe
 
 
+def draws_path(name):
+    return os.path.join(CACHE, name + ".draws")
+
+
+def load_draws(path):
+    """per step (t_ms, vehicle numerical ids, draws, prediction verified) written by sumo_flatten --draws-out"""
+    import numpy as np
+    raw = np.fromfile(path, dtype=np.int64)
+    out, off = [], 0
+    while off < raw.size:
+        t, n, ok = int(raw[off]), int(raw[off + 1]), int(raw[off + 2])
+        rec = raw[off + 3:off + 3 + 2 * n].reshape(n, 2)
+        out.append((t, rec[:, 0].copy(), rec[:, 1].copy().view(np.float64), ok))
+        off += 3 + 2 * n
+    return out
+
+
 def reference_case(name):
     """returns (flat path, trace path) for a case, generating them with the reference binary on first use"""
     exe = ensure_reference()
@@ -46,10 +67,19 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma"):
             base = base.replace(suffix, "")
+        rou = os.path.join(GOLDEN, base + ".rou.xml")
+        extra = []
+        if name.endswith("_sigma"):
+            text = open(rou).read()
+            assert 'sigma="0"' in text
+            rou = os.path.join(CACHE, name + ".rou.xml")
+            with open(rou, "w") as f:
+                f.write(text.replace('sigma="0"', 'sigma="0.5"'))
+            extra = ["--draws-out", draws_path(name)]
         cmd = [exe, "--flat-out", flat, "--trace-out", trace + ".tmp", "-n", os.path.join(GOLDEN, base + ".net.xml"),
-               "-r", os.path.join(GOLDEN, base + ".rou.xml"), "--no-step-log", "--no-warnings"] + CASES[name]
+               "-r", rou, "--no-step-log", "--no-warnings"] + extra + CASES[name]
         subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         os.replace(trace + ".tmp", trace)
     return flat, trace

@@ -10,6 +10,7 @@
  */
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -95,13 +96,15 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut;
+    std::string traceOut, drawsIn;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--draws" && i + 1 < argc) {
+            drawsIn = argv[++i];   // per-vehicle dawdle draws recorded from the reference (sumo_flatten --draws-out)
         } else if (a == "--steps" && i + 1 < argc) {
             maxSteps = atol(argv[++i]);
         } else if (a == "--debug-veh" && i + 1 < argc) {
@@ -129,11 +132,30 @@ int main(int argc, char** argv) {
         order[v] = v;
     }
     std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
+    FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
+    std::vector<double> replay(c.nV, 0.);
+    std::map<int64_t, int> slotOfNumId;
+    for (int v = 0; v < c.nV; v++) {
+        slotOfNumId[c.veh_numid[v]] = v;
+    }
     long steps = 0;
     long long updates = 0;
     int lastErr = 0;
     while ((m.end < 0 || c.t < m.end) && (maxSteps < 0 || steps < maxSteps)) {
         const SUMOTime t = c.t;
+        if (fdraws != nullptr) {
+            int64_t hdr[3];
+            if (fread(hdr, 8, 3, fdraws) == 3) {
+                for (int64_t i = 0; i < hdr[1]; i++) {
+                    int64_t id; double d;
+                    if (fread(&id, 8, 1, fdraws) == 1 && fread(&d, 8, 1, fdraws) == 1) {
+                        replay[slotOfNumId[id]] = d;
+                    }
+                }
+                c.rng_replay = replay.data();
+                c.rng_mode = 2;
+            }
+        }
         step(m);
         steps++;
         int n = 0;

@@ -46,3 +46,35 @@ def test_teleport_condition_is_reported():
         assert r.flags == 0
         r = eng.step(2)
         assert r.flags & 16 and r.teleports >= 1
+
+
+@pytest.mark.parametrize("case", ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma"])
+def test_engine_matches_reference_sigma_with_replayed_draws(case):
+    """Krauss sigma=0.5 (BASELINE config 2's model): per-vehicle trajectories are bit-identical to the reference when the
+    reference's per-vehicle RNG draws are replayed through sumob200_set_random_draws"""
+    from sumo_b200.engine import Engine
+    from conftest import draws_path, load_draws
+    flat, trace = reference_case(case)
+    ref = load_trace(trace)
+    draws = load_draws(draws_path(case))
+    assert all(ok for (_, _, _, ok) in draws)
+    numid = load_flat(flat)["veh_numid"]
+    slot = {int(n): i for i, n in enumerate(numid)}
+    order = np.argsort(numid, kind="stable")
+    compared = 0
+    buf = np.zeros(len(numid))
+    with Engine(flat) as eng:
+        for (t, ids, lanes, pos, speed), (td, dids, dvals, _) in zip(ref, draws):
+            assert td == t == eng.time_ms
+            buf[[slot[int(i)] for i in dids]] = dvals
+            eng.set_random_draws(buf)
+            r = eng.step(1)
+            st = eng.vehicles()[order]
+            on = st["lane"] >= 0
+            assert r.flags == 0, "t=%d: engine raised flags 0x%x" % (t, r.flags)
+            assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
+            assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
+            assert np.array_equal(st["pos"][on].view(np.int64), pos.view(np.int64)), "t=%d: positions differ (bitwise)" % t
+            assert np.array_equal(st["speed"][on].view(np.int64), speed.view(np.int64)), "t=%d: speeds differ (bitwise)" % t
+            compared += len(ids)
+    assert compared > 1000

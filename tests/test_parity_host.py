@@ -33,3 +33,21 @@ def test_host_emulation_matches_reference(case, host_emul, tmp_path):
     subprocess.run([host_emul, flat, "--trace-out", out, "--steps", str(len(ref))], check=True, timeout=600, stderr=subprocess.DEVNULL)
     n = assert_traces_identical(ref, load_trace(out))
     assert n > 1000
+
+
+SIGMA_CASES = ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma"]
+
+
+@pytest.mark.parametrize("case", SIGMA_CASES)
+def test_host_emulation_matches_reference_with_replayed_draws(case, host_emul, tmp_path):
+    """Krauss sigma=0.5: bit-exact when the reference's per-vehicle dawdle draws are replayed (BASELINE north_star)"""
+    from conftest import draws_path, load_draws
+    flat, trace = reference_case(case)
+    draws = load_draws(draws_path(case))
+    assert all(ok for (_, _, _, ok) in draws), "the harness' draw prediction was not confirmed by the reference's RNG call counters"
+    out = str(tmp_path / "emul.trace")
+    ref = load_trace(trace)
+    subprocess.run([host_emul, flat, "--trace-out", out, "--draws", draws_path(case), "--steps", str(len(ref))], check=True, timeout=600,
+                   stderr=subprocess.DEVNULL)
+    n = assert_traces_identical(ref, load_trace(out))
+    assert n > 1000
