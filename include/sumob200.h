@@ -99,6 +99,19 @@ typedef struct sumob200_fcd_row {
     double x, y, angle;       /* MSVehicle::getPosition / computeAngle as navi degrees (MSFCDExport.cpp:119-180) */
 } sumob200_fcd_row;
 int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capacity, int* n);
+/* streaming form (north star: "FCD output is streamed via pinned async D2H copies"): _begin compacts the rows on the
+ * device and starts their D2H copy into a pinned buffer of the engine on a separate copy stream; the caller may issue the
+ * next sumob200_step right away; _end waits for the copy and hands out the pinned rows (valid until the next _begin
+ * after the following one: two buffers alternate).  Replaces the per-vehicle loop of MSFCDExport::write
+ * (src/microsim/output/MSFCDExport.cpp:98-300), whose XML formatting stays on the host. */
+int sumob200_fcd_begin(sumob200_engine* e);
+int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n);
+
+/* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
+ * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],
+ * p = 0 CO2, 1 CO, 2 HC, 3 fuel, 4 NOx, 5 PMx, 6 electricity [mg resp. ml resp. Wh], n = sumob200_num_vehicles.
+ * capacity = number of doubles in out (>= 7 * n).  SUMOB200_EUNSUPPORTED if no vehicle carries the emission device. */
+int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity);
 
 int sumob200_num_vehicles(const sumob200_engine* e);
 int sumob200_num_lanes(const sumob200_engine* e);

@@ -17,6 +17,22 @@
  */
 #include <config.h>
 #include <version.h>
+// The HBEFA coefficient tables (HelpersHBEFA3/4::myFunctionParameter) and the emission device's accumulators
+// (MSDevice_Emissions::myEmissions) have no public accessor; a maintainer's in-tree shim would be a friend.  Here, outside
+// the tree and without touching it, the three headers are read with private members visible.
+#include <string>
+#include <vector>
+#include <map>
+#include <set>
+#include <bitset>
+#include <sstream>
+#define private public
+#include <utils/emissions/PollutantsInterface.h>
+#include <utils/emissions/HelpersHBEFA3.h>
+#include <utils/emissions/HelpersHBEFA4.h>
+#include <microsim/devices/MSDevice_Emissions.h>
+#undef private
+#include <utils/emissions/EnergyParams.h>
 #include <microsim/MSLink.h>
 #include <microsim/MSNet.h>
 #include <microsim/MSEdge.h>
@@ -393,6 +409,7 @@ void flatten(MSNet* net, const std::string& path) {
         std::map<const MSRoute*, int> routeIdx;
         std::vector<const MSRoute*> routes;
         std::vector<int32_t> numid, vtype, vroute, dpp, dsp, dlp, dlane, idrank(vehs.size(), 0);
+        std::vector<uint8_t> hasEmissions;   // vehicle carries MSDevice_Emissions (--device.emissions.probability / explicit)
         std::vector<int64_t> depart;
         std::vector<double> sf, arrpos, dpos, dspeed;
         NameTable vehNames;
@@ -420,6 +437,7 @@ void flatten(MSNet* net, const std::string& path) {
             dspeed.push_back(p.departSpeed);
             dlp.push_back((int)p.departLaneProcedure);
             dlane.push_back(p.departLane);
+            hasEmissions.push_back(v->getDevice(typeid(MSDevice_Emissions)) != nullptr ? 1 : 0);
             vehNames.add(v->getID());
         }
         {
@@ -448,10 +466,12 @@ void flatten(MSNet* net, const std::string& path) {
         ff.put("veh_departlane_proc", dlp);
         ff.put("veh_departlane", dlane);
         ff.put("veh_idrank", idrank);
+        ff.put("veh_emissions", hasEmissions);
         vehNames.put(ff, "veh");
         // types
         std::vector<double> tl, tg, tms, tdms, ta, td, ted, tad, ttau, tsig, timp, tw, tcmg, idmDelta, idmStep;
-        std::vector<int32_t> tcf, tem;
+        std::vector<int32_t> tcf, tem, temModel;
+        std::vector<double> temCoef, temScale, temMass, temIncl;
         std::vector<int64_t> tsd;
         NameTable typeNames;
         for (const MSVehicleType* t : types) {
@@ -473,6 +493,57 @@ void flatten(MSNet* net, const std::string& path) {
             tcf.push_back(cf.getModelID());
             tsd.push_back(cf.getStartupDelay());
             tem.push_back((int)t->getEmissionClass());
+            {
+                // emission model of the type: 0 = none/unsupported (zero emissions are NOT assumed: the engine refuses the
+                // emission device for such a type), 3 = HelpersHBEFA3::compute, 4 = HelpersHBEFA4::compute (gasoline/diesel)
+                const SUMOEmissionClass ec = t->getEmissionClass();
+                const PollutantsInterface::Helper* h = PollutantsInterface::myHelpers[ec >> 16];
+                // PollutantsInterface::Helper::myVolumetricFuel is set from this option (PollutantsInterface.cpp:116)
+                const bool volumetricFuel = OptionsCont::getOptions().exists("emissions.volumetric-fuel") && OptionsCont::getOptions().getBool("emissions.volumetric-fuel");
+                int model = 0;
+                double coef[7][7] = {{0}};
+                double scale[7] = {1, 1, 1, 1, 1, 1, 1};
+                if (h == &PollutantsInterface::myHBEFA3Helper) {
+                    model = 3;
+                    const int index = (ec & ~PollutantsInterface::HEAVY_BIT) - HelpersHBEFA3::HBEFA3_BASE;
+                    for (int e = 0; e < 6; e++) {
+                        for (int k = 0; k < 6; k++) {
+                            coef[e][k] = HelpersHBEFA3::myFunctionParameter[index][e][k];
+                        }
+                        scale[e] = 3.6;
+                        if (e == PollutantsInterface::FUEL && volumetricFuel) {
+                            scale[e] *= (h->getFuel(ec) == "Diesel") ? 836. : 742.;
+                        }
+                    }
+                } else if (h == &PollutantsInterface::myHBEFA4Helper && h->getFuel(ec) != "Electricity") {
+                    model = 4;
+                    const int index = (ec & ~PollutantsInterface::HEAVY_BIT) - HelpersHBEFA4::HBEFA4_BASE;
+                    for (int e = 0; e < 7; e++) {
+                        for (int k = 0; k < 7; k++) {
+                            coef[e][k] = HelpersHBEFA4::myFunctionParameter[index][e][k];
+                        }
+                        if (e == PollutantsInterface::FUEL && volumetricFuel) {
+                            if (h->getFuel(ec) == "Diesel") {
+                                scale[e] *= 836.;
+                            } else if (h->getFuel(ec) == "Gasoline") {
+                                scale[e] *= 742.;
+                            }
+                        }
+                    }
+                }
+                temModel.push_back(model);
+                for (int e = 0; e < 7; e++) {
+                    for (int k = 0; k < 7; k++) {
+                        temCoef.push_back(coef[e][k]);
+                    }
+                    temScale.push_back(scale[e]);
+                }
+                // PollutantsInterface::Helper::getCoastingDecel (PollutantsInterface.cpp:197-210): mass and the speed coefficient
+                const EnergyParams* ep = t->getEmissionParameters();
+                const double mass = ep->getDouble(SUMO_ATTR_MASS);
+                temMass.push_back(mass);
+                temIncl.push_back(ep->getDouble(SUMO_ATTR_FRONTSURFACEAREA) / mass * -9.05337017 + -0.00017774);
+            }
             idmDelta.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_DELTA, 4.));
             idmStep.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_STEPPING, .25));
         }
@@ -492,6 +563,11 @@ void flatten(MSNet* net, const std::string& path) {
         ff.put("vt_cfmodel", tcf);
         ff.put("vt_startupdelay", tsd);
         ff.put("vt_emission_class", tem);
+        ff.put("vt_em_model", temModel);
+        ff.put("vt_em_coef", temCoef);
+        ff.put("vt_em_scale", temScale);
+        ff.put("vt_em_mass", temMass);
+        ff.put("vt_em_incl", temIncl);
         ff.put("vt_idm_delta", idmDelta);
         ff.put("vt_idm_stepping", idmStep);
         typeNames.put(ff, "vt");
@@ -626,7 +702,7 @@ predictDraws(MSNet* net) {
 
 int
 main(int argc, char** argv) {
-    std::string flatOut, traceOut, drawsOut;
+    std::string flatOut, traceOut, drawsOut, emisOut;
     std::vector<char*> args;
     args.push_back(argv[0]);
     for (int i = 1; i < argc; i++) {
@@ -637,6 +713,8 @@ main(int argc, char** argv) {
             traceOut = argv[++i];
         } else if (a == "--draws-out" && i + 1 < argc) {
             drawsOut = argv[++i];
+        } else if (a == "--emissions-out" && i + 1 < argc) {
+            emisOut = argv[++i];   // per step: (t, n) then n x (numerical id, 7 fp64 accumulators of MSDevice_Emissions) as raw bytes
         } else {
             args.push_back(argv[i]);
         }
@@ -671,6 +749,7 @@ main(int argc, char** argv) {
             }
             FILE* f = fopen(traceOut.c_str(), "wb");
             FILE* fd = drawsOut.empty() ? nullptr : fopen(drawsOut.c_str(), "wb");
+            FILE* fe = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
             const SUMOTime begin = string2time(oc.getString("begin"));
             const SUMOTime end = string2time(oc.getString("end"));
             MSNet::SimulationState state = MSNet::SIMSTATE_RUNNING;
@@ -704,6 +783,23 @@ main(int argc, char** argv) {
                     fwrite(ids, 8, 2, f);
                     fwrite(st, 8, 2, f);
                 }
+                if (fe != nullptr) {
+                    std::vector<std::pair<int64_t, const MSDevice_Emissions*> > devs;
+                    for (const MSVehicle* v : on) {
+                        const MSDevice_Emissions* d = static_cast<const MSDevice_Emissions*>(v->getDevice(typeid(MSDevice_Emissions)));
+                        if (d != nullptr) {
+                            devs.push_back(std::make_pair((int64_t)v->getNumericalID(), d));
+                        }
+                    }
+                    const int64_t ehdr[2] = {(int64_t)t, (int64_t)devs.size()};
+                    fwrite(ehdr, 8, 2, fe);
+                    for (const auto& d : devs) {
+                        const PollutantsInterface::Emissions& em = d.second->myEmissions;
+                        const double vals[7] = {em.CO2, em.CO, em.HC, em.fuel, em.NOx, em.PMx, em.electricity};
+                        fwrite(&d.first, 8, 1, fe);
+                        fwrite(vals, 8, 7, fe);
+                    }
+                }
                 state = net->simulationState(end);
                 if (state == MSNet::SIMSTATE_LOADING) {
                     state = MSNet::SIMSTATE_RUNNING;
@@ -712,6 +808,9 @@ main(int argc, char** argv) {
             fclose(f);
             if (fd != nullptr) {
                 fclose(fd);
+            }
+            if (fe != nullptr) {
+                fclose(fe);
             }
             net->closeSimulation(begin, MSNet::getStateMessage(state));
         }

@@ -29,6 +29,7 @@
 #include "sb2_exec.h"
 #include "sb2_lane.h"
 #include "sb2_insert.h"
+#include "sb2_fcd.h"
 
 using namespace sb2;
 
@@ -147,6 +148,91 @@ __global__ void __launch_bounds__(BLOCK) k_count(const __grid_constant__ Ctx c, 
     }
 }
 
+// ---- FCD snapshot (MSFCDExport::write): stream compaction of the on-road vehicle slots, in slot order ------------------
+// pass 1: on-road vehicles per block
+__global__ void __launch_bounds__(BLOCK) k_fcd_count(const __grid_constant__ Ctx c, int32_t* blockCount) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0);
+    if (threadIdx.x == 0) {
+        blockCount[blockIdx.x] = n;
+    }
+}
+// pass 2: exclusive scan of the block counts by one CTA (chunks of 1024 with a running carry); total -> blockCount[nb]
+__global__ void __launch_bounds__(1024) k_fcd_scan(int32_t* blockCount, int nb) {
+    __shared__ int warpSum[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) {
+        carry = 0;
+    }
+    __syncthreads();
+    for (int base = 0; base < nb; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int x = i < nb ? blockCount[i] : 0;
+        int incl = x;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((threadIdx.x & 31) >= d) {
+                incl += o;
+            }
+        }
+        if ((threadIdx.x & 31) == 31) {
+            warpSum[threadIdx.x >> 5] = incl;
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            int w = warpSum[threadIdx.x];
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, w, d);
+                if (threadIdx.x >= d) {
+                    w += o;
+                }
+            }
+            warpSum[threadIdx.x] = w;   // inclusive over warps
+        }
+        __syncthreads();
+        const int warpBase = (threadIdx.x >> 5) > 0 ? warpSum[(threadIdx.x >> 5) - 1] : 0;
+        if (i < nb) {
+            blockCount[i] = carry + warpBase + incl - x;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            carry += warpSum[31];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        blockCount[nb] = carry;
+    }
+}
+// pass 3: one row per on-road vehicle at its compacted position
+__global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx c, const int32_t* blockBase, sumob200_fcd_row* rows) {
+    __shared__ int warpBase[BLOCK / 32];
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const unsigned mask = __ballot_sync(0xffffffffu, on);
+    if ((threadIdx.x & 31) == 0) {
+        warpBase[threadIdx.x >> 5] = __popc(mask);
+    }
+    __syncthreads();
+    int base = blockBase[blockIdx.x];
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
+        base += warpBase[w];
+    }
+    if (on) {
+        const int at = base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1u));
+        const Pos2 p = veh_position(c, v);
+        sumob200_fcd_row r;
+        r.slot = v;
+        r.lane = c.veh_lane[v];
+        r.pos = c.veh_pos[v];
+        r.speed = c.veh_speed[v];
+        r.x = p.x;
+        r.y = p.y;
+        r.angle = naviDegree(veh_computeAngle(c, v, p));
+        rows[at] = r;
+    }
+}
+
 __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
@@ -170,6 +256,14 @@ struct sumob200_engine {
     unsigned long long* dUpdates = nullptr;
     sumob200_vehicle_state* dMirror = nullptr;
     double* dReplay = nullptr;
+    // FCD streaming: device rows + block counts, two pinned host buffers, a copy stream (D2H overlaps the next step)
+    sumob200_fcd_row* dFcd = nullptr;
+    int32_t* dFcdBlocks = nullptr;
+    sumob200_fcd_row* hFcd[2] = {nullptr, nullptr};
+    int32_t* hFcdCount = nullptr;
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t fcdReady = nullptr, fcdCopied[2] = {nullptr, nullptr};
+    int fcdBuf = 0, fcdPendingRows = -1;
     int64_t launches = 0;
     bool profiling = false;
     cudaEvent_t ev[6];
@@ -311,6 +405,17 @@ void sumob200_destroy(sumob200_engine* e) {
     if (e->dReplay != nullptr) {
         cudaFree(e->dReplay);
     }
+    if (e->dFcd != nullptr) {
+        cudaFree(e->dFcd);
+        cudaFree(e->dFcdBlocks);
+        cudaFreeHost(e->hFcd[0]);
+        cudaFreeHost(e->hFcd[1]);
+        cudaFreeHost(e->hFcdCount);
+        cudaEventDestroy(e->fcdReady);
+        cudaEventDestroy(e->fcdCopied[0]);
+        cudaEventDestroy(e->fcdCopied[1]);
+        cudaStreamDestroy(e->copyStream);
+    }
     if (e->stream != nullptr) {
         cudaStreamDestroy(e->stream);
     }
@@ -421,6 +526,21 @@ int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int cap
     return 0;
 }
 
+int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity) {
+    if (e == nullptr || out == nullptr || capacity < (int64_t)7 * e->d.nV) {
+        gLastError = "sumob200_emissions: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    if (!e->model.anyEmissionDevice) {
+        gLastError = "sumob200_emissions: no vehicle of this scenario carries the emission device";
+        return SUMOB200_EUNSUPPORTED;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaMemcpyAsync(out, e->d.veh_em, sizeof(double) * 7 * (size_t)e->d.nV, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
 int sumob200_num_vehicles(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nV; }
 int sumob200_num_lanes(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nL; }
 int64_t sumob200_time_ms(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.t; }
@@ -474,10 +594,78 @@ int sumob200_phase_times(sumob200_engine* e, double* ms, int n_phases, int reset
     return 0;
 }
 
+int sumob200_fcd_begin(sumob200_engine* e) {
+    if (e == nullptr) {
+        gLastError = "sumob200_fcd_begin: null engine";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int nV = e->d.nV;
+    const int nb = grid(nV);
+    if (e->dFcd == nullptr) {
+        const size_t bytes = sizeof(sumob200_fcd_row) * (size_t)(nV > 0 ? nV : 1);
+        CUDA_TRY(cudaMalloc(&e->dFcd, bytes));
+        CUDA_TRY(cudaMalloc(&e->dFcdBlocks, sizeof(int32_t) * (size_t)(nb + 1)));
+        CUDA_TRY(cudaHostAlloc(&e->hFcd[0], bytes, cudaHostAllocDefault));
+        CUDA_TRY(cudaHostAlloc(&e->hFcd[1], bytes, cudaHostAllocDefault));
+        CUDA_TRY(cudaHostAlloc(&e->hFcdCount, sizeof(int32_t), cudaHostAllocDefault));
+        CUDA_TRY(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&e->fcdReady, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&e->fcdCopied[0], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&e->fcdCopied[1], cudaEventDisableTiming));
+    }
+    if (e->fcdPendingRows >= 0) {
+        gLastError = "sumob200_fcd_begin: the previous snapshot was not collected with sumob200_fcd_end";
+        return SUMOB200_EINVAL;
+    }
+    cudaStream_t s = e->stream;
+    // the previous D2H out of dFcd must be done before the rows are overwritten
+    CUDA_TRY(cudaStreamWaitEvent(s, e->fcdCopied[e->fcdBuf ^ 1], 0));
+    k_fcd_count<<<nb, BLOCK, 0, s>>>(e->d, e->dFcdBlocks);
+    k_fcd_scan<<<1, 1024, 0, s>>>(e->dFcdBlocks, nb);
+    k_fcd_write<<<nb, BLOCK, 0, s>>>(e->d, e->dFcdBlocks, e->dFcd);
+    e->launches += 3;
+    CUDA_TRY(cudaMemcpyAsync(e->hFcdCount, e->dFcdBlocks + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaEventRecord(e->fcdReady, s));
+    CUDA_TRY(cudaEventSynchronize(e->fcdReady));
+    const int n = *e->hFcdCount;
+    // rows travel on the copy stream into pinned memory while the caller is free to launch the next step
+    CUDA_TRY(cudaMemcpyAsync(e->hFcd[e->fcdBuf], e->dFcd, sizeof(sumob200_fcd_row) * (size_t)n, cudaMemcpyDeviceToHost, e->copyStream));
+    CUDA_TRY(cudaEventRecord(e->fcdCopied[e->fcdBuf], e->copyStream));
+    e->fcdPendingRows = n;
+    return 0;
+}
+
+int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n) {
+    if (e == nullptr || rows == nullptr || n == nullptr || e->fcdPendingRows < 0) {
+        gLastError = "sumob200_fcd_end: bad argument / no snapshot in flight";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaEventSynchronize(e->fcdCopied[e->fcdBuf]));
+    *rows = e->hFcd[e->fcdBuf];
+    *n = e->fcdPendingRows;
+    e->fcdPendingRows = -1;
+    e->fcdBuf ^= 1;
+    return 0;
+}
+
 int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capacity, int* n) {
-    (void)e; (void)rows; (void)capacity; (void)n;
-    gLastError = "sumob200_fcd_snapshot: not implemented yet";
-    return SUMOB200_EUNSUPPORTED;
+    if (rows == nullptr || n == nullptr) {
+        gLastError = "sumob200_fcd_snapshot: null argument";
+        return SUMOB200_EINVAL;
+    }
+    int rc = sumob200_fcd_begin(e);
+    if (rc != 0) {
+        return rc;
+    }
+    const sumob200_fcd_row* src = nullptr;
+    rc = sumob200_fcd_end(e, &src, n);
+    if (rc != 0) {
+        return rc;
+    }
+    memcpy(rows, src, sizeof(sumob200_fcd_row) * (size_t)(*n < capacity ? *n : capacity));
+    return 0;
 }
 
 }  // extern "C"

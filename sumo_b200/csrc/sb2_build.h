@@ -28,6 +28,8 @@ struct Buffer {
 class Model {
 public:
     Ctx h;                         // host view
+    bool haveEmissionModel = false;
+    bool anyEmissionDevice = false;
     std::vector<Buffer*> buffers;
     std::vector<std::string> lane_names, veh_names;
     SUMOTime begin = 0, end = 0;
@@ -120,6 +122,7 @@ public:
         SB2_COPY(int32_t, lane_inc_begin); SB2_COPY(int32_t, inc_lane); SB2_COPY(int32_t, inc_link); SB2_COPY(double, inc_length);
         SB2_COPY(int32_t, lane_to_junction); SB2_COPY(int32_t, lane_from_junction);
         SB2_COPY(int32_t, edge_lane_begin);
+        SB2_COPY(int32_t, lane_shape_begin); SB2_COPY(double, shape_xy); SB2_COPY(double, lane_geomfactor);
         SB2_DYN(int32_t, lane_first, nL, -1); SB2_DYN(int32_t, lane_last, nL, -1); SB2_DYN(int32_t, lane_nveh, nL, 0);
         SB2_DYN(double, lane_brutto, nL, 0.);
         SB2_DYN(int32_t, lane_npartial, nL, 0); SB2_DYN(int32_t, lane_partial, (size_t)nL * MAX_PARTIAL, -1);
@@ -236,6 +239,15 @@ public:
                 }
             }
             SB2_COPY(double, vt_collision_mingap_factor);
+            // emission model (optional arrays: scenarios flattened without them carry no emission device)
+            haveEmissionModel = ff.has("vt_em_model") && ff.has("vt_em_coef");
+            if (haveEmissionModel) {
+                SB2_COPY(int32_t, vt_em_model); SB2_COPY(double, vt_em_coef); SB2_COPY(double, vt_em_scale);
+                SB2_COPY(double, vt_em_mass); SB2_COPY(double, vt_em_incl);
+            } else {
+                SB2_DYN(int32_t, vt_em_model, nT, 0); SB2_DYN(double, vt_em_coef, (size_t)nT * 49, 0.); SB2_DYN(double, vt_em_scale, (size_t)nT * 7, 1.);
+                SB2_DYN(double, vt_em_mass, nT, 0.); SB2_DYN(double, vt_em_incl, nT, 0.);
+            }
             bool anySigma = false;
             for (int i = 0; i < nT; i++) {
                 anySigma = anySigma || h.vt_sigma[i] != 0.;
@@ -342,6 +354,25 @@ public:
         SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
         SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
         SB2_DYN(double, veh_len_in_front, nV, 0.);
+        {
+            // emission device: per-vehicle flag + 7 accumulators; a vehicle with the device needs a supported (HBEFA3/HBEFA4) model
+            bool anyDevice = false;
+            if (ff.has("veh_emissions")) {
+                uint8_t* flag = SB2_COPY(uint8_t, veh_emissions);
+                for (int v = 0; v < nV; v++) {
+                    if (flag[v]) {
+                        anyDevice = true;
+                        anyEmissionDevice = true;
+                        if (!haveEmissionModel || h.vt_em_model[h.veh_type[v]] == 0) {
+                            throw std::runtime_error("sumob200: emission device on a vehicle whose emission class is not HBEFA3/HBEFA4 (gasoline/diesel)");
+                        }
+                    }
+                }
+            } else {
+                SB2_DYN(uint8_t, veh_emissions, nV, 0);
+            }
+            SB2_DYN(double, veh_em, anyDevice ? (size_t)nV * 7 : 1, 0.);
+        }
         SB2_DYN(int32_t, veh_order, nV, -1);
         const size_t nDI = (size_t)nV * MAX_DRIVE_ITEMS;
         for (int b = 0; b < 2; b++) {

@@ -15,6 +15,7 @@
 #include "sb2_cf.h"
 #include "sb2_veh.h"
 #include "sb2_link.h"
+#include "sb2_emis.h"
 
 namespace sb2 {
 
@@ -344,6 +345,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
     c.veh_havetowait[v] = haveToWait;
     c.veh_routepos[v] = routePos;
     c.veh_odometer[v] = odometer;
+    veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
     if (arrived) {
         c.veh_moved[v] = 2;
         c.veh_lane[v] = -2;

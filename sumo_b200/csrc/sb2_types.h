@@ -100,6 +100,7 @@ struct Ctx {
     const int32_t* lane_inc_begin; const int32_t* inc_lane; const int32_t* inc_link; const double* inc_length;
     const int32_t* lane_to_junction; const int32_t* lane_from_junction;
     const int32_t* edge_lane_begin;
+    const int32_t* lane_shape_begin; const double* shape_xy; const double* lane_geomfactor;   // MSLane::getShape, getLengthGeometryFactor
     // ---- lanes (dynamic) -----------------------------------------------------------------
     int32_t* lane_first;       // front-most vehicle (largest pos) or -1        (MSLane::myVehicles.back())
     int32_t* lane_last;        // rear-most vehicle or -1                        (MSLane::myVehicles.front())
@@ -137,6 +138,8 @@ struct Ctx {
     const int32_t* vt_cfmodel; const SUMOTime* vt_startupdelay;
     const double* vt_collision_mingap_factor;
     const double* vt_idm_delta; const double* vt_idm_stepping;
+    // HBEFA emission model of the type (sb2_emis.h): model id, [7][7] polynomial coefficients, [7] divisors, coasting parameters
+    const int32_t* vt_em_model; const double* vt_em_coef; const double* vt_em_scale; const double* vt_em_mass; const double* vt_em_incl;
     // ---- routes --------------------------------------------------------------------------
     const int32_t* route_begin; const int32_t* route_edges;
     // ---- vehicles (static) ---------------------------------------------------------------
@@ -159,6 +162,8 @@ struct Ctx {
     int32_t* veh_ahead; int32_t* veh_behind;   // lane queue links (towards larger / smaller position)
     int32_t* veh_next_incoming;
     int32_t* veh_nfurther; int32_t* veh_further;     // [nV*MAX_FURTHER] lanes the back still covers, nearest first
+    const uint8_t* veh_emissions;   // vehicle carries the emission device
+    double* veh_em;            // [7*nV] MSDevice_Emissions::myEmissions, pollutant-major (CO2, CO, HC, fuel, NOx, PMx, electricity)
     double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on

@@ -64,6 +64,9 @@ def load_library(path=None):
     lib.sumob200_step_timed.argtypes = [ctypes.c_void_p, ctypes.c_int, P(StepResult), P(ctypes.c_double)]
     lib.sumob200_mirror_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_fcd_snapshot.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int)]
+    lib.sumob200_fcd_begin.argtypes = [ctypes.c_void_p]
+    lib.sumob200_fcd_end.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_int)]
+    lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
     lib.sumob200_num_lanes.argtypes = [ctypes.c_void_p]
     lib.sumob200_time_ms.argtypes = [ctypes.c_void_p]
@@ -158,6 +161,33 @@ class Engine:
         buf = self._state if out is None else out
         _check(self._lib, self._lib.sumob200_mirror_all(self._h, buf.ctypes.data, buf.shape[0]), "sumob200_mirror_all")
         return buf[:self.num_vehicles]
+
+    def fcd(self):
+        """FCD rows (slot, lane, pos, speed, x, y, angle[navi degrees]) of the vehicles on the road, ordered by slot"""
+        rows = np.zeros(max(self.num_vehicles, 1), dtype=FCD_ROW)
+        n = ctypes.c_int()
+        _check(self._lib, self._lib.sumob200_fcd_snapshot(self._h, rows.ctypes.data, rows.shape[0], ctypes.byref(n)), "sumob200_fcd_snapshot")
+        return rows[:n.value]
+
+    def fcd_begin(self):
+        """start the device-side compaction + pinned async D2H of the FCD rows; the next step may be issued right away"""
+        _check(self._lib, self._lib.sumob200_fcd_begin(self._h), "sumob200_fcd_begin")
+
+    def fcd_end(self):
+        """wait for the copy started by fcd_begin; returns a view of the engine's pinned buffer (valid until the second next fcd_begin)"""
+        p = ctypes.c_void_p()
+        n = ctypes.c_int()
+        _check(self._lib, self._lib.sumob200_fcd_end(self._h, ctypes.byref(p), ctypes.byref(n)), "sumob200_fcd_end")
+        if n.value == 0:
+            return np.zeros(0, dtype=FCD_ROW)
+        buf = (ctypes.c_char * (n.value * FCD_ROW.itemsize)).from_address(p.value)
+        return np.frombuffer(buf, dtype=FCD_ROW, count=n.value)
+
+    def emissions(self):
+        """[7, num_vehicles] accumulated CO2, CO, HC, fuel, NOx, PMx, electricity of every vehicle slot"""
+        out = np.zeros((7, self.num_vehicles))
+        _check(self._lib, self._lib.sumob200_emissions(self._h, out.ctypes.data, out.size), "sumob200_emissions")
+        return out
 
     def set_random_draws(self, draws):
         d = np.ascontiguousarray(draws, dtype=np.float64)

@@ -25,6 +25,15 @@ CASES = {
     "grid4_tls_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
     "grid5_dense_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "700"],
     "c1_grid10_sigma": ["--time-to-teleport", "-1", "--end", "2000"],
+    # every vehicle carries MSDevice_Emissions: default class (HBEFA4/PC_petrol_Euro-4) and an explicit HBEFA3 class
+    "grid4_tls_hbefa4": ["--default.speeddev", "0", "--end", "900", "--device.emissions.probability", "1"],
+    "grid4_tls_hbefa3": ["--default.speeddev", "0", "--end", "900", "--device.emissions.probability", "1"],
+    "grid5_dense_hbefa3": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "600", "--device.emissions.probability", "1"],
+}
+# per-case edits of the fixture's route file (old, new)
+ROU_EDITS = {
+    "_sigma": ('sigma="0"', 'sigma="0.5"'),
+    "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
 }
 
 
@@ -44,6 +53,24 @@ def ensure_reference():
 
 def draws_path(name):
     return os.path.join(CACHE, name + ".draws")
+
+
+def emissions_path(name):
+    return os.path.join(CACHE, name + ".emis")
+
+
+def load_emissions(path):
+    """per step (t_ms, vehicle numerical ids, [n,7] accumulated CO2 CO HC fuel NOx PMx electricity) of the on-road vehicles:
+    MSDevice_Emissions::myEmissions of the reference (sumo_flatten --emissions-out) or of the host emulation"""
+    import numpy as np
+    raw = np.fromfile(path, dtype=np.int64)
+    out, off = [], 0
+    while off < raw.size:
+        t, n = int(raw[off]), int(raw[off + 1])
+        rec = raw[off + 2:off + 2 + 8 * n].reshape(n, 8)
+        out.append((t, rec[:, 0].copy(), rec[:, 1:].copy().view(np.float64)))
+        off += 2 + 8 * n
+    return out
 
 
 def load_draws(path):
@@ -67,22 +94,51 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
+        for suffix, (old, new) in ROU_EDITS.items():
+            if name.endswith(suffix):
+                text = open(rou).read()
+                assert old in text
+                rou = os.path.join(CACHE, name + ".rou.xml")
+                with open(rou, "w") as f:
+                    f.write(text.replace(old, new))
         if name.endswith("_sigma"):
-            text = open(rou).read()
-            assert 'sigma="0"' in text
-            rou = os.path.join(CACHE, name + ".rou.xml")
-            with open(rou, "w") as f:
-                f.write(text.replace('sigma="0"', 'sigma="0.5"'))
             extra = ["--draws-out", draws_path(name)]
+        if "_hbefa" in name:
+            extra = ["--emissions-out", emissions_path(name)]
         cmd = [exe, "--flat-out", flat, "--trace-out", trace + ".tmp", "-n", os.path.join(GOLDEN, base + ".net.xml"),
                "-r", rou, "--no-step-log", "--no-warnings"] + extra + CASES[name]
         subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         os.replace(trace + ".tmp", trace)
     return flat, trace
+
+
+def reference_fcd(name):
+    """{(time string, vehicle id): (x, y, angle, speed, pos, lane id)} from the reference's own --fcd-output (2 decimals)"""
+    import re
+    exe = os.path.join(REF, "sumo")
+    ensure_reference()
+    os.makedirs(CACHE, exist_ok=True)
+    out = os.path.join(CACHE, name + ".fcd.xml")
+    if not os.path.exists(out):
+        cmd = [exe, "-n", os.path.join(GOLDEN, name + ".net.xml"), "-r", os.path.join(GOLDEN, name + ".rou.xml"), "--no-step-log",
+               "--no-warnings", "--fcd-output", out + ".tmp"] + CASES[name]
+        subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        os.replace(out + ".tmp", out)
+    ref, t = {}, None
+    veh = re.compile(r'<vehicle id="([^"]+)" x="([^"]+)" y="([^"]+)" angle="([^"]+)" type="[^"]*" speed="([^"]+)" pos="([^"]+)" lane="([^"]+)"')
+    for line in open(out):
+        m = re.search(r'<timestep time="([0-9.]+)"', line)
+        if m:
+            t = m.group(1)
+            continue
+        m = veh.search(line)
+        if m:
+            ref[(t, m.group(1))] = m.groups()[1:]
+    return ref
 
 
 @pytest.fixture(scope="session")

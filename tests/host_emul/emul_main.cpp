@@ -20,6 +20,7 @@
 #include "../../sumo_b200/csrc/sb2_exec.h"
 #include "../../sumo_b200/csrc/sb2_lane.h"
 #include "../../sumo_b200/csrc/sb2_insert.h"
+#include "../../sumo_b200/csrc/sb2_fcd.h"
 
 using namespace sb2;
 
@@ -96,13 +97,17 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn;
+    std::string traceOut, drawsIn, fcdOut, emisOut;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--emissions-out" && i + 1 < argc) {
+            emisOut = argv[++i];   // same binary layout as sumo_flatten --emissions-out
+        } else if (a == "--fcd-out" && i + 1 < argc) {
+            fcdOut = argv[++i];    // text: "t slot lane x y angle pos speed" with FCD's 2 decimals, vehicles in slot order
         } else if (a == "--draws" && i + 1 < argc) {
             drawsIn = argv[++i];   // per-vehicle dawdle draws recorded from the reference (sumo_flatten --draws-out)
         } else if (a == "--steps" && i + 1 < argc) {
@@ -132,6 +137,8 @@ int main(int argc, char** argv) {
         order[v] = v;
     }
     std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
+    FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
+    FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
     std::vector<double> replay(c.nV, 0.);
     std::map<int64_t, int> slotOfNumId;
@@ -175,6 +182,32 @@ int main(int argc, char** argv) {
                 }
             }
         }
+        if (femis != nullptr) {
+            int64_t ne = 0;
+            for (int v : order) {
+                ne += c.veh_lane[v] >= 0 && c.veh_emissions[v];
+            }
+            const int64_t ehdr[2] = {(int64_t)t, ne};
+            fwrite(ehdr, 8, 2, femis);
+            for (int v : order) {
+                if (c.veh_lane[v] >= 0 && c.veh_emissions[v]) {
+                    const int64_t id = c.veh_numid[v];
+                    fwrite(&id, 8, 1, femis);
+                    for (int p = 0; p < 7; p++) {
+                        fwrite(&c.veh_em[(size_t)p * c.nV + v], 8, 1, femis);
+                    }
+                }
+            }
+        }
+        if (ffcd != nullptr) {
+            for (int v = 0; v < c.nV; v++) {
+                if (c.veh_lane[v] >= 0) {
+                    const Pos2 p = veh_position(c, v);
+                    fprintf(ffcd, "%.2f %d %d %.2f %.2f %.2f %.2f %.2f\n", (double)t / 1000., v, c.veh_lane[v], p.x, p.y,
+                            naviDegree(veh_computeAngle(c, v, p)), c.veh_pos[v], c.veh_speed[v]);
+                }
+            }
+        }
         if (*c.err_flags != lastErr) {
             fprintf(stderr, "t=%lld: error flags now 0x%x\n", (long long)t, *c.err_flags);
             lastErr = *c.err_flags;
@@ -186,6 +219,12 @@ int main(int argc, char** argv) {
     }
     if (f != nullptr) {
         fclose(f);
+    }
+    if (ffcd != nullptr) {
+        fclose(ffcd);
+    }
+    if (femis != nullptr) {
+        fclose(femis);
     }
     fprintf(stderr, "steps=%ld vehicle-updates=%lld inserted=%d arrived=%d collisions=%d emergencyStops=%d err=0x%x\n", steps, updates,
             c.counters[2], c.counters[1], c.counters[4], c.counters[5], *c.err_flags);
