@@ -232,10 +232,10 @@ public:
                 } else if (tag[i] == tagIDM) {
                     m[i] = CF_IDM;
                 } else {
-                    throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss)");
+                    throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss, IDM)");
                 }
-                if (m[i] != CF_KRAUSS) {
-                    throw std::runtime_error("sumob200: only the Krauss car-following model is implemented yet");
+                if (m[i] == CF_KRAUSS_ORIG1) {
+                    throw std::runtime_error("sumob200: carFollowModel KraussOrig1 is not implemented (supported: Krauss, IDM)");
                 }
             }
             SB2_COPY(double, vt_collision_mingap_factor);

@@ -20,6 +20,7 @@ struct CF {
     double idmDelta, idmStepping;
     double minGap, length;
     SUMOTime startupDelay;
+    double desSpeed;   // IDM only: veh->getLane()->getVehicleMaxSpeed(veh) of the EGO vehicle's current lane (set by the caller)
 };
 
 SB2_HD CF make_cf(const Ctx& c, int vt) {
@@ -29,6 +30,7 @@ SB2_HD CF make_cf(const Ctx& c, int vt) {
     m.apparentDecel = c.vt_apparentdecel[vt]; m.tau = c.vt_tau[vt]; m.maxSpeed = c.vt_maxspeed[vt]; m.sigma = c.vt_sigma[vt];
     m.model = c.vt_cfmodel[vt]; m.idmDelta = c.vt_idm_delta[vt]; m.idmStepping = c.vt_idm_stepping[vt];
     m.minGap = c.vt_mingap[vt]; m.length = c.vt_length[vt]; m.startupDelay = c.vt_startupdelay[vt];
+    m.desSpeed = 0.;
     return m;
 }
 
@@ -46,7 +48,11 @@ SB2_HD double cf_brakeGap(const CF& m, double speed) { return cf_brakeGapEuler(m
 // MSCFModel.cpp:324-326 (no accel profiles)
 SB2_HD double cf_maxNextSpeed(const CF& m, double speed) { return MIN2(speed + m.accel * m.TS, m.maxSpeed); }
 // MSCFModel.cpp:330-333
-SB2_HD double cf_minNextSpeed(const CF& m, double speed) { return MAX2(speed - m.decel * m.TS, 0.); }
+// IDM: MSCFModel_IDM.cpp:80-88
+SB2_HD double cf_minNextSpeed(const CF& m, double speed) {
+    const double decel = m.model == CF_IDM ? MAX2(m.decel, MIN2(m.emergencyDecel, 1.5)) : m.decel;
+    return MAX2(speed - decel * m.TS, 0.);
+}
 // MSCFModel.cpp:341-343
 SB2_HD double cf_minNextSpeedEmergency(const CF& m, double speed) { return MAX2(speed - m.emergencyDecel * m.TS, 0.); }
 
@@ -66,7 +72,11 @@ SB2_CORE double cfk_freeSpeed(double TS, double decel, double dist, double targe
     const double fullSpeedGain = (yFull + (onInsertion ? 1. : 0.)) * (decel * TS);
     return (MAX2(0.0, dist - exactGap) / (yFull + 1)) / TS + fullSpeedGain + targetSpeed;
 }
-SB2_HD double cf_freeSpeed(const CF& m, double /*currentSpeed*/, double dist, double targetSpeed, bool onInsertion) {
+SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double maxSpeed);
+SB2_HD double cf_freeSpeed(const CF& m, double currentSpeed, double dist, double targetSpeed, bool onInsertion) {
+    if (m.model == CF_IDM) {
+        return cf_idm_freeSpeed(m, currentSpeed, dist, targetSpeed);
+    }
     return cfk_freeSpeed(m.TS, m.decel, dist, targetSpeed, onInsertion);
 }
 
@@ -188,6 +198,24 @@ SB2_HD double cf_maximumSafeFollowSpeed(const CF& m, double gap, double egoSpeed
 // pow(x, delta): delta is 4 by default -> exact repeated squaring is NOT what glibc pow returns in general, but for
 // integer delta in {1,2,4} glibc's correctly rounded pow equals the correctly rounded product only approximately; the
 // IDM path is therefore tolerance-checked, not bit-exact (DESIGN.md "libm").
+// pow(x, delta) of MSCFModel_IDM::_v.  glibc's pow is accurate to ~0.52 ulp but not specified bit for bit, CUDA's to 2 ulp.
+// For the default delta = 4 the device computes x^4 in double-double arithmetic (error-free products through explicit
+// fma) and rounds once: the correctly rounded result, which is what glibc returns except when the exact value lies within
+// ~0.02 ulp of a rounding boundary.  The host build (tests/host_emul) calls glibc's pow like the reference.
+SB2_HD double cf_idm_pow(double x, double delta) {
+#if defined(__CUDA_ARCH__)
+    if (delta == 4. && x >= 0. && x < 1e75) {
+        const double h = x * x;
+        const double l = __fma_rn(x, x, -h);            // x^2 = h + l exactly
+        const double hh = h * h;
+        const double hl = __fma_rn(h, h, -hh);          // h^2 = hh + hl exactly
+        const double cross = 2. * h * l;                // 2hl (l^2 is below the last bit of the sum)
+        return hh + (hl + cross);
+    }
+#endif
+    return pow(x, delta);
+}
+
 SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
     // MSCFModel_IDM.cpp:236-269
     const double twoSqrtAccelDecel = 2 * sqrt(m.accel * m.decel);
@@ -205,35 +233,106 @@ SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double pre
             s += m.minGap;
         }
         gap = MAX2(SB2_NUMERICAL_EPS, gap);
-        const double acc = m.accel * (1. - pow(newSpeed / MAX2(SB2_NUMERICAL_EPS, desSpeed), m.idmDelta) - (s * s) / (gap * gap));
+        const double acc = m.accel * (1. - cf_idm_pow(newSpeed / MAX2(SB2_NUMERICAL_EPS, desSpeed), m.idmDelta) - (s * s) / (gap * gap));
         newSpeed = MAX2(0.0, newSpeed + m.TS * acc / iterations);
         gap -= MAX2(0., (m.TS / iterations) * (newSpeed - predSpeed));
     }
     return MAX2(0., newSpeed);
 }
 
+// MSCFModel_IDM::getSecureGap (MSCFModel_IDM.cpp:228-231)
+SB2_HD double cf_idm_secureGap(const CF& m, double speed, double leaderSpeed) {
+    const double delta_v = speed - leaderSpeed;
+    return MAX2(0.0, speed * m.tau + speed * delta_v / (2 * sqrt(m.accel * m.decel)));
+}
+// MSCFModel_IDM::freeSpeed (MSCFModel_IDM.cpp:104-122)
+SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double maxSpeed) {
+    if (maxSpeed < 0.) {
+        return maxSpeed;
+    }
+    const double secGap = cf_idm_secureGap(m, maxSpeed, 0);
+    double vSafe;
+    if (speed <= maxSpeed) {
+        vSafe = cf_idm_v(m, speed, 1e6, maxSpeed, m.desSpeed, false);
+    } else {
+        vSafe = cf_idm_v(m, speed, MAX2(seen, secGap), 0, m.desSpeed, false);
+    }
+    if (seen < secGap) {
+        vSafe = MIN2(vSafe, maxSpeed);
+    }
+    return vSafe;
+}
+
 // ---- model dispatch -----------------------------------------------------------------------------
 // stopSpeed(veh, speed, gap, decel, usage): MSCFModel_Krauss.cpp:127-134 ; relaxEmergency = (usage != FUTURE)
+// IDM: MSCFModel_IDM.cpp:178-194
 SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap, double decel, bool future) {
+    if (m.model == CF_IDM) {
+        if (gap < 0.01) {
+            return 0;
+        }
+        double result = cf_idm_v(m, speed, gap, 0, m.desSpeed, false);
+        if (gap > 0 && speed < SB2_NUMERICAL_EPS && result < SB2_NUMERICAL_EPS) {
+            result = cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS, false);
+        }
+        if (gap >= 0) {
+            result = MIN2(result, gap / m.TS);
+        }
+        return result;
+    }
     return MIN2(cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS /* actionStepLengthSecs */, !future), cf_maxNextSpeed(m, speed));
 }
 SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel, false); }
 
 // followSpeed: MSCFModel_Krauss.cpp:138-152 (Euler branch)
+// IDM: MSCFModel_IDM.cpp:126-133
 SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predSpeed, double predMaxDecel, bool computeLC = false) {
+    if (m.model == CF_IDM) {
+        return cf_idm_v(m, speed, gap, predSpeed, m.desSpeed, true);
+    }
     const double vsafe = cf_maximumSafeFollowSpeed(m, gap, speed, predSpeed, predMaxDecel, false, computeLC);
     const double vmax = cf_maxNextSpeed(m, speed);
     return MIN2(vsafe, vmax);
 }
 // MSCFModel.cpp:364-366
+// IDM: MSCFModel_IDM.cpp:136-160 (the recursion of the reference is a loop here)
 SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred, double predSpeed, double predMaxDecel) {
+    if (m.model == CF_IDM) {
+        for (int guard = 0; guard < 1000; guard++) {
+            const double s = MAX2(0., speed * m.tau + speed * (speed - predSpeed) / (2 * sqrt(m.accel * m.decel)));
+            if (gap2pred >= s) {
+                return speed;
+            }
+            const double speed2 = cf_followSpeed(m, speed, gap2pred, predSpeed, predMaxDecel);
+            const double speed3 = cf_followSpeed(m, speed2, gap2pred, predSpeed, predMaxDecel);
+            if (speed2 - speed3 < 1 * m.TS) {
+                return speed2;
+            }
+            speed = speed2;
+        }
+        return speed;
+    }
     return cf_maximumSafeFollowSpeed(m, gap2pred, speed, predSpeed, predMaxDecel, true, false);
 }
 // MSCFModel.cpp:375-377
-SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel, true); }
+// IDM: MSCFModel_IDM.cpp:164-174 (base MSCFModel::insertionStopSpeed = stopSpeed(..., FUTURE))
+SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) {
+    double result = cf_stopSpeed(m, speed, gap, m.decel, true);
+    if (m.model == CF_IDM) {
+        int i = 0;
+        while (result - speed < -(m.decel * m.TS) && ++i < 10) {
+            speed = result;
+            result = cf_stopSpeed(m, speed, gap, m.decel, true);
+        }
+    }
+    return result;
+}
 
 // MSCFModel.cpp:178-195 with gComputeLC == false
 SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, double leaderMaxDecel) {
+    if (m.model == CF_IDM) {
+        return cf_idm_secureGap(m, speed, leaderSpeed);
+    }
     const double maxDecel = MAX2(m.decel, leaderMaxDecel);
     const double bgLeader = cf_brakeGap(m, leaderSpeed, maxDecel, 0);
     return MAX2(0.0, cf_brakeGap(m, speed, m.decel, m.tau) - bgLeader);
@@ -241,6 +340,9 @@ SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, dou
 
 // MSCFModel_Krauss.cpp:155-176 ; random in [0,1)
 SB2_HD double cf_dawdle2(const CF& m, double speed, double sigma, double random) {
+    if (m.model == CF_IDM) {
+        return speed;   // MSCFModel::patchSpeedBeforeLC (MSCFModel.h) returns vMax: no dawdling, no draw
+    }
     if (speed < m.accel) {
         speed -= (sigma * speed * random) * m.TS;
     } else {

@@ -170,7 +170,8 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
     }
     const int cur = c.cur;
     const int vt = c.veh_type[v];
-    const CF cf = make_cf(c, vt);
+    CF cf = make_cf(c, vt);
+    cf.desSpeed = lane_vehicle_max_speed(c, myLane, v);
     const double oldSpeed = c.veh_speed[v];
     double pos = c.veh_pos[v];
     SUMOTime waiting = c.veh_waiting[v];

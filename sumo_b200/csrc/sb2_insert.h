@@ -172,7 +172,8 @@ SB2_HD double lane_safeInsertionSpeed(const Ctx& c, int l, const CF& cf, double 
 
 // MSLane::isInsertionSuccess + incorporateVehicle; returns true if the vehicle was inserted
 SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
-    const CF cf = make_cf(c, c.veh_type[v]);
+    CF cf = make_cf(c, c.veh_type[v]);
+    cf.desSpeed = lane_vehicle_max_speed(c, l, v);   // setTentativeLaneAndPosition (MSLane.cpp:851): veh->getLane() == this lane
     // ---- MSLane::getDepartSpeed
     double speed = 0;
     bool patchSpeed = true;

@@ -139,6 +139,13 @@ SB2_HD bool link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTim
                                bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, bool regSpeed = false) {
     for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
         const int foe = r % c.nV;
+#if defined(SB2_DEBUG_LINK) && !defined(__CUDA_ARCH__)
+        if (ego == SB2_DEBUG_LINK_EGO) {
+            fprintf(stderr, "   blockedAtTime link %d foe %d onroad=%d req=%d aviArr=%lld aviLeave=%lld arr=%lld leave=%lld blocked=%d\n", k, foe, (int)veh_on_road(c, foe),
+                    (int)c.di_request[buf][r], (long long)c.di_arrtime[buf][r], (long long)c.di_leavetime[buf][r], (long long)arrivalTime, (long long)leaveTime,
+                    (int)link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime));
+        }
+#endif
         if (foe != ego && veh_on_road(c, foe)
                 && (!lastWasContRed || (regSpeed ? c.di_regspeed[buf][r] : c.veh_speed[foe]) > SB2_HALTING_SPEED)
                 && link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {

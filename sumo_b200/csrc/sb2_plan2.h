@@ -138,6 +138,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v) {
     e.v = v; e.vt = c.veh_type[v]; e.lane = myLane;
     e.pos = c.veh_pos[v]; e.speed = c.veh_speed[v];
     e.cf = make_cf(c, e.vt);
+    e.cf.desSpeed = lane_vehicle_max_speed(c, myLane, v);
     e.length = e.cf.length; e.minGap = e.cf.minGap;
     e.waiting = c.veh_waiting[v];
     const CF& cf = e.cf;

@@ -30,8 +30,15 @@ CASES = {
     "grid4_tls_hbefa3": ["--default.speeddev", "0", "--end", "900", "--device.emissions.probability", "1"],
     "grid5_dense_hbefa3": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "600", "--device.emissions.probability", "1"],
 }
+CASES.update({
+    # carFollowModel IDM (MSCFModel_IDM, delta 4, 4 sub-steps)
+    "grid3_small_idm": ["--default.speeddev", "0"],
+    "grid5_dense_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "c1_grid10_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "2500"],
+})
 # per-case edits of the fixture's route file (old, new)
 ROU_EDITS = {
+    "_idm": ('sigma="0"', 'sigma="0" carFollowModel="IDM"'),
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
     "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
 }
@@ -94,7 +101,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []

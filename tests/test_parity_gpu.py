@@ -78,3 +78,29 @@ def test_engine_matches_reference_sigma_with_replayed_draws(case):
             assert np.array_equal(st["speed"][on].view(np.int64), speed.view(np.int64)), "t=%d: speeds differ (bitwise)" % t
             compared += len(ids)
     assert compared > 1000
+
+
+@pytest.mark.parametrize("case", ["grid3_small_idm", "grid5_dense_idm", "c1_grid10_idm"])
+def test_engine_matches_reference_idm(case):
+    """carFollowModel IDM.  pow(x, delta) is not specified bit for bit by glibc (0.52 ulp) nor by CUDA, so this is the one
+    floating-point tolerance of the suite: the same vehicles on the same lanes after every step, position and speed within
+    1e-9 (m, m/s); the device computes x^4 correctly rounded in double-double arithmetic (measured deviation <= 6e-14)."""
+    from sumo_b200.engine import Engine
+    TOL = 1e-9
+    flat, trace = reference_case(case)
+    ref = load_trace(trace)
+    numid = load_flat(flat)["veh_numid"]
+    order = np.argsort(numid, kind="stable")
+    compared = 0
+    with Engine(flat) as eng:
+        for (t, ids, lanes, pos, speed) in ref:
+            r = eng.step(1)
+            st = eng.vehicles()[order]
+            on = st["lane"] >= 0
+            assert r.flags == 0
+            assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
+            assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
+            assert np.abs(st["pos"][on] - pos).max(initial=0) <= TOL, "t=%d: positions differ by more than %g" % (t, TOL)
+            assert np.abs(st["speed"][on] - speed).max(initial=0) <= TOL, "t=%d: speeds differ by more than %g" % (t, TOL)
+            compared += len(ids)
+    assert compared > 1000
