@@ -31,6 +31,8 @@ CASES = {
     "grid5_dense_hbefa3": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "600", "--device.emissions.probability", "1"],
 }
 CASES.update({
+    # one district of bench.py's workload (10x10 TLS grid, 1800 resident vehicles, sigma 0.5, speedFactor deviation): same options as bench.py
+    "bench_grid10_tls_draws": ["--time-to-teleport", "-1", "--default.departspeed", "0", "--default.departlane", "first", "--end", "700"],
     # carFollowModel IDM (MSCFModel_IDM, delta 4, 4 sub-steps)
     "grid3_small_idm": ["--default.speeddev", "0"],
     "grid5_dense_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
@@ -101,7 +103,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
@@ -112,7 +114,7 @@ def reference_case(name):
                 rou = os.path.join(CACHE, name + ".rou.xml")
                 with open(rou, "w") as f:
                     f.write(text.replace(old, new))
-        if name.endswith("_sigma"):
+        if name.endswith(("_sigma", "_draws")):
             extra = ["--draws-out", draws_path(name)]
         if "_hbefa" in name:
             extra = ["--emissions-out", emissions_path(name)]

@@ -48,7 +48,7 @@ def test_teleport_condition_is_reported():
         assert r.flags & 16 and r.teleports >= 1
 
 
-@pytest.mark.parametrize("case", ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma"])
+@pytest.mark.parametrize("case", ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma", "bench_grid10_tls_draws"])
 def test_engine_matches_reference_sigma_with_replayed_draws(case):
     """Krauss sigma=0.5 (BASELINE config 2's model): per-vehicle trajectories are bit-identical to the reference when the
     reference's per-vehicle RNG draws are replayed through sumob200_set_random_draws"""

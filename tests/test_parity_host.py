@@ -37,7 +37,7 @@ def test_host_emulation_matches_reference(case, host_emul, tmp_path):
     assert n > 1000
 
 
-SIGMA_CASES = ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma"]
+SIGMA_CASES = ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma", "bench_grid10_tls_draws"]
 
 
 @pytest.mark.parametrize("case", SIGMA_CASES)
