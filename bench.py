@@ -177,6 +177,8 @@ def main():
     updates = r1.vehicle_updates - r0.vehicle_updates
     # ---- end-to-end through the public API with host buffers: every step's FCD rows (slot, lane, pos, speed, x, y, angle of
     # every on-road vehicle = what MSFCDExport writes) land in pinned host memory; the D2H of step i overlaps step i+1
+    eng.fcd_begin()          # untimed: the engine allocates its pinned FCD buffers on first use
+    eng.fcd_end()
     barrier()
     e2e_steps = args.steps
     d2h = 0

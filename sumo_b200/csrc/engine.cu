@@ -25,11 +25,7 @@
 
 #include "../../include/sumob200.h"
 #include "sb2_build.h"
-#include "sb2_plan2.h"
-#include "sb2_exec.h"
-#include "sb2_lane.h"
-#include "sb2_insert.h"
-#include "sb2_fcd.h"
+#include "sb2_kernelset.h"
 
 using namespace sb2;
 
@@ -40,216 +36,12 @@ thread_local std::string gLastError;
 #define CUDA_TRY(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
         gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
 
-constexpr int BLOCK = 128;
-// resident CTAs per SM the register allocation of the two per-vehicle kernels is bounded for (profiles/r01_*: both are
-// latency bound -- long scoreboard on dependent gathers -- so occupancy is worth more than a spill-free allocation)
-#ifndef SB2_PLAN_MINB
-#define SB2_PLAN_MINB 8
-#endif
-#ifndef SB2_EXEC_MINB
-#define SB2_EXEC_MINB 8
-#endif
-
-__global__ void k_reset(const __grid_constant__ Ctx c) {
-    if (threadIdx.x == 0) {
-        c.counters[0] = 0;
-        c.counters[7] = 0;
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < c.nTL) {
-        tls_advance(c, i);
-    }
-    // lane-ordered work list: block-wide exclusive scan of the lanes' vehicle counts, one atomic per block for the base
-    __shared__ int warpSum[BLOCK / 32];
-    __shared__ int blockBase;
-    const int n = i < c.nL ? c.lane_nveh[i] : 0;
-    int incl = n;
-    for (int d = 1; d < 32; d <<= 1) {
-        const int o = __shfl_up_sync(0xffffffffu, incl, d);
-        if ((threadIdx.x & 31) >= d) {
-            incl += o;
-        }
-    }
-    if ((threadIdx.x & 31) == 31) {
-        warpSum[threadIdx.x >> 5] = incl;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int tot = 0;
-        for (int w = 0; w < BLOCK / 32; w++) {
-            const int x = warpSum[w];
-            warpSum[w] = tot;
-            tot += x;
-        }
-        blockBase = tot > 0 ? atomicAdd(&c.counters[7], tot) : 0;
-    }
-    __syncthreads();
-    if (i < c.nL) {
-        lane_summary(c, i, blockBase + warpSum[threadIdx.x >> 5] + incl - n);
-    }
-    if (i < c.nK) {
-        c.link_app_head[c.cur][i] = -1;
-    }
-    if (i < 3) {
-        c.fleet[i] = c.fleet_next[i];
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK, SB2_PLAN_MINB) k_plan(const __grid_constant__ Ctx c) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < c.counters[7]) {
-        veh_planMove(c, c.veh_order[i]);
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK, SB2_EXEC_MINB) k_execute(const __grid_constant__ Ctx c) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < c.counters[7]) {
-        const int v = c.veh_order[i];
-        veh_executeMove(c, v, veh_random(c, v));
-        veh_register_partials(c, v);
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK) k_remove(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
-        lane_handoff_remove(c, l);
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
-        lane_handoff_integrate(c, l);
-        lane_detect_collisions(c, l);
-    }
-}
-
-__global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1]) {
-        lane_insertVehicles(c, l);
-    }
-}
-
-// running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
-__global__ void __launch_bounds__(BLOCK) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool on = v < c.nV && c.veh_lane[v] >= 0;
-    const unsigned mask = __ballot_sync(0xffffffffu, on);
-    if ((threadIdx.x & 31) == 0 && mask != 0) {
-        const int n = __popc(mask);
-        atomicAdd(&c.counters[0], n);
-        atomicAdd(updates, (unsigned long long)n);
-    }
-}
-
-// ---- FCD snapshot (MSFCDExport::write): stream compaction of the on-road vehicle slots, in slot order ------------------
-// pass 1: on-road vehicles per block
-__global__ void __launch_bounds__(BLOCK) k_fcd_count(const __grid_constant__ Ctx c, int32_t* blockCount) {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0);
-    if (threadIdx.x == 0) {
-        blockCount[blockIdx.x] = n;
-    }
-}
-// pass 2: exclusive scan of the block counts by one CTA (chunks of 1024 with a running carry); total -> blockCount[nb]
-__global__ void __launch_bounds__(1024) k_fcd_scan(int32_t* blockCount, int nb) {
-    __shared__ int warpSum[32];
-    __shared__ int carry;
-    if (threadIdx.x == 0) {
-        carry = 0;
-    }
-    __syncthreads();
-    for (int base = 0; base < nb; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int x = i < nb ? blockCount[i] : 0;
-        int incl = x;
-        for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, incl, d);
-            if ((threadIdx.x & 31) >= d) {
-                incl += o;
-            }
-        }
-        if ((threadIdx.x & 31) == 31) {
-            warpSum[threadIdx.x >> 5] = incl;
-        }
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            int w = warpSum[threadIdx.x];
-            for (int d = 1; d < 32; d <<= 1) {
-                const int o = __shfl_up_sync(0xffffffffu, w, d);
-                if (threadIdx.x >= d) {
-                    w += o;
-                }
-            }
-            warpSum[threadIdx.x] = w;   // inclusive over warps
-        }
-        __syncthreads();
-        const int warpBase = (threadIdx.x >> 5) > 0 ? warpSum[(threadIdx.x >> 5) - 1] : 0;
-        if (i < nb) {
-            blockCount[i] = carry + warpBase + incl - x;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            carry += warpSum[31];
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        blockCount[nb] = carry;
-    }
-}
-// pass 3: one row per on-road vehicle at its compacted position
-__global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx c, const int32_t* blockBase, sumob200_fcd_row* rows) {
-    __shared__ int warpBase[BLOCK / 32];
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool on = v < c.nV && c.veh_lane[v] >= 0;
-    const unsigned mask = __ballot_sync(0xffffffffu, on);
-    if ((threadIdx.x & 31) == 0) {
-        warpBase[threadIdx.x >> 5] = __popc(mask);
-    }
-    __syncthreads();
-    int base = blockBase[blockIdx.x];
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
-        base += warpBase[w];
-    }
-    if (on) {
-        const int at = base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1u));
-        const Pos2 p = veh_position(c, v);
-        sumob200_fcd_row r;
-        r.slot = v;
-        r.lane = c.veh_lane[v];
-        r.pos = c.veh_pos[v];
-        r.speed = c.veh_speed[v];
-        r.x = p.x;
-        r.y = p.y;
-        r.angle = naviDegree(veh_computeAngle(c, v, p));
-        rows[at] = r;
-    }
-}
-
-__global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v < c.nV) {
-        sumob200_vehicle_state s;
-        s.lane = c.veh_lane[v];
-        s.route_pos = c.veh_routepos[v];
-        s.pos = c.veh_pos[v];
-        s.speed = c.veh_speed[v];
-        out[v] = s;
-    }
-}
-
 }  // namespace
 
 struct sumob200_engine {
     Model model;
     Ctx d;                                  // the Ctx passed by value to every kernel (pointers into device memory)
+    const sb2_kernelset* ks = nullptr;      // kernel set chosen for the scenario (kernels.cu)
     std::vector<void*> dev;                 // device allocation of model.buffers[i]
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -287,6 +79,11 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
     }
     try {
         e->model.build(ff);
+        // kernel set for this scenario (kernels.cu): code the fleet never executes is not compiled in
+        e->ks = e->model.anyIDM ? sb2_kernelset_full() : sb2_kernelset_krauss();
+        if (e->ks->ctx_size != sizeof(Ctx)) {
+            throw std::runtime_error("sumob200: kernel set was built with a different Ctx layout");
+        }
     } catch (const std::exception& ex) {
         gLastError = ex.what();
         delete e;
@@ -337,14 +134,14 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
     return 0;
 }
 
-inline int grid(int n) { return n > 0 ? (n + BLOCK - 1) / BLOCK : 1; }
+inline int gridOf(const sumob200_engine* e, int n) { return n > 0 ? (n + e->ks->block - 1) / e->ks->block : 1; }
 
 }  // namespace
 
 extern "C" {
 
 const char* sumob200_last_error(void) { return gLastError.c_str(); }
-const char* sumob200_version(void) { return "sumob200 0.1 (sm_100a; Krauss, single-lane edges, static TLS)"; }
+const char* sumob200_version(void) { return "sumob200 0.2 (sm_100a; Krauss + IDM, single-lane edges, static TLS, HBEFA3/4, FCD streaming; kernel sets: full, krauss)"; }
 
 int sumob200_create(const sumob200_array* arrays, int n_arrays, int device, sumob200_engine** out) {
     if (arrays == nullptr || out == nullptr || n_arrays <= 0) {
@@ -434,19 +231,19 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     for (int i = 0; i < n_steps; i++) {
         const bool prof = e->profiling;
         if (prof) { cudaEventRecord(e->ev[0], s); }
-        k_reset<<<1, 32, 0, s>>>(e->d);   // counters[0] = running vehicles of this step, counters[7] = length of the work list
-        k_pre<<<grid(nPre < 3 ? 3 : nPre), BLOCK, 0, s>>>(e->d);
+        e->ks->reset(&e->d, s);   // counters[0] = running vehicles of this step, counters[7] = length of the work list
+        e->ks->pre(&e->d, nPre, s);
         if (prof) { cudaEventRecord(e->ev[1], s); }
-        k_plan<<<grid(c.nV), BLOCK, 0, s>>>(e->d);
+        e->ks->plan(&e->d, c.nV, s);
         if (prof) { cudaEventRecord(e->ev[2], s); }
         CUDA_TRY(cudaMemsetAsync(c.lane_npartial, 0, sizeof(int32_t) * (size_t)c.nL, s));
-        k_execute<<<grid(c.nV), BLOCK, 0, s>>>(e->d);
+        e->ks->execute(&e->d, c.nV, s);
         if (prof) { cudaEventRecord(e->ev[3], s); }
-        k_remove<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
-        k_integrate<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
+        e->ks->remove(&e->d, c.nL, s);
+        e->ks->integrate(&e->d, c.nL, s);
         if (prof) { cudaEventRecord(e->ev[4], s); }
-        k_insert<<<grid(c.nL), BLOCK, 0, s>>>(e->d);
-        k_count<<<grid(c.nV), BLOCK, 0, s>>>(e->d, e->dUpdates);
+        e->ks->insert(&e->d, c.nL, s);
+        e->ks->count(&e->d, c.nV, e->dUpdates, s);
         if (prof) {
             cudaEventRecord(e->ev[5], s);
             CUDA_TRY(cudaEventSynchronize(e->ev[5]));
@@ -519,7 +316,7 @@ int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int cap
     if (e->dMirror == nullptr) {
         CUDA_TRY(cudaMalloc(&e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)(nV > 0 ? nV : 1)));
     }
-    k_mirror<<<grid(nV), BLOCK, 0, e->stream>>>(e->d, e->dMirror);
+    e->ks->mirror(&e->d, nV, e->dMirror, e->stream);
     e->launches += 1;
     CUDA_TRY(cudaMemcpyAsync(out, e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)nV, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
@@ -601,7 +398,7 @@ int sumob200_fcd_begin(sumob200_engine* e) {
     }
     CUDA_TRY(cudaSetDevice(e->device));
     const int nV = e->d.nV;
-    const int nb = grid(nV);
+    const int nb = gridOf(e, nV);
     if (e->dFcd == nullptr) {
         const size_t bytes = sizeof(sumob200_fcd_row) * (size_t)(nV > 0 ? nV : 1);
         CUDA_TRY(cudaMalloc(&e->dFcd, bytes));
@@ -621,9 +418,7 @@ int sumob200_fcd_begin(sumob200_engine* e) {
     cudaStream_t s = e->stream;
     // the previous D2H out of dFcd must be done before the rows are overwritten
     CUDA_TRY(cudaStreamWaitEvent(s, e->fcdCopied[e->fcdBuf ^ 1], 0));
-    k_fcd_count<<<nb, BLOCK, 0, s>>>(e->d, e->dFcdBlocks);
-    k_fcd_scan<<<1, 1024, 0, s>>>(e->dFcdBlocks, nb);
-    k_fcd_write<<<nb, BLOCK, 0, s>>>(e->d, e->dFcdBlocks, e->dFcd);
+    e->ks->fcd(&e->d, nV, e->dFcdBlocks, e->dFcd, s);
     e->launches += 3;
     CUDA_TRY(cudaMemcpyAsync(e->hFcdCount, e->dFcdBlocks + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaEventRecord(e->fcdReady, s));

@@ -1,0 +1,276 @@
+/* kernels.cu -- the sm_100a kernels of the step pipeline, compiled once per KERNEL SET.
+ *
+ * A kernel set is this file compiled with a feature selection (-DSB2_KSET=<name> plus -DSB2_NO_* switches); the engine
+ * (engine.cu) picks the set that matches the scenario when it is created.  Measured reason (profiles/r01_*): k_plan is bound
+ * by divergence, instruction fetch and the 64-register allocation, and car-following code that a scenario never executes
+ * (the IDM branches for a Krauss-only fleet) costs 10 % of its time just by being compiled in.
+ *   full    every implemented feature
+ *   krauss  -DSB2_NO_IDM : all vTypes use carFollowModel Krauss
+ * Every set lives in its own namespace, so the inlined device functions of two sets never meet at link time.
+ *
+ * One simulation step = 8 launches on one stream (no host synchronisation in between).  Every kernel takes the Ctx by
+ * value as a __grid_constant__ parameter, so the ~190 array base pointers are read from the constant bank, not from HBM.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include <float.h>
+#include <cstdio>
+
+#include "../../include/sumob200.h"
+#include "sb2_kernelset.h"
+
+#ifndef SB2_KSET
+#error "compile with -DSB2_KSET=<name>"
+#endif
+#define SB2_PASTE2(a, b) a##b
+#define SB2_PASTE(a, b) SB2_PASTE2(a, b)
+#define SB2_STR2(x) #x
+#define SB2_STR(x) SB2_STR2(x)
+
+namespace SB2_PASTE(sb2_kset_, SB2_KSET) {
+
+#include "sb2_types.h"
+#include "sb2_cf.h"
+#include "sb2_veh.h"
+#include "sb2_link.h"
+#include "sb2_plan.h"
+#include "sb2_plan2.h"
+#include "sb2_emis.h"
+#include "sb2_exec.h"
+#include "sb2_lane.h"
+#include "sb2_insert.h"
+#include "sb2_fcd.h"
+
+using namespace sb2;
+
+constexpr int BLOCK = 128;
+// resident CTAs per SM the register allocation of the two per-vehicle kernels is bounded for (profiles/r01_*: both are
+// latency bound -- long scoreboard on dependent gathers -- so occupancy is worth more than a spill-free allocation)
+#ifndef SB2_PLAN_MINB
+#define SB2_PLAN_MINB 8
+#endif
+#ifndef SB2_EXEC_MINB
+#define SB2_EXEC_MINB 8
+#endif
+
+__global__ void k_reset(const __grid_constant__ Ctx c) {
+    if (threadIdx.x == 0) {
+        c.counters[0] = 0;
+        c.counters[7] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.nTL) {
+        tls_advance(c, i);
+    }
+    // lane-ordered work list: block-wide exclusive scan of the lanes' vehicle counts, one atomic per block for the base
+    __shared__ int warpSum[BLOCK / 32];
+    __shared__ int blockBase;
+    const int n = i < c.nL ? c.lane_nveh[i] : 0;
+    int incl = n;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((threadIdx.x & 31) >= d) {
+            incl += o;
+        }
+    }
+    if ((threadIdx.x & 31) == 31) {
+        warpSum[threadIdx.x >> 5] = incl;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int w = 0; w < BLOCK / 32; w++) {
+            const int x = warpSum[w];
+            warpSum[w] = tot;
+            tot += x;
+        }
+        blockBase = tot > 0 ? atomicAdd(&c.counters[7], tot) : 0;
+    }
+    __syncthreads();
+    if (i < c.nL) {
+        lane_summary(c, i, blockBase + warpSum[threadIdx.x >> 5] + incl - n);
+    }
+    if (i < c.nK) {
+        c.link_app_head[c.cur][i] = -1;
+    }
+    if (i < 3) {
+        c.fleet[i] = c.fleet_next[i];
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK, SB2_PLAN_MINB) k_plan(const __grid_constant__ Ctx c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.counters[7]) {
+        veh_planMove(c, c.veh_order[i]);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK, SB2_EXEC_MINB) k_execute(const __grid_constant__ Ctx c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < c.counters[7]) {
+        const int v = c.veh_order[i];
+        veh_executeMove(c, v, veh_random(c, v));
+        veh_register_partials(c, v);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_remove(const __grid_constant__ Ctx c) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        lane_handoff_remove(c, l);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx c) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        lane_handoff_integrate(c, l);
+        lane_detect_collisions(c, l);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1]) {
+        lane_insertVehicles(c, l);
+    }
+}
+
+// running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
+__global__ void __launch_bounds__(BLOCK) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const unsigned mask = __ballot_sync(0xffffffffu, on);
+    if ((threadIdx.x & 31) == 0 && mask != 0) {
+        const int n = __popc(mask);
+        atomicAdd(&c.counters[0], n);
+        atomicAdd(updates, (unsigned long long)n);
+    }
+}
+
+// ---- FCD snapshot (MSFCDExport::write): stream compaction of the on-road vehicle slots, in slot order ------------------
+// pass 1: on-road vehicles per block
+__global__ void __launch_bounds__(BLOCK) k_fcd_count(const __grid_constant__ Ctx c, int32_t* blockCount) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0);
+    if (threadIdx.x == 0) {
+        blockCount[blockIdx.x] = n;
+    }
+}
+// pass 2: exclusive scan of the block counts by one CTA (chunks of 1024 with a running carry); total -> blockCount[nb]
+__global__ void __launch_bounds__(1024) k_fcd_scan(int32_t* blockCount, int nb) {
+    __shared__ int warpSum[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) {
+        carry = 0;
+    }
+    __syncthreads();
+    for (int base = 0; base < nb; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int x = i < nb ? blockCount[i] : 0;
+        int incl = x;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((threadIdx.x & 31) >= d) {
+                incl += o;
+            }
+        }
+        if ((threadIdx.x & 31) == 31) {
+            warpSum[threadIdx.x >> 5] = incl;
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            int w = warpSum[threadIdx.x];
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, w, d);
+                if (threadIdx.x >= d) {
+                    w += o;
+                }
+            }
+            warpSum[threadIdx.x] = w;   // inclusive over warps
+        }
+        __syncthreads();
+        const int warpBase = (threadIdx.x >> 5) > 0 ? warpSum[(threadIdx.x >> 5) - 1] : 0;
+        if (i < nb) {
+            blockCount[i] = carry + warpBase + incl - x;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            carry += warpSum[31];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        blockCount[nb] = carry;
+    }
+}
+// pass 3: one row per on-road vehicle at its compacted position
+__global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx c, const int32_t* blockBase, sumob200_fcd_row* rows) {
+    __shared__ int warpBase[BLOCK / 32];
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const unsigned mask = __ballot_sync(0xffffffffu, on);
+    if ((threadIdx.x & 31) == 0) {
+        warpBase[threadIdx.x >> 5] = __popc(mask);
+    }
+    __syncthreads();
+    int base = blockBase[blockIdx.x];
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
+        base += warpBase[w];
+    }
+    if (on) {
+        const int at = base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1u));
+        const Pos2 p = veh_position(c, v);
+        sumob200_fcd_row r;
+        r.slot = v;
+        r.lane = c.veh_lane[v];
+        r.pos = c.veh_pos[v];
+        r.speed = c.veh_speed[v];
+        r.x = p.x;
+        r.y = p.y;
+        r.angle = naviDegree(veh_computeAngle(c, v, p));
+        rows[at] = r;
+    }
+}
+
+__global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV) {
+        sumob200_vehicle_state s;
+        s.lane = c.veh_lane[v];
+        s.route_pos = c.veh_routepos[v];
+        s.pos = c.veh_pos[v];
+        s.speed = c.veh_speed[v];
+        out[v] = s;
+    }
+}
+
+
+inline int grid(int n) { return n > 0 ? (n + BLOCK - 1) / BLOCK : 1; }
+inline const Ctx& ctx(const void* p) { return *static_cast<const Ctx*>(p); }   // same layout as the engine's sb2::Ctx (one header)
+
+void l_reset(const void* c, cudaStream_t s) { k_reset<<<1, 32, 0, s>>>(ctx(c)); }
+void l_pre(const void* c, int n, cudaStream_t s) { k_pre<<<grid(n < 3 ? 3 : n), BLOCK, 0, s>>>(ctx(c)); }
+void l_plan(const void* c, int n, cudaStream_t s) { k_plan<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_execute(const void* c, int n, cudaStream_t s) { k_execute<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_remove(const void* c, int n, cudaStream_t s) { k_remove<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<grid(n), BLOCK, 0, s>>>(ctx(c), updates); }
+void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
+void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaStream_t s) {
+    const int nb = grid(n);
+    k_fcd_count<<<nb, BLOCK, 0, s>>>(ctx(c), blocks);
+    k_fcd_scan<<<1, 1024, 0, s>>>(blocks, nb);
+    k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
+}
+
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd};
+
+}  // namespace sb2_kset_<name>
+
+extern "C" const sb2_kernelset* SB2_PASTE(sb2_kernelset_, SB2_KSET)(void) { return &SB2_PASTE(sb2_kset_, SB2_KSET)::kSet; }

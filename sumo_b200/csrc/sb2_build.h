@@ -14,7 +14,6 @@
 
 #include "../../include/sumob200_flatfile.h"
 #include "sb2_types.h"
-#include "sb2_insert.h"
 
 namespace sb2 {
 
@@ -28,6 +27,7 @@ struct Buffer {
 class Model {
 public:
     Ctx h;                         // host view
+    bool anyIDM = false;           // some vType uses carFollowModel IDM (selects the kernel set)
     bool haveEmissionModel = false;
     bool anyEmissionDevice = false;
     std::vector<Buffer*> buffers;
@@ -231,6 +231,7 @@ public:
                     m[i] = CF_KRAUSS_ORIG1;
                 } else if (tag[i] == tagIDM) {
                     m[i] = CF_IDM;
+                    anyIDM = true;
                 } else {
                     throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss, IDM)");
                 }

@@ -13,6 +13,12 @@
 
 namespace sb2 {
 
+#if defined(SB2_NO_IDM)
+#define SB2_IS_IDM(m) false
+#else
+#define SB2_IS_IDM(m) ((m).model == CF_IDM)
+#endif
+
 struct CF {
     double TS;
     double accel, decel, emergencyDecel, apparentDecel, tau, maxSpeed /* vType maxSpeed */, sigma;
@@ -50,7 +56,7 @@ SB2_HD double cf_maxNextSpeed(const CF& m, double speed) { return MIN2(speed + m
 // MSCFModel.cpp:330-333
 // IDM: MSCFModel_IDM.cpp:80-88
 SB2_HD double cf_minNextSpeed(const CF& m, double speed) {
-    const double decel = m.model == CF_IDM ? MAX2(m.decel, MIN2(m.emergencyDecel, 1.5)) : m.decel;
+    const double decel = SB2_IS_IDM(m) ? MAX2(m.decel, MIN2(m.emergencyDecel, 1.5)) : m.decel;
     return MAX2(speed - decel * m.TS, 0.);
 }
 // MSCFModel.cpp:341-343
@@ -74,7 +80,7 @@ SB2_CORE double cfk_freeSpeed(double TS, double decel, double dist, double targe
 }
 SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double maxSpeed);
 SB2_HD double cf_freeSpeed(const CF& m, double currentSpeed, double dist, double targetSpeed, bool onInsertion) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         return cf_idm_freeSpeed(m, currentSpeed, dist, targetSpeed);
     }
     return cfk_freeSpeed(m.TS, m.decel, dist, targetSpeed, onInsertion);
@@ -216,28 +222,32 @@ SB2_HD double cf_idm_pow(double x, double delta) {
     return pow(x, delta);
 }
 
-SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
+SB2_CORE double cfk_idm_v(double TS, double accel, double decel, double tau, double minGap, double idmDelta, double idmStepping,
+                          double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
     // MSCFModel_IDM.cpp:236-269
-    const double twoSqrtAccelDecel = 2 * sqrt(m.accel * m.decel);
-    const int iterations = MAX2(1, int(m.TS / m.idmStepping + .5));
-    const double headwayTime = m.tau;
+    const double twoSqrtAccelDecel = 2 * sqrt(accel * decel);
+    const int iterations = MAX2(1, int(TS / idmStepping + .5));
+    const double headwayTime = tau;
     double newSpeed = egoSpeed;
     double gap = gap2pred;
     if (respectMinGap) {
-        gap += m.minGap;
+        gap += minGap;
     }
     for (int i = 0; i < iterations; i++) {
         const double delta_v = newSpeed - predSpeed;
         double s = MAX2(0., newSpeed * headwayTime + newSpeed * delta_v / twoSqrtAccelDecel);
         if (respectMinGap) {
-            s += m.minGap;
+            s += minGap;
         }
         gap = MAX2(SB2_NUMERICAL_EPS, gap);
-        const double acc = m.accel * (1. - cf_idm_pow(newSpeed / MAX2(SB2_NUMERICAL_EPS, desSpeed), m.idmDelta) - (s * s) / (gap * gap));
-        newSpeed = MAX2(0.0, newSpeed + m.TS * acc / iterations);
-        gap -= MAX2(0., (m.TS / iterations) * (newSpeed - predSpeed));
+        const double acc = accel * (1. - cf_idm_pow(newSpeed / MAX2(SB2_NUMERICAL_EPS, desSpeed), idmDelta) - (s * s) / (gap * gap));
+        newSpeed = MAX2(0.0, newSpeed + (acc * TS) / iterations);   // ACCEL2SPEED(acc) / myIterations
+        gap -= MAX2(0., ((newSpeed - predSpeed) * TS) / iterations);   // SPEED2DIST(newSpeed - predSpeed) / myIterations
     }
     return MAX2(0., newSpeed);
+}
+SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
+    return cfk_idm_v(m.TS, m.accel, m.decel, m.tau, m.minGap, m.idmDelta, m.idmStepping, egoSpeed, gap2pred, predSpeed, desSpeed, respectMinGap);
 }
 
 // MSCFModel_IDM::getSecureGap (MSCFModel_IDM.cpp:228-231)
@@ -267,7 +277,7 @@ SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double ma
 // stopSpeed(veh, speed, gap, decel, usage): MSCFModel_Krauss.cpp:127-134 ; relaxEmergency = (usage != FUTURE)
 // IDM: MSCFModel_IDM.cpp:178-194
 SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap, double decel, bool future) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         if (gap < 0.01) {
             return 0;
         }
@@ -287,7 +297,7 @@ SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_st
 // followSpeed: MSCFModel_Krauss.cpp:138-152 (Euler branch)
 // IDM: MSCFModel_IDM.cpp:126-133
 SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predSpeed, double predMaxDecel, bool computeLC = false) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         return cf_idm_v(m, speed, gap, predSpeed, m.desSpeed, true);
     }
     const double vsafe = cf_maximumSafeFollowSpeed(m, gap, speed, predSpeed, predMaxDecel, false, computeLC);
@@ -297,7 +307,7 @@ SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predS
 // MSCFModel.cpp:364-366
 // IDM: MSCFModel_IDM.cpp:136-160 (the recursion of the reference is a loop here)
 SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred, double predSpeed, double predMaxDecel) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         for (int guard = 0; guard < 1000; guard++) {
             const double s = MAX2(0., speed * m.tau + speed * (speed - predSpeed) / (2 * sqrt(m.accel * m.decel)));
             if (gap2pred >= s) {
@@ -318,7 +328,7 @@ SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred
 // IDM: MSCFModel_IDM.cpp:164-174 (base MSCFModel::insertionStopSpeed = stopSpeed(..., FUTURE))
 SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) {
     double result = cf_stopSpeed(m, speed, gap, m.decel, true);
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         int i = 0;
         while (result - speed < -(m.decel * m.TS) && ++i < 10) {
             speed = result;
@@ -330,7 +340,7 @@ SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) {
 
 // MSCFModel.cpp:178-195 with gComputeLC == false
 SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, double leaderMaxDecel) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         return cf_idm_secureGap(m, speed, leaderSpeed);
     }
     const double maxDecel = MAX2(m.decel, leaderMaxDecel);
@@ -340,7 +350,7 @@ SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, dou
 
 // MSCFModel_Krauss.cpp:155-176 ; random in [0,1)
 SB2_HD double cf_dawdle2(const CF& m, double speed, double sigma, double random) {
-    if (m.model == CF_IDM) {
+    if (SB2_IS_IDM(m)) {
         return speed;   // MSCFModel::patchSpeedBeforeLC (MSCFModel.h) returns vMax: no dawdling, no draw
     }
     if (speed < m.accel) {

@@ -14,10 +14,6 @@
 
 namespace sb2 {
 
-// DepartSpeedDefinition / DepartPosDefinition values (utils/vehicle/SUMOVehicleParameter.h)
-enum { DSD_DEFAULT = 0, DSD_GIVEN = 1, DSD_GIVEN_VEHROUTE = 2, DSD_RANDOM = 3, DSD_MAX = 4, DSD_DESIRED = 5, DSD_LIMIT = 6, DSD_LAST = 7, DSD_AVG = 8 };
-enum { DPD_DEFAULT = 0, DPD_GIVEN = 1, DPD_GIVEN_VEHROUTE = 2, DPD_RANDOM = 3, DPD_FREE = 4, DPD_BASE = 5, DPD_LAST = 6, DPD_RANDOM_FREE = 7 };
-enum { DLD_DEFAULT = 0, DLD_GIVEN = 1, DLD_FIRST_ALLOWED = 7 };
 
 struct FollowerInfo {
     int veh;

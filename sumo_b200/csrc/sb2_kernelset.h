@@ -1,0 +1,25 @@
+/* sb2_kernelset.h -- table of launchers one kernel set (kernels.cu compiled with one feature selection) exports to the
+ * engine.  `ctx` points at the engine's sb2::Ctx; the launchers pass it to their kernels by value. */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/sumob200.h"
+
+struct sb2_kernelset {
+    const char* name;
+    int block;                 // threads per CTA of every kernel
+    size_t ctx_size;           // sizeof(Ctx) the set was compiled with (checked by the engine)
+    void (*reset)(const void* ctx, cudaStream_t s);
+    void (*pre)(const void* ctx, int n_threads, cudaStream_t s);
+    void (*plan)(const void* ctx, int n_vehicles, cudaStream_t s);
+    void (*execute)(const void* ctx, int n_vehicles, cudaStream_t s);
+    void (*remove)(const void* ctx, int n_lanes, cudaStream_t s);
+    void (*integrate)(const void* ctx, int n_lanes, cudaStream_t s);
+    void (*insert)(const void* ctx, int n_lanes, cudaStream_t s);
+    void (*count)(const void* ctx, int n_vehicles, unsigned long long* updates, cudaStream_t s);
+    void (*mirror)(const void* ctx, int n_vehicles, sumob200_vehicle_state* out, cudaStream_t s);
+    void (*fcd)(const void* ctx, int n_vehicles, int32_t* block_counts /* [blocks + 1] */, sumob200_fcd_row* rows, cudaStream_t s);   // 3 launches
+};
+
+extern "C" const sb2_kernelset* sb2_kernelset_full(void);
+extern "C" const sb2_kernelset* sb2_kernelset_krauss(void);

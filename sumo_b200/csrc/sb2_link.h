@@ -156,7 +156,7 @@ SB2_HD bool link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTim
 }
 
 // MSLink.cpp:837-1022
-SB2_HD bool link_opened(const Ctx& c, int k, int buf, SUMOTime arrivalTime, double arrivalSpeed, double leaveSpeed, double vehicleLength,
+SB2_RARE bool link_opened(const Ctx& c, int k, int buf, SUMOTime arrivalTime, double arrivalSpeed, double leaveSpeed, double vehicleLength,
                         double impatience, double decel, SUMOTime waitingTime, bool ignoreRed, int ego, bool regSpeed = false) {
     const uint8_t state = c.link_state[k];
     if (state_red(state) && !ignoreRed) {

@@ -32,10 +32,18 @@
 #else
 #define SB2_CORE __host__ __device__ __noinline__
 #endif
+/* rarely executed, register-hungry blocks (right-of-way check against the approach tables): out of line, so that their
+ * register demand does not set the allocation of the whole kernel; they get the Ctx by reference (generic loads) */
+#if !defined(SB2_RARE_CALL)
+#define SB2_RARE __host__ __device__ __forceinline__
+#else
+#define SB2_RARE __host__ __device__ __noinline__
+#endif
 #else
 #define SB2_HD inline
 #define SB2_HDN inline
 #define SB2_CORE inline
+#define SB2_RARE inline
 #endif
 
 namespace sb2 {
@@ -79,6 +87,11 @@ enum {
 };
 // car-following model ids = SUMO_TAG_CF_* values are remapped at load time
 enum { CF_KRAUSS = 0, CF_KRAUSS_ORIG1 = 1, CF_IDM = 2 };
+
+// DepartSpeedDefinition / DepartPosDefinition values (utils/vehicle/SUMOVehicleParameter.h)
+enum { DSD_DEFAULT = 0, DSD_GIVEN = 1, DSD_GIVEN_VEHROUTE = 2, DSD_RANDOM = 3, DSD_MAX = 4, DSD_DESIRED = 5, DSD_LIMIT = 6, DSD_LAST = 7, DSD_AVG = 8 };
+enum { DPD_DEFAULT = 0, DPD_GIVEN = 1, DPD_GIVEN_VEHROUTE = 2, DPD_RANDOM = 3, DPD_FREE = 4, DPD_BASE = 5, DPD_LAST = 6, DPD_RANDOM_FREE = 7 };
+enum { DLD_DEFAULT = 0, DLD_GIVEN = 1, DLD_FIRST_ALLOWED = 7 };
 
 struct Ctx {
     // ---- options (MSGlobals) -------------------------------------------------------------

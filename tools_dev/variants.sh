@@ -1,10 +1,14 @@
 #!/bin/bash
 # dev helper: build tuning variants of the engine into /root/repo/build_variants/ (travels to the GPU box)
-# usage: variants.sh name:"-Dflags" ...
+# usage: variants.sh name:"-Dflag -Dflag" ...
 cd /root/repo; mkdir -p build_variants
-F="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -prec-div=true -prec-sqrt=true -Xcompiler -fPIC,-ffp-contract=off -shared"
 for v in "$@"; do
   n=${v%%:*}; x=${v#*:}
-  nvcc $F $x -o build_variants/lib_$n.so sumo_b200/csrc/engine.cu 2>/dev/null &
+  python - "$n" $x <<'PY'
+import sys
+sys.path.insert(0, "/root/repo")
+from sumo_b200 import build
+print(build.build(force=True, extra_flags=sys.argv[2:], out="/root/repo/build_variants/lib_%s.so" % sys.argv[1]))
+PY
 done
-wait; ls build_variants
+ls build_variants
