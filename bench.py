@@ -30,6 +30,7 @@ SPINUP_STEPS = 420          # all departures happen in [0, 300 + 16) s; afterwar
 # algorithmic bytes per vehicle-update (SURVEY.md section 8d / DESIGN.md "roofline"): whole step, and the plan kernel alone
 BYTES_PER_UPDATE_STEP = 576
 BYTES_PER_UPDATE_PLAN = 320
+NCU_PLAN_TRAFFIC_BYTES = 2218052000 + 1312588000   # k_plan, ncu --set full, round 1 (profiles/r01_k_plan_ncu.txt)
 
 
 def measured_peak_gbs():
@@ -85,21 +86,35 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def reference_ups(total_steps, cores_note=True):
-    """the reference's own CPU implementation (oracle/_ref/sumo, unmodified sources) on ONE district"""
+def reference_ups(total_steps, procs=None, repeats=3):
+    """the reference's own CPU implementation (oracle/_ref/sumo, unmodified sources).  `sumo --threads` needs the FOX toolkit
+    (src/microsim/MSFrame.cpp:1119-1124), which is absent, so one sumo process is single-threaded; the workload is made of
+    independent districts, so all host cores are used the way the workload allows: `procs` concurrent sumo processes, one
+    district each (the same district file), `repeats` rounds.  Aggregate = sum of the processes' own UPS (vehicle updates /
+    their simulation wall time, MSNet.cpp:959) while they run side by side."""
     exe = os.path.join(ROOT, "oracle", "_ref", "sumo")
     if not os.path.exists(exe):
         return None
+    procs = procs or max(1, os.cpu_count() or 1)
     cmd = [exe, "-n", BASE + ".net.xml", "-r", BASE + ".rou.xml", "--no-step-log", "--no-warnings", "--time-to-teleport", "-1",
            "--default.departspeed", "0", "--default.departlane", "first", "--end", str(total_steps), "--duration-log.statistics"]
+    ups_rounds, dur = [], []
     t0 = time.time()
-    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True).stdout
+    for _ in range(repeats):
+        ps = [subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for _ in range(procs)]
+        total = 0.0
+        for p in ps:
+            out = p.communicate()[0]
+            m = re.search(r"UPS: ([0-9.]+)", out)
+            d = re.search(r"Duration: ([0-9.]+)s", out)
+            if not m:
+                return None
+            total += float(m.group(1))
+            dur.append(float(d.group(1)) if d else 0.0)
+        ups_rounds.append(total)
     wall = time.time() - t0
-    m = re.search(r"UPS: ([0-9.]+)", out)
-    d = re.search(r"Duration: ([0-9.]+)s", out)
-    if not m:
-        return None
-    return {"ups": float(m.group(1)), "duration_s": float(d.group(1)) if d else wall, "wall_s": wall, "steps": total_steps}
+    return {"ups": float(np.mean(ups_rounds)), "ups_per_process": float(np.mean(ups_rounds)) / procs, "duration_s": float(np.mean(dur)),
+            "wall_s": wall, "steps": total_steps, "procs": procs, "repeats": repeats}
 
 
 def run_reference(args):
@@ -111,14 +126,15 @@ def run_reference(args):
     if r is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/sumo not built"}))
         return 0
-    sample = "1 district (10x10 TLS grid, %d vehicles) x %d steps, single thread (--threads needs FOX, absent)" % (VEH_PER_TILE, total)
+    sample = ("%d concurrent sumo processes (one per host core; --threads needs FOX, absent), each 1 district (10x10 TLS grid, %d vehicles) x %d steps, "
+              "%d rounds, %.1f s wall; %.0f veh*steps/s per process" % (r["procs"], VEH_PER_TILE, total, r["repeats"], r["wall_s"], r["ups_per_process"]))
     line = {
         "impl": "reference", "metric": "vehicle-updates/s", "value": r["ups"], "unit": "veh*steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * r["duration_s"] / total, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "netgenerate 10x10 grid, 200 m, static traffic lights, Krauss sigma=%.1f, step-length 1 s; reference sumo on one district" % args.sigma,
-                   "vehicles": VEH_PER_TILE},
-        "cpu_baseline": {"value": r["ups"], "unit": "veh*steps/s", "cores": 1, "kind": "reference", "sample": sample},
+        "config": {"workload": "netgenerate 10x10 grid, 200 m, static traffic lights, Krauss sigma=%.1f, step-length 1 s; reference sumo, one district per process" % args.sigma,
+                   "vehicles": VEH_PER_TILE, "processes": r["procs"]},
+        "cpu_baseline": {"value": r["ups"], "unit": "veh*steps/s", "cores": r["procs"], "kind": "reference", "sample": sample},
         "e2e": {"value": r["ups"], "unit": "veh*steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -239,7 +255,8 @@ def main():
                         "the scenario is uploaded once at create, a step has no host input"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_plan", "achieved": plan_gbs, "peak": peak, "unit": "GB/s", "frac": plan_gbs / peak,
-                     "traffic": None, "peak_source": peak_src, "bytes_per_update": BYTES_PER_UPDATE_PLAN, "kernel_ms": plan_ms,
+                     "traffic": NCU_PLAN_TRAFFIC_BYTES if nV == 1000800 else None, "traffic_source": "profiles/r01_k_plan_ncu.txt (dram__bytes_read.sum + dram__bytes_write.sum, one launch, 1,000,800 vehicles)",
+                     "peak_source": peak_src, "bytes_per_update": BYTES_PER_UPDATE_PLAN, "kernel_ms": plan_ms,
                      "phase_ms_per_step": {k: v / 20.0 for k, v in phases.items()},
                      "whole_step": {"bytes_per_update": BYTES_PER_UPDATE_STEP, "achieved": BYTES_PER_UPDATE_STEP * value / 1e9,
                                     "frac": BYTES_PER_UPDATE_STEP * value / 1e9 / (peak * world)}},
@@ -248,9 +265,10 @@ def main():
         total = SPINUP_STEPS + 280
         cb = reference_ups(total)
         if cb is not None:
-            line["cpu_baseline"] = {"value": cb["ups"], "unit": "veh*steps/s", "cores": 1, "kind": "reference",
-                                    "sample": "oracle/_ref/sumo (unmodified reference) on 1 district (%d vehicles) x %d steps, %.1f s, single thread "
-                                              "(--threads needs the FOX toolkit, absent)" % (VEH_PER_TILE, total, cb["duration_s"])}
+            line["cpu_baseline"] = {"value": cb["ups"], "unit": "veh*steps/s", "cores": cb["procs"], "kind": "reference",
+                                    "sample": "oracle/_ref/sumo (unmodified reference; single-threaded: --threads needs the FOX toolkit, absent): %d concurrent "
+                                              "processes, one per host core, each 1 district (%d vehicles) x %d steps, %d rounds, %.1f s wall; %.0f veh*steps/s per process"
+                                              % (cb["procs"], VEH_PER_TILE, total, cb["repeats"], cb["wall_s"], cb["ups_per_process"])}
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
