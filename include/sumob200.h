@@ -63,7 +63,7 @@ typedef struct sumob200_step_result {
     int32_t emergency_stops;  /* emergency stops at lane ends so far */
     int32_t teleports;        /* teleport conditions detected so far (not executed) */
     int32_t flags;            /* OR of SUMOB200_F_* raised so far */
-    int32_t reserved;
+    int32_t halting;          /* on-road vehicles slower than 0.1 m/s     (MSVehicleControl::getHaltingVehicleNo, summary output) */
     int64_t vehicle_updates;  /* sum over the executed steps of vehicles on the road (numerator of SUMO's UPS, MSNet.cpp:959) */
 } sumob200_step_result;
 

@@ -260,7 +260,7 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     }
     CUDA_TRY(cudaGetLastError());
     if (out != nullptr) {
-        int32_t counters[8];
+        int32_t counters[16];
         int32_t flags = 0;
         unsigned long long updates = 0;
         CUDA_TRY(cudaMemcpyAsync(counters, c.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
@@ -275,7 +275,7 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         out->emergency_stops = counters[5];
         out->teleports = counters[6];
         out->flags = flags;
-        out->reserved = 0;
+        out->halting = counters[8];
         out->vehicle_updates = (int64_t)updates;
     }
     return 0;

@@ -374,10 +374,10 @@ public:
             }
             SB2_DYN(double, veh_em, anyDevice ? (size_t)nV * 7 : 1, 0.);
         }
-        SB2_DYN(int32_t, veh_order, nV, -1);
         const size_t nDI = (size_t)nV * MAX_DRIVE_ITEMS;
         for (int b = 0; b < 2; b++) {
             SB2_DYN2(int32_t, veh_ndi, b, nV, 0);
+            SB2_DYN2(int32_t, veh_order, b, nV, -1);
             SB2_DYN2(int32_t, di_link, b, nDI, -1); SB2_DYN2(uint8_t, di_request, b, nDI, (uint8_t)0); SB2_DYN2(uint8_t, di_hadstopped, b, nDI, (uint8_t)0);
             SB2_DYN2(double, di_vpass, b, nDI, 0.); SB2_DYN2(double, di_vwait, b, nDI, 0.); SB2_DYN2(double, di_arrspeed, b, nDI, 0.);
             SB2_DYN2(double, di_arrspeedbraking, b, nDI, 0.); SB2_DYN2(double, di_dist, b, nDI, 0.); SB2_DYN2(double, di_accelv, b, nDI, 0.);
@@ -395,7 +395,7 @@ public:
             f[2] = g[2] = ff.scalar<double>("opt_max_mingap", 0.);
         }
         SB2_DYN(int32_t, err_flags, 1, 0);
-        SB2_DYN(int32_t, counters, 8, 0);
+        SB2_DYN(int32_t, counters, 16, 0);
     }
 };
 

@@ -25,16 +25,16 @@ struct ExecScratch {
 };
 
 // MSVehicle::processLinkApproaches
-SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, const CF& cf, double speed, double pos, int myLane, SUMOTime waiting,
+SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf, double speed, double pos, int myLane, SUMOTime waiting,
                                       double& vSafe, double& vSafeMin, double& vSafeMinDist, bool& haveToWait,
                                       SUMOTime& jentry, SUMOTime& jconflict) {
     const int cur = c.cur;
     haveToWait = false;
     bool canBrakeVSafeMin = false;
-    const int n = c.veh_ndi[cur][v];
+    const int n = c.veh_ndi[cur][wp];
     const double vehLength = cf.length;
     for (int i = 0; i < n; i++) {
-        const size_t r = (size_t)i * c.nV + v;
+        const size_t r = (size_t)i * c.nV + wp;
         const int link = c.di_link[cur][r];
         const bool setRequest = c.di_request[cur][r] != 0;
         const double dpiDist = c.di_dist[cur][r];
@@ -162,7 +162,7 @@ SB2_HD double veh_random(const Ctx& c, int v) {
 }
 
 // MSVehicle::executeMove; `random` = RandHelper::rand(getRNG()) for the dawdle step
-SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
+SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     int myLane = c.veh_lane[v];
     c.veh_moved[v] = 0;
     if (myLane < 0) {
@@ -181,7 +181,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
     double vSafeMin = -SB2_DBL_MAX;
     double vSafeMinDist = 0;
     bool haveToWait = false;
-    veh_processLinkApproaches(c, v, cf, oldSpeed, pos, myLane, waiting, vSafe, vSafeMin, vSafeMinDist, haveToWait, jentry, jconflict);
+    veh_processLinkApproaches(c, v, wp, cf, oldSpeed, pos, myLane, waiting, vSafe, vSafeMin, vSafeMinDist, haveToWait, jentry, jconflict);
 
     double vNext = vSafe;
     const double rawAccel = (MAX2(vNext, 0.) - oldSpeed) / c.TS;
@@ -236,9 +236,9 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, double random) {
         if (routePos != routeLen - 1) {
             int approachedLane = myLane;
             int item = 0;
-            const int n = c.veh_ndi[cur][v];
+            const int n = c.veh_ndi[cur][wp];
             while (item < n && approachedLane >= 0 && pos > c.lane_length[approachedLane]) {
-                const size_t r = (size_t)item * c.nV + v;
+                const size_t r = (size_t)item * c.nV + wp;
                 const int link = c.di_link[cur][r];
                 ++item;
                 if (link >= 0) {

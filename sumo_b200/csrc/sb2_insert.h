@@ -364,7 +364,6 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     c.veh_jentry[v] = SB2_TIME_MAX; c.veh_jentry_ny[v] = SB2_TIME_MAX; c.veh_jconflict[v] = SB2_TIME_MAX;
     c.veh_havetowait[v] = 0;
     c.veh_nfurther[v] = 0;
-    c.veh_ndi[0][v] = 0; c.veh_ndi[1][v] = 0;
     c.veh_depart_time[v] = c.t;
     c.veh_odometer[v] = 0;
     c.veh_timeloss[v] = 0;

@@ -17,12 +17,13 @@ namespace sb2 {
 
 // before planMove: cumulated lengths in front of every vehicle, space till last standing vehicle
 // orderBase = first slot of this lane in the lane-ordered work list veh_order
-SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase) {
+SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1) {
     // front -> back (MSLane.cpp:1608-1623)
     double cum = 0.;
     for (int v = c.lane_first[l]; v >= 0; v = c.veh_behind[v]) {
         c.veh_len_in_front[v] = cum;
-        c.veh_order[orderBase++] = v;
+        c.veh_order[c.cur][orderBase] = v;
+        orderBase += orderStep;
         cum += veh_length_with_gap(c, v);
     }
     // back -> front (MSLane.cpp:4734-4754); `last != ego` never excludes anything for the lanes ahead of ego

@@ -127,7 +127,8 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
 
 // MSVehicle::planMove + planMoveInternal for vehicle v at time t; writes the drive items of buffer c.cur and registers
 // them in the approach table of buffer c.cur (MSVehicle::setApproachingForAllLinks).
-SB2_HDN void veh_planMove(const Ctx& c, int v) {
+// wp = position of v in this step's work list (addresses its drive-item records)
+SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     const int myLane = c.veh_lane[v];
     if (myLane < 0) {
         return;
@@ -322,9 +323,9 @@ SB2_HDN void veh_planMove(const Ctx& c, int v) {
     veh_checkRewindLinkLanes(c, e, c.veh_len_in_front[v], lf, n, prev);
 
     // store items + register approaches (MSVehicle::setApproachingForAllLinks -> MSLink::setApproaching, MSLink.cpp:718-736)
-    c.veh_ndi[cur][v] = n;
+    c.veh_ndi[cur][wp] = n;
     for (int i = 0; i < n; i++) {
-        const size_t r = (size_t)i * c.nV + v;
+        const size_t r = (size_t)i * c.nV + wp;
         const DriveItem& d = lf[i];
         c.di_link[cur][r] = d.link;
         c.di_vpass[cur][r] = d.vPass;

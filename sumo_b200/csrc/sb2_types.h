@@ -181,8 +181,12 @@ struct Ctx {
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
     // neighbouring lanes, see the same links and foes and take the same branches.  counters[7] = its length.
-    int32_t* veh_order;
-    // drive items, double buffered [2][MAX_DRIVE_ITEMS*nV], item-major (item i of vehicle v at i*nV+v)
+    // Double buffered like the drive items (index c.cur): a drive-item record of step t is addressed by the vehicle's
+    // POSITION wp in that step's work list (record = item * nV + wp), so the plan kernel writes and the execute kernel reads the
+    // records fully coalesced; veh_order[buf][wp] gives the vehicle back (approach tables of the previous step use buf = cur ^ 1).
+    int32_t* veh_order[2];
+    // drive items, double buffered [2][MAX_DRIVE_ITEMS*nV], item-major (item i of the vehicle at work-list position wp at i*nV+wp);
+    // veh_ndi[buf][wp] likewise
     int32_t* veh_ndi[2];
     int32_t* di_link[2]; uint8_t* di_request[2]; uint8_t* di_hadstopped[2];
     double* di_vpass[2]; double* di_vwait[2]; double* di_arrspeed[2]; double* di_arrspeedbraking[2];
@@ -200,7 +204,7 @@ struct Ctx {
     int rng_mode; uint64_t rng_seed; const double* rng_replay;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
-    int32_t* counters;         // [8]: 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports
+    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports
 };
 
 SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }

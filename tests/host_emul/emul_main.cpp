@@ -28,8 +28,17 @@ static int gDebugVeh = -1;
 static void dumpItems(const Model& m, int v, const char* tag) {
     const Ctx& c = m.h;
     const int cur = c.cur;
+    int wp = -1;
+    for (int i = 0; i < c.counters[7]; i++) {
+        if (c.veh_order[cur][i] == v) {
+            wp = i;
+        }
+    }
+    if (wp < 0) {
+        return;
+    }
     fprintf(stderr, "%s t=%lld veh=%s lane=%s pos=%.6f speed=%.6f wait=%lld ndi=%d htw=%d\n", tag, (long long)c.t, m.veh_names[v].c_str(),
-            c.veh_lane[v] >= 0 ? m.lane_names[c.veh_lane[v]].c_str() : "-", c.veh_pos[v], c.veh_speed[v], (long long)c.veh_waiting[v], c.veh_ndi[cur][v], c.veh_havetowait[v]);
+            c.veh_lane[v] >= 0 ? m.lane_names[c.veh_lane[v]].c_str() : "-", c.veh_pos[v], c.veh_speed[v], (long long)c.veh_waiting[v], c.veh_ndi[cur][wp], c.veh_havetowait[v]);
     if (c.veh_lane[v] >= 0) {
         fprintf(stderr, "   queue(front->back):");
         for (int x = c.lane_first[c.veh_lane[v]]; x >= 0; x = c.veh_behind[x]) {
@@ -37,8 +46,8 @@ static void dumpItems(const Model& m, int v, const char* tag) {
         }
         fprintf(stderr, " | lenInFront=%.2f brutto=%.2f npartial=%d\n", c.veh_len_in_front[v], c.lane_brutto[c.veh_lane[v]], c.lane_npartial[c.veh_lane[v]]);
     }
-    for (int i = 0; i < c.veh_ndi[cur][v]; i++) {
-        const size_t r = (size_t)i * c.nV + v;
+    for (int i = 0; i < c.veh_ndi[cur][wp]; i++) {
+        const size_t r = (size_t)i * c.nV + wp;
         const int k = c.di_link[cur][r];
         fprintf(stderr, "   item %d link=%d(%s->%s state=%c) vPass=%.6f vWait=%.6f req=%d arrT=%lld arrV=%.4f arrVB=%.4f dist=%.4f accelV=%.4f avail=%.4f hadStopped=%d\n", i, k,
                 k >= 0 ? m.lane_names[c.link_from[k]].c_str() : "-", k >= 0 ? m.lane_names[c.link_via[k] >= 0 ? c.link_via[k] : c.link_to[k]].c_str() : "-",
@@ -52,24 +61,25 @@ static void step(Model& m) {
     for (int tl = 0; tl < c.nTL; tl++) {
         tls_advance(c, tl);
     }
+    c.cur ^= 1;   // the work list and the drive items of this step go to buffer c.cur
     int nOrder = 0;
     for (int l = 0; l < c.nL; l++) {
         lane_summary(c, l, nOrder);
         nOrder += c.lane_nveh[l];
     }
     c.counters[7] = nOrder;
-    c.cur ^= 1;
+    c.counters[3] = 0;
     std::fill(c.link_app_head[c.cur], c.link_app_head[c.cur] + c.nK, -1);
     for (int i = 0; i < nOrder; i++) {
-        veh_planMove(c, c.veh_order[i]);
+        veh_planMove(c, c.veh_order[c.cur][i], i);
     }
     if (gDebugVeh >= 0 && c.veh_lane[gDebugVeh] >= 0) {
         dumpItems(m, gDebugVeh, "plan");
     }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
     for (int i = 0; i < nOrder; i++) {
-        const int v = c.veh_order[i];
-        veh_executeMove(c, v, veh_random(c, v));
+        const int v = c.veh_order[c.cur][i];
+        veh_executeMove(c, v, i, veh_random(c, v));
         veh_register_partials(c, v);
     }
     for (int l = 0; l < c.nL; l++) {

@@ -26,6 +26,7 @@ def test_engine_matches_reference(case):
             on = st["lane"] >= 0
             assert r.flags == 0, "t=%d: engine raised flags 0x%x" % (t, r.flags)
             assert r.running == int(on.sum()) == len(ids), "t=%d: running vehicles differ" % t
+            assert r.halting == int((speed < 0.1).sum()), "t=%d: halting vehicles (summary output) differ" % t
             assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
             assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
             assert np.array_equal(st["pos"][on].view(np.int64), pos.view(np.int64)), "t=%d: positions differ (bitwise)" % t
