@@ -20,7 +20,11 @@ namespace sb2 {
 SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1) {
     // front -> back (MSLane.cpp:1608-1623)
     double cum = 0.;
+    int guard = 0;
     for (int v = c.lane_first[l]; v >= 0; v = c.veh_behind[v]) {
+        (void)SB2_CHK(v, 0, c.nV, 11);
+        (void)SB2_CHK(orderBase, 0, c.nV, 12);
+        (void)SB2_CHK(guard++, 0, c.lane_nveh[l], 13);
         c.veh_len_in_front[v] = cum;
         c.veh_order[c.cur][orderBase] = v;
         orderBase += orderStep;

@@ -138,7 +138,7 @@ SB2_HD bool link_blockedByFoe(const Ctx& c, int k, int buf, int r, int foe,
 SB2_HD bool link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime, SUMOTime leaveTime, double arrivalSpeed, double leaveSpeed,
                                bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, bool regSpeed = false) {
     for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        const int foe = c.veh_order[buf][r % c.nV];
+        const int foe = SB2_CHK(c.veh_order[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8) % c.nV], 0, c.nV, 9);
 #if defined(SB2_DEBUG_LINK) && !defined(__CUDA_ARCH__)
         if (ego == SB2_DEBUG_LINK_EGO) {
             fprintf(stderr, "   blockedAtTime link %d foe %d onroad=%d req=%d aviArr=%lld aviLeave=%lld arr=%lld leave=%lld blocked=%d\n", k, foe, (int)veh_on_road(c, foe),

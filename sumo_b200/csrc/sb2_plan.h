@@ -289,6 +289,7 @@ SB2_HD void veh_checkLinkLeader(const Ctx& c, const Ego& e, int link, int lane, 
             }
             AnyVehIter it = any_begin(c, foeLane);
             for (int leader = any_next(c, foeLane, it); leader >= 0; leader = any_next(c, foeLane, it)) {
+                (void)SB2_CHK(leader, 0, c.nV, 10);
                 const int lt = c.veh_type[leader];
                 const double leaderLen = c.vt_length[lt];
                 const double leaderBack = veh_back_pos_on_lane(c, leader, foeLane) - 0 /*extraGap*/;

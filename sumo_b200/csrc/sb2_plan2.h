@@ -129,7 +129,8 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
 // them in the approach table of buffer c.cur (MSVehicle::setApproachingForAllLinks).
 // wp = position of v in this step's work list (addresses its drive-item records)
 SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
-    const int myLane = c.veh_lane[v];
+    (void)SB2_CHK(v, 0, c.nV, 2);
+    const int myLane = SB2_CHK(c.veh_lane[v], -2, c.nL, 3);
     if (myLane < 0) {
         return;
     }
@@ -155,7 +156,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     // leader on the own lane (MSLane::planMovements / updateLeaderInfo, MSLane.cpp:1608-1685)
     int ahead = c.veh_ahead[v];
     if (ahead < 0 && c.lane_npartial[myLane] > 0) {
-        ahead = c.lane_partial[(size_t)myLane * MAX_PARTIAL];
+        ahead = SB2_CHK(c.lane_partial[(size_t)myLane * MAX_PARTIAL], 0, c.nV, 1);
     }
 
     const double vehicleLength = e.length;
@@ -310,7 +311,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
             seenNonInternal += c.lane_length[lane];
         }
         leaderLane = lane;
-        ahead = lane_last_any(c, leaderLane);   // getLastVehicleInformation(nullptr, 0)
+        ahead = SB2_CHK(lane_last_any(c, SB2_CHK(leaderLane, 0, c.nL, 4)), -1, c.nV, 5);   // getLastVehicleInformation(nullptr, 0)
         seen += c.lane_length[lane];
         vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, c.lane_length[lane], vv, cf.accel), laneMaxV);
         lastLink = &lf[n - 1];

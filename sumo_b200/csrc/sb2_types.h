@@ -271,6 +271,21 @@ SB2_HD void atomic_min_double(double* p, double v) {
 #endif
 }
 
+// -DSB2_CHECK: debug build that validates indices taken from dynamic tables before they are used (dev stress runs only)
+#if defined(SB2_CHECK)
+SB2_HD int sb2_chk(const Ctx& c, long long x, long long lo, long long hi, int site) {
+    if (x < lo || x >= hi) {
+        printf("SB2_CHECK site %d: %lld not in [%lld, %lld) t=%lld\n", site, x, lo, hi, (long long)c.t);
+        raise(c, 1 << 30);
+        return (int)lo < 0 ? -1 : 0;
+    }
+    return (int)x;
+}
+#define SB2_CHK(x, lo, hi, site) sb2_chk(c, (x), (lo), (hi), (site))
+#else
+#define SB2_CHK(x, lo, hi, site) (x)
+#endif
+
 SB2_HD bool lane_internal(const Ctx& c, int l) { return (c.lane_flags[l] & LF_INTERNAL) != 0; }
 SB2_HD bool state_priority(uint8_t s) { return s >= 'A' && s <= 'Z'; }               // MSLink.h:473
 SB2_HD bool state_red(uint8_t s) { return s == 'r' || s == 'u'; }                     // MSLink.h:484

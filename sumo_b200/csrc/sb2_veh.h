@@ -38,6 +38,7 @@ SB2_HD int veh_succ_edge(const Ctx& c, int v, int n) {
 
 // MSVehicle::getBackPositionOnLane(lane) for the cases of the non-sublane, non-opposite model
 SB2_HD double veh_back_pos_on_lane(const Ctx& c, int v, int lane) {
+    (void)SB2_CHK(v, 0, c.nV, 6);
     const double len = veh_length(c, v);
     if (lane == c.veh_lane[v]) {
         return c.veh_pos[v] - len;
@@ -49,7 +50,7 @@ SB2_HD double veh_back_pos_on_lane(const Ctx& c, int v, int lane) {
     }
     double leftLength = len - c.veh_pos[v];
     for (int i = 0; i < nf && leftLength > 0; i++) {
-        leftLength -= c.lane_length[f[i]];
+        leftLength -= c.lane_length[SB2_CHK(f[i], 0, c.nL, 7)];
         if (f[i] == lane) {
             return -leftLength;
         }
