@@ -107,6 +107,21 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
 int sumob200_fcd_begin(sumob200_engine* e);
 int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n);
 
+/* per-trip record of one vehicle slot: the fields MSDevice_Tripinfo::generateOutput writes
+ * (src/microsim/devices/MSDevice_Tripinfo.cpp:313-410); times in ms like SUMOTime */
+typedef struct sumob200_tripinfo {
+    int64_t depart_ms;        /* MSBaseVehicle::getDeparture; -1 = not departed yet */
+    int64_t depart_delay_ms;  /* getDepartDelay = departure - depart attribute */
+    int64_t arrival_ms;       /* myArrivalTime; -1 = not arrived */
+    int64_t duration_ms;      /* arrival (or current time) - departure */
+    int64_t waiting_ms;       /* myWaitingTime */
+    int64_t time_loss_ms;     /* MSVehicle::getTimeLoss = TIME2STEPS(myTimeLoss) */
+    int32_t depart_lane, arrival_lane, waiting_count, reserved;
+    double depart_pos, depart_speed, arrival_pos, arrival_speed, route_length, speed_factor;
+} sumob200_tripinfo;
+/* trip records of all vehicle slots (n = sumob200_num_vehicles) */
+int sumob200_tripinfo_all(sumob200_engine* e, sumob200_tripinfo* out, int capacity);
+
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],
  * p = 0 CO2, 1 CO, 2 HC, 3 fuel, 4 NOx, 5 PMx, 6 electricity [mg resp. ml resp. Wh], n = sumob200_num_vehicles.

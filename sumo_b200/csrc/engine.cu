@@ -323,6 +323,29 @@ int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int cap
     return 0;
 }
 
+int sumob200_tripinfo_all(sumob200_engine* e, sumob200_tripinfo* out, int capacity) {
+    if (e == nullptr || out == nullptr || capacity < e->d.nV) {
+        gLastError = "sumob200_tripinfo_all: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int nV = e->d.nV;
+    sumob200_tripinfo* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, sizeof(sumob200_tripinfo) * (size_t)(nV > 0 ? nV : 1)));
+    e->ks->tripinfo(&e->d, nV, d, e->stream);
+    e->launches += 1;
+    cudaError_t err = cudaMemcpyAsync(out, d, sizeof(sumob200_tripinfo) * (size_t)nV, cudaMemcpyDeviceToHost, e->stream);
+    if (err == cudaSuccess) {
+        err = cudaStreamSynchronize(e->stream);
+    }
+    cudaFree(d);
+    if (err != cudaSuccess) {
+        gLastError = std::string("sumob200_tripinfo_all: ") + cudaGetErrorString(err);
+        return SUMOB200_ECUDA;
+    }
+    return 0;
+}
+
 int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity) {
     if (e == nullptr || out == nullptr || capacity < (int64_t)7 * e->d.nV) {
         gLastError = "sumob200_emissions: bad argument / capacity too small";

@@ -259,6 +259,32 @@ __global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx
     }
 }
 
+__global__ void __launch_bounds__(BLOCK) k_tripinfo(const __grid_constant__ Ctx c, sumob200_tripinfo* out) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV) {
+        sumob200_tripinfo r;
+        const int lane = c.veh_lane[v];
+        const bool departed = lane != -1, arrived = lane == -2;
+        r.depart_ms = departed ? c.veh_depart_time[v] : -1;
+        r.depart_delay_ms = departed ? c.veh_depart_time[v] - c.veh_depart_param[v] : c.t - c.veh_depart_param[v];
+        r.arrival_ms = arrived ? c.veh_arrival_time[v] : -1;
+        r.duration_ms = departed ? (arrived ? c.veh_arrival_time[v] : c.t) - c.veh_depart_time[v] : 0;
+        r.waiting_ms = c.veh_trip_wait[v];
+        r.time_loss_ms = departed ? TIME2STEPS(c.veh_timeloss[v]) : 0;
+        r.depart_lane = c.veh_departlane[v];
+        r.arrival_lane = c.veh_arrival_lane[v];
+        r.waiting_count = c.veh_trip_waitcount[v];
+        r.reserved = 0;
+        r.depart_pos = c.veh_trip_departpos[v];
+        r.depart_speed = c.veh_trip_departspeed[v];
+        r.arrival_pos = c.veh_arrivalpos[v];
+        r.arrival_speed = c.veh_speed[v];
+        r.route_length = c.veh_trip_routelen[v] + (arrived ? c.veh_arrivalpos[v] : (departed ? c.veh_pos[v] : 0.));
+        r.speed_factor = c.veh_speedfactor[v];
+        out[v] = r;
+    }
+}
+
 __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
@@ -284,6 +310,7 @@ void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), 
 void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<grid(n), BLOCK, 0, s>>>(ctx(c), updates); }
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
+void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaStream_t s) {
     const int nb = grid(n);
     k_fcd_count<<<nb, BLOCK, 0, s>>>(ctx(c), blocks);
@@ -291,7 +318,7 @@ void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaSt
     k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo};
 
 }  // namespace sb2_kset_<name>
 

@@ -266,6 +266,7 @@ public:
             // depart time = MSVehicleContainer bucket (rounded up to the step grid, MSVehicleContainer.cpp:80-81)
             const int64_t* d = ff.ptr<int64_t>("veh_depart");
             int64_t* o = add<int64_t>("veh_depart", SB2_OFF(veh_depart), nV, false, (int64_t)0);
+            SB2_COPY2(SUMOTime, veh_depart_param, "veh_depart");
             for (int v = 0; v < nV; v++) {
                 const int64_t delay = d[v] % h.DELTA_T;
                 o[v] = d[v] + (delay == 0 ? 0 : h.DELTA_T - delay);
@@ -355,6 +356,9 @@ public:
         SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
         SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
         SB2_DYN(double, veh_len_in_front, nV, 0.);
+        SB2_DYN(SUMOTime, veh_trip_wait, nV, 0); SB2_DYN(int32_t, veh_trip_waitcount, nV, 0); SB2_DYN(uint8_t, veh_trip_amwaiting, nV, 0);
+        SB2_DYN(double, veh_trip_routelen, nV, 0.); SB2_DYN(double, veh_trip_departpos, nV, 0.); SB2_DYN(double, veh_trip_departspeed, nV, 0.);
+        SB2_DYN(SUMOTime, veh_arrival_time, nV, -1); SB2_DYN(int32_t, veh_arrival_lane, nV, -1);
         {
             // emission device: per-vehicle flag + 7 accumulators; a vehicle with the device needs a supported (HBEFA3/HBEFA4) model
             bool anyDevice = false;

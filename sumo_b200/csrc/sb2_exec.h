@@ -230,6 +230,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     const int routeLen = veh_route_len(c, v);
     const int oldLane = myLane;
     double odometer = c.veh_odometer[v];
+    double tripRouteLen = c.veh_trip_routelen[v];
     bool arrived = false;
     bool emergency = false;
     if (pos > c.lane_length[myLane]) {
@@ -256,7 +257,8 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
                     break;
                 }
                 if (approachedLane != myLane && approachedLane >= 0) {
-                    // leaveLane(NOTIFICATION_JUNCTION)
+                    // leaveLane(NOTIFICATION_JUNCTION); MSDevice_Tripinfo::notifyLeave adds the length of the lane that is left
+                    tripRouteLen += c.lane_length[myLane];
                     odometer += c.lane_length[myLane];
                     pos -= c.lane_length[myLane];
                     // enterLaneAtMove
@@ -346,9 +348,22 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     c.veh_havetowait[v] = haveToWait;
     c.veh_routepos[v] = routePos;
     c.veh_odometer[v] = odometer;
+    c.veh_trip_routelen[v] = tripRouteLen;
+    // MSDevice_Tripinfo::notifyMove (not stopped): waiting = slow and not accelerating (accelThresholdForWaiting, MSVehicle.h:2100)
+    if (speed <= SB2_HALTING_SPEED && accelOut <= 0.5 * cf.accel) {
+        c.veh_trip_wait[v] += c.DELTA_T;
+        if (!c.veh_trip_amwaiting[v]) {
+            c.veh_trip_waitcount[v] += 1;
+            c.veh_trip_amwaiting[v] = 1;
+        }
+    } else {
+        c.veh_trip_amwaiting[v] = 0;
+    }
     veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
     if (arrived) {
         c.veh_moved[v] = 2;
+        c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
+        c.veh_arrival_lane[v] = myLane;
         c.veh_lane[v] = -2;
         atomic_inc(&c.counters[1]);
     } else if (myLane != oldLane) {

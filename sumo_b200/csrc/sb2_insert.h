@@ -365,6 +365,12 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     c.veh_havetowait[v] = 0;
     c.veh_nfurther[v] = 0;
     c.veh_depart_time[v] = c.t;
+    // MSDevice_Tripinfo::notifyEnter(NOTIFICATION_DEPARTED)
+    c.veh_trip_routelen[v] = -pos;
+    c.veh_trip_departpos[v] = pos;
+    c.veh_trip_departspeed[v] = speed;
+    c.veh_trip_wait[v] = 0; c.veh_trip_waitcount[v] = 0; c.veh_trip_amwaiting[v] = 0;
+    c.veh_arrival_time[v] = -1; c.veh_arrival_lane[v] = -1;
     c.veh_odometer[v] = 0;
     c.veh_timeloss[v] = 0;
     c.veh_stopspeed[v] = SB2_DBL_MAX;

@@ -19,6 +19,7 @@ struct sb2_kernelset {
     void (*count)(const void* ctx, int n_vehicles, unsigned long long* updates, cudaStream_t s);
     void (*mirror)(const void* ctx, int n_vehicles, sumob200_vehicle_state* out, cudaStream_t s);
     void (*fcd)(const void* ctx, int n_vehicles, int32_t* block_counts /* [blocks + 1] */, sumob200_fcd_row* rows, cudaStream_t s);   // 3 launches
+    void (*tripinfo)(const void* ctx, int n_vehicles, sumob200_tripinfo* out, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

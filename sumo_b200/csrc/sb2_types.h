@@ -157,7 +157,7 @@ struct Ctx {
     const int32_t* route_begin; const int32_t* route_edges;
     // ---- vehicles (static) ---------------------------------------------------------------
     const int32_t* veh_type; const int32_t* veh_route; const int32_t* veh_numid; const int32_t* veh_idrank;
-    const SUMOTime* veh_depart; const double* veh_speedfactor; const double* veh_arrivalpos;
+    const SUMOTime* veh_depart; const SUMOTime* veh_depart_param; /* as given (tripinfo departDelay) */ const double* veh_speedfactor; const double* veh_arrivalpos;
     const int32_t* veh_departlane;                   // resolved departure lane index
     const double* veh_departpos; const int32_t* veh_departpos_proc;
     const double* veh_departspeed; const int32_t* veh_departspeed_proc;
@@ -175,6 +175,10 @@ struct Ctx {
     int32_t* veh_ahead; int32_t* veh_behind;   // lane queue links (towards larger / smaller position)
     int32_t* veh_next_incoming;
     int32_t* veh_nfurther; int32_t* veh_further;     // [nV*MAX_FURTHER] lanes the back still covers, nearest first
+    // MSDevice_Tripinfo (src/microsim/devices/MSDevice_Tripinfo.cpp:182-310): myWaitingTime, myWaitingCount, myAmWaiting,
+    // myRouteLength (without the arrival position), myDepartPos/Speed, myArrivalTime (-1 = not arrived), arrival lane
+    SUMOTime* veh_trip_wait; int32_t* veh_trip_waitcount; uint8_t* veh_trip_amwaiting; double* veh_trip_routelen;
+    double* veh_trip_departpos; double* veh_trip_departspeed; SUMOTime* veh_arrival_time; int32_t* veh_arrival_lane;
     const uint8_t* veh_emissions;   // vehicle carries the emission device
     double* veh_em;            // [7*nV] MSDevice_Emissions::myEmissions, pollutant-major (CO2, CO, HC, fuel, NOx, PMx, electricity)
     double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)

@@ -38,6 +38,10 @@ class StepResult(ctypes.Structure):
 
 
 VEHICLE_STATE = np.dtype([("lane", np.int32), ("route_pos", np.int32), ("pos", np.float64), ("speed", np.float64)])
+TRIPINFO = np.dtype([("depart_ms", np.int64), ("depart_delay_ms", np.int64), ("arrival_ms", np.int64), ("duration_ms", np.int64),
+                     ("waiting_ms", np.int64), ("time_loss_ms", np.int64), ("depart_lane", np.int32), ("arrival_lane", np.int32),
+                     ("waiting_count", np.int32), ("reserved", np.int32), ("depart_pos", np.float64), ("depart_speed", np.float64),
+                     ("arrival_pos", np.float64), ("arrival_speed", np.float64), ("route_length", np.float64), ("speed_factor", np.float64)])
 FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
                     ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
 
@@ -66,6 +70,7 @@ def load_library(path=None):
     lib.sumob200_fcd_snapshot.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int)]
     lib.sumob200_fcd_begin.argtypes = [ctypes.c_void_p]
     lib.sumob200_fcd_end.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_int)]
+    lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
     lib.sumob200_num_lanes.argtypes = [ctypes.c_void_p]
@@ -182,6 +187,12 @@ class Engine:
             return np.zeros(0, dtype=FCD_ROW)
         buf = (ctypes.c_char * (n.value * FCD_ROW.itemsize)).from_address(p.value)
         return np.frombuffer(buf, dtype=FCD_ROW, count=n.value)
+
+    def tripinfo(self):
+        """trip record of every vehicle slot (MSDevice_Tripinfo::generateOutput fields), structured array TRIPINFO"""
+        out = np.zeros(max(self.num_vehicles, 1), dtype=TRIPINFO)
+        _check(self._lib, self._lib.sumob200_tripinfo_all(self._h, out.ctypes.data, out.shape[0]), "sumob200_tripinfo_all")
+        return out[:self.num_vehicles]
 
     def emissions(self):
         """[7, num_vehicles] accumulated CO2, CO, HC, fuel, NOx, PMx, electricity of every vehicle slot"""

@@ -150,6 +150,38 @@ def reference_fcd(name):
     return ref
 
 
+def reference_tripinfo(name):
+    """{vehicle id: dict of the attributes of its <tripinfo>} from the reference's own --tripinfo-output"""
+    import re
+    exe = os.path.join(REF, "sumo")
+    ensure_reference()
+    os.makedirs(CACHE, exist_ok=True)
+    out = os.path.join(CACHE, name + ".tripinfo.xml")
+    if not os.path.exists(out):
+        cmd = [exe, "-n", os.path.join(GOLDEN, name + ".net.xml"), "-r", os.path.join(GOLDEN, name + ".rou.xml"), "--no-step-log",
+               "--no-warnings", "--tripinfo-output", out + ".tmp"] + CASES[name]
+        subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        os.replace(out + ".tmp", out)
+    ref = {}
+    for line in open(out):
+        if "<tripinfo " in line:
+            a = dict(re.findall(r'(\w+)="([^"]*)"', line))
+            ref[a["id"]] = a
+    return ref
+
+
+def tripinfo_strings(rec, lane_names):
+    """a trip record (engine TRIPINFO row or the same fields from the host emulation) formatted like MSDevice_Tripinfo::generateOutput
+    with the default precision 2 (time2string rounds the ms value half up)"""
+    def t(ms):
+        return "%.2f" % (((int(ms) + 5) // 10) / 100.)
+    return {"depart": t(rec["depart_ms"]), "departLane": lane_names[int(rec["depart_lane"])], "departPos": "%.2f" % rec["depart_pos"],
+            "departSpeed": "%.2f" % rec["depart_speed"], "departDelay": t(rec["depart_delay_ms"]), "arrival": t(rec["arrival_ms"]),
+            "arrivalLane": lane_names[int(rec["arrival_lane"])], "arrivalPos": "%.2f" % rec["arrival_pos"], "arrivalSpeed": "%.2f" % rec["arrival_speed"],
+            "duration": t(rec["duration_ms"]), "routeLength": "%.2f" % rec["route_length"], "waitingTime": t(rec["waiting_ms"]),
+            "waitingCount": str(int(rec["waiting_count"])), "timeLoss": t(rec["time_loss_ms"]), "speedFactor": "%.2f" % rec["speed_factor"]}
+
+
 @pytest.fixture(scope="session")
 def host_emul():
     """tests/host_emul: the device functions compiled for the host (test infrastructure, see its header)"""

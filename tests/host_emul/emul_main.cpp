@@ -107,13 +107,15 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--tripinfo-out" && i + 1 < argc) {
+            tripOut = argv[++i];   // text, one line per arrived vehicle, at the end of the run
         } else if (a == "--emissions-out" && i + 1 < argc) {
             emisOut = argv[++i];   // same binary layout as sumo_flatten --emissions-out
         } else if (a == "--fcd-out" && i + 1 < argc) {
@@ -235,6 +237,20 @@ int main(int argc, char** argv) {
     }
     if (femis != nullptr) {
         fclose(femis);
+    }
+    if (!tripOut.empty()) {
+        FILE* ft = fopen(tripOut.c_str(), "w");
+        for (int v = 0; v < c.nV; v++) {
+            if (c.veh_lane[v] == -2) {
+                // slot depart departLane departPos departSpeed departDelay arrival arrivalLane arrivalPos arrivalSpeed duration routeLength waitingTime waitingCount timeLoss speedFactor
+                fprintf(ft, "%d %lld %d %.17g %.17g %lld %lld %d %.17g %.17g %lld %.17g %lld %d %lld %.17g\n", v, (long long)c.veh_depart_time[v], c.veh_departlane[v],
+                        c.veh_trip_departpos[v], c.veh_trip_departspeed[v], (long long)(c.veh_depart_time[v] - c.veh_depart_param[v]), (long long)c.veh_arrival_time[v],
+                        c.veh_arrival_lane[v], c.veh_arrivalpos[v], c.veh_speed[v], (long long)(c.veh_arrival_time[v] - c.veh_depart_time[v]),
+                        c.veh_trip_routelen[v] + c.veh_arrivalpos[v], (long long)c.veh_trip_wait[v], c.veh_trip_waitcount[v], (long long)TIME2STEPS(c.veh_timeloss[v]),
+                        c.veh_speedfactor[v]);
+            }
+        }
+        fclose(ft);
     }
     fprintf(stderr, "steps=%ld vehicle-updates=%lld inserted=%d arrived=%d collisions=%d emergencyStops=%d err=0x%x\n", steps, updates,
             c.counters[2], c.counters[1], c.counters[4], c.counters[5], *c.err_flags);
