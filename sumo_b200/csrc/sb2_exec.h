@@ -364,6 +364,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
         c.veh_moved[v] = 2;
         c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
         c.veh_arrival_lane[v] = myLane;
+        c.lane_arrived[oldLane] = 1;   // its queue entry is removed by lane_handoff_remove wherever it sits
         c.veh_lane[v] = -2;
         atomic_inc(&c.counters[1]);
     } else if (myLane != oldLane) {

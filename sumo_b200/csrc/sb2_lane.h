@@ -63,6 +63,28 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         f = c.veh_behind[f];
         removed++;
     }
+    if (c.lane_arrived[l]) {
+        // a vehicle that reached its arrivalPos behind the front vehicle (explicit arrivalPos inside the lane): MSLane::executeMovements
+        // erases it where it is (MSLane.cpp:2334-2340); unlink every arrived entry behind the new front, front -> back like the reference
+        c.lane_arrived[l] = 0;
+        int ahead = f;
+        for (int x = f >= 0 ? c.veh_behind[f] : -1; x >= 0;) {
+            const int next = c.veh_behind[x];
+            if (c.veh_lane[x] != l) {
+                toRemove += veh_length_with_gap(c, x);
+                removed++;
+                c.veh_behind[ahead] = next;
+                if (next >= 0) {
+                    c.veh_ahead[next] = ahead;
+                } else {
+                    c.lane_last[l] = ahead;
+                }
+            } else {
+                ahead = x;
+            }
+            x = next;
+        }
+    }
     if (removed > 0) {
         c.lane_first[l] = f;
         if (f >= 0) {

@@ -120,6 +120,7 @@ struct Ctx {
     int32_t* lane_nveh;
     double* lane_brutto;       // myBruttoVehicleLengthSum
     int32_t* lane_npartial; int32_t* lane_partial;   // [nL*MAX_PARTIAL] partial occupators, sorted by back position
+    int32_t* lane_arrived;     // set by executeMove when a vehicle of this lane's queue arrived (it may sit behind the front vehicle)
     int32_t* lane_incoming;    // head of the list of vehicles that entered this lane in executeMove (myVehBuffer)
     // per-step lane summary (k_lane_summary)
     int32_t* ls_lastveh;       // getLastVehicleInformation(nullptr,0): rear-most of vehicles+partials, -1 if none

@@ -31,6 +31,8 @@ CASES = {
     "grid5_dense_hbefa3": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "600", "--device.emissions.probability", "1"],
 }
 CASES.update({
+    # explicit arrivalPos inside the last lane: vehicles arrive (and leave the lane queue) behind the front vehicle
+    "grid4_tls_arrivalpos": ["--default.speeddev", "0", "--end", "1000"],
     # one district of bench.py's workload (10x10 TLS grid, 1800 resident vehicles, sigma 0.5, speedFactor deviation): same options as bench.py
     "bench_grid10_tls_draws": ["--time-to-teleport", "-1", "--default.departspeed", "0", "--default.departlane", "first", "--end", "700"],
     # carFollowModel IDM (MSCFModel_IDM, delta 4, 4 sub-steps)
@@ -40,6 +42,7 @@ CASES.update({
 })
 # per-case edits of the fixture's route file (old, new)
 ROU_EDITS = {
+    "_arrivalpos": ('<vehicle ', '<vehicle arrivalPos="60" '),
     "_idm": ('sigma="0"', 'sigma="0" carFollowModel="IDM"'),
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
     "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
@@ -103,7 +106,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
