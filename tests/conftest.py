@@ -40,8 +40,29 @@ CASES.update({
     "grid5_dense_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
     "c1_grid10_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "2500"],
 })
-# per-case edits of the fixture's route file (old, new)
+def _mixed_fleet(text):
+    """three vTypes (default car, long slow truck, short quick car with impatience), assigned pseudo-randomly but reproducibly"""
+    import random
+    import re
+    rnd = random.Random(7)
+    text = text.replace('<vType id="car" sigma="0"/>', '''<vType id="car" sigma="0"/>
+    <vType id="truck" sigma="0" length="12" minGap="3" accel="1.3" maxSpeed="25" tau="1.4" speedFactor="0.9"/>
+    <vType id="fast" sigma="0" length="4.3" minGap="2" accel="3.5" maxSpeed="60" tau="1.2" impatience="0.3"/>''')
+    return re.sub(r'type="car"', lambda m: 'type="%s"' % rnd.choice(["car", "car", "truck", "fast"]), text)
+
+
+CASES.update({
+    # other option combinations of the reference's command line
+    "grid4_tls_step05": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--step-length", "0.5", "--end", "600"],
+    "grid5_dense_optmix": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],
+    # heterogeneous fleet: length, minGap, accel, maxSpeed, tau, speedFactor, impatience differ between vehicles
+    "grid4_tls_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
+    "grid5_dense_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "c1_grid10_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
+})
+# per-case edits of the fixture's route file: (old, new) or a function text -> text
 ROU_EDITS = {
+    "_mixed": _mixed_fleet,
     "_arrivalpos": ('<vehicle ', '<vehicle arrivalPos="60" '),
     "_idm": ('sigma="0"', 'sigma="0" carFollowModel="IDM"'),
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
@@ -106,17 +127,22 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
-        for suffix, (old, new) in ROU_EDITS.items():
+        for suffix, edit in ROU_EDITS.items():
             if name.endswith(suffix):
                 text = open(rou).read()
-                assert old in text
+                if callable(edit):
+                    new_text = edit(text)
+                else:
+                    assert edit[0] in text
+                    new_text = text.replace(edit[0], edit[1])
+                assert new_text != text
                 rou = os.path.join(CACHE, name + ".rou.xml")
                 with open(rou, "w") as f:
-                    f.write(text.replace(old, new))
+                    f.write(new_text)
         if name.endswith(("_sigma", "_draws")):
             extra = ["--draws-out", draws_path(name)]
         if "_hbefa" in name:
