@@ -66,17 +66,6 @@ struct sumob200_engine {
 namespace {
 
 int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_engine** out) {
-    int nDev = 0;
-    if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev <= 0) {
-        gLastError = "sumob200: no CUDA device available (this library has no CPU path)";
-        delete e;
-        return SUMOB200_ENODEVICE;
-    }
-    if (device < 0 || device >= nDev) {
-        gLastError = "sumob200: invalid device index";
-        delete e;
-        return SUMOB200_EINVAL;
-    }
     try {
         e->model.build(ff);
         // kernel set for this scenario (kernels.cu): code the fleet never executes is not compiled in
@@ -88,6 +77,18 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
         gLastError = ex.what();
         delete e;
         return SUMOB200_EUNSUPPORTED;
+    }
+    // (the scenario is validated first, so an unsupported feature is reported as such even where no GPU is present)
+    int nDev = 0;
+    if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev <= 0) {
+        gLastError = "sumob200: no CUDA device available (this library has no CPU path)";
+        delete e;
+        return SUMOB200_ENODEVICE;
+    }
+    if (device < 0 || device >= nDev) {
+        gLastError = "sumob200: invalid device index";
+        delete e;
+        return SUMOB200_EINVAL;
     }
     e->device = device;
     cudaError_t err = cudaSetDevice(device);

@@ -147,6 +147,15 @@ public:
                 if (p[k] == 'Z') {
                     throw std::runtime_error("sumob200: zipper links are not supported");
                 }
+                // both junction types draw from the lane RNG streams inside planMove / setApproaching (right-before-left deadlock
+                // breaker MSVehicle.cpp:3002-3020, all-way-stop arrival tie breaker MSVehicle.cpp:5500-5502): not reproducible
+                // without the reference's stream order, so the scenario is refused instead of diverging silently
+                if (p[k] == 'w') {
+                    throw std::runtime_error("sumob200: allway_stop junctions are not supported (their arrival-time tie breaker draws from the lane RNG)");
+                }
+                if (p[k] == '=') {
+                    throw std::runtime_error("sumob200: right_before_left junctions are not supported (their deadlock breaker draws from the lane RNG)");
+                }
             }
         }
         SB2_COPY(uint8_t, link_dir);

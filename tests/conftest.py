@@ -52,6 +52,10 @@ def _mixed_fleet(text):
 
 
 CASES.update({
+    # other network shapes / junction types (netgenerate --rand, priority_stop, short traffic-light blocks with spill-back)
+    "rand_net": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "grid4_stop": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "grid3_tls_short": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
     # other option combinations of the reference's command line
     "grid4_tls_step05": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--step-length", "0.5", "--end", "600"],
     "grid5_dense_optmix": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],

@@ -91,6 +91,12 @@ SCENARIOS = {
     # static traffic lights (config 2 in miniature)
     "grid4_tls": dict(netgen=["--grid", "--grid.number=4", "--grid.length=200", "--default-junction-type", "traffic_light"],
                       n=800, end=900, seed=11, vtype='sigma="0"'),
+    # other network shapes / junction types of netgenerate
+    "rand_net": dict(netgen=["--rand", "--rand.iterations=40", "--seed", "5"], n=500, end=400, seed=3, vtype='sigma="0"', min_edges=2),
+    "grid4_stop": dict(netgen=["--grid", "--grid.number=4", "--grid.length=150", "--default-junction-type", "priority_stop"],
+                       n=500, end=400, seed=3, vtype='sigma="0"', min_edges=2),
+    "grid3_tls_short": dict(netgen=["--grid", "--grid.number=3", "--grid.length=60", "--default-junction-type", "traffic_light"],
+                            n=500, end=400, seed=3, vtype='sigma="0"', min_edges=2),
     # a tiny case that finishes in a blink (smoke)
     "grid3_small": dict(netgen=["--grid", "--grid.number=3", "--grid.length=100"], n=60, end=120, seed=3, vtype='sigma="0"'),
 }
@@ -111,7 +117,7 @@ def main():
         if start >= 0 and stop > start:
             txt = txt[:start] + txt[stop + 3:]
         open(net, "w").write(txt)
-        make_routes(net, rou, sc["n"], sc["end"], sc["seed"], sc["vtype"])
+        make_routes(net, rou, sc["n"], sc["end"], sc["seed"], sc["vtype"], sc.get("min_edges", 3))
         print(name, os.path.getsize(net), os.path.getsize(rou))
 
 

@@ -44,3 +44,24 @@ def test_bad_arguments_are_rejected():
     assert lib.sumob200_create_from_file(b"/nonexistent.flat", 0, ctypes.byref(out)) < 0
     assert lib.sumob200_step(None, 1, None) < 0
     assert lib.sumob200_num_vehicles(None) == 0
+
+
+def test_unsupported_scenarios_are_refused_at_load(tmp_path):
+    """a scenario whose junction logic draws random numbers inside the step (all-way stop, right-before-left) must be refused by
+    sumob200_create, not simulated approximately; checked on the host side of the library (Model::build runs before any CUDA call)"""
+    import numpy as np
+    from sumo_b200.engine import Engine, SumoB200Error
+    from sumo_b200.flatfile import load_flat
+    base = load_flat(os.path.join(ROOT, "tests", "golden", "grid3_small.golden.flat"))
+    for state, word in ((ord("w"), "allway_stop"), (ord("="), "right_before_left"), (ord("Z"), "zipper")):
+        sc = dict(base)
+        ls = base["link_state"].copy()
+        ls[0] = state
+        sc["link_state"] = ls
+        with pytest.raises(SumoB200Error) as ei:
+            Engine(sc)
+        assert word in str(ei.value), str(ei.value)
+    sc = dict(base)
+    sc["lane_flags"] = base["lane_flags"] | 8   # LF_LANECHANGER: an edge with several lanes
+    with pytest.raises(SumoB200Error):
+        Engine(sc)
