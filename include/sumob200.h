@@ -104,6 +104,10 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
  * next sumob200_step right away; _end waits for the copy and hands out the pinned rows (valid until the next _begin
  * after the following one: two buffers alternate).  Replaces the per-vehicle loop of MSFCDExport::write
  * (src/microsim/output/MSFCDExport.cpp:98-300), whose XML formatting stays on the host. */
+/* host-side formatter: the <timestep> element MSFCDExport::write emits for these rows, byte for byte
+ * (ids in std::string order, 2 decimals), formatted on all host threads.  Writes at most `capacity` bytes to buf and the
+ * full length to *length (call again with a larger buffer if *length > capacity).  Needs a scenario flattened with ids. */
+int sumob200_fcd_format_xml(sumob200_engine* e, const sumob200_fcd_row* rows, int n, int64_t time_ms, char* buf, uint64_t capacity, uint64_t* length);
 int sumob200_fcd_begin(sumob200_engine* e);
 int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n);
 

@@ -26,6 +26,7 @@
 #include "../../include/sumob200.h"
 #include "sb2_build.h"
 #include "sb2_kernelset.h"
+#include "sb2_fcdxml.h"
 
 using namespace sb2;
 
@@ -411,6 +412,32 @@ int sumob200_phase_times(sumob200_engine* e, double* ms, int n_phases, int reset
         for (double& x : e->phaseMs) {
             x = 0;
         }
+    }
+    return 0;
+}
+
+int sumob200_fcd_format_xml(sumob200_engine* e, const sumob200_fcd_row* rows, int n, int64_t time_ms, char* buf, uint64_t capacity, uint64_t* length) {
+    if (e == nullptr || (n > 0 && rows == nullptr) || length == nullptr || (capacity > 0 && buf == nullptr)) {
+        gLastError = "sumob200_fcd_format_xml: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    const Model& m = e->model;
+    if (m.veh_names.empty() || m.lane_names.empty() || m.vt_names.empty()) {
+        gLastError = "sumob200_fcd_format_xml: the scenario was flattened without ids (veh_names / lane_names / vt_names)";
+        return SUMOB200_EUNSUPPORTED;
+    }
+    for (int i = 0; i < n; i++) {
+        if (rows[i].slot < 0 || rows[i].slot >= m.h.nV || rows[i].lane < 0 || rows[i].lane >= m.h.nL) {
+            gLastError = "sumob200_fcd_format_xml: row with an invalid slot or lane";
+            return SUMOB200_EINVAL;
+        }
+    }
+    const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, m.h.veh_type, m.h.veh_idrank};
+    std::string out;
+    fcdxml_timestep(nm, rows, n, time_ms, out);
+    *length = out.size();
+    if (capacity > 0) {
+        memcpy(buf, out.data(), out.size() < capacity ? out.size() : capacity);
     }
     return 0;
 }

@@ -31,7 +31,7 @@ public:
     bool haveEmissionModel = false;
     bool anyEmissionDevice = false;
     std::vector<Buffer*> buffers;
-    std::vector<std::string> lane_names, veh_names;
+    std::vector<std::string> lane_names, veh_names, vt_names;
     SUMOTime begin = 0, end = 0;
 
     Model() { memset(&h, 0, sizeof(h)); }
@@ -114,6 +114,9 @@ public:
         if (ff.has("lane_names") && ff.has("veh_names")) {   // ids are only needed for diagnostics and output writers
             lane_names = names(ff, "lane");
             veh_names = names(ff, "veh");
+        }
+        if (ff.has("vt_names")) {
+            vt_names = names(ff, "vt");
         }
         // ---------------- lanes
         SB2_COPY(double, lane_length); SB2_COPY(double, lane_speed);

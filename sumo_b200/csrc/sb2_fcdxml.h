@@ -1,0 +1,96 @@
+/* sb2_fcdxml.h -- host side of the FCD output: formats the binary rows the device produced
+ * (sumob200_fcd_row) into the text MSFCDExport::write emits (src/microsim/output/MSFCDExport.cpp:98-300 with the default
+ * attribute mask x, y, angle, type, speed, pos, lane, slope; src/microsim/devices/MSDevice_FCD.cpp:102-122), byte for byte:
+ *     <timestep time="4.00">
+ *         <vehicle id="v0" x="163.92" y="201.60" angle="270.00" type="car" speed="13.89" pos="32.88" lane="C2B2_0" slope="0.00"/>
+ *     </timestep>
+ * Vehicles appear in std::string order of their ids (the reference iterates a std::map<std::string, SUMOVehicle*>,
+ * MSVehicleControl.h) = ascending veh_idrank.  Numbers: fixed, gPrecision = 2 decimals; times: time2string
+ * (utils/common/SUMOTime.cpp:91-137).  Formatting is spread over host threads: at 1M vehicles the text (120 MB per step),
+ * not the GPU, bounds the output rate.  Flat networks: slope="0.00".
+ */
+#pragma once
+#include <algorithm>
+#include <cstdio>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/sumob200.h"
+
+namespace sb2 {
+
+inline std::string fcdxml_time2string(int64_t t) {
+    const bool neg = t < 0;
+    unsigned long long a = (unsigned long long)(neg ? -t : t);
+    a = (a + 5) / 10;   // scale = 10^(3 - gPrecision)
+    char buf[48];
+    snprintf(buf, sizeof(buf), "%s%llu.%02llu", neg ? "-" : "", a / 100, a % 100);
+    return buf;
+}
+
+struct FcdXmlNames {
+    const std::vector<std::string>* veh;     // by slot
+    const std::vector<std::string>* lane;    // by lane index
+    const std::vector<std::string>* vtype;   // by vType index
+    const int32_t* veh_type;                 // by slot
+    const int32_t* veh_idrank;               // by slot
+};
+
+// appends one <timestep> element for `rows` (any order) to `out`
+inline void fcdxml_timestep(const FcdXmlNames& nm, const sumob200_fcd_row* rows, int n, int64_t time_ms, std::string& out, int max_threads = 0) {
+    if (n <= 0) {
+        out += "    <timestep time=\"" + fcdxml_time2string(time_ms) + "\"/>\n";
+        return;
+    }
+    std::vector<int> order(n);
+    for (int i = 0; i < n; i++) {
+        order[i] = i;
+    }
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return nm.veh_idrank[rows[a].slot] < nm.veh_idrank[rows[b].slot]; });
+    int nt = max_threads > 0 ? max_threads : (int)std::thread::hardware_concurrency();
+    nt = std::max(1, std::min(nt, n / 4096 + 1));
+    std::vector<std::string> parts(nt);
+    auto work = [&](int k) {
+        std::string& s = parts[k];
+        const int b = (int)((long long)n * k / nt), e = (int)((long long)n * (k + 1) / nt);
+        s.reserve((size_t)(e - b) * 140);
+        char num[6][40];
+        for (int i = b; i < e; i++) {
+            const sumob200_fcd_row& r = rows[order[i]];
+            snprintf(num[0], 40, "%.2f", r.x);
+            snprintf(num[1], 40, "%.2f", r.y);
+            snprintf(num[2], 40, "%.2f", r.angle);
+            snprintf(num[3], 40, "%.2f", r.speed);
+            snprintf(num[4], 40, "%.2f", r.pos);
+            s += "        <vehicle id=\"";
+            s += (*nm.veh)[r.slot];
+            s += "\" x=\""; s += num[0];
+            s += "\" y=\""; s += num[1];
+            s += "\" angle=\""; s += num[2];
+            s += "\" type=\""; s += (*nm.vtype)[nm.veh_type[r.slot]];
+            s += "\" speed=\""; s += num[3];
+            s += "\" pos=\""; s += num[4];
+            s += "\" lane=\""; s += (*nm.lane)[r.lane];
+            s += "\" slope=\"0.00\"/>\n";
+        }
+    };
+    if (nt == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < nt; k++) {
+            th.emplace_back(work, k);
+        }
+        for (std::thread& t : th) {
+            t.join();
+        }
+    }
+    out += "    <timestep time=\"" + fcdxml_time2string(time_ms) + "\">\n";
+    for (const std::string& p : parts) {
+        out += p;
+    }
+    out += "    </timestep>\n";
+}
+
+}  // namespace sb2

@@ -68,6 +68,7 @@ def load_library(path=None):
     lib.sumob200_step_timed.argtypes = [ctypes.c_void_p, ctypes.c_int, P(StepResult), P(ctypes.c_double)]
     lib.sumob200_mirror_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_fcd_snapshot.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int)]
+    lib.sumob200_fcd_format_xml.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_char_p, ctypes.c_uint64, P(ctypes.c_uint64)]
     lib.sumob200_fcd_begin.argtypes = [ctypes.c_void_p]
     lib.sumob200_fcd_end.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_int)]
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
@@ -173,6 +174,19 @@ class Engine:
         n = ctypes.c_int()
         _check(self._lib, self._lib.sumob200_fcd_snapshot(self._h, rows.ctypes.data, rows.shape[0], ctypes.byref(n)), "sumob200_fcd_snapshot")
         return rows[:n.value]
+
+    def fcd_xml(self, rows, time_ms):
+        """the <timestep> element of the reference's --fcd-output for these rows (bytes)"""
+        rows = np.ascontiguousarray(rows, dtype=FCD_ROW)
+        n = ctypes.c_uint64()
+        cap = 160 * len(rows) + 256
+        buf = ctypes.create_string_buffer(cap)
+        _check(self._lib, self._lib.sumob200_fcd_format_xml(self._h, rows.ctypes.data, len(rows), time_ms, buf, cap, ctypes.byref(n)), "sumob200_fcd_format_xml")
+        if n.value > cap:
+            cap = n.value
+            buf = ctypes.create_string_buffer(cap)
+            _check(self._lib, self._lib.sumob200_fcd_format_xml(self._h, rows.ctypes.data, len(rows), time_ms, buf, cap, ctypes.byref(n)), "sumob200_fcd_format_xml")
+        return buf.raw[:n.value]
 
     def fcd_begin(self):
         """start the device-side compaction + pinned async D2H of the FCD rows; the next step may be issued right away"""

@@ -183,6 +183,13 @@ def reference_fcd(name):
     return ref
 
 
+def reference_fcd_body(name):
+    """the <timestep> ... </timestep> lines of the reference's --fcd-output file, as bytes"""
+    reference_fcd(name)
+    out = os.path.join(CACHE, name + ".fcd.xml")
+    return b"".join(l for l in open(out, "rb") if b"timestep" in l or b"<vehicle" in l)
+
+
 def reference_tripinfo(name):
     """{vehicle id: dict of the attributes of its <tripinfo>} from the reference's own --tripinfo-output"""
     import re
@@ -223,5 +230,5 @@ def host_emul():
     src = os.path.join(ROOT, "tests", "host_emul", "emul_main.cpp")
     deps = [src] + [os.path.join(ROOT, "sumo_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "sumo_b200", "csrc"))]
     if not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-o", exe, src])
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-pthread", "-o", exe, src])
     return exe

@@ -21,6 +21,7 @@
 #include "../../sumo_b200/csrc/sb2_lane.h"
 #include "../../sumo_b200/csrc/sb2_insert.h"
 #include "../../sumo_b200/csrc/sb2_fcd.h"
+#include "../../sumo_b200/csrc/sb2_fcdxml.h"
 
 using namespace sb2;
 
@@ -107,13 +108,15 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--fcd-xml-out" && i + 1 < argc) {
+            fcdXmlOut = argv[++i];   // the <timestep> elements of the reference's --fcd-output
         } else if (a == "--tripinfo-out" && i + 1 < argc) {
             tripOut = argv[++i];   // text, one line per arrived vehicle, at the end of the run
         } else if (a == "--emissions-out" && i + 1 < argc) {
@@ -149,6 +152,7 @@ int main(int argc, char** argv) {
         order[v] = v;
     }
     std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
+    FILE* ffcdxml = fcdXmlOut.empty() ? nullptr : fopen(fcdXmlOut.c_str(), "w");
     FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
     FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
@@ -194,6 +198,22 @@ int main(int argc, char** argv) {
                 }
             }
         }
+        if (ffcdxml != nullptr) {
+            std::vector<sumob200_fcd_row> rows;
+            for (int v = 0; v < c.nV; v++) {
+                if (c.veh_lane[v] >= 0) {
+                    const Pos2 p = veh_position(c, v);
+                    sumob200_fcd_row r;
+                    r.slot = v; r.lane = c.veh_lane[v]; r.pos = c.veh_pos[v]; r.speed = c.veh_speed[v];
+                    r.x = p.x; r.y = p.y; r.angle = naviDegree(veh_computeAngle(c, v, p));
+                    rows.push_back(r);
+                }
+            }
+            const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, c.veh_type, c.veh_idrank};
+            std::string xml;
+            fcdxml_timestep(nm, rows.data(), (int)rows.size(), t, xml, 2);
+            fwrite(xml.data(), 1, xml.size(), ffcdxml);
+        }
         if (femis != nullptr) {
             int64_t ne = 0;
             for (int v : order) {
@@ -237,6 +257,9 @@ int main(int argc, char** argv) {
     }
     if (femis != nullptr) {
         fclose(femis);
+    }
+    if (ffcdxml != nullptr) {
+        fclose(ffcdxml);
     }
     if (!tripOut.empty()) {
         FILE* ft = fopen(tripOut.c_str(), "w");

@@ -4,7 +4,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from conftest import reference_case, reference_fcd
+from conftest import reference_case, reference_fcd, reference_fcd_body
 from sumo_b200.flatfile import load_flat, names
 
 FCD_CASES = ["grid3_small", "grid4_tls"]
@@ -59,3 +59,45 @@ def test_engine_fcd_matches_reference(case):
                 assert min(d, 360. - d) <= 0.011
                 compared += 1
     assert compared == len(ref)
+
+
+@pytest.mark.parametrize("case", FCD_CASES)
+def test_host_emulation_fcd_xml_is_byte_identical(case, host_emul, tmp_path):
+    """the formatter of sumob200_fcd_format_xml (sb2_fcdxml.h) over the host emulation's rows: the reference's fcd-output, byte for byte"""
+    flat, _ = reference_case(case)
+    body = reference_fcd_body(case)
+    out = str(tmp_path / "fcd.body")
+    subprocess.run([host_emul, flat, "--fcd-xml-out", out], check=True, timeout=600, stderr=subprocess.DEVNULL)
+    got = open(out, "rb").read()
+    assert len(body) > 100000
+    assert got == body
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", FCD_CASES)
+def test_engine_fcd_xml_matches_reference_file(case):
+    """sumob200_step + sumob200_fcd_begin/_end + sumob200_fcd_format_xml reproduce the reference's --fcd-output file; a line may
+    differ only in the last digit of angle= (atan2 is not correctly rounded on either side)"""
+    import re
+    from sumo_b200.engine import Engine
+    flat, _ = reference_case(case)
+    ref_lines = reference_fcd_body(case).split(b"\n")
+    got = []
+    with Engine(flat) as eng:
+        nsteps = sum(1 for l in ref_lines if l.startswith(b"    <timestep"))
+        for _ in range(nsteps):
+            t = eng.time_ms
+            eng.step(1, result=False)
+            eng.fcd_begin()
+            got.append(eng.fcd_xml(eng.fcd_end(), t))
+    got_lines = b"".join(got).split(b"\n")
+    assert len(got_lines) == len(ref_lines)
+    differing = 0
+    for a, b in zip(ref_lines, got_lines):
+        if a != b:
+            differing += 1
+            strip = lambda l: re.sub(rb' angle="[^"]*"', b"", l)
+            assert strip(a) == strip(b)
+            fa, fb = float(re.search(rb'angle="([^"]*)"', a).group(1)), float(re.search(rb'angle="([^"]*)"', b).group(1))
+            assert min(abs(fa - fb), 360 - abs(fa - fb)) <= 0.011
+    assert differing <= len(ref_lines) // 1000
