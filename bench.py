@@ -150,6 +150,7 @@ def main():
     ap.add_argument("--vehicles", type=int, default=1000000, help="resident vehicles per GPU")
     ap.add_argument("--sigma", type=float, default=0.5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--emissions", action="store_true", help="every vehicle carries the HBEFA emission device (BASELINE.json configs[4] flavour)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -171,6 +172,8 @@ def main():
     base = load_flat(BASE + ".flat")
     tiles = max(1, (args.vehicles + VEH_PER_TILE - 1) // VEH_PER_TILE)
     scenario = tile(base, tiles, overrides={"vt_sigma": np.full(base["vt_sigma"].shape, args.sigma)})
+    if not args.emissions:
+        scenario["veh_emissions"] = np.zeros_like(scenario["veh_emissions"])
     eng = Engine(scenario, device=local_rank)
     del scenario
     nV = eng.num_vehicles
@@ -244,7 +247,7 @@ def main():
         "metric": "vehicle-updates/s", "value": value, "unit": "veh*steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "%d disjoint districts per GPU, each netgenerate 10x10 grid / 200 m / static traffic lights with %d resident vehicles "
-                               "(25 veh/lane-km), Krauss sigma=%.1f, step-length 1 s" % (tiles, VEH_PER_TILE, args.sigma),
+                               "(25 veh/lane-km), Krauss sigma=%.1f, step-length 1 s%s" % (tiles, VEH_PER_TILE, args.sigma, ", HBEFA4 emission device on every vehicle" if args.emissions else ""),
                    "vehicles_per_gpu": nV, "resident_per_gpu": int(r1.running), "districts_per_gpu": tiles, "mean_speed_mps": mean_speed,
                    "l2": "state arrays (%.1f GB) are far larger than the 126 MB L2, no flush needed" % (nV * 1700 / 1e9),
                    "engine_flags": describe_flags(flags), "spinup_steps": SPINUP_STEPS},

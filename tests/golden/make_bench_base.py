@@ -54,7 +54,10 @@ def main():
         f.write("</routes>\n")
     flat = os.path.join(HERE, NAME + ".flat")
     subprocess.check_call([os.path.join(REF, "sumo_flatten"), "--flat-out", flat, "-n", net, "-r", rou, "--no-step-log",
-                           "--no-warnings", "--time-to-teleport", "-1", "--default.departspeed", "0", "--default.departlane", "first"],
+                           "--no-warnings", "--time-to-teleport", "-1", "--default.departspeed", "0", "--default.departlane", "first",
+                           # every vehicle carries MSDevice_Emissions (default class HBEFA4/PC_petrol_Euro-4); bench.py switches the
+                           # device off (veh_emissions = 0) unless it is run with --emissions (BASELINE.json configs[4])
+                           "--device.emissions.probability", "1"],
                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     for p in (net, rou, flat):
         print(p, os.path.getsize(p))
