@@ -126,6 +126,26 @@ typedef struct sumob200_tripinfo {
 /* trip records of all vehicle slots (n = sumob200_num_vehicles) */
 int sumob200_tripinfo_all(sumob200_engine* e, sumob200_tripinfo* out, int capacity);
 
+/* the attributes of one <step .../> line of --summary-output (MSNet::writeSummaryOutput, src/microsim/MSNet.cpp:688-730) for
+ * the step executed last; `loaded`, `discarded` and `duration` stay with the loader / the host (not engine state) */
+typedef struct sumob200_summary {
+    int64_t time_ms;          /* time of the step executed last (= the line's time attribute) */
+    int32_t inserted;         /* getDepartedVehicleNo */
+    int32_t running;          /* getRunningVehicleNo */
+    int32_t waiting;          /* MSInsertionControl::getWaitingVehicleNo: depart time reached, no room yet */
+    int32_t ended;            /* getEndedVehicleNo */
+    int32_t arrived;          /* getArrivedVehicleNo */
+    int32_t collisions, teleports;
+    int32_t halting;          /* getHaltingVehicleNo */
+    int32_t stopped;          /* always 0: <stop>s are outside the path (refused at load) */
+    int32_t reserved;
+    double mean_waiting_time; /* getTotalDepartureDelay / inserted, -1 if none inserted yet */
+    double mean_travel_time;  /* getTotalTravelTime / ended, -1 if none ended yet */
+    double mean_speed;        /* getVehicleMeanSpeeds().first, -1 if no vehicle on the road */
+    double mean_speed_relative;
+} sumob200_summary;
+int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out);
+
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],
  * p = 0 CO2, 1 CO, 2 HC, 3 fuel, 4 NOx, 5 PMx, 6 electricity [mg resp. ml resp. Wh], n = sumob200_num_vehicles.

@@ -27,6 +27,7 @@
 #include "sb2_build.h"
 #include "sb2_kernelset.h"
 #include "sb2_fcdxml.h"
+#include "sb2_summary.h"
 
 using namespace sb2;
 
@@ -48,6 +49,7 @@ struct sumob200_engine {
     cudaStream_t stream = nullptr;
     unsigned long long* dUpdates = nullptr;
     sumob200_vehicle_state* dMirror = nullptr;
+    void* dSummary = nullptr;   // SummaryPart scratch of sumob200_summary_now
     double* dReplay = nullptr;
     // FCD streaming: device rows + block counts, two pinned host buffers, a copy stream (D2H overlaps the next step)
     sumob200_fcd_row* dFcd = nullptr;
@@ -198,6 +200,9 @@ void sumob200_destroy(sumob200_engine* e) {
     if (e->dUpdates != nullptr) {
         cudaFree(e->dUpdates);
     }
+    if (e->dSummary != nullptr) {
+        cudaFree(e->dSummary);
+    }
     if (e->dMirror != nullptr) {
         cudaFree(e->dMirror);
     }
@@ -322,6 +327,42 @@ int sumob200_mirror_all(sumob200_engine* e, sumob200_vehicle_state* out, int cap
     e->launches += 1;
     CUDA_TRY(cudaMemcpyAsync(out, e->dMirror, sizeof(sumob200_vehicle_state) * (size_t)nV, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out) {
+    if (e == nullptr || out == nullptr) {
+        gLastError = "sumob200_summary_now: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int nV = e->d.nV;
+    const int bytes = e->ks->summary(&e->d, nV, nullptr, nullptr, e->stream);
+    if (e->dSummary == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->dSummary, (size_t)bytes));
+    }
+    sb2::SummaryPart* res = reinterpret_cast<sb2::SummaryPart*>(static_cast<char*>(e->dSummary) + bytes) - 1;
+    e->launches += e->ks->summary(&e->d, nV, e->dSummary, res, e->stream);
+    sb2::SummaryPart p;
+    int32_t counters[16];
+    CUDA_TRY(cudaMemcpyAsync(&p, res, sizeof(p), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    out->time_ms = e->d.t - e->d.DELTA_T;
+    out->inserted = p.departed;
+    out->running = p.count;
+    out->waiting = p.waiting;
+    out->ended = p.ended;
+    out->arrived = p.ended;
+    out->collisions = counters[4];
+    out->teleports = counters[6];
+    out->halting = p.halting;
+    out->stopped = 0;
+    out->reserved = 0;
+    out->mean_waiting_time = p.departed != 0 ? ((double)p.delay_ms / 1000.) / (double)p.departed : -1.;
+    out->mean_travel_time = p.ended != 0 ? ((double)p.travel_ms / 1000.) / (double)p.ended : -1.;
+    out->mean_speed = p.count > 0 ? p.speedSum / p.count : -1.;
+    out->mean_speed_relative = p.count > 0 ? p.relSpeedSum / p.count : -1.;
     return 0;
 }
 

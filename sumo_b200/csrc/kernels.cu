@@ -41,6 +41,7 @@ namespace SB2_PASTE(sb2_kset_, SB2_KSET) {
 #include "sb2_lane.h"
 #include "sb2_insert.h"
 #include "sb2_fcd.h"
+#include "sb2_summary.h"
 
 using namespace sb2;
 
@@ -285,6 +286,46 @@ __global__ void __launch_bounds__(BLOCK) k_tripinfo(const __grid_constant__ Ctx 
     }
 }
 
+// ---- summary aggregates (MSNet::writeSummaryOutput): per-block tree reduction in a fixed order, then one block over the block
+// results -- deterministic, no floating-point atomics
+__device__ __forceinline__ void summary_block_reduce(SummaryPart& p, SummaryPart* sh) {
+    sh[threadIdx.x] = p;
+    __syncthreads();
+    for (int d = blockDim.x >> 1; d > 0; d >>= 1) {
+        if ((int)threadIdx.x < d) {
+            summary_add(sh[threadIdx.x], sh[threadIdx.x + d]);
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_summary(const __grid_constant__ Ctx c, SummaryPart* parts) {
+    __shared__ SummaryPart sh[BLOCK];
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    SummaryPart p;
+    summary_zero(p);
+    if (v < c.nV) {
+        summary_vehicle(c, v, c.t - c.DELTA_T, p);
+    }
+    summary_block_reduce(p, sh);
+    if (threadIdx.x == 0) {
+        parts[blockIdx.x] = sh[0];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_summary_final(const SummaryPart* parts, int n, SummaryPart* out) {
+    __shared__ SummaryPart sh[256];
+    SummaryPart p;
+    summary_zero(p);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        summary_add(p, parts[i]);
+    }
+    summary_block_reduce(p, sh);
+    if (threadIdx.x == 0) {
+        *out = sh[0];
+    }
+}
+
 __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
@@ -311,6 +352,15 @@ void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK,
 void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<grid(n), BLOCK, 0, s>>>(ctx(c), updates); }
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
+int l_summary(const void* c, int n, void* parts, void* out, cudaStream_t s) {   // parts = NULL: number of bytes parts needs
+    const int nb = grid(n);
+    if (parts == nullptr) {
+        return (int)sizeof(SummaryPart) * (nb + 1);
+    }
+    k_summary<<<nb, BLOCK, 0, s>>>(ctx(c), static_cast<SummaryPart*>(parts));
+    k_summary_final<<<1, 256, 0, s>>>(static_cast<SummaryPart*>(parts), nb, static_cast<SummaryPart*>(out));
+    return 2;
+}
 void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaStream_t s) {
     const int nb = grid(n);
     k_fcd_count<<<nb, BLOCK, 0, s>>>(ctx(c), blocks);
@@ -318,7 +368,7 @@ void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaSt
     k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary};
 
 }  // namespace sb2_kset_<name>
 

@@ -20,6 +20,8 @@ struct sb2_kernelset {
     void (*mirror)(const void* ctx, int n_vehicles, sumob200_vehicle_state* out, cudaStream_t s);
     void (*fcd)(const void* ctx, int n_vehicles, int32_t* block_counts /* [blocks + 1] */, sumob200_fcd_row* rows, cudaStream_t s);   // 3 launches
     void (*tripinfo)(const void* ctx, int n_vehicles, sumob200_tripinfo* out, cudaStream_t s);
+    /* summary aggregates (sb2_summary.h:SummaryPart): parts == NULL returns the scratch size in bytes, else launches (returns the launch count) */
+    int (*summary)(const void* ctx, int n_vehicles, void* parts, void* out, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

@@ -42,6 +42,10 @@ TRIPINFO = np.dtype([("depart_ms", np.int64), ("depart_delay_ms", np.int64), ("a
                      ("waiting_ms", np.int64), ("time_loss_ms", np.int64), ("depart_lane", np.int32), ("arrival_lane", np.int32),
                      ("waiting_count", np.int32), ("reserved", np.int32), ("depart_pos", np.float64), ("depart_speed", np.float64),
                      ("arrival_pos", np.float64), ("arrival_speed", np.float64), ("route_length", np.float64), ("speed_factor", np.float64)])
+SUMMARY = np.dtype([("time_ms", np.int64), ("inserted", np.int32), ("running", np.int32), ("waiting", np.int32), ("ended", np.int32),
+                    ("arrived", np.int32), ("collisions", np.int32), ("teleports", np.int32), ("halting", np.int32), ("stopped", np.int32),
+                    ("reserved", np.int32), ("mean_waiting_time", np.float64), ("mean_travel_time", np.float64), ("mean_speed", np.float64),
+                    ("mean_speed_relative", np.float64)])
 FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
                     ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
 
@@ -72,6 +76,7 @@ def load_library(path=None):
     lib.sumob200_fcd_begin.argtypes = [ctypes.c_void_p]
     lib.sumob200_fcd_end.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_int)]
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
     lib.sumob200_num_lanes.argtypes = [ctypes.c_void_p]
@@ -207,6 +212,12 @@ class Engine:
         out = np.zeros(max(self.num_vehicles, 1), dtype=TRIPINFO)
         _check(self._lib, self._lib.sumob200_tripinfo_all(self._h, out.ctypes.data, out.shape[0]), "sumob200_tripinfo_all")
         return out[:self.num_vehicles]
+
+    def summary(self):
+        """the attributes of the <step> line MSNet::writeSummaryOutput writes for the step executed last (record of dtype SUMMARY)"""
+        out = np.zeros(1, dtype=SUMMARY)
+        _check(self._lib, self._lib.sumob200_summary_now(self._h, out.ctypes.data), "sumob200_summary_now")
+        return out[0]
 
     def emissions(self):
         """[7, num_vehicles] accumulated CO2, CO, HC, fuel, NOx, PMx, electricity of every vehicle slot"""

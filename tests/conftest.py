@@ -210,6 +210,33 @@ def reference_tripinfo(name):
     return ref
 
 
+def reference_summary(name):
+    """[dict of the attributes of every <step> of the reference's own --summary-output]; cases whose suffix only adds options"""
+    import re
+    exe = os.path.join(REF, "sumo")
+    ensure_reference()
+    os.makedirs(CACHE, exist_ok=True)
+    out = os.path.join(CACHE, name + ".summary.xml")
+    base = name
+    for suffix in ("_depart0", "_step05", "_optmix"):
+        base = base.replace(suffix, "")
+    if not os.path.exists(out):
+        cmd = [exe, "-n", os.path.join(GOLDEN, base + ".net.xml"), "-r", os.path.join(GOLDEN, base + ".rou.xml"), "--no-step-log",
+               "--no-warnings", "--summary-output", out + ".tmp"] + CASES[name]
+        subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        os.replace(out + ".tmp", out)
+    return [dict(re.findall(r'(\w+)="([^"]*)"', line)) for line in open(out) if "<step " in line]
+
+
+def summary_strings(rec):
+    """a summary record (engine SUMMARY row or the same fields from the host emulation) formatted like MSNet::writeSummaryOutput"""
+    return {"time": "%.2f" % (int(rec["time_ms"]) / 1000.), "inserted": str(int(rec["inserted"])), "running": str(int(rec["running"])),
+            "waiting": str(int(rec["waiting"])), "ended": str(int(rec["ended"])), "arrived": str(int(rec["arrived"])),
+            "collisions": str(int(rec["collisions"])), "teleports": str(int(rec["teleports"])), "halting": str(int(rec["halting"])),
+            "stopped": str(int(rec["stopped"])), "meanWaitingTime": "%.2f" % rec["mean_waiting_time"], "meanTravelTime": "%.2f" % rec["mean_travel_time"],
+            "meanSpeed": "%.2f" % rec["mean_speed"], "meanSpeedRelative": "%.2f" % rec["mean_speed_relative"]}
+
+
 def tripinfo_strings(rec, lane_names):
     """a trip record (engine TRIPINFO row or the same fields from the host emulation) formatted like MSDevice_Tripinfo::generateOutput
     with the default precision 2 (time2string rounds the ms value half up)"""

@@ -22,6 +22,7 @@
 #include "../../sumo_b200/csrc/sb2_insert.h"
 #include "../../sumo_b200/csrc/sb2_fcd.h"
 #include "../../sumo_b200/csrc/sb2_fcdxml.h"
+#include "../../sumo_b200/csrc/sb2_summary.h"
 
 using namespace sb2;
 
@@ -108,7 +109,7 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
@@ -117,6 +118,8 @@ int main(int argc, char** argv) {
             traceOut = argv[++i];
         } else if (a == "--fcd-xml-out" && i + 1 < argc) {
             fcdXmlOut = argv[++i];   // the <timestep> elements of the reference's --fcd-output
+        } else if (a == "--summary-out" && i + 1 < argc) {
+            summaryOut = argv[++i];   // text, one line per step: the attributes of the reference's --summary-output
         } else if (a == "--tripinfo-out" && i + 1 < argc) {
             tripOut = argv[++i];   // text, one line per arrived vehicle, at the end of the run
         } else if (a == "--emissions-out" && i + 1 < argc) {
@@ -153,6 +156,7 @@ int main(int argc, char** argv) {
     }
     std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
     FILE* ffcdxml = fcdXmlOut.empty() ? nullptr : fopen(fcdXmlOut.c_str(), "w");
+    FILE* fsum = summaryOut.empty() ? nullptr : fopen(summaryOut.c_str(), "w");
     FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
     FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
@@ -214,6 +218,18 @@ int main(int argc, char** argv) {
             fcdxml_timestep(nm, rows.data(), (int)rows.size(), t, xml, 2);
             fwrite(xml.data(), 1, xml.size(), ffcdxml);
         }
+        if (fsum != nullptr) {
+            SummaryPart p;
+            summary_zero(p);
+            for (int v = 0; v < c.nV; v++) {
+                summary_vehicle(c, v, t, p);
+            }
+            // time inserted running waiting ended arrived collisions teleports halting stopped meanWaitingTime meanTravelTime meanSpeed meanSpeedRelative
+            fprintf(fsum, "%lld %d %d %d %d %d %d %d %d %d %.17g %.17g %.17g %.17g\n", (long long)t, p.departed, p.count, p.waiting, p.ended, p.ended,
+                    c.counters[4], c.counters[6], p.halting, 0, p.departed != 0 ? ((double)p.delay_ms / 1000.) / (double)p.departed : -1.,
+                    p.ended != 0 ? ((double)p.travel_ms / 1000.) / (double)p.ended : -1., p.count > 0 ? p.speedSum / p.count : -1.,
+                    p.count > 0 ? p.relSpeedSum / p.count : -1.);
+        }
         if (femis != nullptr) {
             int64_t ne = 0;
             for (int v : order) {
@@ -254,6 +270,9 @@ int main(int argc, char** argv) {
     }
     if (ffcd != nullptr) {
         fclose(ffcd);
+    }
+    if (fsum != nullptr) {
+        fclose(fsum);
     }
     if (femis != nullptr) {
         fclose(femis);
