@@ -49,7 +49,7 @@ constexpr int BLOCK = 128;
 // resident CTAs per SM the register allocation of the two per-vehicle kernels is bounded for (profiles/r01_*: both are
 // latency bound -- long scoreboard on dependent gathers -- so occupancy is worth more than a spill-free allocation)
 #ifndef SB2_PLAN_MINB
-#define SB2_PLAN_MINB 8
+#define SB2_PLAN_MINB 16
 #endif
 #ifndef SB2_EXEC_MINB
 #define SB2_EXEC_MINB 8
