@@ -16,29 +16,78 @@ namespace sb2 {
 #if defined(SB2_NO_IDM)
 #define SB2_IS_IDM(m) false
 #else
-#define SB2_IS_IDM(m) ((m).model == CF_IDM)
+#define SB2_IS_IDM(m) ((m).model() == CF_IDM)
 #endif
 
+// The car-following parameters of one vehicle type.  With -DSB2_CF_TABLE a VIEW of the vType table (vType index + context): every use
+// is a load from a few-KB table that stays in L1 and is the same address for (most of) a warp.  Holding the 13 values in
+// registers for the whole of planMove costs 26 of the kernel's 32 registers, i.e. spills to local memory at two 32 B sectors
+// per thread and value (profiles/r01_k_plan_ncu.txt).  Default: the by-value copy (see DESIGN.md section 5 for the measured comparison).
+#if defined(__CUDA_ARCH__) && defined(SB2_CF_TABLE)
+// not CSE-able on purpose: the compiler would hoist the loads and keep (spill) the values again
+__device__ __forceinline__ double cf_tab(const double* p) { double v; asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p)); return v; }
+#else
+SB2_HD double cf_tab(const double* p) { return *p; }
+#endif
+#if defined(SB2_CF_TABLE)
 struct CF {
-    double TS;
-    double accel, decel, emergencyDecel, apparentDecel, tau, maxSpeed /* vType maxSpeed */, sigma;
-    int model;
-    double idmDelta, idmStepping;
-    double minGap, length;
-    SUMOTime startupDelay;
+    const Ctx* c;
+    int vt;
     double desSpeed;   // IDM only: veh->getLane()->getVehicleMaxSpeed(veh) of the EGO vehicle's current lane (set by the caller)
+    SB2_HD double TS() const { return c->TS; }
+    SB2_HD double accel() const { return cf_tab(c->vt_accel + vt); }
+    SB2_HD double decel() const { return cf_tab(c->vt_decel + vt); }
+    SB2_HD double emergencyDecel() const { return cf_tab(c->vt_emergencydecel + vt); }
+    SB2_HD double apparentDecel() const { return cf_tab(c->vt_apparentdecel + vt); }
+    SB2_HD double tau() const { return cf_tab(c->vt_tau + vt); }
+    SB2_HD double maxSpeed() const { return cf_tab(c->vt_maxspeed + vt); }   // vType maxSpeed
+    SB2_HD double sigma() const { return cf_tab(c->vt_sigma + vt); }
+    SB2_HD int model() const { return c->vt_cfmodel[vt]; }
+    SB2_HD double idmDelta() const { return cf_tab(c->vt_idm_delta + vt); }
+    SB2_HD double idmStepping() const { return cf_tab(c->vt_idm_stepping + vt); }
+    SB2_HD double minGap() const { return cf_tab(c->vt_mingap + vt); }
+    SB2_HD double length() const { return cf_tab(c->vt_length + vt); }
+    SB2_HD SUMOTime startupDelay() const { return c->vt_startupdelay[vt]; }
 };
 
 SB2_HD CF make_cf(const Ctx& c, int vt) {
     CF m;
-    m.TS = c.TS;
-    m.accel = c.vt_accel[vt]; m.decel = c.vt_decel[vt]; m.emergencyDecel = c.vt_emergencydecel[vt];
-    m.apparentDecel = c.vt_apparentdecel[vt]; m.tau = c.vt_tau[vt]; m.maxSpeed = c.vt_maxspeed[vt]; m.sigma = c.vt_sigma[vt];
-    m.model = c.vt_cfmodel[vt]; m.idmDelta = c.vt_idm_delta[vt]; m.idmStepping = c.vt_idm_stepping[vt];
-    m.minGap = c.vt_mingap[vt]; m.length = c.vt_length[vt]; m.startupDelay = c.vt_startupdelay[vt];
+    m.c = &c; m.vt = vt; m.desSpeed = 0.;
+    return m;
+}
+#else
+struct CF {
+    double TS_, accel_, decel_, emergencyDecel_, apparentDecel_, tau_, maxSpeed_, sigma_, idmDelta_, idmStepping_, minGap_, length_;
+    int model_;
+    SUMOTime startupDelay_;
+    double desSpeed;
+    SB2_HD double TS() const { return TS_; }
+    SB2_HD double accel() const { return accel_; }
+    SB2_HD double decel() const { return decel_; }
+    SB2_HD double emergencyDecel() const { return emergencyDecel_; }
+    SB2_HD double apparentDecel() const { return apparentDecel_; }
+    SB2_HD double tau() const { return tau_; }
+    SB2_HD double maxSpeed() const { return maxSpeed_; }
+    SB2_HD double sigma() const { return sigma_; }
+    SB2_HD int model() const { return model_; }
+    SB2_HD double idmDelta() const { return idmDelta_; }
+    SB2_HD double idmStepping() const { return idmStepping_; }
+    SB2_HD double minGap() const { return minGap_; }
+    SB2_HD double length() const { return length_; }
+    SB2_HD SUMOTime startupDelay() const { return startupDelay_; }
+};
+
+SB2_HD CF make_cf(const Ctx& c, int vt) {
+    CF m;
+    m.TS_ = c.TS;
+    m.accel_ = c.vt_accel[vt]; m.decel_ = c.vt_decel[vt]; m.emergencyDecel_ = c.vt_emergencydecel[vt];
+    m.apparentDecel_ = c.vt_apparentdecel[vt]; m.tau_ = c.vt_tau[vt]; m.maxSpeed_ = c.vt_maxspeed[vt]; m.sigma_ = c.vt_sigma[vt];
+    m.model_ = c.vt_cfmodel[vt]; m.idmDelta_ = c.vt_idm_delta[vt]; m.idmStepping_ = c.vt_idm_stepping[vt];
+    m.minGap_ = c.vt_mingap[vt]; m.length_ = c.vt_length[vt]; m.startupDelay_ = c.vt_startupdelay[vt];
     m.desSpeed = 0.;
     return m;
 }
+#endif
 
 // MSCFModel.cpp:101-108
 SB2_CORE double cfk_brakeGapEuler(double TS, double speed, double decel, double headwayTime) {
@@ -46,21 +95,21 @@ SB2_CORE double cfk_brakeGapEuler(double TS, double speed, double decel, double 
     const int steps = int(speed / speedReduction);
     return (steps * speed - speedReduction * steps * (steps + 1) / 2) * TS + speed * headwayTime;
 }
-SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) { return cfk_brakeGapEuler(m.TS, speed, decel, headwayTime); }
+SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) { return cfk_brakeGapEuler(m.TS(), speed, decel, headwayTime); }
 SB2_HD double cf_brakeGap(const CF& m, double speed, double decel, double headwayTime) { return cf_brakeGapEuler(m, speed, decel, headwayTime); }
 // MSCFModel.h: brakeGap(speed) = brakeGap(speed, myDecel, myHeadwayTime)
-SB2_HD double cf_brakeGap(const CF& m, double speed) { return cf_brakeGapEuler(m, speed, m.decel, m.tau); }
+SB2_HD double cf_brakeGap(const CF& m, double speed) { return cf_brakeGapEuler(m, speed, m.decel(), m.tau()); }
 
 // MSCFModel.cpp:324-326 (no accel profiles)
-SB2_HD double cf_maxNextSpeed(const CF& m, double speed) { return MIN2(speed + m.accel * m.TS, m.maxSpeed); }
+SB2_HD double cf_maxNextSpeed(const CF& m, double speed) { return MIN2(speed + m.accel() * m.TS(), m.maxSpeed()); }
 // MSCFModel.cpp:330-333
 // IDM: MSCFModel_IDM.cpp:80-88
 SB2_HD double cf_minNextSpeed(const CF& m, double speed) {
-    const double decel = SB2_IS_IDM(m) ? MAX2(m.decel, MIN2(m.emergencyDecel, 1.5)) : m.decel;
-    return MAX2(speed - decel * m.TS, 0.);
+    const double decel = SB2_IS_IDM(m) ? MAX2(m.decel(), MIN2(m.emergencyDecel(), 1.5)) : m.decel();
+    return MAX2(speed - decel * m.TS(), 0.);
 }
 // MSCFModel.cpp:341-343
-SB2_HD double cf_minNextSpeedEmergency(const CF& m, double speed) { return MAX2(speed - m.emergencyDecel * m.TS, 0.); }
+SB2_HD double cf_minNextSpeedEmergency(const CF& m, double speed) { return MAX2(speed - m.emergencyDecel() * m.TS(), 0.); }
 
 // MSCFModel.cpp:112-132 (Euler branch); freeSpeed(veh, speed, seen, maxSpeed, onInsertion) at :353-360
 SB2_CORE double cfk_freeSpeed(double TS, double decel, double dist, double targetSpeed, bool onInsertion) {
@@ -83,14 +132,14 @@ SB2_HD double cf_freeSpeed(const CF& m, double currentSpeed, double dist, double
     if (SB2_IS_IDM(m)) {
         return cf_idm_freeSpeed(m, currentSpeed, dist, targetSpeed);
     }
-    return cfk_freeSpeed(m.TS, m.decel, dist, targetSpeed, onInsertion);
+    return cfk_freeSpeed(m.TS(), m.decel(), dist, targetSpeed, onInsertion);
 }
 
 // MSCFModel.cpp:798-802
 SB2_CORE double cfk_estimateSpeedAfterDistance(double maxSpeed, double dist, double v, double accel) {
     return MIN2(maxSpeed, (double)sqrt(MAX2(0., 2 * dist * accel + v * v)));
 }
-SB2_HD double cf_estimateSpeedAfterDistance(const CF& m, double dist, double v, double accel) { return cfk_estimateSpeedAfterDistance(m.maxSpeed, dist, v, accel); }
+SB2_HD double cf_estimateSpeedAfterDistance(const CF& m, double dist, double v, double accel) { return cfk_estimateSpeedAfterDistance(m.maxSpeed(), dist, v, accel); }
 
 // MSCFModel.cpp:461-479
 SB2_CORE SUMOTime cfk_getMinimalArrivalTime(double mAccel, double mDecel, double dist, double currentSpeed, double arrivalSpeed) {
@@ -109,7 +158,7 @@ SB2_CORE SUMOTime cfk_getMinimalArrivalTime(double mAccel, double mDecel, double
     return TIME2STEPS(-(currentSpeed - sqrt(currentSpeed * currentSpeed + 2 * accel * dist)) / accel);
 }
 SB2_HD SUMOTime cf_getMinimalArrivalTime(const CF& m, double dist, double currentSpeed, double arrivalSpeed) {
-    return cfk_getMinimalArrivalTime(m.accel, m.decel, dist, currentSpeed, arrivalSpeed);
+    return cfk_getMinimalArrivalTime(m.accel(), m.decel(), dist, currentSpeed, arrivalSpeed);
 }
 
 // MSCFModel.cpp:578-591
@@ -117,10 +166,10 @@ SB2_HD double cf_getMinimalArrivalSpeedEuler(const CF& m, double dist, double cu
     double arrivalSpeedBraking;
     if (dist < currentSpeed) {
         arrivalSpeedBraking = SB2_INVALID_SPEED;
-    } else if (2 * (dist - currentSpeed * m.tau) * -m.decel + currentSpeed * currentSpeed >= 0) {
-        arrivalSpeedBraking = cf_estimateSpeedAfterDistance(m, dist - currentSpeed * m.tau, currentSpeed, -m.decel);
+    } else if (2 * (dist - currentSpeed * m.tau()) * -m.decel() + currentSpeed * currentSpeed >= 0) {
+        arrivalSpeedBraking = cf_estimateSpeedAfterDistance(m, dist - currentSpeed * m.tau(), currentSpeed, -m.decel());
     } else {
-        arrivalSpeedBraking = m.decel;
+        arrivalSpeedBraking = m.decel();
     }
     return arrivalSpeedBraking;
 }
@@ -139,7 +188,7 @@ SB2_CORE double cfk_calculateEmergencyDeceleration(double emergencyDecel, double
     return b2;
 }
 SB2_HD double cf_calculateEmergencyDeceleration(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel) {
-    return cfk_calculateEmergencyDeceleration(m.emergencyDecel, gap, egoSpeed, predSpeed, predMaxDecel);
+    return cfk_calculateEmergencyDeceleration(m.emergencyDecel(), gap, egoSpeed, predSpeed, predMaxDecel);
 }
 
 // MSCFModel.cpp:860-884
@@ -158,19 +207,19 @@ SB2_CORE double cfk_maximumSafeStopSpeedEuler(double TS, double tau, double gap,
     return x;
 }
 SB2_HD double cf_maximumSafeStopSpeedEuler(const CF& m, double gap, double decel, double headway) {
-    return cfk_maximumSafeStopSpeedEuler(m.TS, m.tau, gap, decel, headway);
+    return cfk_maximumSafeStopSpeedEuler(m.TS(), m.tau(), gap, decel, headway);
 }
 
 // MSCFModel.cpp:807-856
 SB2_HD double cf_maximumSafeStopSpeed(const CF& m, double gap, double decel, double currentSpeed, bool /*onInsertion*/, double headway, bool relaxEmergency) {
     double vsafe = cf_maximumSafeStopSpeedEuler(m, gap, decel, headway);
-    if (relaxEmergency && m.decel != m.emergencyDecel) {
-        double origSafeDecel = (currentSpeed - vsafe) / m.TS;
-        if (origSafeDecel > m.decel + SB2_NUMERICAL_EPS) {
+    if (relaxEmergency && m.decel() != m.emergencyDecel()) {
+        double origSafeDecel = (currentSpeed - vsafe) / m.TS();
+        if (origSafeDecel > m.decel() + SB2_NUMERICAL_EPS) {
             double safeDecel = SB2_EMERGENCY_DECEL_AMPLIFIER * cf_calculateEmergencyDeceleration(m, gap, currentSpeed, 0., 1);
-            safeDecel = MAX2(safeDecel, m.decel);
+            safeDecel = MAX2(safeDecel, m.decel());
             safeDecel = MIN2(safeDecel, origSafeDecel);
-            vsafe = currentSpeed - safeDecel * m.TS;
+            vsafe = currentSpeed - safeDecel * m.TS();
             vsafe = MAX2(vsafe, 0.);
         }
     }
@@ -179,21 +228,21 @@ SB2_HD double cf_maximumSafeStopSpeed(const CF& m, double gap, double decel, dou
 
 // MSCFModel.cpp:958-1034 (gComputeLC false outside the lane changer)
 SB2_HD double cf_maximumSafeFollowSpeed(const CF& m, double gap, double egoSpeed, double predSpeed, double predMaxDecel, bool onInsertion, bool computeLC) {
-    const double headway = m.tau;
+    const double headway = m.tau();
     double x;
     if (gap >= 0 || computeLC) {
-        x = cf_maximumSafeStopSpeed(m, gap + cf_brakeGap(m, predSpeed, MAX2(m.decel, predMaxDecel), 0), m.decel, egoSpeed, onInsertion, headway, false);
+        x = cf_maximumSafeStopSpeed(m, gap + cf_brakeGap(m, predSpeed, MAX2(m.decel(), predMaxDecel), 0), m.decel(), egoSpeed, onInsertion, headway, false);
     } else {
-        x = egoSpeed - m.emergencyDecel * m.TS;
+        x = egoSpeed - m.emergencyDecel() * m.TS();
         x = MAX2(x, 0.);
     }
-    if (m.decel != m.emergencyDecel && !onInsertion && !computeLC) {
-        double origSafeDecel = (egoSpeed - x) / m.TS;
-        if (origSafeDecel > m.decel + SB2_NUMERICAL_EPS) {
+    if (m.decel() != m.emergencyDecel() && !onInsertion && !computeLC) {
+        double origSafeDecel = (egoSpeed - x) / m.TS();
+        if (origSafeDecel > m.decel() + SB2_NUMERICAL_EPS) {
             double safeDecel = SB2_EMERGENCY_DECEL_AMPLIFIER * cf_calculateEmergencyDeceleration(m, gap, egoSpeed, predSpeed, predMaxDecel);
-            safeDecel = MAX2(safeDecel, m.decel);
+            safeDecel = MAX2(safeDecel, m.decel());
             safeDecel = MIN2(safeDecel, origSafeDecel);
-            x = egoSpeed - safeDecel * m.TS;
+            x = egoSpeed - safeDecel * m.TS();
             x = MAX2(x, 0.);
         }
     }
@@ -247,13 +296,13 @@ SB2_CORE double cfk_idm_v(double TS, double accel, double decel, double tau, dou
     return MAX2(0., newSpeed);
 }
 SB2_HD double cf_idm_v(const CF& m, double egoSpeed, double gap2pred, double predSpeed, double desSpeed, bool respectMinGap) {
-    return cfk_idm_v(m.TS, m.accel, m.decel, m.tau, m.minGap, m.idmDelta, m.idmStepping, egoSpeed, gap2pred, predSpeed, desSpeed, respectMinGap);
+    return cfk_idm_v(m.TS(), m.accel(), m.decel(), m.tau(), m.minGap(), m.idmDelta(), m.idmStepping(), egoSpeed, gap2pred, predSpeed, desSpeed, respectMinGap);
 }
 
 // MSCFModel_IDM::getSecureGap (MSCFModel_IDM.cpp:228-231)
 SB2_HD double cf_idm_secureGap(const CF& m, double speed, double leaderSpeed) {
     const double delta_v = speed - leaderSpeed;
-    return MAX2(0.0, speed * m.tau + speed * delta_v / (2 * sqrt(m.accel * m.decel)));
+    return MAX2(0.0, speed * m.tau() + speed * delta_v / (2 * sqrt(m.accel() * m.decel())));
 }
 // MSCFModel_IDM::freeSpeed (MSCFModel_IDM.cpp:104-122)
 SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double maxSpeed) {
@@ -283,16 +332,16 @@ SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap, double decel, 
         }
         double result = cf_idm_v(m, speed, gap, 0, m.desSpeed, false);
         if (gap > 0 && speed < SB2_NUMERICAL_EPS && result < SB2_NUMERICAL_EPS) {
-            result = cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS, false);
+            result = cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS(), false);
         }
         if (gap >= 0) {
-            result = MIN2(result, gap / m.TS);
+            result = MIN2(result, gap / m.TS());
         }
         return result;
     }
-    return MIN2(cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS /* actionStepLengthSecs */, !future), cf_maxNextSpeed(m, speed));
+    return MIN2(cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS() /* actionStepLengthSecs */, !future), cf_maxNextSpeed(m, speed));
 }
-SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel, false); }
+SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel(), false); }
 
 // followSpeed: MSCFModel_Krauss.cpp:138-152 (Euler branch)
 // IDM: MSCFModel_IDM.cpp:126-133
@@ -309,13 +358,13 @@ SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predS
 SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred, double predSpeed, double predMaxDecel) {
     if (SB2_IS_IDM(m)) {
         for (int guard = 0; guard < 1000; guard++) {
-            const double s = MAX2(0., speed * m.tau + speed * (speed - predSpeed) / (2 * sqrt(m.accel * m.decel)));
+            const double s = MAX2(0., speed * m.tau() + speed * (speed - predSpeed) / (2 * sqrt(m.accel() * m.decel())));
             if (gap2pred >= s) {
                 return speed;
             }
             const double speed2 = cf_followSpeed(m, speed, gap2pred, predSpeed, predMaxDecel);
             const double speed3 = cf_followSpeed(m, speed2, gap2pred, predSpeed, predMaxDecel);
-            if (speed2 - speed3 < 1 * m.TS) {
+            if (speed2 - speed3 < 1 * m.TS()) {
                 return speed2;
             }
             speed = speed2;
@@ -327,12 +376,12 @@ SB2_HD double cf_insertionFollowSpeed(const CF& m, double speed, double gap2pred
 // MSCFModel.cpp:375-377
 // IDM: MSCFModel_IDM.cpp:164-174 (base MSCFModel::insertionStopSpeed = stopSpeed(..., FUTURE))
 SB2_HD double cf_insertionStopSpeed(const CF& m, double speed, double gap) {
-    double result = cf_stopSpeed(m, speed, gap, m.decel, true);
+    double result = cf_stopSpeed(m, speed, gap, m.decel(), true);
     if (SB2_IS_IDM(m)) {
         int i = 0;
-        while (result - speed < -(m.decel * m.TS) && ++i < 10) {
+        while (result - speed < -(m.decel() * m.TS()) && ++i < 10) {
             speed = result;
-            result = cf_stopSpeed(m, speed, gap, m.decel, true);
+            result = cf_stopSpeed(m, speed, gap, m.decel(), true);
         }
     }
     return result;
@@ -343,9 +392,9 @@ SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, dou
     if (SB2_IS_IDM(m)) {
         return cf_idm_secureGap(m, speed, leaderSpeed);
     }
-    const double maxDecel = MAX2(m.decel, leaderMaxDecel);
+    const double maxDecel = MAX2(m.decel(), leaderMaxDecel);
     const double bgLeader = cf_brakeGap(m, leaderSpeed, maxDecel, 0);
-    return MAX2(0.0, cf_brakeGap(m, speed, m.decel, m.tau) - bgLeader);
+    return MAX2(0.0, cf_brakeGap(m, speed, m.decel(), m.tau()) - bgLeader);
 }
 
 // MSCFModel_Krauss.cpp:155-176 ; random in [0,1)
@@ -353,10 +402,10 @@ SB2_HD double cf_dawdle2(const CF& m, double speed, double sigma, double random)
     if (SB2_IS_IDM(m)) {
         return speed;   // MSCFModel::patchSpeedBeforeLC (MSCFModel.h) returns vMax: no dawdling, no draw
     }
-    if (speed < m.accel) {
-        speed -= (sigma * speed * random) * m.TS;
+    if (speed < m.accel()) {
+        speed -= (sigma * speed * random) * m.TS();
     } else {
-        speed -= (sigma * m.accel * random) * m.TS;
+        speed -= (sigma * m.accel() * random) * m.TS();
     }
     return MAX2(0., speed);
 }

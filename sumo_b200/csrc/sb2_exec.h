@@ -32,7 +32,7 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
     haveToWait = false;
     bool canBrakeVSafeMin = false;
     const int n = c.veh_ndi[cur][wp];
-    const double vehLength = cf.length;
+    const double vehLength = cf.length();
     for (int i = 0; i < n; i++) {
         const size_t r = (size_t)i * c.nV + wp;
         const int link = c.di_link[cur][r];
@@ -43,8 +43,8 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
         if (link >= 0 && setRequest) {
             const uint8_t ls = c.link_state[link];
             const bool yellow = state_yellow(ls);
-            const bool canBrake = (dpiDist > cf_brakeGap(cf, speed, cf.decel, 0.)
-                                   || (speed < cf.decel * c.TS));
+            const bool canBrake = (dpiDist > cf_brakeGap(cf, speed, cf.decel(), 0.)
+                                   || (speed < cf.decel() * c.TS));
             const bool beyondStopLine = dpiDist < 0.;   // getVehicleStopOffset == 0
             const bool ignoreRedLink = false || beyondStopLine;
             if (yellow && canBrake && !ignoreRedLink) {
@@ -56,7 +56,7 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
             const double leaveSpeed = accelV < 0 ? vLinkPass : accelV;
             bool opened = (yellow
                            || link_opened(c, link, cur, c.di_arrtime[cur][r], c.di_arrspeed[cur][r], leaveSpeed,
-                                          vehLength, canBrake ? veh_impatience(c, v) : 1, cf.decel, waiting, ignoreRedLink, v, true));
+                                          vehLength, canBrake ? veh_impatience(c, v) : 1, cf.decel(), waiting, ignoreRedLink, v, true));
             const double visibilityDistance = c.link_foevis[link];
             const bool determinedFoePresence = dpiDist <= visibilityDistance;
             if (opened && !state_priority(ls) && !link_lastWasContMajor(c, link) && !link_isCont(c, link) && !ignoreRedLink) {
@@ -72,14 +72,14 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
             }
             if (opened) {
                 vSafe = vLinkPass;
-                if (vSafe < cf.decel && vSafe <= vLinkWait && vSafe < cf_maxNextSpeed(cf, speed)) {
+                if (vSafe < cf.decel() && vSafe <= vLinkWait && vSafe < cf_maxNextSpeed(cf, speed)) {
                     haveToWait = true;
                 }
             } else if (ls == 'Z') {
                 raise(c, ERR_UNSUPPORTED_LINKSTATE);
             } else if (!canBrake
                        && c.link_tl[link] < 0
-                       && dpiDist < cf_brakeGap(cf, speed, cf.emergencyDecel, 0.)) {
+                       && dpiDist < cf_brakeGap(cf, speed, cf.emergencyDecel(), 0.)) {
                 vSafe = vLinkPass;
             } else {
                 vSafe = vLinkWait;
@@ -130,11 +130,11 @@ SB2_HD double cf_finalizeSpeed(const Ctx& c, const CF& cf, int v, int lane, doub
     double aMax = (MAX2(lane_vehicle_max_speed(c, lane, v), vPos) * factor - oldV) / c.TS;
     double vMax = MIN3(oldV + aMax * c.TS, cf_maxNextSpeed(cf, oldV), vStop);
     vMax = MAX2(vMin, vMax);
-    double vNext = MAX2(vMin, cf_dawdle2(cf, vMax, cf.sigma, random));
+    double vNext = MAX2(vMin, cf_dawdle2(cf, vMax, cf.sigma(), random));
     // MSLCM_LC2013::patchSpeed is the identity while the vehicle carries no lane-change state (single-lane edges)
     // applyStartupDelay (MSCFModel.cpp:269-285)
-    if (timeSinceStartup > 0 && timeSinceStartup - c.DELTA_T < cf.startupDelay) {
-        const SUMOTime remainingDelay = cf.startupDelay - (timeSinceStartup - c.DELTA_T);
+    if (timeSinceStartup > 0 && timeSinceStartup - c.DELTA_T < cf.startupDelay()) {
+        const SUMOTime remainingDelay = cf.startupDelay() - (timeSinceStartup - c.DELTA_T);
         if (remainingDelay >= c.DELTA_T) {
             vNext = 0;
         } else {
@@ -186,7 +186,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     double vNext = vSafe;
     const double rawAccel = (MAX2(vNext, 0.) - oldSpeed) / c.TS;
     SUMOTime timeSinceStartup = c.veh_since_startup[v];
-    if (vNext <= SB2_HALTING_SPEED * c.TS && waiting > c.startupWaitThreshold && rawAccel <= 0.5 * cf.accel) {
+    if (vNext <= SB2_HALTING_SPEED * c.TS && waiting > c.startupWaitThreshold && rawAccel <= 0.5 * cf.accel()) {
         timeSinceStartup = 0;
     } else {
         timeSinceStartup += c.DELTA_T;
@@ -209,7 +209,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     pos += deltaPos;
     double lastDist = deltaPos;
     // updateWaitingTime (MSVehicle.cpp:4291-4302)
-    if (vNext <= SB2_HALTING_SPEED && accel <= 0.5 * cf.accel) {
+    if (vNext <= SB2_HALTING_SPEED && accel <= 0.5 * cf.accel()) {
         waiting += c.DELTA_T;
     } else {
         waiting = 0;
@@ -316,7 +316,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
             accelOut = 0;
         }
         // updateFurtherLanes (MSVehicle.cpp:5055-5131)
-        double backPosOnPreviousLane = pos - cf.length;
+        double backPosOnPreviousLane = pos - cf.length();
         int newFurther[MAX_FURTHER];
         if (np > 1) {
             for (int pi = np - 2; pi >= 0 && backPosOnPreviousLane < 0; --pi) {
@@ -350,7 +350,7 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     c.veh_odometer[v] = odometer;
     c.veh_trip_routelen[v] = tripRouteLen;
     // MSDevice_Tripinfo::notifyMove (not stopped): waiting = slow and not accelerating (accelThresholdForWaiting, MSVehicle.h:2100)
-    if (speed <= SB2_HALTING_SPEED && accelOut <= 0.5 * cf.accel) {
+    if (speed <= SB2_HALTING_SPEED && accelOut <= 0.5 * cf.accel()) {
         c.veh_trip_wait[v] += c.DELTA_T;
         if (!c.veh_trip_amwaiting[v]) {
             c.veh_trip_waitcount[v] += 1;

@@ -145,7 +145,7 @@ SB2_HD bool ins_checkFailure(const CF& cf, double& speed, double& dist, double n
     if (nspeed < speed) {
         if (patchSpeed) {
             speed = MIN2(nspeed, speed);
-            dist = cf_brakeGap(cf, speed) + cf.minGap;
+            dist = cf_brakeGap(cf, speed) + cf.minGap();
         } else if (speed > 0) {
             return true;
         }
@@ -157,7 +157,7 @@ SB2_HD bool ins_checkFailure(const CF& cf, double& speed, double& dist, double n
 SB2_HD double lane_safeInsertionSpeed(const Ctx& c, int l, const CF& cf, double seen, int leader, double speed) {
     double nspeed = speed;
     if (leader >= 0) {
-        const double gap = veh_back_pos_on_lane(c, leader, l) + seen - cf.minGap;
+        const double gap = veh_back_pos_on_lane(c, leader, l) + seen - cf.minGap();
         if (gap < 0) {
             return SB2_INVALID_SPEED;
         }
@@ -216,14 +216,14 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
             pos += c.lane_length[l];
         }
     } else {
-        pos = MIN2(cf.length + SB2_POSITION_EPS, c.lane_length[l]);   // basePos (edge min length == lane length: one lane per edge)
+        pos = MIN2(cf.length() + SB2_POSITION_EPS, c.lane_length[l]);   // basePos (edge min length == lane length: one lane per edge)
     }
     if (pos < 0 || pos > c.lane_length[l]) {
         pos = c.lane_length[l];
     }
     // ---- isInsertionSuccess
     double seen = c.lane_length[l] - pos;
-    double dist = cf_brakeGap(cf, speed) + cf.minGap;
+    double dist = cf_brakeGap(cf, speed) + cf.minGap();
     const bool patchSpeedSpecial = patchSpeed || dsd != DSD_GIVEN;
     // leader on the insertion lane: getLastVehicleInformation(aVehicle, 0, pos)
     int leader = -1;
@@ -243,7 +243,7 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     // continuation lanes
     Ego e;
     e.v = v; e.vt = c.veh_type[v]; e.lane = l; e.pos = pos; e.speed = 0. /* getSpeed() of a not yet departed vehicle */;
-    e.cf = cf; e.length = cf.length; e.minGap = cf.minGap; e.waiting = 0;
+    e.cf = cf; e.length = cf.length(); e.minGap = cf.minGap(); e.waiting = 0;
     int nRouteSuccs = 1;
     int currentLane = l;
     const int r = c.veh_route[v];
@@ -265,14 +265,14 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
         }
         const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
         const uint8_t state = c.link_state[link];
-        if (!link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length, veh_impatience(c, v), cf.decel, 0, false, v)
+        if (!link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v)
                 || !state_priority(state)
                 || state == 'Z') {
             const double remaining = seen - 0.;
             if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, remaining), patchSpeedSpecial)) {
                 return false;
             }
-            if (seen >= cf.minGap) {
+            if (seen >= cf.minGap()) {
                 break;
             }
         } else if (lane_internal(c, nextLane)) {
@@ -296,15 +296,15 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
         if (freeSpeed < speed) {
             if (patchSpeedSpecial) {
                 speed = freeSpeed;
-                dist = cf_brakeGap(cf, speed) + cf.minGap;
+                dist = cf_brakeGap(cf, speed) + cf.minGap();
             }
             // else: warning only (gCheckRoutes false is not the default; the reference deschedules -> treat as failure)
             else {
                 return false;
             }
         }
-        const SUMOTime leaveTime = link_getLeaveTime(c, link, arrivalTime, speed, speed, cf.length);
-        if (link_hasApproachingFoe(c, link, c.cur, arrivalTime, leaveTime, speed, cf.decel)) {
+        const SUMOTime leaveTime = link_getLeaveTime(c, link, arrivalTime, speed, speed, cf.length());
+        if (link_hasApproachingFoe(c, link, c.cur, arrivalTime, leaveTime, speed, cf.decel())) {
             if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeed)) {
                 return false;
             }
@@ -317,11 +317,11 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
         }
     }
     // followers
-    const double backOffset = pos - cf.length;
-    const FollowerInfo fi = lane_followers_on_consecutive(c, l, v, cf.length, cf.decel, backOffset);
+    const double backOffset = pos - cf.length();
+    const FollowerInfo fi = lane_followers_on_consecutive(c, l, v, cf.length(), cf.decel(), backOffset);
     if (fi.veh >= 0) {
         const CF fcf = make_cf(c, c.veh_type[fi.veh]);
-        const double backGapNeeded = cf_getSecureGap(fcf, c.veh_speed[fi.veh], speed, cf.decel);
+        const double backGapNeeded = cf_getSecureGap(fcf, c.veh_speed[fi.veh], speed, cf.decel());
         if (fi.dist < backGapNeeded) {
             return false;
         }
@@ -350,13 +350,13 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
         c.lane_last[l] = v;
     }
     c.lane_nveh[l] += 1;
-    c.lane_brutto[l] += cf.length + cf.minGap;
+    c.lane_brutto[l] += cf.length() + cf.minGap();
     c.veh_lane[v] = l;
     c.veh_routepos[v] = 0;
     c.veh_pos[v] = pos;
     c.veh_speed[v] = speed;
     c.veh_prevspeed[v] = speed;
-    c.veh_backpos[v] = pos - cf.length;
+    c.veh_backpos[v] = pos - cf.length();
     c.veh_accel[v] = 0;
     c.veh_lastdist[v] = 0;
     c.veh_waiting[v] = 0;
@@ -376,8 +376,8 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     c.veh_stopspeed[v] = SB2_DBL_MAX;
     // MSVehicleControl::vehicleDeparted
     atomic_max_double(&c.fleet_next[0], c.veh_speedfactor[v]);
-    atomic_min_double(&c.fleet_next[1], cf.decel);
-    atomic_max_double(&c.fleet_next[2], cf.minGap);
+    atomic_min_double(&c.fleet_next[1], cf.decel());
+    atomic_max_double(&c.fleet_next[2], cf.minGap());
     atomic_inc(&c.counters[2]);
     return true;
 }

@@ -39,7 +39,7 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1)
             found = true;
             const CF cf = make_cf(c, c.veh_type[last]);
             const double lastBrakeGap = cf_brakeGap(cf, c.veh_speed[last]);
-            ret = (c.veh_pos[last] - cf.length) + lastBrakeGap - lengths;
+            ret = (c.veh_pos[last] - cf.length()) + lastBrakeGap - lengths;
             break;
         }
         lengths += veh_length_with_gap(c, last);

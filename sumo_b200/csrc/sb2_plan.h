@@ -80,8 +80,8 @@ SB2_HD bool veh_isLeader(const Ctx& c, const Ego& e, int link, int veh, double g
                     if (!state_red(fs) && c.veh_speed[veh] > SB2_HALTING_SPEED && gap < 0) {
                         const int ft = c.veh_type[veh];
                         const CF fcf = make_cf(c, ft);
-                        const double foeNextSpeed = c.veh_speed[veh] + fcf.accel * c.TS;
-                        const double foeBrakeGap = cf_brakeGap(fcf, foeNextSpeed, fcf.decel, fcf.tau);
+                        const double foeNextSpeed = c.veh_speed[veh] + fcf.accel() * c.TS;
+                        const double foeBrakeGap = cf_brakeGap(fcf, foeNextSpeed, fcf.decel(), fcf.tau());
                         const double foeGap = -gap - c.vt_length[ft] - 2 * e.minGap;
                         if (foeGap < foeBrakeGap) {
                             response = true; response2 = false;

@@ -76,7 +76,7 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
                                  || i == 1
                                  || link_opened(c, item.link, tableBuf, item.arrivalTime, item.arrivalSpeed,
                                                 di_getLeaveSpeed(item), e.length,
-                                                veh_impatience(c, e.v), e.cf.decel, e.waiting, false, e.v)));
+                                                veh_impatience(c, e.v), e.cf.decel(), e.waiting, false, e.v)));
         bool allowsContinuation = (item.link < 0 || link_isCont(c, item.link) || opened) && !item.hadStoppedVehicle;
         if (!opened && item.link >= 0) {
             foundStopped = true;
@@ -108,7 +108,7 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
     }
     // abort requests
     if (removalBegin != -1 && !(removalBegin == 0 && lane_internal(c, e.lane))) {
-        const double brakeGap = cf_brakeGap(e.cf, e.speed, e.cf.decel, 0.);
+        const double brakeGap = cf_brakeGap(e.cf, e.speed, e.cf.decel(), 0.);
         while (removalBegin < n) {
             DriveItem& dpi = lf[removalBegin];
             if (dpi.link < 0) {
@@ -141,7 +141,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     e.pos = c.veh_pos[v]; e.speed = c.veh_speed[v];
     e.cf = make_cf(c, e.vt);
     e.cf.desSpeed = lane_vehicle_max_speed(c, myLane, v);
-    e.length = e.cf.length; e.minGap = e.cf.minGap;
+    e.length = e.cf.length(); e.minGap = e.cf.minGap();
     e.waiting = c.veh_waiting[v];
     const CF& cf = e.cf;
 
@@ -173,7 +173,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     double seen = c.lane_length[myLane] - e.pos;
     double seenNonInternal = 0;
     double seenInternal = lane_internal(c, myLane) ? seen : 0;
-    double vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, seen, vv, cf.accel), laneMaxV);
+    double vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, seen, vv, cf.accel()), laneMaxV);
     int view = 0;
     DriveItem* lastLink = nullptr;
     bool slowedDownForMinor = false;
@@ -214,7 +214,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         const bool yellowOrRed = state_red(lstate) || state_yellow(lstate);
         double laneStopOffset;
         const double majorStopOffset = MAX2(SB2_DIST_TO_STOPLINE_EXPECT_PRIORITY, 0.);
-        const double stopDecel = yellowOrRed ? MAX2(MIN2(c.tlsYellowMinDecel, cf.emergencyDecel), cf.decel) : cf.decel;
+        const double stopDecel = yellowOrRed ? MAX2(MIN2(c.tlsYellowMinDecel, cf.emergencyDecel()), cf.decel()) : cf.decel();
         const double brakeDist = cf_brakeGap(cf, e.speed, stopDecel, 0);
         const bool canBrakeBeforeLaneEnd = seen >= brakeDist;
         const bool canBrakeBeforeStopLine = seen - 0 >= brakeDist;
@@ -263,8 +263,8 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         const bool determinedFoePresence = seen <= visibilityDistance;
         const bool couldBrakeForMinor = !state_priority(lstate) && brakeDist < seen && !link_lastWasContMajor(c, link);
         if (couldBrakeForMinor && !determinedFoePresence) {
-            double maxSpeedAtVisibilityDist = cf_maximumSafeStopSpeed(cf, visibilityDistance, cf.decel, e.speed, false, 0., false);
-            double maxArrivalSpeed = cf_estimateSpeedAfterDistance(cf, visibilityDistance, maxSpeedAtVisibilityDist, cf.accel);
+            double maxSpeedAtVisibilityDist = cf_maximumSafeStopSpeed(cf, visibilityDistance, cf.decel(), e.speed, false, 0., false);
+            double maxArrivalSpeed = cf_estimateSpeedAfterDistance(cf, visibilityDistance, maxSpeedAtVisibilityDist, cf.accel());
             arrivalSpeed = MIN2(vLinkPass, maxArrivalSpeed);
             slowedDownForMinor = true;
         } else if (lstate == '=' && e.waiting > 0) {
@@ -274,7 +274,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         const SUMOTime arrivalTime = veh_getArrivalTime(c, e, t, seen, vv, arrivalSpeed);
         if (couldBrakeForMinor && determinedFoePresence && (c.lane_flags[c.link_to[link]] & LF_ROUNDABOUT)) {
             const bool wasOpened = link_opened(c, link, prev, arrivalTime, arrivalSpeed, arrivalSpeed, e.length, veh_impatience(c, v),
-                                               cf.decel, e.waiting, false, v);
+                                               cf.decel(), e.waiting, false, v);
             if (!wasOpened) {
                 slowedDownForMinor = true;
             }
@@ -287,7 +287,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         }
         const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
         const double estimatedLeaveSpeed = MIN2(lane_vehicle_max_speed(c, nextLane, v, maxVD),
-                                                cf_estimateSpeedAfterDistance(cf, c.link_length[link], arrivalSpeed, cf.accel));
+                                                cf_estimateSpeedAfterDistance(cf, c.link_length[link], arrivalSpeed, cf.accel()));
         SB2_PUSH(di_make(link, vv, vLinkWait, setRequest, arrivalTime, arrivalSpeed, arrivalSpeedBraking, seen, estimatedLeaveSpeed));
         if (c.link_via[link] < 0) {
             hadNonInternal = true;
@@ -313,7 +313,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         leaderLane = lane;
         ahead = SB2_CHK(lane_last_any(c, SB2_CHK(leaderLane, 0, c.nL, 4)), -1, c.nV, 5);   // getLastVehicleInformation(nullptr, 0)
         seen += c.lane_length[lane];
-        vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, c.lane_length[lane], vv, cf.accel), laneMaxV);
+        vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, c.lane_length[lane], vv, cf.accel()), laneMaxV);
         lastLink = &lf[n - 1];
     }
 #undef SB2_PUSH
