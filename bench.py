@@ -26,6 +26,8 @@ sys.path.insert(0, ROOT)
 
 BASE = os.path.join(ROOT, "tests", "golden", "bench_grid10_tls")
 VEH_PER_TILE = 1800
+TLS_CYCLE_STEPS = 90        # every traffic light of the workload runs the same 90 s program with offset 0: the cost of a step is periodic in it
+PROF_STEPS = TLS_CYCLE_STEPS  # window of the per-kernel (roofline) timing: one whole cycle
 SPINUP_STEPS = 420          # all departures happen in [0, 300 + 16) s; afterwards the resident count is constant
 # algorithmic bytes per vehicle-update (SURVEY.md section 8d / DESIGN.md "roofline"): whole step, and the plan kernel alone
 BYTES_PER_UPDATE_STEP = 576
@@ -195,7 +197,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=TLS_CYCLE_STEPS)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--vehicles", type=int, default=1000000, help="resident vehicles per GPU")
@@ -272,7 +274,7 @@ def main():
     # ---- roofline of the dominant kernel (k_plan): per-phase CUDA events on the engine's stream
     eng.set_profiling(True)
     eng.phase_times(reset=True)
-    r2 = eng.step(20)
+    r2 = eng.step(PROF_STEPS)
     phases = eng.phase_times(reset=True)
     eng.set_profiling(False)
     prof_updates = r2.vehicle_updates - rr.vehicle_updates
@@ -292,8 +294,8 @@ def main():
 
     peak, peak_src = measured_peak_gbs()
     value = updates / (ms / 1000.0)
-    plan_ms = phases["plan"] / 20.0
-    plan_gbs = BYTES_PER_UPDATE_PLAN * (prof_updates / 20.0) / (plan_ms / 1000.0) / 1e9
+    plan_ms = phases["plan"] / PROF_STEPS
+    plan_gbs = BYTES_PER_UPDATE_PLAN * (prof_updates / PROF_STEPS) / (plan_ms / 1000.0) / 1e9
     line = {
         "metric": "vehicle-updates/s", "value": value, "unit": "veh*steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -311,7 +313,7 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "k_plan", "achieved": plan_gbs, "peak": peak, "unit": "GB/s", "frac": plan_gbs / peak,
                      "traffic": NCU_PLAN_TRAFFIC_BYTES if nV == 1000800 else None, "traffic_source": "profiles/r01_k_plan_ncu.txt (dram__bytes_read.sum + dram__bytes_write.sum, one launch, 1,000,800 vehicles)",
                      "peak_source": peak_src, "bytes_per_update": BYTES_PER_UPDATE_PLAN, "kernel_ms": plan_ms,
-                     "phase_ms_per_step": {k: v / 20.0 for k, v in phases.items()},
+                     "phase_ms_per_step": {k: v / PROF_STEPS for k, v in phases.items()},
                      "whole_step": {"bytes_per_update": BYTES_PER_UPDATE_STEP, "achieved": BYTES_PER_UPDATE_STEP * value / 1e9,
                                     "frac": BYTES_PER_UPDATE_STEP * value / 1e9 / (peak * world)}},
     }
