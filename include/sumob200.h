@@ -152,6 +152,14 @@ int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out);
  * capacity = number of doubles in out (>= 7 * n).  SUMOB200_EUNSUPPORTED if no vehicle carries the emission device. */
 int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity);
 
+/* TraCI-style traffic light control between two steps.  tls = index of the program in the flattened scenario (tl_names).
+ * _set_phase = libsumo::TrafficLight::setPhase (src/libsumo/TrafficLight.cpp:823-832): switch to `phase` now, its full duration
+ * starts now (MSSimpleTrafficLightLogic::changeStepAndDuration, MSSimpleTrafficLightLogic.cpp:294-309); a phase index out of
+ * range is SUMOB200_EINVAL with TraCI's message.  _get_phase = getPhase / getNextSwitch. */
+int sumob200_num_tls(const sumob200_engine* e);
+int sumob200_tls_set_phase(sumob200_engine* e, int tls, int phase);
+int sumob200_tls_get_phase(sumob200_engine* e, int tls, int* phase, int64_t* next_switch_ms);
+
 int sumob200_num_vehicles(const sumob200_engine* e);
 int sumob200_num_lanes(const sumob200_engine* e);
 int64_t sumob200_time_ms(const sumob200_engine* e);

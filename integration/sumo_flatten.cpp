@@ -65,6 +65,7 @@
 #include <list>
 #include <set>
 #include <traci-server/TraCIServer.h>
+#include <libsumo/TrafficLight.h>
 
 #include <algorithm>
 #include <map>
@@ -702,7 +703,7 @@ predictDraws(MSNet* net) {
 
 int
 main(int argc, char** argv) {
-    std::string flatOut, traceOut, drawsOut, emisOut;
+    std::string flatOut, traceOut, drawsOut, emisOut, tlsSetPhase;
     std::vector<char*> args;
     args.push_back(argv[0]);
     for (int i = 1; i < argc; i++) {
@@ -713,6 +714,8 @@ main(int argc, char** argv) {
             traceOut = argv[++i];
         } else if (a == "--draws-out" && i + 1 < argc) {
             drawsOut = argv[++i];
+        } else if (a == "--tls-set-phase" && i + 1 < argc) {
+            tlsSetPhase = argv[++i];   // "timeMs:tlsID:phase;..." -> libsumo::TrafficLight::setPhase before the step at that time (what a TraCI client does)
         } else if (a == "--emissions-out" && i + 1 < argc) {
             emisOut = argv[++i];   // per step: (t, n) then n x (numerical id, 7 fp64 accumulators of MSDevice_Emissions) as raw bytes
         } else {
@@ -753,9 +756,19 @@ main(int argc, char** argv) {
             const SUMOTime begin = string2time(oc.getString("begin"));
             const SUMOTime end = string2time(oc.getString("end"));
             MSNet::SimulationState state = MSNet::SIMSTATE_RUNNING;
+            std::multimap<SUMOTime, std::pair<std::string, int> > phaseEvents;
+            for (const std::string& ev : StringTokenizer(tlsSetPhase, ";").getVector()) {
+                const std::vector<std::string> f = StringTokenizer(ev, ":").getVector();
+                if (f.size() == 3) {
+                    phaseEvents.insert(std::make_pair((SUMOTime)StringUtils::toLong(f[0]), std::make_pair(f[1], StringUtils::toInt(f[2]))));
+                }
+            }
             // mirror MSNet::simulate (MSNet.cpp:462-500) but record the state after every step
             while (state == MSNet::SIMSTATE_RUNNING) {
                 const SUMOTime t = net->getCurrentTimeStep();
+                for (auto it = phaseEvents.lower_bound(t); it != phaseEvents.end() && it->first == t; ++it) {
+                    libsumo::TrafficLight::setPhase(it->second.first, it->second.second);
+                }
                 DrawPrediction pred;
                 if (fd != nullptr) {
                     pred = predictDraws(net);

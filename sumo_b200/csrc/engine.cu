@@ -409,6 +409,44 @@ int sumob200_num_lanes(const sumob200_engine* e) { return e == nullptr ? 0 : e->
 int64_t sumob200_time_ms(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.t; }
 int64_t sumob200_kernel_launches(const sumob200_engine* e) { return e == nullptr ? 0 : e->launches; }
 
+int sumob200_num_tls(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nTL; }
+
+int sumob200_tls_set_phase(sumob200_engine* e, int tls, int phase) {
+    if (e == nullptr || tls < 0 || tls >= e->d.nTL) {
+        gLastError = "sumob200_tls_set_phase: bad engine / traffic light index";
+        return SUMOB200_EINVAL;
+    }
+    const int nPhases = e->model.h.tl_phase_begin[tls + 1] - e->model.h.tl_phase_begin[tls];
+    if (phase < 0 || phase >= nPhases) {
+        // the message of libsumo::TrafficLight::setPhase (TrafficLight.cpp:826)
+        gLastError = "The phase index " + std::to_string(phase) + " is not in the allowed range [0," + std::to_string(nPhases - 1) + "].";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    e->ks->tls_set_phase(&e->d, tls, phase, e->stream);
+    e->launches += 1;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int sumob200_tls_get_phase(sumob200_engine* e, int tls, int* phase, int64_t* next_switch_ms) {
+    if (e == nullptr || tls < 0 || tls >= e->d.nTL || phase == nullptr) {
+        gLastError = "sumob200_tls_get_phase: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    int32_t p = 0;
+    int64_t ns = 0;
+    CUDA_TRY(cudaMemcpyAsync(&p, e->d.tl_cur_phase + tls, sizeof(p), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(&ns, e->d.tl_next_switch + tls, sizeof(ns), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    *phase = p;
+    if (next_switch_ms != nullptr) {
+        *next_switch_ms = ns;
+    }
+    return 0;
+}
+
 int sumob200_set_random_draws(sumob200_engine* e, const double* draws, int n) {
     if (e == nullptr || draws == nullptr || n != e->d.nV) {
         gLastError = "sumob200_set_random_draws: bad argument";

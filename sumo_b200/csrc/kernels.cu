@@ -326,6 +326,13 @@ __global__ void __launch_bounds__(256) k_summary_final(const SummaryPart* parts,
     }
 }
 
+// TraCI-style control between two steps (libsumo::TrafficLight::setPhase)
+__global__ void k_tls_set_phase(const __grid_constant__ Ctx c, int tl, int phase) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        tls_set_phase(c, tl, phase);
+    }
+}
+
 __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
@@ -352,6 +359,7 @@ void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK,
 void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<grid(n), BLOCK, 0, s>>>(ctx(c), updates); }
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
+void l_tls_set_phase(const void* c, int tl, int phase, cudaStream_t s) { k_tls_set_phase<<<1, 32, 0, s>>>(ctx(c), tl, phase); }
 int l_summary(const void* c, int n, void* parts, void* out, cudaStream_t s) {   // parts = NULL: number of bytes parts needs
     const int nb = grid(n);
     if (parts == nullptr) {
@@ -368,7 +376,7 @@ void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaSt
     k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase};
 
 }  // namespace sb2_kset_<name>
 

@@ -22,6 +22,7 @@ struct sb2_kernelset {
     void (*tripinfo)(const void* ctx, int n_vehicles, sumob200_tripinfo* out, cudaStream_t s);
     /* summary aggregates (sb2_summary.h:SummaryPart): parts == NULL returns the scratch size in bytes, else launches (returns the launch count) */
     int (*summary)(const void* ctx, int n_vehicles, void* parts, void* out, cudaStream_t s);
+    void (*tls_set_phase)(const void* ctx, int tls, int phase, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

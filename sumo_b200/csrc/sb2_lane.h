@@ -223,6 +223,23 @@ SB2_HDN void lane_detect_collisions(const Ctx& c, int l) {
     }
 }
 
+// MSTrafficLightLogic::setTrafficLightSignals(t) for phase `step` of program tl (MSTrafficLightLogic.cpp:402-414)
+SB2_HD void tls_set_signals(const Ctx& c, int tl, int step, SUMOTime switchTime) {
+    const uint8_t* st = c.phase_states + c.phase_state_begin[c.tl_phase_begin[tl] + step];
+    for (int i = c.tl_link_begin[tl]; i < c.tl_link_begin[tl + 1]; i++) {
+        const int k = c.tllink_link[i];
+        const uint8_t s = st[c.tllink_index[i]];
+        // MSLink::setTLState (MSLink.cpp:1325-1336)
+        if (c.link_state[k] != s) {
+            c.link_last_change[k] = switchTime;
+        }
+        c.link_state[k] = s;
+        if (state_green(s)) {
+            c.link_last_green[k] = s;
+        }
+    }
+}
+
 // static program phase clock: fires like MSTrafficLightLogic::SwitchCommand at the begin of the step
 SB2_HDN void tls_advance(const Ctx& c, int tl) {
     const int p0 = c.tl_phase_begin[tl];
@@ -241,20 +258,19 @@ SB2_HDN void tls_advance(const Ctx& c, int tl) {
         c.tl_cur_phase[tl] = step;
         const SUMOTime switchTime = c.tl_next_switch[tl];
         c.tl_next_switch[tl] = switchTime + c.phase_dur[p0 + step];
-        // setTrafficLightSignals(t)
-        const uint8_t* st = c.phase_states + c.phase_state_begin[p0 + step];
-        for (int i = c.tl_link_begin[tl]; i < c.tl_link_begin[tl + 1]; i++) {
-            const int k = c.tllink_link[i];
-            const uint8_t s = st[c.tllink_index[i]];
-            // MSLink::setTLState (MSLink.cpp:1325-1336)
-            if (c.link_state[k] != s) {
-                c.link_last_change[k] = switchTime;
-            }
-            c.link_state[k] = s;
-            if (state_green(s)) {
-                c.link_last_green[k] = s;
-            }
-        }
+        tls_set_signals(c, tl, step, switchTime);
+    }
+}
+
+// libsumo::TrafficLight::setPhase (src/libsumo/TrafficLight.cpp:823-832) -> MSSimpleTrafficLightLogic::changeStepAndDuration
+// (MSSimpleTrafficLightLogic.cpp:294-309) between two steps: the pending switch is rescheduled to now + the phase's duration;
+// if the phase changes, the signals are set at once with the current time as their change time
+SB2_HD void tls_set_phase(const Ctx& c, int tl, int step) {
+    const SUMOTime now = c.t;
+    c.tl_next_switch[tl] = now + c.phase_dur[c.tl_phase_begin[tl] + step];
+    if (step != c.tl_cur_phase[tl]) {
+        c.tl_cur_phase[tl] = step;
+        tls_set_signals(c, tl, step, now);
     }
 }
 

@@ -78,6 +78,9 @@ def load_library(path=None):
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
+    lib.sumob200_num_tls.argtypes = [ctypes.c_void_p]
+    lib.sumob200_tls_set_phase.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+    lib.sumob200_tls_get_phase.argtypes = [ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int64)]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
     lib.sumob200_num_lanes.argtypes = [ctypes.c_void_p]
     lib.sumob200_time_ms.argtypes = [ctypes.c_void_p]
@@ -224,6 +227,20 @@ class Engine:
         out = np.zeros((7, self.num_vehicles))
         _check(self._lib, self._lib.sumob200_emissions(self._h, out.ctypes.data, out.size), "sumob200_emissions")
         return out
+
+    @property
+    def num_tls(self):
+        return self._lib.sumob200_num_tls(self._h)
+
+    def tls_set_phase(self, tls, phase):
+        """libsumo.trafficlight.setPhase between two steps; tls = index in the scenario's tl_names"""
+        _check(self._lib, self._lib.sumob200_tls_set_phase(self._h, int(tls), int(phase)), "sumob200_tls_set_phase")
+
+    def tls_phase(self, tls):
+        """(current phase index, next switch time in ms) = trafficlight.getPhase / getNextSwitch"""
+        ph, ns = ctypes.c_int(), ctypes.c_int64()
+        _check(self._lib, self._lib.sumob200_tls_get_phase(self._h, int(tls), ctypes.byref(ph), ctypes.byref(ns)), "sumob200_tls_get_phase")
+        return ph.value, ns.value
 
     def set_random_draws(self, draws):
         d = np.ascontiguousarray(draws, dtype=np.float64)

@@ -60,6 +60,7 @@ CASES.update({
     "grid4_tls_step05": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--step-length", "0.5", "--end", "600"],
     "grid5_dense_optmix": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],
     # heterogeneous fleet: length, minGap, accel, maxSpeed, tau, speedFactor, impatience differ between vehicles
+    "grid4_tls_setphase": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
     "grid4_tls_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
     "grid5_dense_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
     "c1_grid10_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
@@ -72,6 +73,23 @@ ROU_EDITS = {
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
     "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
 }
+
+
+def tls_phase_events(base, period_s=37, end_s=1100):
+    """deterministic trafficlight.setPhase events for the case <base>_setphase: every period_s seconds one program is set to some
+    phase (sometimes the one it is in: only the switch is rescheduled).  [(time ms, tls id, phase)]"""
+    import re
+    text = open(os.path.join(GOLDEN, base + ".net.xml")).read()
+    logics = [(m.group(1), len(re.findall(r"<phase ", m.group(2)))) for m in re.finditer(r'<tlLogic id="([^"]+)"[^>]*>(.*?)</tlLogic>', text, re.S)]
+    logics = [l for l in logics if l[1] > 1]
+    ev = []
+    for k, t in enumerate(range(period_s, end_s, period_s)):
+        tid, n = logics[(k * 7) % len(logics)]
+        ev.append((t * 1000, tid, (k * 3) % n))
+        if k % 4 == 0:   # two programs in the same step
+            tid2, n2 = logics[(k * 7 + 3) % len(logics)]
+            ev.append((t * 1000, tid2, (k + 1) % n2))
+    return ev
 
 
 def pytest_configure(config):
@@ -131,7 +149,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
@@ -147,6 +165,8 @@ def reference_case(name):
                 rou = os.path.join(CACHE, name + ".rou.xml")
                 with open(rou, "w") as f:
                     f.write(new_text)
+        if name.endswith("_setphase"):
+            extra = ["--tls-set-phase", ";".join("%d:%s:%d" % e for e in tls_phase_events(base))]
         if name.endswith(("_sigma", "_draws")):
             extra = ["--draws-out", draws_path(name)]
         if "_hbefa" in name:

@@ -109,7 +109,7 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
@@ -118,6 +118,8 @@ int main(int argc, char** argv) {
             traceOut = argv[++i];
         } else if (a == "--fcd-xml-out" && i + 1 < argc) {
             fcdXmlOut = argv[++i];   // the <timestep> elements of the reference's --fcd-output
+        } else if (a == "--tls-set-phase" && i + 1 < argc) {
+            tlsSetPhase = argv[++i];   // "timeMs:tlsIndex:phase;..." applied before the step at that time (sumob200_tls_set_phase)
         } else if (a == "--summary-out" && i + 1 < argc) {
             summaryOut = argv[++i];   // text, one line per step: the attributes of the reference's --summary-output
         } else if (a == "--tripinfo-out" && i + 1 < argc) {
@@ -165,6 +167,18 @@ int main(int argc, char** argv) {
     for (int v = 0; v < c.nV; v++) {
         slotOfNumId[c.veh_numid[v]] = v;
     }
+    std::multimap<int64_t, std::pair<int, int> > phaseEvents;
+    for (size_t a = 0; a < tlsSetPhase.size();) {
+        size_t b = tlsSetPhase.find(';', a);
+        if (b == std::string::npos) {
+            b = tlsSetPhase.size();
+        }
+        long long tm; int tl, ph;
+        if (sscanf(tlsSetPhase.substr(a, b - a).c_str(), "%lld:%d:%d", &tm, &tl, &ph) == 3) {
+            phaseEvents.insert(std::make_pair((int64_t)tm, std::make_pair(tl, ph)));
+        }
+        a = b + 1;
+    }
     long steps = 0;
     long long updates = 0;
     int lastErr = 0;
@@ -182,6 +196,9 @@ int main(int argc, char** argv) {
                 c.rng_replay = replay.data();
                 c.rng_mode = 2;
             }
+        }
+        for (auto it = phaseEvents.lower_bound(t); it != phaseEvents.end() && it->first == t; ++it) {
+            tls_set_phase(c, it->second.first, it->second.second);
         }
         step(m);
         steps++;
