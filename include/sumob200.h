@@ -160,6 +160,12 @@ int sumob200_num_tls(const sumob200_engine* e);
 int sumob200_tls_set_phase(sumob200_engine* e, int tls, int phase);
 int sumob200_tls_get_phase(sumob200_engine* e, int tls, int* phase, int64_t* next_switch_ms);
 
+/* libsumo::Vehicle::setSpeed (src/libsumo/Vehicle.cpp:1924-1938) for n vehicle slots between two steps: from the next step on
+ * the vehicle drives speeds[i] as far as its safe speed and its acceleration / deceleration bounds allow (default speed mode 31:
+ * MSVehicle::Influencer::influenceSpeed, MSVehicle.cpp:493-520, applied in planMove :2313-2326 and executeMove :4025-4056);
+ * speeds[i] < 0 hands the vehicle back to the car-following model.  An unknown slot is SUMOB200_EINVAL. */
+int sumob200_vehicles_set_speed(sumob200_engine* e, const int32_t* slots, const double* speeds, int n);
+
 int sumob200_num_vehicles(const sumob200_engine* e);
 int sumob200_num_lanes(const sumob200_engine* e);
 int64_t sumob200_time_ms(const sumob200_engine* e);

@@ -66,6 +66,7 @@
 #include <set>
 #include <traci-server/TraCIServer.h>
 #include <libsumo/TrafficLight.h>
+#include <libsumo/Vehicle.h>
 
 #include <algorithm>
 #include <map>
@@ -703,7 +704,7 @@ predictDraws(MSNet* net) {
 
 int
 main(int argc, char** argv) {
-    std::string flatOut, traceOut, drawsOut, emisOut, tlsSetPhase;
+    std::string flatOut, traceOut, drawsOut, emisOut, tlsSetPhase, vehSetSpeed;
     std::vector<char*> args;
     args.push_back(argv[0]);
     for (int i = 1; i < argc; i++) {
@@ -716,6 +717,8 @@ main(int argc, char** argv) {
             drawsOut = argv[++i];
         } else if (a == "--tls-set-phase" && i + 1 < argc) {
             tlsSetPhase = argv[++i];   // "timeMs:tlsID:phase;..." -> libsumo::TrafficLight::setPhase before the step at that time (what a TraCI client does)
+        } else if (a == "--veh-set-speed" && i + 1 < argc) {
+            vehSetSpeed = argv[++i];   // "timeMs:vehID:speed;..." -> libsumo::Vehicle::setSpeed before the step at that time, if the vehicle is on the road then
         } else if (a == "--emissions-out" && i + 1 < argc) {
             emisOut = argv[++i];   // per step: (t, n) then n x (numerical id, 7 fp64 accumulators of MSDevice_Emissions) as raw bytes
         } else {
@@ -763,9 +766,22 @@ main(int argc, char** argv) {
                     phaseEvents.insert(std::make_pair((SUMOTime)StringUtils::toLong(f[0]), std::make_pair(f[1], StringUtils::toInt(f[2]))));
                 }
             }
+            std::multimap<SUMOTime, std::pair<std::string, double> > speedEvents;
+            for (const std::string& ev : StringTokenizer(vehSetSpeed, ";").getVector()) {
+                const std::vector<std::string> f = StringTokenizer(ev, ":").getVector();
+                if (f.size() == 3) {
+                    speedEvents.insert(std::make_pair((SUMOTime)StringUtils::toLong(f[0]), std::make_pair(f[1], StringUtils::toDouble(f[2]))));
+                }
+            }
             // mirror MSNet::simulate (MSNet.cpp:462-500) but record the state after every step
             while (state == MSNet::SIMSTATE_RUNNING) {
                 const SUMOTime t = net->getCurrentTimeStep();
+                for (auto it = speedEvents.lower_bound(t); it != speedEvents.end() && it->first == t; ++it) {
+                    SUMOVehicle* sv = net->getVehicleControl().getVehicle(it->second.first);
+                    if (sv != nullptr && sv->isOnRoad()) {
+                        libsumo::Vehicle::setSpeed(it->second.first, it->second.second);
+                    }
+                }
                 for (auto it = phaseEvents.lower_bound(t); it != phaseEvents.end() && it->first == t; ++it) {
                     libsumo::TrafficLight::setPhase(it->second.first, it->second.second);
                 }

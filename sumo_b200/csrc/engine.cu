@@ -409,6 +409,46 @@ int sumob200_num_lanes(const sumob200_engine* e) { return e == nullptr ? 0 : e->
 int64_t sumob200_time_ms(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.t; }
 int64_t sumob200_kernel_launches(const sumob200_engine* e) { return e == nullptr ? 0 : e->launches; }
 
+int sumob200_vehicles_set_speed(sumob200_engine* e, const int32_t* slots, const double* speeds, int n) {
+    if (e == nullptr || n < 0 || (n > 0 && (slots == nullptr || speeds == nullptr))) {
+        gLastError = "sumob200_vehicles_set_speed: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || slots[i] >= e->d.nV) {
+            gLastError = "sumob200_vehicles_set_speed: vehicle slot " + std::to_string(slots[i]) + " is not known";
+            return SUMOB200_EINVAL;
+        }
+    }
+    if (n == 0) {
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    int32_t* dSlots = nullptr;
+    double* dSpeeds = nullptr;
+    CUDA_TRY(cudaMalloc(&dSlots, sizeof(int32_t) * (size_t)n));
+    cudaError_t err = cudaMalloc(&dSpeeds, sizeof(double) * (size_t)n);
+    if (err == cudaSuccess) {
+        err = cudaMemcpyAsync(dSlots, slots, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, e->stream);
+    }
+    if (err == cudaSuccess) {
+        err = cudaMemcpyAsync(dSpeeds, speeds, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, e->stream);
+    }
+    if (err == cudaSuccess) {
+        e->d.traci_speed_used = 1;   // from now on k_plan / k_execute read veh_traci_speed
+        e->ks->set_speed(&e->d, dSlots, dSpeeds, n, e->stream);
+        e->launches += 1;
+        err = cudaStreamSynchronize(e->stream);
+    }
+    cudaFree(dSlots);
+    cudaFree(dSpeeds);
+    if (err != cudaSuccess) {
+        gLastError = std::string("sumob200_vehicles_set_speed: ") + cudaGetErrorString(err);
+        return SUMOB200_ECUDA;
+    }
+    return 0;
+}
+
 int sumob200_num_tls(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nTL; }
 
 int sumob200_tls_set_phase(sumob200_engine* e, int tls, int phase) {

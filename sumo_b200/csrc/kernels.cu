@@ -333,6 +333,14 @@ __global__ void k_tls_set_phase(const __grid_constant__ Ctx c, int tl, int phase
     }
 }
 
+// libsumo::Vehicle::setSpeed for a batch of vehicle slots (speed < 0 removes the advice)
+__global__ void k_set_speed(const __grid_constant__ Ctx c, const int32_t* slots, const double* speeds, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && slots[i] >= 0 && slots[i] < c.nV) {
+        c.veh_traci_speed[slots[i]] = speeds[i] >= 0. ? speeds[i] : -1.;
+    }
+}
+
 __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* out) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < c.nV) {
@@ -360,6 +368,7 @@ void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) 
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tls_set_phase(const void* c, int tl, int phase, cudaStream_t s) { k_tls_set_phase<<<1, 32, 0, s>>>(ctx(c), tl, phase); }
+void l_set_speed(const void* c, const int32_t* slots, const double* speeds, int n, cudaStream_t s) { k_set_speed<<<grid(n), BLOCK, 0, s>>>(ctx(c), slots, speeds, n); }
 int l_summary(const void* c, int n, void* parts, void* out, cudaStream_t s) {   // parts = NULL: number of bytes parts needs
     const int nb = grid(n);
     if (parts == nullptr) {
@@ -376,7 +385,7 @@ void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaSt
     k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed};
 
 }  // namespace sb2_kset_<name>
 

@@ -268,6 +268,8 @@ public:
             h.rng_mode = anySigma ? 1 : 0;
             h.rng_seed = (uint64_t)ff.scalar<int64_t>("opt_seed", 23423);
             h.rng_replay = nullptr;
+            h.traci_speed_used = 0;
+            SB2_DYN(double, veh_traci_speed, nV, -1.);
         }
         // ---------------- routes, vehicles
         SB2_COPY(int32_t, route_begin); SB2_COPY(int32_t, route_edges);

@@ -89,6 +89,17 @@ SB2_HD CF make_cf(const Ctx& c, int vt) {
 }
 #endif
 
+// MSVehicle::Influencer::influenceSpeed (MSVehicle.cpp:493-520) for the time line libsumo::Vehicle::setSpeed installs
+// (Vehicle.cpp:1924-1938: two entries with the same speed, from now to the end of time) under the default speed mode 31
+// (safe speed, max acceleration and max deceleration all respected): speed = s - (s - s) * td = s, then the three bounds
+SB2_HD double traci_influenceSpeed(double advised, double vSafe, double vMin, double vMax) {
+    double speed = advised;
+    speed = vSafe < speed ? vSafe : speed;
+    speed = vMax < speed ? vMax : speed;
+    speed = vMin > speed ? vMin : speed;
+    return speed;
+}
+
 // MSCFModel.cpp:101-108
 SB2_CORE double cfk_brakeGapEuler(double TS, double speed, double decel, double headwayTime) {
     const double speedReduction = decel * TS;

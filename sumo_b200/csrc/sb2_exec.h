@@ -200,6 +200,10 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
         vNext = 0.;
     }
     vNext = MAX2(vNext, 0.);
+    if (c.traci_speed_used && c.veh_traci_speed[v] >= 0.) {
+        // MSVehicle::processTraCISpeedControl (MSVehicle.cpp:4025-4056)
+        vNext = traci_influenceSpeed(c.veh_traci_speed[v], vSafe, MAX2(0., cf_minNextSpeed(cf, oldSpeed)), cf_maxNextSpeed(cf, oldSpeed));
+    }
 
     // updateState (MSVehicle.cpp:4965-5018)
     const double deltaPos = vNext * c.TS;

@@ -23,6 +23,7 @@ struct sb2_kernelset {
     /* summary aggregates (sb2_summary.h:SummaryPart): parts == NULL returns the scratch size in bytes, else launches (returns the launch count) */
     int (*summary)(const void* ctx, int n_vehicles, void* parts, void* out, cudaStream_t s);
     void (*tls_set_phase)(const void* ctx, int tls, int phase, cudaStream_t s);
+    void (*set_speed)(const void* ctx, const int32_t* slots, const double* speeds, int n, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

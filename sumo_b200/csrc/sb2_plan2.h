@@ -168,6 +168,10 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     laneMaxV = MAX2(laneMaxV, vMinComfortable);
     // maximumLaneSpeedCF (MSCFModel.h:245)
     double vv = MIN2(maxV, laneMaxV);
+    if (c.traci_speed_used && c.veh_traci_speed[v] >= 0.) {
+        // MSVehicle.cpp:2313-2326: v = myInfluencer->influenceSpeed(t, v, v, MAX2(0, minNextSpeed), maxV)
+        vv = traci_influenceSpeed(c.veh_traci_speed[v], vv, MAX2(0., vMinComfortable), maxV);
+    }
     const double dist = maxV * c.TS + cf_brakeGap(cf, maxV);
     bool hadNonInternal = false;
     double seen = c.lane_length[myLane] - e.pos;

@@ -207,6 +207,10 @@ struct Ctx {
     // ---- random numbers for the dawdle step (MSCFModel_Krauss::dawdle2): 0 = none needed (all sigma == 0),
     // 1 = counter-based generator keyed by (seed, vehicle, step), 2 = replay of host-supplied draws (rng_replay[v])
     int rng_mode; uint64_t rng_seed; const double* rng_replay;
+    // ---- TraCI speed advice (libsumo::Vehicle::setSpeed -> MSVehicle::Influencer speed time line with one constant entry):
+    // veh_traci_speed[v] >= 0 = advised speed, < 0 = none.  traci_speed_used == 0 (no advice given in this run yet) lets the
+    // per-vehicle kernels skip the array
+    int traci_speed_used; double* veh_traci_speed;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
     int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports

@@ -79,6 +79,7 @@ def load_library(path=None):
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_tls.argtypes = [ctypes.c_void_p]
+    lib.sumob200_vehicles_set_speed.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_tls_set_phase.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
     lib.sumob200_tls_get_phase.argtypes = [ctypes.c_void_p, ctypes.c_int, P(ctypes.c_int), P(ctypes.c_int64)]
     lib.sumob200_num_vehicles.argtypes = [ctypes.c_void_p]
@@ -227,6 +228,13 @@ class Engine:
         out = np.zeros((7, self.num_vehicles))
         _check(self._lib, self._lib.sumob200_emissions(self._h, out.ctypes.data, out.size), "sumob200_emissions")
         return out
+
+    def set_speed(self, slots, speeds):
+        """libsumo.vehicle.setSpeed for a batch of vehicle slots (speed < 0 = back to the car-following model)"""
+        s = np.ascontiguousarray(np.atleast_1d(slots), dtype=np.int32)
+        v = np.ascontiguousarray(np.atleast_1d(speeds), dtype=np.float64)
+        assert s.shape == v.shape
+        _check(self._lib, self._lib.sumob200_vehicles_set_speed(self._h, s.ctypes.data, v.ctypes.data, s.size), "sumob200_vehicles_set_speed")
 
     @property
     def num_tls(self):

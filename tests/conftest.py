@@ -60,6 +60,9 @@ CASES.update({
     "grid4_tls_step05": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--step-length", "0.5", "--end", "600"],
     "grid5_dense_optmix": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],
     # heterogeneous fleet: length, minGap, accel, maxSpeed, tau, speedFactor, impatience differ between vehicles
+    # ends before t = 1086 s, where the advised speeds lead to a collision in the reference (which it resolves by teleporting; the
+    # engine raises SUMOB200_F_COLLISION at that very step)
+    "grid4_tls_setspeed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1050"],
     "grid4_tls_setphase": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
     "grid4_tls_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
     "grid5_dense_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
@@ -90,6 +93,25 @@ def tls_phase_events(base, period_s=37, end_s=1100):
             tid2, n2 = logics[(k * 7 + 3) % len(logics)]
             ev.append((t * 1000, tid2, (k + 1) % n2))
     return ev
+
+
+def veh_speed_events(base, end_s=1040):
+    """deterministic vehicle.setSpeed events for the case <base>_setspeed: every 5 s two vehicles get a speed advice (0 = stop,
+    slow, medium, above the lane limit, or -1 = release), slow ones are released 30 s later.  Both sides skip an event whose
+    vehicle is not on the road at that time.  [(time ms, vehicle id, speed)]"""
+    import re
+    ids = re.findall(r'<vehicle id="([^"]+)"', open(os.path.join(GOLDEN, base + ".rou.xml")).read())
+    speeds = [0., 3., 7.5, 20., -1., 11.]
+    ev = []
+    for k, t in enumerate(range(50, end_s, 5)):
+        for j in range(2):
+            # vehicles depart in id order over the run: aim at those that left a little while ago
+            i = max(0, min(int(len(ids) * t / 900.), len(ids) - 1) - 20 - ((k * 13 + j * 29) % 60))
+            sp = speeds[(k * 2 + j) % len(speeds)]
+            ev.append((t * 1000, ids[i], sp))
+            if 0 <= sp < 5:
+                ev.append(((t + 30) * 1000, ids[i], -1.))
+    return sorted(ev, key=lambda e: e[0])
 
 
 def pytest_configure(config):
@@ -149,7 +171,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase", "_setspeed"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
@@ -165,6 +187,8 @@ def reference_case(name):
                 rou = os.path.join(CACHE, name + ".rou.xml")
                 with open(rou, "w") as f:
                     f.write(new_text)
+        if name.endswith("_setspeed"):
+            extra = ["--veh-set-speed", ";".join("%d:%s:%.17g" % e for e in veh_speed_events(base))]
         if name.endswith("_setphase"):
             extra = ["--tls-set-phase", ";".join("%d:%s:%d" % e for e in tls_phase_events(base))]
         if name.endswith(("_sigma", "_draws")):

@@ -109,7 +109,7 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed;
     long maxSteps = -1;
     std::string debugName;
     for (int i = 2; i < argc; i++) {
@@ -120,6 +120,8 @@ int main(int argc, char** argv) {
             fcdXmlOut = argv[++i];   // the <timestep> elements of the reference's --fcd-output
         } else if (a == "--tls-set-phase" && i + 1 < argc) {
             tlsSetPhase = argv[++i];   // "timeMs:tlsIndex:phase;..." applied before the step at that time (sumob200_tls_set_phase)
+        } else if (a == "--veh-set-speed" && i + 1 < argc) {
+            vehSetSpeed = argv[++i];   // "timeMs:slot:speed;..." applied before the step at that time if the vehicle is on the road (sumob200_vehicles_set_speed)
         } else if (a == "--summary-out" && i + 1 < argc) {
             summaryOut = argv[++i];   // text, one line per step: the attributes of the reference's --summary-output
         } else if (a == "--tripinfo-out" && i + 1 < argc) {
@@ -179,6 +181,18 @@ int main(int argc, char** argv) {
         }
         a = b + 1;
     }
+    std::multimap<int64_t, std::pair<int, double> > speedEvents;
+    for (size_t a = 0; a < vehSetSpeed.size();) {
+        size_t b = vehSetSpeed.find(';', a);
+        if (b == std::string::npos) {
+            b = vehSetSpeed.size();
+        }
+        long long tm; int slot; double sp;
+        if (sscanf(vehSetSpeed.substr(a, b - a).c_str(), "%lld:%d:%lf", &tm, &slot, &sp) == 3) {
+            speedEvents.insert(std::make_pair((int64_t)tm, std::make_pair(slot, sp)));
+        }
+        a = b + 1;
+    }
     long steps = 0;
     long long updates = 0;
     int lastErr = 0;
@@ -199,6 +213,12 @@ int main(int argc, char** argv) {
         }
         for (auto it = phaseEvents.lower_bound(t); it != phaseEvents.end() && it->first == t; ++it) {
             tls_set_phase(c, it->second.first, it->second.second);
+        }
+        for (auto it = speedEvents.lower_bound(t); it != speedEvents.end() && it->first == t; ++it) {
+            if (c.veh_lane[it->second.first] >= 0) {
+                c.traci_speed_used = 1;
+                c.veh_traci_speed[it->second.first] = it->second.second >= 0. ? it->second.second : -1.;
+            }
         }
         step(m);
         steps++;
