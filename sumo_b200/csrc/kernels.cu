@@ -70,15 +70,26 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
         tls_advance(c, i);
     }
     // lane-ordered work list: block-wide exclusive scan of the lanes' vehicle counts, one atomic per block for the base.
-    // Optionally (-DSB2_SPLIT_INTERNAL) vehicles on internal (junction) lanes get their own segment, filled from the end of
-    // veh_order backwards: [0, counters[7]) normal lanes, [nV - counters[3], nV) internal lanes.
+    // The list has two segments: [0, counters[7]) filled forwards and [nV - counters[3], nV) filled from the end backwards.
+    // Default split: lanes whose first link is red/yellow go to the second segment (measured on B200, 1M vehicles on the
+    // traffic-light grid: k_plan 2.07 -> 1.44 ms, because a warp then holds vehicles that all stop at the red link after one
+    // look-ahead iteration, or none).  -DSB2_SPLIT_INTERNAL (internal lanes in the second segment) measured no gain.
     __shared__ int warpSum[2][BLOCK / 32];
     __shared__ int blockBase[2];
     const int nveh = i < c.nL ? c.lane_nveh[i] : 0;
 #if defined(SB2_SPLIT_INTERNAL)
     const bool internal = i < c.nL && (c.lane_flags[i] & LF_INTERNAL) != 0;
+#elif !defined(SB2_NO_SPLIT_RED)
+    // second segment = lanes whose first link shows red or yellow: their vehicles mostly end planMove's look-ahead loop at that
+    // link (stopAtRed), the others run 2-4 iterations.  (The state may be the one before or after this step's switch: the order
+    // of the work list never changes a result.)
+    bool internal = false;
+    if (i < c.nL && c.lane_link_begin[i] < c.lane_link_begin[i + 1]) {
+        const uint8_t s0 = c.link_state[c.lane_link_begin[i]];
+        internal = state_red(s0) || state_yellow(s0);
+    }
 #else
-    const bool internal = false;   // measured on B200 (1M vehicles): k_plan 2.67 ms with the split, 2.69 ms without, k_execute slower: off
+    const bool internal = false;
 #endif
     const int n0 = internal ? 0 : nveh, n1 = internal ? nveh : 0;
     int incl0 = n0, incl1 = n1;
