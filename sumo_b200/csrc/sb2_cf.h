@@ -100,10 +100,15 @@ SB2_HD double traci_influenceSpeed(double advised, double vSafe, double vMin, do
     return speed;
 }
 
+// x / y for y > 0 with the common x == 0 answered directly (the quotient is x itself, sign included).  Same value as the plain
+// division; on the device a zero numerator sends the fp64 division into its ~60-instruction slow path (3 such calls per vehicle and
+// step in k_plan before this: standing vehicles have speed 0, profiles/r01_k_plan_ncu.txt)
+SB2_HD double div_pos(double x, double y) { return x == 0. ? x : x / y; }
+
 // MSCFModel.cpp:101-108
 SB2_CORE double cfk_brakeGapEuler(double TS, double speed, double decel, double headwayTime) {
     const double speedReduction = decel * TS;
-    const int steps = int(speed / speedReduction);
+    const int steps = int(div_pos(speed, speedReduction));
     return (steps * speed - speedReduction * steps * (steps + 1) / 2) * TS + speed * headwayTime;
 }
 SB2_HD double cf_brakeGapEuler(const CF& m, double speed, double decel, double headwayTime) { return cfk_brakeGapEuler(m.TS(), speed, decel, headwayTime); }
@@ -136,7 +141,7 @@ SB2_CORE double cfk_freeSpeed(double TS, double decel, double dist, double targe
     const double yFull = floor(y);
     const double exactGap = (yFull * yFull + yFull) * 0.5 * b + yFull * v + (y > yFull ? v : 0.0);
     const double fullSpeedGain = (yFull + (onInsertion ? 1. : 0.)) * (decel * TS);
-    return (MAX2(0.0, dist - exactGap) / (yFull + 1)) / TS + fullSpeedGain + targetSpeed;
+    return div_pos(div_pos(MAX2(0.0, dist - exactGap), yFull + 1), TS) + fullSpeedGain + targetSpeed;
 }
 SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double maxSpeed);
 SB2_HD double cf_freeSpeed(const CF& m, double currentSpeed, double dist, double targetSpeed, bool onInsertion) {
@@ -159,12 +164,12 @@ SB2_CORE SUMOTime cfk_getMinimalArrivalTime(double mAccel, double mDecel, double
     }
     arrivalSpeed = MAX2(0.0, arrivalSpeed);
     const double accel = (arrivalSpeed >= currentSpeed) ? mAccel : -mDecel;
-    const double accelTime = accel == 0. ? 0. : (arrivalSpeed - currentSpeed) / accel;
+    const double accelTime = accel == 0. ? 0. : (arrivalSpeed == currentSpeed ? 0. : (arrivalSpeed - currentSpeed) / accel);   // x - x = +0, accel > 0 then
     const double accelWay = accelTime * (arrivalSpeed + currentSpeed) * 0.5;
     if (dist >= accelWay) {
         const double nonAccelWay = dist - accelWay;
         const double nonAccelSpeed = MAX3(currentSpeed, arrivalSpeed, SB2_HALTING_SPEED);
-        return TIME2STEPS(accelTime + nonAccelWay / nonAccelSpeed);
+        return TIME2STEPS(accelTime + div_pos(nonAccelWay, nonAccelSpeed));
     }
     return TIME2STEPS(-(currentSpeed - sqrt(currentSpeed * currentSpeed + 2 * accel * dist)) / accel);
 }

@@ -63,7 +63,7 @@ SB2_HD SUMOTime link_getLeaveTime(const Ctx& c, int k, SUMOTime arrivalTime, dou
 
 // MSLink.h:730
 SB2_HD bool unsafeMergeSpeeds(double leaderSpeed, double followerSpeed, double leaderDecel, double followerDecel) {
-    return (leaderSpeed * leaderSpeed / leaderDecel) <= (followerSpeed * followerSpeed / followerDecel);
+    return div_pos(leaderSpeed * leaderSpeed, leaderDecel) <= div_pos(followerSpeed * followerSpeed, followerDecel);   // decels > 0
 }
 
 // MSLink.cpp:1225-1285

@@ -25,7 +25,7 @@ SB2_HD double lane_vehicle_max_speed(const Ctx& c, int l, int v) { return lane_v
 SB2_HD double veh_impatience(const Ctx& c, int v) {
     return MAX2(0., MIN2(1., c.vt_impatience[c.veh_type[v]]
                          + 0
-                         + (c.timeToImpatience > 0 ? (double)c.veh_waiting[v] / (double)c.timeToImpatience : 0.)));
+                         + (c.timeToImpatience > 0 ? div_pos((double)c.veh_waiting[v], (double)c.timeToImpatience) : 0.)));
 }
 
 SB2_HD int veh_route_len(const Ctx& c, int v) { const int r = c.veh_route[v]; return c.route_begin[r + 1] - c.route_begin[r]; }
