@@ -185,7 +185,8 @@ struct Ctx {
     double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
-    // neighbouring lanes, see the same links and foes and take the same branches.  counters[7] = its length.
+    // neighbouring lanes, see the same links and foes and take the same branches.  Two segments: [0, counters[7]) = lanes whose
+    // first link is not red/yellow, [nV - counters[3], nV) = lanes facing red/yellow (filled backwards), see k_pre.
     // Double buffered like the drive items (index c.cur): a drive-item record of step t is addressed by the vehicle's
     // POSITION wp in that step's work list (record = item * nV + wp), so the plan kernel writes and the execute kernel reads the
     // records fully coalesced; veh_order[buf][wp] gives the vehicle back (approach tables of the previous step use buf = cur ^ 1).
