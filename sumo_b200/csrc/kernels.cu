@@ -170,18 +170,20 @@ __global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c)
 }
 
 // running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
-__global__ void __launch_bounds__(BLOCK) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
+__global__ void __launch_bounds__(1024) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     const bool on = v < c.nV && c.veh_lane[v] >= 0;
-    const unsigned mask = __ballot_sync(0xffffffffu, on);
     // MSVehicleControl::getHaltingVehicleNo (MSVehicleControl.cpp:568-580): on the road and slower than SUMO_const_haltingSpeed
-    const unsigned halting = __ballot_sync(0xffffffffu, on && c.veh_speed[v] < SB2_HALTING_SPEED);
-    if ((threadIdx.x & 31) == 0 && mask != 0) {
-        const int n = __popc(mask);
-        atomicAdd(&c.counters[0], n);
-        atomicAdd(updates, (unsigned long long)n);
-        if (halting != 0) {
-            atomicAdd(&c.counters[8], __popc(halting));
+    const bool halting = on && c.veh_speed[v] < SB2_HALTING_SPEED;
+    // one atomic per 1024-thread block and counter: with one per warp the 3 x 31 k same-address atomics of a 1 M-vehicle step
+    // serialised in L2 and made this the slowest of the small kernels (59 us, profiles/r01_launches_summary.txt)
+    const int nOn = __syncthreads_count(on);
+    const int nHalting = __syncthreads_count(halting);
+    if (threadIdx.x == 0 && nOn != 0) {
+        atomicAdd(&c.counters[0], nOn);
+        atomicAdd(updates, (unsigned long long)nOn);
+        if (nHalting != 0) {
+            atomicAdd(&c.counters[8], nHalting);
         }
     }
 }
@@ -375,7 +377,7 @@ void l_execute(const void* c, int n, cudaStream_t s) { k_execute<<<grid(n), BLOC
 void l_remove(const void* c, int n, cudaStream_t s) { k_remove<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
-void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<grid(n), BLOCK, 0, s>>>(ctx(c), updates); }
+void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<n > 0 ? (n + 1023) / 1024 : 1, 1024, 0, s>>>(ctx(c), updates); }
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tls_set_phase(const void* c, int tl, int phase, cudaStream_t s) { k_tls_set_phase<<<1, 32, 0, s>>>(ctx(c), tl, phase); }
