@@ -32,7 +32,7 @@ SPINUP_STEPS = 420          # all departures happen in [0, 300 + 16) s; afterwar
 # algorithmic bytes per vehicle-update (SURVEY.md section 8d / DESIGN.md "roofline"): whole step, and the plan kernel alone
 BYTES_PER_UPDATE_STEP = 576
 BYTES_PER_UPDATE_PLAN = 320
-NCU_PLAN_TRAFFIC_BYTES = 3743012000 + 1452749000    # profiles/r01_k_plan_ncu.txt: dram__bytes_read.sum + dram__bytes_write.sum of one k_plan launch (mostly register-spill traffic)
+NCU_PLAN_TRAFFIC_BYTES = 3733032000 + 1453889000    # profiles/r01_k_plan_ncu.txt: dram__bytes_read.sum + dram__bytes_write.sum of one k_plan launch (mostly register-spill traffic)
 
 
 def measured_peak_gbs():
