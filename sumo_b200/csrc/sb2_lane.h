@@ -16,8 +16,9 @@
 namespace sb2 {
 
 // before planMove: cumulated lengths in front of every vehicle, space till last standing vehicle
-// orderBase = first slot of this lane in the lane-ordered work list veh_order
-SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1) {
+// orderBase = first slot of this lane in the lane-ordered work list veh_order; firstSlot >= 0: the lane's front vehicle goes
+// there instead (k_pre groups the front vehicles of a block's lanes), the followers start at orderBase
+SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1, int firstSlot = -1) {
     // front -> back (MSLane.cpp:1608-1623)
     double cum = 0.;
     int guard = 0;
@@ -26,8 +27,13 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1)
         (void)SB2_CHK(orderBase, 0, c.nV, 12);
         (void)SB2_CHK(guard++, 0, c.lane_nveh[l], 13);
         c.veh_len_in_front[v] = cum;
-        c.veh_order[c.cur][orderBase] = v;
-        orderBase += orderStep;
+        if (firstSlot >= 0) {
+            c.veh_order[c.cur][firstSlot] = v;
+            firstSlot = -1;
+        } else {
+            c.veh_order[c.cur][orderBase] = v;
+            orderBase += orderStep;
+        }
         cum += veh_length_with_gap(c, v);
     }
     // back -> front (MSLane.cpp:4734-4754); `last != ego` never excludes anything for the lanes ahead of ego
