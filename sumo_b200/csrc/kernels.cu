@@ -75,8 +75,11 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
     // traffic-light grid: k_plan 2.07 -> 1.44 ms, because a warp then holds vehicles that all stop at the red link after one
     // look-ahead iteration, or none).  -DSB2_SPLIT_INTERNAL (internal lanes in the second segment) measured no gain.
     __shared__ int warpSum[2][BLOCK / 32];
+    __shared__ int blockBase[2];
+#if defined(SB2_SPLIT_FIRST)
     __shared__ int warpSumF[2][BLOCK / 32];
-    __shared__ int blockBase[2], blockFirsts[2];
+    __shared__ int blockFirsts[2];
+#endif
     const int nveh = i < c.nL ? c.lane_nveh[i] : 0;
 #if defined(SB2_SPLIT_INTERNAL)
     const bool internal = i < c.nL && (c.lane_flags[i] & LF_INTERNAL) != 0;
@@ -92,14 +95,11 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
 #else
     const bool internal = false;
 #endif
+#if defined(SB2_SPLIT_FIRST)   // experiment, off by default until measured on B200 (tools_dev/ab_first.sh)
     const int n0 = internal ? 0 : nveh, n1 = internal ? nveh : 0;
-#if defined(SB2_SPLIT_FIRST)   // experiment, off by default until measured on B200
     // within the block's range of each segment the front vehicles of its lanes come first, their followers after them: a
     // warp then holds front vehicles (next-lane leaders, link leaders, foes) or followers (leader on the own lane), not both
     const int f0 = n0 > 0 ? 1 : 0, f1 = n1 > 0 ? 1 : 0;
-#else
-    const int f0 = 0, f1 = 0;
-#endif
     int incl0 = n0 - f0, incl1 = n1 - f1, inclF0 = f0, inclF1 = f1;
     for (int d = 1; d < 32; d <<= 1) {
         const int o0 = __shfl_up_sync(0xffffffffu, incl0, d);
@@ -147,6 +147,40 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
     } else if (i < c.nL) {
         lane_summary(c, i, 0, 1);
     }
+#else
+    const int n0 = internal ? 0 : nveh, n1 = internal ? nveh : 0;
+    int incl0 = n0, incl1 = n1;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o0 = __shfl_up_sync(0xffffffffu, incl0, d);
+        const int o1 = __shfl_up_sync(0xffffffffu, incl1, d);
+        if ((threadIdx.x & 31) >= d) {
+            incl0 += o0;
+            incl1 += o1;
+        }
+    }
+    if ((threadIdx.x & 31) == 31) {
+        warpSum[0][threadIdx.x >> 5] = incl0;
+        warpSum[1][threadIdx.x >> 5] = incl1;
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        int tot = 0;
+        for (int w = 0; w < BLOCK / 32; w++) {
+            const int x = warpSum[threadIdx.x][w];
+            warpSum[threadIdx.x][w] = tot;
+            tot += x;
+        }
+        blockBase[threadIdx.x] = tot > 0 ? atomicAdd(&c.counters[threadIdx.x == 0 ? 7 : 3], tot) : 0;
+    }
+    __syncthreads();
+    if (i < c.nL) {
+        if (!internal) {
+            lane_summary(c, i, blockBase[0] + warpSum[0][threadIdx.x >> 5] + incl0 - n0, 1);
+        } else {
+            lane_summary(c, i, c.nV - 1 - (blockBase[1] + warpSum[1][threadIdx.x >> 5] + incl1 - n1), -1);
+        }
+    }
+#endif
     if (i < c.nK) {
         c.link_app_head[c.cur][i] = -1;
     }
