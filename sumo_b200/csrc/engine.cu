@@ -260,7 +260,7 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
                 e->phaseMs[p] += ms;
             }
         }
-        e->launches += 8;
+        e->launches += 9;
         c.t += c.DELTA_T;
         c.cur ^= 1;
         e->stepsDone++;

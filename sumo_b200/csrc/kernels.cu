@@ -61,6 +61,7 @@ __global__ void k_reset(const __grid_constant__ Ctx c) {
         c.counters[7] = 0;
         c.counters[3] = 0;
         c.counters[8] = 0;
+        c.counters[9] = 0;
     }
 }
 
@@ -199,9 +200,37 @@ __global__ void __launch_bounds__(BLOCK, SB2_PLAN_MINB) k_plan(const __grid_cons
 __global__ void __launch_bounds__(BLOCK, SB2_EXEC_MINB) k_execute(const __grid_constant__ Ctx c) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < c.counters[7] || (i < c.nV && i >= c.nV - c.counters[3])) {
-        const int v = c.veh_order[c.cur][i];
-        veh_executeMove(c, v, i, veh_random(c, v));
-        veh_register_partials(c, v);
+        veh_executeMove_pass1(c, i);
+    }
+}
+
+// second pass of executeMove for the (rare) vehicles whose right of way depends on the new speed of a foe the reference moves
+// earlier in the step (MSLink::blockedAtTime under lastWasContRed, see sb2_link.h LIVE_PASS1): one CTA, rounds until all are done
+__global__ void __launch_bounds__(256) k_execute2(const __grid_constant__ Ctx c) {
+    const int n = c.counters[9];
+    if (n == 0) {
+        return;
+    }
+    __shared__ int left;
+    for (int round = 0; round < 16; round++) {
+        if (threadIdx.x == 0) {
+            left = 0;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            if (!veh_execute_deferred(c, i)) {
+                atomicAdd(&left, 1);
+            }
+        }
+        __threadfence();
+        __syncthreads();
+        if (left == 0) {
+            return;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        raise(c, ERR_DEFERRED_UNRESOLVED);
     }
 }
 
@@ -431,7 +460,7 @@ inline const Ctx& ctx(const void* p) { return *static_cast<const Ctx*>(p); }   /
 void l_reset(const void* c, cudaStream_t s) { k_reset<<<1, 32, 0, s>>>(ctx(c)); }
 void l_pre(const void* c, int n, cudaStream_t s) { k_pre<<<grid(n < 3 ? 3 : n), BLOCK, 0, s>>>(ctx(c)); }
 void l_plan(const void* c, int n, cudaStream_t s) { k_plan<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
-void l_execute(const void* c, int n, cudaStream_t s) { k_execute<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_execute(const void* c, int n, cudaStream_t s) { k_execute<<<grid(n), BLOCK, 0, s>>>(ctx(c)); k_execute2<<<1, 256, 0, s>>>(ctx(c)); }
 void l_remove(const void* c, int n, cudaStream_t s) { k_remove<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }

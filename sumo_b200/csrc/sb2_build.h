@@ -126,6 +126,28 @@ public:
         SB2_COPY(int32_t, lane_to_junction); SB2_COPY(int32_t, lane_from_junction);
         SB2_COPY(int32_t, edge_lane_begin);
         SB2_COPY(int32_t, lane_shape_begin); SB2_COPY(double, shape_xy); SB2_COPY(double, lane_geomfactor);
+        {
+            // order keys of MSEdgeControl's lane containers: numerical id (myChangedStateLanes) and id string order (myWithVehicles2Integrate)
+            int32_t* numid = add<int32_t>("lane_numid", SB2_OFF(lane_numid), nL, false, 0);
+            int32_t* rank = add<int32_t>("lane_idrank", SB2_OFF(lane_idrank), nL, false, 0);
+            for (int l = 0; l < nL; l++) {
+                numid[l] = ff.has("lane_numid") ? ff.ptr<int32_t>("lane_numid")[l] : l;
+                rank[l] = l;
+            }
+            if (ff.has("lane_idrank")) {
+                memcpy(rank, ff.ptr<int32_t>("lane_idrank"), sizeof(int32_t) * (size_t)nL);
+            } else if ((int)lane_names.size() == nL) {
+                std::vector<int32_t> byName(nL);
+                for (int l = 0; l < nL; l++) {
+                    byName[l] = l;
+                }
+                std::sort(byName.begin(), byName.end(), [&](int a, int b) { return lane_names[a] < lane_names[b]; });
+                for (int i = 0; i < nL; i++) {
+                    rank[byName[i]] = i;
+                }
+            }
+        }
+        SB2_DYN(int64_t, lane_actkey, nL, (int64_t)0); SB2_DYN(uint8_t, lane_changed, nL, (uint8_t)0);
         SB2_DYN(int32_t, lane_first, nL, -1); SB2_DYN(int32_t, lane_last, nL, -1); SB2_DYN(int32_t, lane_nveh, nL, 0);
         SB2_DYN(double, lane_brutto, nL, 0.);
         SB2_DYN(int32_t, lane_npartial, nL, 0); SB2_DYN(int32_t, lane_partial, (size_t)nL * MAX_PARTIAL, -1);
@@ -370,6 +392,7 @@ public:
         SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
         SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
         SB2_DYN(double, veh_len_in_front, nV, 0.);
+        SB2_DYN(int32_t, veh_qlane, nV, -1); SB2_DYN(uint8_t, veh_deferred, nV, (uint8_t)0); SB2_DYN(int32_t, deferred_list, nV, -1);
         SB2_DYN(int32_t, lane_arrived, nL, 0);
         SB2_DYN(SUMOTime, veh_trip_wait, nV, 0); SB2_DYN(int32_t, veh_trip_waitcount, nV, 0); SB2_DYN(uint8_t, veh_trip_amwaiting, nV, 0);
         SB2_DYN(double, veh_trip_routelen, nV, 0.); SB2_DYN(double, veh_trip_departpos, nV, 0.); SB2_DYN(double, veh_trip_departspeed, nV, 0.);

@@ -24,10 +24,11 @@ struct ExecScratch {
     bool haveToWait;
 };
 
-// MSVehicle::processLinkApproaches
-SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf, double speed, double pos, int myLane, SUMOTime waiting,
+// MSVehicle::processLinkApproaches; returns false if the right of way at some link depends on the new speed of a foe that is not
+// known yet (live == LIVE_PASS1 / LIVE_PASS2, see sb2_link.h): the caller defers the vehicle, nothing has been written
+SB2_HD bool veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf, double speed, double pos, int myLane, SUMOTime waiting,
                                       double& vSafe, double& vSafeMin, double& vSafeMinDist, bool& haveToWait,
-                                      SUMOTime& jentry, SUMOTime& jconflict) {
+                                      SUMOTime& jentry, SUMOTime& jconflict, int live) {
     const int cur = c.cur;
     haveToWait = false;
     bool canBrakeVSafeMin = false;
@@ -54,9 +55,15 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
             }
             const double accelV = c.di_accelv[cur][r];
             const double leaveSpeed = accelV < 0 ? vLinkPass : accelV;
-            bool opened = (yellow
-                           || link_opened(c, link, cur, c.di_arrtime[cur][r], c.di_arrspeed[cur][r], leaveSpeed,
-                                          vehLength, canBrake ? veh_impatience(c, v) : 1, cf.decel(), waiting, ignoreRedLink, v, true));
+            bool opened = yellow;
+            if (!opened) {
+                const int o = link_opened(c, link, cur, c.di_arrtime[cur][r], c.di_arrspeed[cur][r], leaveSpeed,
+                                          vehLength, canBrake ? veh_impatience(c, v) : 1, cf.decel(), waiting, ignoreRedLink, v, live);
+                if (o == OPEN_UNDETERMINED) {
+                    return false;
+                }
+                opened = o == OPEN_YES;
+            }
             const double visibilityDistance = c.link_foevis[link];
             const bool determinedFoePresence = dpiDist <= visibilityDistance;
             if (opened && !state_priority(ls) && !link_lastWasContMajor(c, link) && !link_isCont(c, link) && !ignoreRedLink) {
@@ -119,6 +126,7 @@ SB2_HD void veh_processLinkApproaches(const Ctx& c, int v, int wp, const CF& cf,
         haveToWait = false;
     }
     (void)pos;
+    return true;
 }
 
 // MSCFModel::finalizeSpeed (MSCFModel.cpp:199-265) with Krauss patchSpeedBeforeLC; `random` is the lane-RNG draw
@@ -161,12 +169,13 @@ SB2_HD double veh_random(const Ctx& c, int v) {
     return (double)(z >> 32) / 4294967296.0;   // 32 random bits like rng() / 4294967296.0
 }
 
-// MSVehicle::executeMove; `random` = RandHelper::rand(getRNG()) for the dawdle step
-SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
+// MSVehicle::executeMove; `random` = RandHelper::rand(getRNG()) for the dawdle step.  Returns false if the vehicle had to be
+// deferred to the second pass (nothing written; see LIVE_PASS1 in sb2_link.h)
+SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int live = LIVE_PASS1) {
     int myLane = c.veh_lane[v];
     c.veh_moved[v] = 0;
     if (myLane < 0) {
-        return;
+        return true;
     }
     const int cur = c.cur;
     const int vt = c.veh_type[v];
@@ -181,7 +190,9 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
     double vSafeMin = -SB2_DBL_MAX;
     double vSafeMinDist = 0;
     bool haveToWait = false;
-    veh_processLinkApproaches(c, v, wp, cf, oldSpeed, pos, myLane, waiting, vSafe, vSafeMin, vSafeMinDist, haveToWait, jentry, jconflict);
+    if (!veh_processLinkApproaches(c, v, wp, cf, oldSpeed, pos, myLane, waiting, vSafe, vSafeMin, vSafeMinDist, haveToWait, jentry, jconflict, live)) {
+        return false;
+    }
 
     double vNext = vSafe;
     const double rawAccel = (MAX2(vNext, 0.) - oldSpeed) / c.TS;
@@ -368,14 +379,48 @@ SB2_HDN void veh_executeMove(const Ctx& c, int v, int wp, double random) {
         c.veh_moved[v] = 2;
         c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
         c.veh_arrival_lane[v] = myLane;
-        c.lane_arrived[oldLane] = 1;   // its queue entry is removed by lane_handoff_remove wherever it sits
-        c.veh_lane[v] = -2;
+        c.lane_arrived[oldLane] = 1;   // its queue entry is removed by lane_handoff_remove wherever it sits; veh_lane becomes -2 there
         atomic_inc(&c.counters[1]);
     } else if (myLane != oldLane) {
         c.veh_moved[v] = 1;
         c.veh_lane[v] = myLane;
         c.veh_next_incoming[v] = atomic_exch(&c.lane_incoming[myLane], v);
     }
+    return true;
+}
+
+// first pass of executeMove for the vehicle at work-list position wp; a deferred vehicle is queued for veh_execute_deferred
+SB2_HDN void veh_executeMove_pass1(const Ctx& c, int wp) {
+    const int v = c.veh_order[c.cur][wp];
+    if (veh_executeMove(c, v, wp, veh_random(c, v), LIVE_PASS1)) {
+        veh_register_partials(c, v);
+    } else {
+        c.veh_deferred[v] = 1;
+#if defined(__CUDA_ARCH__)
+        const int at = atomicAdd(&c.counters[9], 1);
+#else
+        const int at = c.counters[9]++;
+#endif
+        c.deferred_list[at] = wp;
+    }
+}
+
+// one round of the second pass for entry i of the deferred list; returns true if the vehicle is (now) done
+SB2_HDN bool veh_execute_deferred(const Ctx& c, int i) {
+    const int wp = c.deferred_list[i];
+    const int v = c.veh_order[c.cur][wp];
+    if (!c.veh_deferred[v]) {
+        return true;
+    }
+    if (!veh_executeMove(c, v, wp, veh_random(c, v), LIVE_PASS2)) {
+        return false;
+    }
+    veh_register_partials(c, v);
+#if defined(__CUDA_ARCH__)
+    __threadfence();
+#endif
+    c.veh_deferred[v] = 0;
+    return true;
 }
 
 }  // namespace sb2

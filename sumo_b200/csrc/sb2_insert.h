@@ -15,6 +15,33 @@
 namespace sb2 {
 
 
+// Departures of one step run one thread per departure lane, concurrently.  A vehicle that another lane's thread inserts in this
+// very step is INVISIBLE to this thread (snapshot semantics: deterministic, independent of thread timing): lane_tryInsert
+// publishes the new vehicle's state before it links it into the lane queue (fence in between), and every read of ANOTHER lane's
+// queue here skips entries with veh_depart_time == now.  (The reference inserts sequentially in load order, so there the later
+// vehicle sees the earlier one; that only matters when two vehicles depart in the same step on lanes closer to each other than
+// the insertion look-ahead -- brake gap downstream, getMaximumBrakeDist upstream.)
+SB2_HD bool ins_is_new(const Ctx& c, int v) { return c.veh_depart_time[v] == c.t; }
+// getLastAnyVehicle of another lane, without this step's departures
+SB2_HD int ins_lane_last_any(const Ctx& c, int l) {
+    int last = c.lane_last[l];
+    while (last >= 0 && ins_is_new(c, last)) {
+        last = c.veh_ahead[last];
+    }
+    if (last >= 0) {
+        return last;
+    }
+    return c.lane_npartial[l] > 0 ? c.lane_partial[(size_t)l * MAX_PARTIAL] : -1;
+}
+// front-most vehicle of another lane, without this step's departures
+SB2_HD int ins_lane_first(const Ctx& c, int l) {
+    int first = c.lane_first[l];
+    while (first >= 0 && ins_is_new(c, first)) {
+        first = c.veh_behind[first];
+    }
+    return first;
+}
+
 struct FollowerInfo {
     int veh;
     double dist, missingGap;
@@ -84,15 +111,15 @@ SB2_HD FollowerInfo lane_followers_on_consecutive(const Ctx& c, int l, int ego, 
                 searchDist = MIN2(searchDist, lane_max_brake_dist(c, next) - backOffset);
                 // getFirstVehicleInformation: front-most of vehicles and partial occupators / front-most vehicle with front on lane
                 const int np = c.lane_npartial[next];
-                int first = np > 0 ? c.lane_partial[(size_t)next * MAX_PARTIAL + np - 1] : c.lane_first[next];
-                const int firstFront = c.lane_first[next];
+                const int firstFront = ins_lane_first(c, next);
+                int first = np > 0 ? c.lane_partial[(size_t)next * MAX_PARTIAL + np - 1] : firstFront;
                 int v = first == ego ? firstFront : first;
                 double agap = 0;
                 if (v >= 0 && v != ego) {
                     if (!veh_front_on_lane(c, v, next)) {
                         agap = ilen - c.lane_length[next] + backOffset;
                         agap -= veh_mingap(c, v);
-                        const bool differentEdge = c.lane_edge[c.veh_lane[v]] != c.lane_edge[l];
+                        const bool differentEdge = c.lane_edge[SB2_CHK(c.veh_lane[v], 0, c.nL, 20)] != c.lane_edge[l];
                         if (agap > 0 && differentEdge) {
                             v = firstFront;
                             if (v >= 0 && v != ego) {
@@ -265,7 +292,7 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
         }
         const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
         const uint8_t state = c.link_state[link];
-        if (!link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v)
+        if (link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v) == OPEN_NO
                 || !state_priority(state)
                 || state == 'Z') {
             const double remaining = seen - 0.;
@@ -285,7 +312,7 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
             }
         }
         // leader on next lane: getLastVehicleInformation(aVehicle, 0, 0)
-        const int nextLeader = lane_last_any(c, nextLane);
+        const int nextLeader = ins_lane_last_any(c, nextLane);
         if (nextLeader >= 0 && nextLeader != v) {
             const double nextLaneSpeed = lane_safeInsertionSpeed(c, nextLane, cf, seen, nextLeader, speed);
             if (nextLaneSpeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nextLaneSpeed, patchSpeed)) {
@@ -329,7 +356,33 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     if (speed < 0) {
         return false;
     }
-    // ---- incorporateVehicle + enterLaneAtInsertion
+    // ---- incorporateVehicle + enterLaneAtInsertion: the vehicle's state first, then (after a fence) the queue links, so that a
+    // thread of another lane that meets the new entry finds it complete (and skips it, see ins_is_new)
+    c.veh_depart_time[v] = c.t;
+    c.veh_lane[v] = l;
+    c.veh_qlane[v] = l;
+    c.veh_routepos[v] = 0;
+    c.veh_pos[v] = pos;
+    c.veh_speed[v] = speed;
+    c.veh_prevspeed[v] = speed;
+    c.veh_backpos[v] = pos - cf.length();
+    c.veh_accel[v] = 0;
+    c.veh_lastdist[v] = 0;
+    c.veh_waiting[v] = 0;
+    c.veh_since_startup[v] = 86400000;   // MSVehicle ctor: myTimeSinceStartup(TIME2STEPS(3600 * 24)), MSVehicle.cpp:1023
+    c.veh_jentry[v] = SB2_TIME_MAX; c.veh_jentry_ny[v] = SB2_TIME_MAX; c.veh_jconflict[v] = SB2_TIME_MAX;
+    c.veh_havetowait[v] = 0;
+    c.veh_moved[v] = 0;
+    c.veh_nfurther[v] = 0;
+    // MSDevice_Tripinfo::notifyEnter(NOTIFICATION_DEPARTED)
+    c.veh_trip_routelen[v] = -pos;
+    c.veh_trip_departpos[v] = pos;
+    c.veh_trip_departspeed[v] = speed;
+    c.veh_trip_wait[v] = 0; c.veh_trip_waitcount[v] = 0; c.veh_trip_amwaiting[v] = 0;
+    c.veh_arrival_time[v] = -1; c.veh_arrival_lane[v] = -1;
+    c.veh_odometer[v] = 0;
+    c.veh_timeloss[v] = 0;
+    c.veh_stopspeed[v] = SB2_DBL_MAX;
     // position in the queue: before the first vehicle (from the rear) with pos >= ours
     int behind = -1;              // vehicle that ends up directly behind the new one
     int aheadV = c.lane_last[l];  // walks rear -> front
@@ -339,6 +392,9 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     }
     c.veh_ahead[v] = aheadV;
     c.veh_behind[v] = behind;
+#if defined(__CUDA_ARCH__)
+    __threadfence();
+#endif
     if (aheadV >= 0) {
         c.veh_behind[aheadV] = v;
     } else {
@@ -351,29 +407,7 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     }
     c.lane_nveh[l] += 1;
     c.lane_brutto[l] += cf.length() + cf.minGap();
-    c.veh_lane[v] = l;
-    c.veh_routepos[v] = 0;
-    c.veh_pos[v] = pos;
-    c.veh_speed[v] = speed;
-    c.veh_prevspeed[v] = speed;
-    c.veh_backpos[v] = pos - cf.length();
-    c.veh_accel[v] = 0;
-    c.veh_lastdist[v] = 0;
-    c.veh_waiting[v] = 0;
-    c.veh_since_startup[v] = 86400000;   // MSVehicle ctor: myTimeSinceStartup(TIME2STEPS(3600 * 24)), MSVehicle.cpp:1023
-    c.veh_jentry[v] = SB2_TIME_MAX; c.veh_jentry_ny[v] = SB2_TIME_MAX; c.veh_jconflict[v] = SB2_TIME_MAX;
-    c.veh_havetowait[v] = 0;
-    c.veh_nfurther[v] = 0;
-    c.veh_depart_time[v] = c.t;
-    // MSDevice_Tripinfo::notifyEnter(NOTIFICATION_DEPARTED)
-    c.veh_trip_routelen[v] = -pos;
-    c.veh_trip_departpos[v] = pos;
-    c.veh_trip_departspeed[v] = speed;
-    c.veh_trip_wait[v] = 0; c.veh_trip_waitcount[v] = 0; c.veh_trip_amwaiting[v] = 0;
-    c.veh_arrival_time[v] = -1; c.veh_arrival_lane[v] = -1;
-    c.veh_odometer[v] = 0;
-    c.veh_timeloss[v] = 0;
-    c.veh_stopspeed[v] = SB2_DBL_MAX;
+    c.lane_changed[l] = 1;   // MSLane::incorporateVehicle -> MSEdgeControl::gotActive (MSLane.cpp:471)
     // MSVehicleControl::vehicleDeparted
     atomic_max_double(&c.fleet_next[0], c.veh_speedfactor[v]);
     atomic_min_double(&c.fleet_next[1], cf.decel());

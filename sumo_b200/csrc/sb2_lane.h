@@ -15,10 +15,32 @@
 
 namespace sb2 {
 
+// MSEdgeControl::myActiveLanes as keys (see Ctx::lane_actkey).  phase 0 = patchActiveLanes (rank: numerical id, the order of
+// myChangedStateLanes), 1 = integrateNewVehicles loop (rank: id order), 2 = changeLanes' toAdd
+SB2_HD int64_t lane_make_actkey(const Ctx& c, int l, int phase) {
+    const int64_t step = c.t / c.DELTA_T + 1;
+    const int64_t rank = phase == 1 ? c.lane_idrank[l] : c.lane_numid[l];
+    const int64_t key = ((step * 4 + phase) << 32) | rank;
+    return (c.lane_flags[l] & LF_LANECHANGER) ? -key : key;   // haveNeighbors: push_front
+}
+// begin of the step: patchActiveLanes (MSEdgeControl.cpp:118-134), then the erase of empty lanes in planMovements (:150-153)
+SB2_HD void lane_patch_active(const Ctx& c, int l) {
+    if (c.lane_changed[l]) {
+        c.lane_changed[l] = 0;
+        if (c.lane_actkey[l] == 0 && c.lane_nveh[l] > 0) {
+            c.lane_actkey[l] = lane_make_actkey(c, l, 0);
+        }
+    }
+    if (c.lane_nveh[l] == 0) {
+        c.lane_actkey[l] = 0;
+    }
+}
+
 // before planMove: cumulated lengths in front of every vehicle, space till last standing vehicle
 // orderBase = first slot of this lane in the lane-ordered work list veh_order; firstSlot >= 0: the lane's front vehicle goes
 // there instead (k_pre groups the front vehicles of a block's lanes), the followers start at orderBase
 SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1, int firstSlot = -1) {
+    lane_patch_active(c, l);
     // front -> back (MSLane.cpp:1608-1623)
     double cum = 0.;
     int guard = 0;
@@ -27,6 +49,7 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1,
         (void)SB2_CHK(orderBase, 0, c.nV, 12);
         (void)SB2_CHK(guard++, 0, c.lane_nveh[l], 13);
         c.veh_len_in_front[v] = cum;
+        c.veh_qlane[v] = l;
         if (firstSlot >= 0) {
             c.veh_order[c.cur][firstSlot] = v;
             firstSlot = -1;
@@ -64,8 +87,11 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
     double toRemove = 0;
     int f = c.lane_first[l];
     int removed = 0;
-    while (f >= 0 && c.veh_lane[f] != l) {
+    while (f >= 0 && (c.veh_lane[f] != l || c.veh_moved[f] == 2)) {
         toRemove += veh_length_with_gap(c, f);
+        if (c.veh_moved[f] == 2) {
+            c.veh_lane[f] = -2;   // arrived (executeMove leaves veh_lane alone so that it stays readable during the whole pass)
+        }
         f = c.veh_behind[f];
         removed++;
     }
@@ -76,7 +102,10 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         int ahead = f;
         for (int x = f >= 0 ? c.veh_behind[f] : -1; x >= 0;) {
             const int next = c.veh_behind[x];
-            if (c.veh_lane[x] != l) {
+            if (c.veh_lane[x] != l || c.veh_moved[x] == 2) {
+                if (c.veh_moved[x] == 2) {
+                    c.veh_lane[x] = -2;
+                }
                 toRemove += veh_length_with_gap(c, x);
                 removed++;
                 c.veh_behind[ahead] = next;
@@ -105,6 +134,10 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         brutto = 0;
     }
     c.lane_brutto[l] = brutto;
+    // MSEdgeControl::executeMovements (MSEdgeControl.cpp:229-232): a lane without vehicles leaves the active list
+    if (c.lane_nveh[l] == 0) {
+        c.lane_actkey[l] = 0;
+    }
     // MSLane.cpp:2402-2456: the front-most remaining vehicle is teleported after waiting longer than time-to-teleport.
     // Teleporting (MSVehicleTransfer) is host-side logic the engine does not implement: report it, never ignore it.
     if (f >= 0 && c.timeToTeleport > 0 && c.veh_waiting[f] > c.timeToTeleport) {
@@ -159,6 +192,10 @@ SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
     }
     c.lane_nveh[l] += ni;
     c.lane_brutto[l] = brutto;
+    // MSEdgeControl.cpp:246-259: a lane that was empty joins the active list, in id order
+    if (ni > 0 && c.lane_actkey[l] == 0) {
+        c.lane_actkey[l] = lane_make_actkey(c, l, 1);
+    }
     // ---- partial occupators were appended by executeMove; keep them sorted by back position (sortPartialVehicles)
     int np = c.lane_npartial[l];
     if (np > MAX_PARTIAL) {
@@ -181,25 +218,6 @@ SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
             j--;
         }
         p[j + 1] = x;
-    }
-}
-
-// executeMove appends the vehicle to the partial list of every lane its back still covers
-SB2_HD void veh_register_partials(const Ctx& c, int v) {
-    if (c.veh_lane[v] < 0) {
-        return;
-    }
-    const int nf = c.veh_nfurther[v];
-    for (int i = 0; i < nf; i++) {
-        const int l = c.veh_further[(size_t)v * MAX_FURTHER + i];
-#if defined(__CUDA_ARCH__)
-        const int slot = atomicAdd(&c.lane_npartial[l], 1);
-#else
-        const int slot = c.lane_npartial[l]++;
-#endif
-        if (slot < MAX_PARTIAL) {
-            c.lane_partial[(size_t)l * MAX_PARTIAL + slot] = v;
-        }
     }
 }
 

@@ -134,60 +134,99 @@ SB2_HD bool link_blockedByFoe(const Ctx& c, int k, int buf, int r, int foe,
     return false;
 }
 
-// MSLink.cpp:1026-1059 (no persons, jmIgnoreFoeProb == 0, no ignoreFoe lists)
-SB2_HD bool link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime, SUMOTime leaveTime, double arrivalSpeed, double leaveSpeed,
-                               bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, bool regSpeed = false) {
-    for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        const int foe = SB2_CHK(c.veh_order[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8) % c.nV], 0, c.nV, 9);
-#if defined(SB2_DEBUG_LINK) && !defined(__CUDA_ARCH__)
-        if (ego == SB2_DEBUG_LINK_EGO) {
-            fprintf(stderr, "   blockedAtTime link %d foe %d onroad=%d req=%d aviArr=%lld aviLeave=%lld arr=%lld leave=%lld blocked=%d\n", k, foe, (int)veh_on_road(c, foe),
-                    (int)c.di_request[buf][r], (long long)c.di_arrtime[buf][r], (long long)c.di_leavetime[buf][r], (long long)arrivalTime, (long long)leaveTime,
-                    (int)link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime));
-        }
-#endif
-        if (foe != ego && veh_on_road(c, foe)
-                && (!lastWasContRed || (regSpeed ? c.di_regspeed[buf][r] : c.veh_speed[foe]) > SB2_HALTING_SPEED)
-                && link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
-            return true;
-        }
+// how MSLink::blockedAtTime reads a foe's speed under lastWasContRed (`it.first->getSpeed()`, MSLink.cpp:1050): the reference
+// executes lanes one after the other, so the speed is the foe's NEW one if the foe moved earlier in this step:
+//   LIVE_NOW   the caller runs while no vehicle moves (planMove: previous-step table and start-of-step speeds; insertion: this
+//              step's table and end-of-step speeds) -> veh_speed
+//   LIVE_PASS1 executeMove, first pass: a foe that moves later counts with its registered (start-of-step) speed; a blocking foe
+//              that moves earlier makes the answer OPEN_UNDETERMINED (the vehicle is deferred to pass 2)
+//   LIVE_PASS2 executeMove, second pass: earlier foes have their new speed in veh_speed unless they are deferred themselves
+enum { LIVE_NOW = 0, LIVE_PASS1 = 1, LIVE_PASS2 = 2 };
+enum { OPEN_NO = 0, OPEN_YES = 1, OPEN_UNDETERMINED = 2 };
+
+// true if the reference moves `foe` before `ego` in this step: MSEdgeControl::executeMovements walks myActiveLanes in list order
+// (lane_actkey), MSLane::executeMovements walks a lane front to back
+SB2_HD bool veh_executes_before(const Ctx& c, int foe, int ego) {
+    const int lf = c.veh_qlane[foe], le = c.veh_qlane[ego];
+    if (lf == le) {
+        return c.veh_len_in_front[foe] < c.veh_len_in_front[ego];
     }
-    return false;
+    return c.lane_actkey[lf] < c.lane_actkey[le];
 }
 
-// MSLink.cpp:837-1022
-SB2_RARE bool link_opened(const Ctx& c, int k, int buf, SUMOTime arrivalTime, double arrivalSpeed, double leaveSpeed, double vehicleLength,
-                        double impatience, double decel, SUMOTime waitingTime, bool ignoreRed, int ego, bool regSpeed = false) {
+// MSLink.cpp:1026-1059 (no persons, jmIgnoreFoeProb == 0, no ignoreFoe lists); returns OPEN_NO (= blocked) / OPEN_YES / OPEN_UNDETERMINED
+SB2_HD int link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime, SUMOTime leaveTime, double arrivalSpeed, double leaveSpeed,
+                              bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, int live = LIVE_NOW) {
+    int result = OPEN_YES;
+    for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
+        const int foe = SB2_CHK(c.veh_order[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8) % c.nV], 0, c.nV, 9);
+        if (foe == ego || !veh_on_road(c, foe)) {
+            continue;
+        }
+        if (lastWasContRed) {
+            double foeSpeed;
+            if (live == LIVE_NOW) {
+                foeSpeed = c.veh_speed[foe];
+            } else if (!veh_executes_before(c, foe, ego)) {
+                foeSpeed = c.di_regspeed[buf][r];
+            } else if (live == LIVE_PASS2 && !c.veh_deferred[foe]) {
+                foeSpeed = c.veh_speed[foe];
+            } else {
+                // the foe's new speed is not known yet: it only matters if this record would block
+                if (link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
+                    result = OPEN_UNDETERMINED;
+                }
+                continue;
+            }
+            if (!(foeSpeed > SB2_HALTING_SPEED)) {
+                continue;
+            }
+        }
+        if (link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
+            return OPEN_NO;
+        }
+    }
+    return result;
+}
+
+// MSLink.cpp:837-1022; OPEN_NO / OPEN_YES, or OPEN_UNDETERMINED in executeMove's first pass (see LIVE_PASS1)
+SB2_RARE int link_opened(const Ctx& c, int k, int buf, SUMOTime arrivalTime, double arrivalSpeed, double leaveSpeed, double vehicleLength,
+                        double impatience, double decel, SUMOTime waitingTime, bool ignoreRed, int ego, int live = LIVE_NOW) {
     const uint8_t state = c.link_state[k];
     if (state_red(state) && !ignoreRed) {
-        return false;
+        return OPEN_NO;
     }
     if (link_isCont(c, k)) {
-        return true;
+        return OPEN_YES;
     }
     const SUMOTime leaveTime = link_getLeaveTime(c, k, arrivalTime, arrivalSpeed, leaveSpeed, vehicleLength);
     if ((state_priority(state)
             || link_lastWasContState(c, k, 'G')
             || ((c.link_flags[k] & KF_EXIT_AFTER_IJ) && c.link_state[c.link_entry[k]] == 'G'))
             && state != 'Z') {
-        return true;
+        return OPEN_YES;
     }
     // jmAllwayStopWait / jmStopSignWait default TS
     if (state == 'w' && waitingTime < TIME2STEPS(c.TS)) {
-        return false;
+        return OPEN_NO;
     } else if (state == 's' && waitingTime < TIME2STEPS(c.TS)) {
-        return false;
+        return OPEN_NO;
     }
     const bool lastWasContRed = link_lastWasContState(c, k, 'r');
     const int to = c.link_to[k];
+    int result = OPEN_YES;
     for (int i = c.link_foelink_begin[k]; i < c.link_foelink_begin[k + 1]; i++) {
         const int fl = c.foelink[i];
-        if (link_blockedAtTime(c, fl, buf, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, to == c.link_to[fl],
-                               impatience, decel, waitingTime, ego, lastWasContRed, regSpeed)) {
-            return false;
+        const int b = link_blockedAtTime(c, fl, buf, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, to == c.link_to[fl],
+                                         impatience, decel, waitingTime, ego, lastWasContRed, live);
+        if (b == OPEN_NO) {
+            return OPEN_NO;
+        }
+        if (b == OPEN_UNDETERMINED) {
+            result = OPEN_UNDETERMINED;
         }
     }
-    return true;
+    return result;
 }
 
 SB2_HD int lane_nveh_with_partials(const Ctx& c, int l) { return c.lane_nveh[l] + c.lane_npartial[l]; }
@@ -197,7 +236,7 @@ SB2_HD bool link_hasApproachingFoe(const Ctx& c, int k, int buf, SUMOTime arriva
     const int to = c.link_to[k];
     for (int i = c.link_foelink_begin[k]; i < c.link_foelink_begin[k + 1]; i++) {
         const int fl = c.foelink[i];
-        if (link_blockedAtTime(c, fl, buf, arrivalTime, leaveTime, speed, speed, to == c.link_to[fl], 0, decel, 0, -1, false)) {
+        if (link_blockedAtTime(c, fl, buf, arrivalTime, leaveTime, speed, speed, to == c.link_to[fl], 0, decel, 0, -1, false) == OPEN_NO) {
             return true;
         }
     }

@@ -76,7 +76,7 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
                                  || i == 1
                                  || link_opened(c, item.link, tableBuf, item.arrivalTime, item.arrivalSpeed,
                                                 di_getLeaveSpeed(item), e.length,
-                                                veh_impatience(c, e.v), e.cf.decel(), e.waiting, false, e.v)));
+                                                veh_impatience(c, e.v), e.cf.decel(), e.waiting, false, e.v) != OPEN_NO));
         bool allowsContinuation = (item.link < 0 || link_isCont(c, item.link) || opened) && !item.hadStoppedVehicle;
         if (!opened && item.link >= 0) {
             foundStopped = true;
@@ -278,7 +278,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         const SUMOTime arrivalTime = veh_getArrivalTime(c, e, t, seen, vv, arrivalSpeed);
         if (couldBrakeForMinor && determinedFoePresence && (c.lane_flags[c.link_to[link]] & LF_ROUNDABOUT)) {
             const bool wasOpened = link_opened(c, link, prev, arrivalTime, arrivalSpeed, arrivalSpeed, e.length, veh_impatience(c, v),
-                                               cf.decel(), e.waiting, false, v);
+                                               cf.decel(), e.waiting, false, v) != OPEN_NO;
             if (!wasOpened) {
                 slowedDownForMinor = true;
             }

@@ -83,7 +83,7 @@ enum { LL_IN_THE_WAY = 1, LL_FROM_LEFT = 2, LL_SAME_SOURCE = 4, LL_SAME_TARGET =
 // error / event flags raised by kernels (never silently ignored: sumob200_step returns them)
 enum {
     ERR_DRIVE_ITEM_OVERFLOW = 1, ERR_FURTHER_OVERFLOW = 2, ERR_PARTIAL_OVERFLOW = 4, ERR_COLLISION = 8, ERR_TELEPORT = 16,
-    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512
+    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512, ERR_DEFERRED_UNRESOLVED = 1024
 };
 // car-following model ids = SUMO_TAG_CF_* values are remapped at load time
 enum { CF_KRAUSS = 0, CF_KRAUSS_ORIG1 = 1, CF_IDM = 2 };
@@ -113,6 +113,8 @@ struct Ctx {
     const int32_t* lane_inc_begin; const int32_t* inc_lane; const int32_t* inc_link; const double* inc_length;
     const int32_t* lane_to_junction; const int32_t* lane_from_junction;
     const int32_t* edge_lane_begin;
+    const int32_t* lane_numid;     // MSLane::getNumericalID (order of myChangedStateLanes, MSEdgeControl.h:296)
+    const int32_t* lane_idrank;    // rank of MSLane::getID in std::string order (ComparatorIdLess, MSEdgeControl.cpp:245)
     const int32_t* lane_shape_begin; const double* shape_xy; const double* lane_geomfactor;   // MSLane::getShape, getLengthGeometryFactor
     // ---- lanes (dynamic) -----------------------------------------------------------------
     int32_t* lane_first;       // front-most vehicle (largest pos) or -1        (MSLane::myVehicles.back())
@@ -122,6 +124,10 @@ struct Ctx {
     int32_t* lane_npartial; int32_t* lane_partial;   // [nL*MAX_PARTIAL] partial occupators, sorted by back position
     int32_t* lane_arrived;     // set by executeMove when a vehicle of this lane's queue arrived (it may sit behind the front vehicle)
     int32_t* lane_incoming;    // head of the list of vehicles that entered this lane in executeMove (myVehBuffer)
+    // MSEdgeControl::myActiveLanes (a std::list whose order decides who executes first, MSEdgeControl.cpp:118-262) as one key per
+    // lane: 0 = not active, else ((step * 4 + phase) << 32 | rank), negated for lanes of multi-lane edges (push_front).  Lane A
+    // executes before lane B iff key(A) < key(B).  lane_changed = myChangedStateLanes (gotActive since the last patchActiveLanes).
+    int64_t* lane_actkey; uint8_t* lane_changed;
     // per-step lane summary (k_lane_summary)
     int32_t* ls_lastveh;       // getLastVehicleInformation(nullptr,0): rear-most of vehicles+partials, -1 if none
     double* ls_space;          // getSpaceTillLastStanding(...)
@@ -183,6 +189,10 @@ struct Ctx {
     const uint8_t* veh_emissions;   // vehicle carries the emission device
     double* veh_em;            // [7*nV] MSDevice_Emissions::myEmissions, pollutant-major (CO2, CO, HC, fuel, NOx, PMx, electricity)
     double* veh_len_in_front;  // cumulatedVehLength handed to planMove (MSLane.cpp:1621)
+    int32_t* veh_qlane;        // lane whose queue holds the vehicle during this step's plan/execute (stable while veh_lane is rewritten)
+    // executeMove pass 2 (sb2_exec.h): vehicles whose right of way depends on the NEW speed of a foe that the reference executes
+    // earlier (MSLink::blockedAtTime reads the live speed, MSLink.cpp:1050): veh_deferred 1 = waiting, list + counters[9]
+    uint8_t* veh_deferred; int32_t* deferred_list;
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
     // neighbouring lanes, see the same links and foes and take the same branches.  Two segments: [0, counters[7]) = lanes whose

@@ -121,4 +121,23 @@ SB2_HD int lane_succ_link(const Ctx& c, int l, int nextEdge) {
     return -1;
 }
 
+// executeMove appends the vehicle to the partial list of every lane its back still covers
+SB2_HD void veh_register_partials(const Ctx& c, int v) {
+    if (c.veh_lane[v] < 0 || c.veh_moved[v] == 2) {
+        return;
+    }
+    const int nf = c.veh_nfurther[v];
+    for (int i = 0; i < nf; i++) {
+        const int l = c.veh_further[(size_t)v * MAX_FURTHER + i];
+#if defined(__CUDA_ARCH__)
+        const int slot = atomicAdd(&c.lane_npartial[l], 1);
+#else
+        const int slot = c.lane_npartial[l]++;
+#endif
+        if (slot < MAX_PARTIAL) {
+            c.lane_partial[(size_t)l * MAX_PARTIAL + slot] = v;
+        }
+    }
+}
+
 }  // namespace sb2

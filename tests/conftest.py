@@ -39,6 +39,9 @@ CASES.update({
     "grid3_small_idm": ["--default.speeddev", "0"],
     "grid5_dense_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
     "c1_grid10_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "2500"],
+    # the case that exposed MSLink::blockedAtTime's LIVE foe speed under lastWasContRed (MSLink.cpp:1050) at t = 514 s: a left turner
+    # waiting on the junction sees a foe whose lane the reference executes earlier in the step (executeMove pass 2, sb2_link.h)
+    "grid4_tls_idm": ["--default.speeddev", "0", "--end", "1200"],
 })
 def _mixed_fleet(text):
     """three vTypes (default car, long slow truck, short quick car with impatience), assigned pseudo-randomly but reproducibly"""

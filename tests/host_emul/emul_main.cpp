@@ -79,10 +79,19 @@ static void step(Model& m) {
         dumpItems(m, gDebugVeh, "plan");
     }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
+    c.counters[9] = 0;
     for (int i = 0; i < nOrder; i++) {
-        const int v = c.veh_order[c.cur][i];
-        veh_executeMove(c, v, i, veh_random(c, v));
-        veh_register_partials(c, v);
+        veh_executeMove_pass1(c, i);
+    }
+    for (int round = 0, left = c.counters[9]; left > 0; round++) {
+        left = 0;
+        for (int i = 0; i < c.counters[9]; i++) {
+            left += veh_execute_deferred(c, i) ? 0 : 1;
+        }
+        if (round == 8 && left > 0) {
+            raise(c, ERR_DEFERRED_UNRESOLVED);
+            break;
+        }
     }
     for (int l = 0; l < c.nL; l++) {
         lane_handoff_remove(c, l);

@@ -81,7 +81,7 @@ def test_engine_matches_reference_sigma_with_replayed_draws(case):
     assert compared > 1000
 
 
-@pytest.mark.parametrize("case", ["grid3_small_idm", "grid5_dense_idm", "c1_grid10_idm"])
+@pytest.mark.parametrize("case", ["grid3_small_idm", "grid5_dense_idm", "c1_grid10_idm", "grid4_tls_idm"])
 def test_engine_matches_reference_idm(case):
     """carFollowModel IDM.  pow(x, delta) is not specified bit for bit by glibc (0.52 ulp) nor by CUDA, so this is the one
     floating-point tolerance of the suite: the same vehicles on the same lanes after every step, position and speed within
