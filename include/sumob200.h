@@ -28,10 +28,11 @@ extern "C" {
 #define SUMOB200_ENODEVICE (-3)   /* no usable CUDA device */
 #define SUMOB200_ECUDA (-4)       /* CUDA runtime error */
 
-/* bits of sumob200_step_result.flags: events the engine detects but does not resolve itself (the reference resolves them
- * on the host: teleporting MSVehicleTransfer, collision handling MSLane.cpp:2078, emergency stop warnings) or capacity
- * overflows of its fixed-size per-vehicle tables.  A non-zero value means the run diverges from the reference from that
- * step on; the caller must treat it as an error, it is never silently ignored. */
+/* bits of sumob200_step_result.flags: events the engine cannot follow the reference through (emergency stops at a lane end,
+ * link states it refuses) or capacity overflows of its fixed-size per-vehicle tables.  A non-zero value means the run diverges
+ * from the reference from that step on; the caller must treat it as an error, it is never silently ignored.  Teleports and
+ * collisions are EXECUTED on the device like the reference does (MSLane.cpp:2402-2456, 2078-2211, MSVehicleTransfer.cpp) and only
+ * counted (teleports, collisions); bits 8 and 16 are kept for ABI stability and never raised. */
 #define SUMOB200_F_DRIVE_ITEM_OVERFLOW 1
 #define SUMOB200_F_FURTHER_OVERFLOW 2
 #define SUMOB200_F_PARTIAL_OVERFLOW 4
@@ -42,6 +43,7 @@ extern "C" {
 #define SUMOB200_F_UNSUPPORTED_LINKSTATE 128
 #define SUMOB200_F_LANE_ORDER 256
 #define SUMOB200_F_SEARCH_OVERFLOW 512
+#define SUMOB200_F_DEFERRED_UNRESOLVED 1024  /* executeMove pass 2 did not converge (sb2_exec.h) */
 
 typedef struct sumob200_engine sumob200_engine;
 
@@ -56,15 +58,17 @@ typedef struct sumob200_array {
 
 typedef struct sumob200_step_result {
     int64_t time_ms;          /* simulation time after the last executed step (MSNet::getCurrentTimeStep) */
-    int32_t running;          /* vehicles on the road                  (MSVehicleControl::getRunningVehicleNo) */
+    int32_t running;          /* vehicles on the road + teleporting ones (MSVehicleControl::getRunningVehicleNo) */
     int32_t departed_total;   /* vehicles inserted so far              (getDepartedVehicleNo) */
     int32_t arrived_total;    /* vehicles that reached their arrival   (getArrivedVehicleNo) */
     int32_t collisions;       /* collisions detected so far */
     int32_t emergency_stops;  /* emergency stops at lane ends so far */
-    int32_t teleports;        /* teleport conditions detected so far (not executed) */
+    int32_t teleports;        /* teleports so far: waited longer than time-to-teleport, or collided (MSVehicleControl::getTeleportCount) */
     int32_t flags;            /* OR of SUMOB200_F_* raised so far */
     int32_t halting;          /* on-road vehicles slower than 0.1 m/s     (MSVehicleControl::getHaltingVehicleNo, summary output) */
     int64_t vehicle_updates;  /* sum over the executed steps of vehicles on the road (numerator of SUMO's UPS, MSNet.cpp:959) */
+    int32_t teleporting;      /* vehicles currently off the road in MSVehicleTransfer (part of `running`) */
+    int32_t reserved;
 } sumob200_step_result;
 
 /* state mirror of one vehicle slot (slot = index in the veh_* arrays = load order); what libsumo::Vehicle getters read

@@ -260,7 +260,7 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
                 e->phaseMs[p] += ms;
             }
         }
-        e->launches += 9;
+        e->launches += 12;
         c.t += c.DELTA_T;
         c.cur ^= 1;
         e->stepsDone++;
@@ -275,7 +275,9 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         CUDA_TRY(cudaMemcpyAsync(&updates, e->dUpdates, sizeof(updates), cudaMemcpyDeviceToHost, s));
         CUDA_TRY(cudaStreamSynchronize(s));
         out->time_ms = c.t;
-        out->running = counters[0];
+        out->running = counters[0] + counters[10];
+        out->teleporting = counters[10];
+        out->reserved = 0;
         out->arrived_total = counters[1];
         out->departed_total = counters[2];
         out->collisions = counters[4];
@@ -350,7 +352,7 @@ int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out) {
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     out->time_ms = e->d.t - e->d.DELTA_T;
     out->inserted = p.departed;
-    out->running = p.count;
+    out->running = p.count + p.teleporting;
     out->waiting = p.waiting;
     out->ended = p.ended;
     out->arrived = p.ended;

@@ -40,6 +40,7 @@ namespace SB2_PASTE(sb2_kset_, SB2_KSET) {
 #include "sb2_exec.h"
 #include "sb2_lane.h"
 #include "sb2_insert.h"
+#include "sb2_transfer.h"
 #include "sb2_fcd.h"
 #include "sb2_summary.h"
 
@@ -245,7 +246,28 @@ __global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l < c.nL) {
         lane_handoff_integrate(c, l);
+    }
+}
+
+// MSEdgeControl::detectCollisions(STAGE_MOVEMENTS): a collider is teleported (collision.action teleport, the default)
+__global__ void __launch_bounds__(BLOCK) k_collide(const __grid_constant__ Ctx c) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
         lane_detect_collisions(c, l);
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) k_partials(const __grid_constant__ Ctx c) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        lane_sort_partials(c, l);
+    }
+}
+
+// MSVehicleTransfer::checkInsertions: the teleporting vehicles are handled one after the other, in numerical id order
+__global__ void k_transfer(const __grid_constant__ Ctx c) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && c.counters[10] > 0) {
+        transfer_checkInsertions(c);
     }
 }
 
@@ -462,8 +484,8 @@ void l_pre(const void* c, int n, cudaStream_t s) { k_pre<<<grid(n < 3 ? 3 : n), 
 void l_plan(const void* c, int n, cudaStream_t s) { k_plan<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 void l_execute(const void* c, int n, cudaStream_t s) { k_execute<<<grid(n), BLOCK, 0, s>>>(ctx(c)); k_execute2<<<1, 256, 0, s>>>(ctx(c)); }
 void l_remove(const void* c, int n, cudaStream_t s) { k_remove<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
-void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
-void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_integrate(const void* c, int n, cudaStream_t s) { k_integrate<<<grid(n), BLOCK, 0, s>>>(ctx(c)); k_collide<<<grid(n), BLOCK, 0, s>>>(ctx(c)); k_partials<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_insert(const void* c, int n, cudaStream_t s) { k_insert<<<grid(n), BLOCK, 0, s>>>(ctx(c)); k_transfer<<<1, 32, 0, s>>>(ctx(c)); }
 void l_count(const void* c, int n, unsigned long long* updates, cudaStream_t s) { k_count<<<n > 0 ? (n + 1023) / 1024 : 1, 1024, 0, s>>>(ctx(c), updates); }
 void l_mirror(const void* c, int n, sumob200_vehicle_state* out, cudaStream_t s) { k_mirror<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 void l_tripinfo(const void* c, int n, sumob200_tripinfo* out, cudaStream_t s) { k_tripinfo<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }

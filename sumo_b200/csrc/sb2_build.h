@@ -392,6 +392,8 @@ public:
         SB2_DYN(int32_t, veh_ahead, nV, -1); SB2_DYN(int32_t, veh_behind, nV, -1); SB2_DYN(int32_t, veh_next_incoming, nV, -1);
         SB2_DYN(int32_t, veh_nfurther, nV, 0); SB2_DYN(int32_t, veh_further, (size_t)nV * MAX_FURTHER, -1);
         SB2_DYN(double, veh_len_in_front, nV, 0.);
+        SB2_DYN(int32_t, tp_list, nV, -1); SB2_DYN(SUMOTime, veh_tp_proceed, nV, (SUMOTime)-1);
+        SB2_DYN(uint8_t, edge_delayed, h.nE, (uint8_t)0);
         SB2_DYN(int32_t, veh_qlane, nV, -1); SB2_DYN(uint8_t, veh_deferred, nV, (uint8_t)0); SB2_DYN(int32_t, deferred_list, nV, -1);
         SB2_DYN(int32_t, lane_arrived, nL, 0);
         SB2_DYN(SUMOTime, veh_trip_wait, nV, 0); SB2_DYN(int32_t, veh_trip_waitcount, nV, 0); SB2_DYN(uint8_t, veh_trip_amwaiting, nV, 0);

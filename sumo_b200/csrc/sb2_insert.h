@@ -18,14 +18,14 @@ namespace sb2 {
 // Departures of one step run one thread per departure lane, concurrently.  A vehicle that another lane's thread inserts in this
 // very step is INVISIBLE to this thread (snapshot semantics: deterministic, independent of thread timing): lane_tryInsert
 // publishes the new vehicle's state before it links it into the lane queue (fence in between), and every read of ANOTHER lane's
-// queue here skips entries with veh_depart_time == now.  (The reference inserts sequentially in load order, so there the later
+// queue here skips entries with veh_depart_time == now.  (Teleporting vehicles re-enter afterwards, one by one, and see everything: snapshot == false.  The reference inserts sequentially in load order, so there the later
 // vehicle sees the earlier one; that only matters when two vehicles depart in the same step on lanes closer to each other than
 // the insertion look-ahead -- brake gap downstream, getMaximumBrakeDist upstream.)
 SB2_HD bool ins_is_new(const Ctx& c, int v) { return c.veh_depart_time[v] == c.t; }
 // getLastAnyVehicle of another lane, without this step's departures
-SB2_HD int ins_lane_last_any(const Ctx& c, int l) {
+SB2_HD int ins_lane_last_any(const Ctx& c, int l, bool snapshot) {
     int last = c.lane_last[l];
-    while (last >= 0 && ins_is_new(c, last)) {
+    while (snapshot && last >= 0 && ins_is_new(c, last)) {
         last = c.veh_ahead[last];
     }
     if (last >= 0) {
@@ -34,9 +34,9 @@ SB2_HD int ins_lane_last_any(const Ctx& c, int l) {
     return c.lane_npartial[l] > 0 ? c.lane_partial[(size_t)l * MAX_PARTIAL] : -1;
 }
 // front-most vehicle of another lane, without this step's departures
-SB2_HD int ins_lane_first(const Ctx& c, int l) {
+SB2_HD int ins_lane_first(const Ctx& c, int l, bool snapshot) {
     int first = c.lane_first[l];
-    while (first >= 0 && ins_is_new(c, first)) {
+    while (snapshot && first >= 0 && ins_is_new(c, first)) {
         first = c.veh_behind[first];
     }
     return first;
@@ -73,11 +73,10 @@ SB2_HD double lane_max_brake_dist(const Ctx& c, int l) {
 }
 
 // MSLane::getFollowersOnConsecutive(ego, backOffset, false) for a vehicle about to be inserted on lane l at pos
-SB2_HD FollowerInfo lane_followers_on_consecutive(const Ctx& c, int l, int ego, double egoLength, double egoDecel, double backOffset) {
+SB2_HD FollowerInfo lane_followers_on_consecutive(const Ctx& c, int l, int ego, double egoLength, double egoDecel, double backOffset, double egoSpeed, bool snapshot) {
     FollowerInfo fi;
     fi.veh = -1; fi.dist = SB2_DBL_MAX; fi.missingGap = -SB2_DBL_MAX;
     const double egoPos = backOffset + egoLength;
-    const double egoSpeed = 0.;   // ego->getSpeed(): not yet departed
     AnyVehIter it = any_begin(c, l);
     for (int veh = any_next(c, l, it); veh >= 0; veh = any_next(c, l, it)) {
         const double vpos = veh_pos_on_lane(c, veh, l);
@@ -111,7 +110,7 @@ SB2_HD FollowerInfo lane_followers_on_consecutive(const Ctx& c, int l, int ego, 
                 searchDist = MIN2(searchDist, lane_max_brake_dist(c, next) - backOffset);
                 // getFirstVehicleInformation: front-most of vehicles and partial occupators / front-most vehicle with front on lane
                 const int np = c.lane_npartial[next];
-                const int firstFront = ins_lane_first(c, next);
+                const int firstFront = ins_lane_first(c, next, snapshot);
                 int first = np > 0 ? c.lane_partial[(size_t)next * MAX_PARTIAL + np - 1] : firstFront;
                 int v = first == ego ? firstFront : first;
                 double agap = 0;
@@ -193,7 +192,192 @@ SB2_HD double lane_safeInsertionSpeed(const Ctx& c, int l, const CF& cf, double 
     return nspeed;
 }
 
-// MSLane::isInsertionSuccess + incorporateVehicle; returns true if the vehicle was inserted
+// MSLane::isInsertionSuccess + incorporateVehicle (MSLane.cpp:851-1420, 456-477); returns true if the vehicle was inserted.
+// teleport = the vehicle re-enters from MSVehicleTransfer (notification NOTIFICATION_TELEPORT): it has departed before, keeps its
+// route position, speed (ego->getSpeed() in the follower / link-leader checks) and trip records
+SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, double pos, bool patchSpeed, bool patchSpeedSpecial, bool teleport) {
+    CF cf = make_cf(c, c.veh_type[v]);
+    cf.desSpeed = lane_vehicle_max_speed(c, l, v);   // setTentativeLaneAndPosition (MSLane.cpp:851): veh->getLane() == this lane
+    const double egoSpeed = teleport ? c.veh_speed[v] : 0.;   // getSpeed() of a not yet departed vehicle is 0
+    const int routePos0 = teleport ? c.veh_routepos[v] : 0;
+    if (pos < 0 || pos > c.lane_length[l]) {
+        pos = c.lane_length[l];
+    }
+    double seen = c.lane_length[l] - pos;
+    double dist = cf_brakeGap(cf, speed) + cf.minGap();
+    // leader on the insertion lane: getLastVehicleInformation(aVehicle, 0, pos)
+    int leader = -1;
+    {
+        AnyVehIter it = any_begin(c, l);
+        for (int veh = any_next(c, l, it); veh >= 0; veh = any_next(c, l, it)) {
+            if (veh != v && MAX2(0.0, veh_pos_on_lane(c, veh, l)) >= pos) {
+                leader = veh;
+                break;
+            }
+        }
+    }
+    const double nspeed = lane_safeInsertionSpeed(c, l, cf, -pos, leader, speed);
+    if (nspeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nspeed, patchSpeed)) {
+        return false;
+    }
+    // continuation lanes
+    Ego e;
+    e.v = v; e.vt = c.veh_type[v]; e.lane = l; e.pos = pos; e.speed = egoSpeed;
+    e.cf = cf; e.length = cf.length(); e.minGap = cf.minGap(); e.waiting = 0;
+    int nRouteSuccs = 1;
+    int currentLane = l;
+    const int r = c.veh_route[v];
+    const int routeLen = c.route_begin[r + 1] - c.route_begin[r];
+    SUMOTime arrivalTime = c.t + TIME2STEPS(seen / MAX2(speed, SB2_HALTING_SPEED));
+    int guard = 0;
+    while (seen < dist && guard++ < 32) {
+        const int nextEdge = routePos0 + nRouteSuccs < routeLen ? c.route_edges[c.route_begin[r] + routePos0 + nRouteSuccs] : -1;
+        const int link = lane_succ_link(c, currentLane, nextEdge);
+        if (link < 0) {
+            if (c.lane_edge[currentLane] == c.route_edges[c.route_begin[r + 1] - 1]) {
+                // reached the end of the route (arrivalSpeed not given; mayContinue: no further route)
+            } else {
+                if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeedSpecial)) {
+                    return false;
+                }
+            }
+            break;
+        }
+        const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
+        const uint8_t state = c.link_state[link];
+        if (link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v) == OPEN_NO
+                || !state_priority(state)
+                || state == 'Z') {
+            const double remaining = seen - 0.;
+            if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, remaining), patchSpeedSpecial)) {
+                return false;
+            }
+            if (seen >= cf.minGap()) {
+                break;
+            }
+        } else if (lane_internal(c, nextLane)) {
+            double tmp = 0;
+            bool dummyReq = true;
+            double nSpeed = speed;
+            veh_checkLinkLeader(c, e, c.lane_link_begin[nextLane], nextLane, seen + c.lane_length[nextLane], nullptr, nSpeed, tmp, tmp, dummyReq, c.cur, teleport);
+            if (ins_checkFailure(cf, speed, dist, nSpeed, patchSpeed)) {
+                return false;
+            }
+        }
+        // leader on next lane: getLastVehicleInformation(aVehicle, 0, 0)
+        const int nextLeader = ins_lane_last_any(c, nextLane, !teleport);
+        if (nextLeader >= 0 && nextLeader != v) {
+            const double nextLaneSpeed = lane_safeInsertionSpeed(c, nextLane, cf, seen, nextLeader, speed);
+            if (nextLaneSpeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nextLaneSpeed, patchSpeed)) {
+                return false;
+            }
+        }
+        const double freeSpeed = cf_freeSpeed(cf, speed, seen, lane_vehicle_max_speed(c, nextLane, v), true);
+        if (freeSpeed < speed) {
+            if (patchSpeedSpecial) {
+                speed = freeSpeed;
+                dist = cf_brakeGap(cf, speed) + cf.minGap();
+            }
+            // else: warning only (gCheckRoutes false is not the default; the reference deschedules -> treat as failure)
+            else {
+                return false;
+            }
+        }
+        const SUMOTime leaveTime = link_getLeaveTime(c, link, arrivalTime, speed, speed, cf.length());
+        if (link_hasApproachingFoe(c, link, c.cur, arrivalTime, leaveTime, speed, cf.decel())) {
+            if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeed)) {
+                return false;
+            }
+        }
+        arrivalTime += TIME2STEPS(c.lane_length[nextLane] / MAX2(speed, SB2_NUMERICAL_EPS));
+        seen += c.lane_length[nextLane];
+        currentLane = nextLane;
+        if (c.link_via[link] < 0) {
+            nRouteSuccs++;
+        }
+    }
+    // followers
+    const double backOffset = pos - cf.length();
+    const FollowerInfo fi = lane_followers_on_consecutive(c, l, v, cf.length(), cf.decel(), backOffset, egoSpeed, !teleport);
+    if (fi.veh >= 0) {
+        const CF fcf = make_cf(c, c.veh_type[fi.veh]);
+        const double backGapNeeded = cf_getSecureGap(fcf, c.veh_speed[fi.veh], speed, cf.decel());
+        if (fi.dist < backGapNeeded) {
+            return false;
+        }
+    }
+    if (speed < 0) {
+        return false;
+    }
+    // ---- incorporateVehicle + enterLaneAtInsertion: the vehicle's state first, then (after a fence) the queue links, so that a
+    // thread of another lane that meets the new entry finds it complete (and skips it, see ins_is_new)
+    if (!teleport) {
+        c.veh_depart_time[v] = c.t;
+        c.veh_routepos[v] = 0;
+        c.veh_prevspeed[v] = speed;
+        c.veh_waiting[v] = 0;
+        c.veh_since_startup[v] = 86400000;   // MSVehicle ctor: myTimeSinceStartup(TIME2STEPS(3600 * 24)), MSVehicle.cpp:1023
+        c.veh_jentry[v] = SB2_TIME_MAX; c.veh_jentry_ny[v] = SB2_TIME_MAX; c.veh_jconflict[v] = SB2_TIME_MAX;
+        // MSDevice_Tripinfo::notifyEnter(NOTIFICATION_DEPARTED)
+        c.veh_trip_routelen[v] = -pos;
+        c.veh_trip_departpos[v] = pos;
+        c.veh_trip_departspeed[v] = speed;
+        c.veh_trip_wait[v] = 0; c.veh_trip_waitcount[v] = 0; c.veh_trip_amwaiting[v] = 0;
+        c.veh_arrival_time[v] = -1; c.veh_arrival_lane[v] = -1;
+        c.veh_odometer[v] = 0;
+        c.veh_timeloss[v] = 0;
+    } else {
+        // MSVehicle::enterLaneAtInsertion(NOTIFICATION_TELEPORT) (MSVehicle.cpp:5793-5858): "avoid startup-effects after teleport"
+        c.veh_since_startup[v] = cf.startupDelay() + c.DELTA_T;
+    }
+    c.veh_lane[v] = l;
+    c.veh_qlane[v] = l;
+    c.veh_pos[v] = pos;
+    c.veh_speed[v] = speed;
+    c.veh_backpos[v] = pos - cf.length();
+    c.veh_accel[v] = 0;
+    c.veh_lastdist[v] = 0;
+    c.veh_havetowait[v] = 0;
+    c.veh_moved[v] = 0;
+    c.veh_nfurther[v] = 0;
+    c.veh_stopspeed[v] = SB2_DBL_MAX;
+    // position in the queue: before the first vehicle (from the rear) with pos >= ours
+    int behind = -1;              // vehicle that ends up directly behind the new one
+    int aheadV = c.lane_last[l];  // walks rear -> front
+    while (aheadV >= 0 && !(c.veh_pos[aheadV] >= pos)) {
+        behind = aheadV;
+        aheadV = c.veh_ahead[aheadV];
+    }
+    c.veh_ahead[v] = aheadV;
+    c.veh_behind[v] = behind;
+#if defined(__CUDA_ARCH__)
+    __threadfence();
+#endif
+    if (aheadV >= 0) {
+        c.veh_behind[aheadV] = v;
+    } else {
+        c.lane_first[l] = v;
+    }
+    if (behind >= 0) {
+        c.veh_ahead[behind] = v;
+    } else {
+        c.lane_last[l] = v;
+    }
+    c.lane_nveh[l] += 1;
+    c.lane_brutto[l] += cf.length() + cf.minGap();
+    c.lane_changed[l] = 1;   // MSLane::incorporateVehicle -> MSEdgeControl::gotActive (MSLane.cpp:471)
+    c.edge_delayed[c.lane_edge[l]] = 1;   // MSEdge::markDelayed (MSLane.cpp:469)
+    if (!teleport) {
+        // MSVehicleControl::vehicleDeparted
+        atomic_max_double(&c.fleet_next[0], c.veh_speedfactor[v]);
+        atomic_min_double(&c.fleet_next[1], cf.decel());
+        atomic_max_double(&c.fleet_next[2], cf.minGap());
+        atomic_inc(&c.counters[2]);
+    }
+    return true;
+}
+
+// MSLane::insertVehicle (departure): depart speed and position, then isInsertionSuccess; returns true if the vehicle was inserted
 SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     CF cf = make_cf(c, c.veh_type[v]);
     cf.desSpeed = lane_vehicle_max_speed(c, l, v);   // setTentativeLaneAndPosition (MSLane.cpp:851): veh->getLane() == this lane
@@ -248,172 +432,7 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     if (pos < 0 || pos > c.lane_length[l]) {
         pos = c.lane_length[l];
     }
-    // ---- isInsertionSuccess
-    double seen = c.lane_length[l] - pos;
-    double dist = cf_brakeGap(cf, speed) + cf.minGap();
-    const bool patchSpeedSpecial = patchSpeed || dsd != DSD_GIVEN;
-    // leader on the insertion lane: getLastVehicleInformation(aVehicle, 0, pos)
-    int leader = -1;
-    {
-        AnyVehIter it = any_begin(c, l);
-        for (int veh = any_next(c, l, it); veh >= 0; veh = any_next(c, l, it)) {
-            if (veh != v && MAX2(0.0, veh_pos_on_lane(c, veh, l)) >= pos) {
-                leader = veh;
-                break;
-            }
-        }
-    }
-    const double nspeed = lane_safeInsertionSpeed(c, l, cf, -pos, leader, speed);
-    if (nspeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nspeed, patchSpeed)) {
-        return false;
-    }
-    // continuation lanes
-    Ego e;
-    e.v = v; e.vt = c.veh_type[v]; e.lane = l; e.pos = pos; e.speed = 0. /* getSpeed() of a not yet departed vehicle */;
-    e.cf = cf; e.length = cf.length(); e.minGap = cf.minGap(); e.waiting = 0;
-    int nRouteSuccs = 1;
-    int currentLane = l;
-    const int r = c.veh_route[v];
-    const int routeLen = c.route_begin[r + 1] - c.route_begin[r];
-    SUMOTime arrivalTime = c.t + TIME2STEPS(seen / MAX2(speed, SB2_HALTING_SPEED));
-    int guard = 0;
-    while (seen < dist && guard++ < 32) {
-        const int nextEdge = nRouteSuccs < routeLen ? c.route_edges[c.route_begin[r] + nRouteSuccs] : -1;   // routepos == 0
-        const int link = lane_succ_link(c, currentLane, nextEdge);
-        if (link < 0) {
-            if (c.lane_edge[currentLane] == c.route_edges[c.route_begin[r + 1] - 1]) {
-                // reached the end of the route (arrivalSpeed not given; mayContinue: no further route)
-            } else {
-                if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeedSpecial)) {
-                    return false;
-                }
-            }
-            break;
-        }
-        const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
-        const uint8_t state = c.link_state[link];
-        if (link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v) == OPEN_NO
-                || !state_priority(state)
-                || state == 'Z') {
-            const double remaining = seen - 0.;
-            if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, remaining), patchSpeedSpecial)) {
-                return false;
-            }
-            if (seen >= cf.minGap()) {
-                break;
-            }
-        } else if (lane_internal(c, nextLane)) {
-            double tmp = 0;
-            bool dummyReq = true;
-            double nSpeed = speed;
-            veh_checkLinkLeader(c, e, c.lane_link_begin[nextLane], nextLane, seen + c.lane_length[nextLane], nullptr, nSpeed, tmp, tmp, dummyReq, c.cur, false);
-            if (ins_checkFailure(cf, speed, dist, nSpeed, patchSpeed)) {
-                return false;
-            }
-        }
-        // leader on next lane: getLastVehicleInformation(aVehicle, 0, 0)
-        const int nextLeader = ins_lane_last_any(c, nextLane);
-        if (nextLeader >= 0 && nextLeader != v) {
-            const double nextLaneSpeed = lane_safeInsertionSpeed(c, nextLane, cf, seen, nextLeader, speed);
-            if (nextLaneSpeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nextLaneSpeed, patchSpeed)) {
-                return false;
-            }
-        }
-        const double freeSpeed = cf_freeSpeed(cf, speed, seen, lane_vehicle_max_speed(c, nextLane, v), true);
-        if (freeSpeed < speed) {
-            if (patchSpeedSpecial) {
-                speed = freeSpeed;
-                dist = cf_brakeGap(cf, speed) + cf.minGap();
-            }
-            // else: warning only (gCheckRoutes false is not the default; the reference deschedules -> treat as failure)
-            else {
-                return false;
-            }
-        }
-        const SUMOTime leaveTime = link_getLeaveTime(c, link, arrivalTime, speed, speed, cf.length());
-        if (link_hasApproachingFoe(c, link, c.cur, arrivalTime, leaveTime, speed, cf.decel())) {
-            if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeed)) {
-                return false;
-            }
-        }
-        arrivalTime += TIME2STEPS(c.lane_length[nextLane] / MAX2(speed, SB2_NUMERICAL_EPS));
-        seen += c.lane_length[nextLane];
-        currentLane = nextLane;
-        if (c.link_via[link] < 0) {
-            nRouteSuccs++;
-        }
-    }
-    // followers
-    const double backOffset = pos - cf.length();
-    const FollowerInfo fi = lane_followers_on_consecutive(c, l, v, cf.length(), cf.decel(), backOffset);
-    if (fi.veh >= 0) {
-        const CF fcf = make_cf(c, c.veh_type[fi.veh]);
-        const double backGapNeeded = cf_getSecureGap(fcf, c.veh_speed[fi.veh], speed, cf.decel());
-        if (fi.dist < backGapNeeded) {
-            return false;
-        }
-    }
-    if (speed < 0) {
-        return false;
-    }
-    // ---- incorporateVehicle + enterLaneAtInsertion: the vehicle's state first, then (after a fence) the queue links, so that a
-    // thread of another lane that meets the new entry finds it complete (and skips it, see ins_is_new)
-    c.veh_depart_time[v] = c.t;
-    c.veh_lane[v] = l;
-    c.veh_qlane[v] = l;
-    c.veh_routepos[v] = 0;
-    c.veh_pos[v] = pos;
-    c.veh_speed[v] = speed;
-    c.veh_prevspeed[v] = speed;
-    c.veh_backpos[v] = pos - cf.length();
-    c.veh_accel[v] = 0;
-    c.veh_lastdist[v] = 0;
-    c.veh_waiting[v] = 0;
-    c.veh_since_startup[v] = 86400000;   // MSVehicle ctor: myTimeSinceStartup(TIME2STEPS(3600 * 24)), MSVehicle.cpp:1023
-    c.veh_jentry[v] = SB2_TIME_MAX; c.veh_jentry_ny[v] = SB2_TIME_MAX; c.veh_jconflict[v] = SB2_TIME_MAX;
-    c.veh_havetowait[v] = 0;
-    c.veh_moved[v] = 0;
-    c.veh_nfurther[v] = 0;
-    // MSDevice_Tripinfo::notifyEnter(NOTIFICATION_DEPARTED)
-    c.veh_trip_routelen[v] = -pos;
-    c.veh_trip_departpos[v] = pos;
-    c.veh_trip_departspeed[v] = speed;
-    c.veh_trip_wait[v] = 0; c.veh_trip_waitcount[v] = 0; c.veh_trip_amwaiting[v] = 0;
-    c.veh_arrival_time[v] = -1; c.veh_arrival_lane[v] = -1;
-    c.veh_odometer[v] = 0;
-    c.veh_timeloss[v] = 0;
-    c.veh_stopspeed[v] = SB2_DBL_MAX;
-    // position in the queue: before the first vehicle (from the rear) with pos >= ours
-    int behind = -1;              // vehicle that ends up directly behind the new one
-    int aheadV = c.lane_last[l];  // walks rear -> front
-    while (aheadV >= 0 && !(c.veh_pos[aheadV] >= pos)) {
-        behind = aheadV;
-        aheadV = c.veh_ahead[aheadV];
-    }
-    c.veh_ahead[v] = aheadV;
-    c.veh_behind[v] = behind;
-#if defined(__CUDA_ARCH__)
-    __threadfence();
-#endif
-    if (aheadV >= 0) {
-        c.veh_behind[aheadV] = v;
-    } else {
-        c.lane_first[l] = v;
-    }
-    if (behind >= 0) {
-        c.veh_ahead[behind] = v;
-    } else {
-        c.lane_last[l] = v;
-    }
-    c.lane_nveh[l] += 1;
-    c.lane_brutto[l] += cf.length() + cf.minGap();
-    c.lane_changed[l] = 1;   // MSLane::incorporateVehicle -> MSEdgeControl::gotActive (MSLane.cpp:471)
-    // MSVehicleControl::vehicleDeparted
-    atomic_max_double(&c.fleet_next[0], c.veh_speedfactor[v]);
-    atomic_min_double(&c.fleet_next[1], cf.decel());
-    atomic_max_double(&c.fleet_next[2], cf.minGap());
-    atomic_inc(&c.counters[2]);
-    return true;
+    return lane_isInsertionSuccess(c, l, v, speed, pos, patchSpeed, patchSpeed || dsd != DSD_GIVEN, false);
 }
 
 // all due candidates of departure lane l, in load order

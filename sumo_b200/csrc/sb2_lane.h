@@ -80,6 +80,36 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1,
     c.ls_found_stopped[l] = found;
 }
 
+// MSVehicleTransfer::add for a teleporting vehicle that its lane's queue has just dropped (MSVehicleTransfer.cpp:54-77):
+// onRemovalFromNet(NOTIFICATION_TELEPORT) -> leaveLane (odometer, further lanes, waiting time := 0), then enterLaneAtMove(first lane
+// of the next route edge, onTeleporting) puts it at position 0 of that edge, off the road.  Its approach records stay in the
+// table but every reader skips vehicles that are not on the road; partial occupations are dropped in lane_handoff_integrate.
+SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
+    if (c.veh_routepos[v] + 1 >= veh_route_len(c, v)) {
+        // "teleports beyond arrival edge": removed from the simulation (NOTIFICATION_TELEPORT_ARRIVED)
+        c.veh_arrival_time[v] = c.t;
+        c.veh_arrival_lane[v] = lane;
+        c.veh_moved[v] = 2;
+        c.veh_lane[v] = -2;
+        atomic_inc(&c.counters[1]);
+        return;
+    }
+    c.veh_odometer[v] += c.lane_length[lane];
+    c.veh_trip_routelen[v] += c.lane_length[lane];   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_TELEPORT)
+    c.veh_nfurther[v] = 0;
+    c.veh_waiting[v] = 0;
+    c.veh_routepos[v] += 1;
+    c.veh_pos[v] = 0;
+    c.veh_lane[v] = -3;
+    c.veh_tp_proceed[v] = -1;
+#if defined(__CUDA_ARCH__)
+    const int at = atomicAdd(&c.counters[10], 1);
+#else
+    const int at = c.counters[10]++;
+#endif
+    c.tp_list[at] = v;
+}
+
 // after executeMove, pass 1: pop the vehicles that left at the front (reads veh_behind of the leavers, which pass 2
 // overwrites when it links them into their new lane -- hence two passes with a grid-wide barrier in between)
 SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
@@ -134,19 +164,28 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         brutto = 0;
     }
     c.lane_brutto[l] = brutto;
+    // MSLane.cpp:2402-2456: the front-most remaining vehicle (firstNotStopped; there are no stops on this path) is teleported after
+    // waiting longer than time-to-teleport (r1; the highway / disconnected / bidi / rail-signal rules need options that are refused)
+    if (f >= 0 && c.timeToTeleport > 0 && c.veh_waiting[f] > c.timeToTeleport) {
+        const int next = c.veh_behind[f];
+        c.lane_first[l] = next;
+        if (next >= 0) {
+            c.veh_ahead[next] = -1;
+        } else {
+            c.lane_last[l] = -1;
+        }
+        c.lane_nveh[l] -= 1;
+        c.lane_brutto[l] = c.lane_nveh[l] == 0 ? 0. : c.lane_brutto[l] - veh_length_with_gap(c, f);
+        atomic_inc(&c.counters[6]);
+        veh_transfer_add(c, f, l);
+    }
     // MSEdgeControl::executeMovements (MSEdgeControl.cpp:229-232): a lane without vehicles leaves the active list
     if (c.lane_nveh[l] == 0) {
         c.lane_actkey[l] = 0;
     }
-    // MSLane.cpp:2402-2456: the front-most remaining vehicle is teleported after waiting longer than time-to-teleport.
-    // Teleporting (MSVehicleTransfer) is host-side logic the engine does not implement: report it, never ignore it.
-    if (f >= 0 && c.timeToTeleport > 0 && c.veh_waiting[f] > c.timeToTeleport) {
-        raise(c, ERR_TELEPORT);
-        atomic_inc(&c.counters[6]);
-    }
 }
 
-// pass 2: append the arrivals at the rear, sort partial occupators
+// pass 2: append the arrivals at the rear
 SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
     double brutto = c.lane_brutto[l];
     // ---- MSLane::integrateNewVehicles
@@ -196,14 +235,37 @@ SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
     if (ni > 0 && c.lane_actkey[l] == 0) {
         c.lane_actkey[l] = lane_make_actkey(c, l, 1);
     }
-    // ---- partial occupators were appended by executeMove; keep them sorted by back position (sortPartialVehicles)
+    if (ni > 0) {
+        c.edge_delayed[c.lane_edge[l]] = 1;   // MSEdge::markDelayed (MSLane.cpp:2608)
+    }
+}
+
+// pass 4 (after the collision check, which may teleport vehicles): partial occupators were appended by executeMove; drop the
+// ones that left the road, keep the rest sorted by back position (MSLane::sortPartialVehicles, MSLane.cpp:2625-2629)
+SB2_HDN void lane_sort_partials(const Ctx& c, int l) {
     int np = c.lane_npartial[l];
+    if (np == 0) {
+        return;
+    }
     if (np > MAX_PARTIAL) {
         raise(c, ERR_PARTIAL_OVERFLOW);
         np = MAX_PARTIAL;
         c.lane_npartial[l] = np;
     }
     int32_t* p = c.lane_partial + (size_t)l * MAX_PARTIAL;
+    {
+        // a vehicle that was teleported in this step (lane_handoff_remove) has left all lanes (MSVehicle::leaveLane resets its partial occupations)
+        int keep = 0;
+        for (int i = 0; i < np; i++) {
+            if (c.veh_lane[p[i]] >= 0) {
+                p[keep++] = p[i];
+            }
+        }
+        if (keep != np) {
+            np = keep;
+            c.lane_npartial[l] = np;
+        }
+    }
     for (int i = 1; i < np; i++) {
         const int x = p[i];
         const double px = veh_back_pos_on_lane(c, x, l);
@@ -221,30 +283,64 @@ SB2_HDN void lane_handoff_integrate(const Ctx& c, int l) {
     }
 }
 
-// MSLane::detectCollisions (non-sublane): adjacent pairs + rear-most partial occupator.  The engine does not implement
-// the teleport that follows a collision: it raises ERR_COLLISION and counts it.
+// MSLane::detectCollisions (non-sublane, MSLane.cpp:1826-1835, 1971-2074) with the default collision.action teleport
+// (handleCollisionBetween, MSLane.cpp:2078-2211: the collider is taken off the lane and handed to MSVehicleTransfer): adjacent
+// pairs front -> back, then the rear-most vehicle against the rear-most partial occupator (`*lastVeh` is myVehicles.front()).
+// All pairs are tested on the queue as it is; the colliders are removed afterwards (toRemove / toTeleport sets).
 SB2_HDN void lane_detect_collisions(const Ctx& c, int l) {
     const double* vt_collision_mingap_factor = c.vt_collision_mingap_factor;
     int pred = c.lane_first[l];
     if (pred < 0) {
         return;
     }
-    if (c.lane_npartial[l] > 0) {
-        const int victim = c.lane_partial[(size_t)l * MAX_PARTIAL];
-        const int collider = pred;
-        const double gap = veh_back_pos_on_lane(c, victim, l) - c.veh_pos[collider] - vt_collision_mingap_factor[c.veh_type[collider]] * veh_mingap(c, collider);
-        if (gap < -SB2_NUMERICAL_EPS) {
-            raise(c, ERR_COLLISION);
-            atomic_inc(&c.counters[4]);
-        }
-    }
+    bool any = false;
     for (int veh = c.veh_behind[pred]; veh >= 0; pred = veh, veh = c.veh_behind[veh]) {
         const double gap = (c.veh_pos[pred] - veh_length(c, pred)) - c.veh_pos[veh] - vt_collision_mingap_factor[c.veh_type[veh]] * veh_mingap(c, veh);
         if (gap < -SB2_NUMERICAL_EPS) {
-            raise(c, ERR_COLLISION);
-            atomic_inc(&c.counters[4]);
+            c.veh_moved[veh] = 3;   // collider: to be removed
+            any = true;
         }
     }
+    if (c.lane_npartial[l] > 0) {
+        const int victim = c.lane_partial[(size_t)l * MAX_PARTIAL];
+        const int collider = c.lane_last[l];
+        const double gap = veh_back_pos_on_lane(c, victim, l) - c.veh_pos[collider] - vt_collision_mingap_factor[c.veh_type[collider]] * veh_mingap(c, collider);
+        if (gap < -SB2_NUMERICAL_EPS && c.veh_moved[collider] != 3) {
+            c.veh_moved[collider] = 3;
+            any = true;
+        }
+    }
+    if (!any) {
+        return;
+    }
+    int ahead = -1;
+    double brutto = c.lane_brutto[l];
+    for (int x = c.lane_first[l]; x >= 0;) {
+        const int next = c.veh_behind[x];
+        if (c.veh_moved[x] == 3) {
+            c.veh_moved[x] = 0;
+            // MSLane::removeVehicle (MSLane.cpp:2870-2890)
+            if (ahead >= 0) {
+                c.veh_behind[ahead] = next;
+            } else {
+                c.lane_first[l] = next;
+            }
+            if (next >= 0) {
+                c.veh_ahead[next] = ahead;
+            } else {
+                c.lane_last[l] = ahead;
+            }
+            c.lane_nveh[l] -= 1;
+            brutto -= veh_length_with_gap(c, x);
+            atomic_inc(&c.counters[4]);   // MSVehicleControl::countCollision(teleport = true): a collision and a teleport
+            atomic_inc(&c.counters[6]);
+            veh_transfer_add(c, x, l);
+        } else {
+            ahead = x;
+        }
+        x = next;
+    }
+    c.lane_brutto[l] = c.lane_nveh[l] == 0 ? 0. : brutto;
 }
 
 // MSTrafficLightLogic::setTrafficLightSignals(t) for phase `step` of program tl (MSTrafficLightLogic.cpp:402-414)

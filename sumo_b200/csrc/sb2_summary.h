@@ -21,19 +21,19 @@ struct SummaryPart {
     int32_t waiting;     // depart time reached, not inserted yet
     int32_t departed;
     int32_t ended;
-    int32_t pad;
+    int32_t teleporting; // in MSVehicleTransfer: still running (MSVehicleControl::getRunningVehicleNo), not on the road
     int64_t delay_ms;    // sum over departed vehicles of departure - STEPFLOOR(depart)
     int64_t travel_ms;   // sum over ended vehicles of arrival - departure
     double speedSum, relSpeedSum;
 };
 
 SB2_HD void summary_zero(SummaryPart& p) {
-    p.count = 0; p.halting = 0; p.waiting = 0; p.departed = 0; p.ended = 0; p.pad = 0;
+    p.count = 0; p.halting = 0; p.waiting = 0; p.departed = 0; p.ended = 0; p.teleporting = 0;
     p.delay_ms = 0; p.travel_ms = 0; p.speedSum = 0.; p.relSpeedSum = 0.;
 }
 
 SB2_HD void summary_add(SummaryPart& a, const SummaryPart& b) {
-    a.count += b.count; a.halting += b.halting; a.waiting += b.waiting; a.departed += b.departed; a.ended += b.ended;
+    a.count += b.count; a.halting += b.halting; a.waiting += b.waiting; a.departed += b.departed; a.ended += b.ended; a.teleporting += b.teleporting;
     a.delay_ms += b.delay_ms; a.travel_ms += b.travel_ms; a.speedSum += b.speedSum; a.relSpeedSum += b.relSpeedSum;
 }
 
@@ -52,12 +52,18 @@ SB2_HD void summary_vehicle(const Ctx& c, int v, SUMOTime tStep, SummaryPart& p)
             p.halting++;
         }
     }
+    // removal still pending (teleported beyond its arrival edge in MSVehicleTransfer::checkInsertions of this very step)
+    const bool pendingRemoval = lane == -2 && c.veh_moved[v] == 4 && c.veh_arrival_time[v] == tStep;
+    if (lane == -3 || pendingRemoval) {
+        p.teleporting++;
+    }
     if (lane != -1) {
         p.departed++;
         p.delay_ms += c.veh_depart_time[v] - (c.veh_depart_param[v] / c.DELTA_T) * c.DELTA_T;
-        if (lane == -2) {
+        if (lane == -2 && !pendingRemoval) {
             p.ended++;
-            p.travel_ms += c.veh_arrival_time[v] - c.veh_depart_time[v];
+            // MSVehicleControl::removePending adds the time of the REMOVAL (MSVehicleControl.cpp:164), one step later for veh_moved 4
+            p.travel_ms += c.veh_arrival_time[v] + (c.veh_moved[v] == 4 ? c.DELTA_T : 0) - c.veh_depart_time[v];
         }
     } else if (c.veh_depart[v] <= tStep) {
         p.waiting++;

@@ -169,7 +169,7 @@ struct Ctx {
     const double* veh_departpos; const int32_t* veh_departpos_proc;
     const double* veh_departspeed; const int32_t* veh_departspeed_proc;
     // ---- vehicles (dynamic) --------------------------------------------------------------
-    int32_t* veh_lane;         // -1 pending, -2 arrived, else lane index
+    int32_t* veh_lane;         // -1 pending, -2 arrived, -3 teleporting (in MSVehicleTransfer, off the road), else lane index
     int32_t* veh_routepos;     // myCurrEdge - myRoute->begin()
     double* veh_pos; double* veh_speed; double* veh_prevspeed; double* veh_accel; double* veh_backpos;
     double* veh_lastdist;      // myLastCoveredDist
@@ -193,6 +193,11 @@ struct Ctx {
     // executeMove pass 2 (sb2_exec.h): vehicles whose right of way depends on the NEW speed of a foe that the reference executes
     // earlier (MSLink::blockedAtTime reads the live speed, MSLink.cpp:1050): veh_deferred 1 = waiting, list + counters[9]
     uint8_t* veh_deferred; int32_t* deferred_list;
+    // MSVehicleTransfer (src/microsim/MSVehicleTransfer.cpp): vehicles that were teleported (jam / collision) wait off the road on
+    // route edge veh_routepos until they fit on a lane again.  tp_list[0 .. counters[10]) = their slots (appended with an atomic,
+    // sorted by numerical id in checkInsertions like the reference's std::sort), veh_tp_proceed = myProceedTime (-1 = not set)
+    int32_t* tp_list; SUMOTime* veh_tp_proceed;
+    uint8_t* edge_delayed;     // MSEdge::myAmDelayed (a vehicle has entered the edge at some time, MSEdge.h:750)
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
     // neighbouring lanes, see the same links and foes and take the same branches.  Two segments: [0, counters[7]) = lanes whose
@@ -224,7 +229,7 @@ struct Ctx {
     int traci_speed_used; double* veh_traci_speed;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
-    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports
+    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list
 };
 
 SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }

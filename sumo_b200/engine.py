@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("SUMOB200_LIB") or os.path.join(_HERE, "libsumob200.so
 
 FLAGS = {
     1: "drive item overflow", 2: "further-lane overflow", 4: "partial occupator overflow", 8: "collision", 16: "teleport",
-    32: "emergency stop", 64: "no connection", 128: "unsupported link state", 256: "lane order", 512: "search overflow",
+    32: "emergency stop", 64: "no connection", 128: "unsupported link state", 256: "lane order", 512: "search overflow", 1024: "executeMove pass 2 unresolved",
 }
 
 
@@ -34,7 +34,7 @@ class StepResult(ctypes.Structure):
     _fields_ = [("time_ms", ctypes.c_int64), ("running", ctypes.c_int32), ("departed_total", ctypes.c_int32),
                 ("arrived_total", ctypes.c_int32), ("collisions", ctypes.c_int32), ("emergency_stops", ctypes.c_int32),
                 ("teleports", ctypes.c_int32), ("flags", ctypes.c_int32), ("halting", ctypes.c_int32),
-                ("vehicle_updates", ctypes.c_int64)]
+                ("vehicle_updates", ctypes.c_int64), ("teleporting", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 VEHICLE_STATE = np.dtype([("lane", np.int32), ("route_pos", np.int32), ("pos", np.float64), ("speed", np.float64)])

@@ -18,27 +18,27 @@ CASES = {
     "c1_grid10": ["--default.speeddev", "0", "--end", "3700"],
     "c1_grid10_depart0": ["--default.speeddev", "0", "--default.departspeed", "0", "--default.departlane", "first", "--end", "3700"],
     "grid4_tls": ["--default.speeddev", "0", "--end", "1200"],
-    "grid5_dense": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "grid5_dense": ["--default.speeddev", "0", "--end", "900"],
     # vehicles with individual speed factors (normc(1,0.1,0.2,2), sampled by the reference's loader)
     "grid4_tls_speeddev": ["--end", "1000"],
     # Krauss sigma = 0.5 (the vType default): the reference's per-vehicle dawdle draws are recorded (--draws-out) and replayed
-    "grid4_tls_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
-    "grid5_dense_sigma": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "700"],
-    "c1_grid10_sigma": ["--time-to-teleport", "-1", "--end", "2000"],
+    "grid4_tls_sigma": ["--default.speeddev", "0", "--end", "1200"],
+    "grid5_dense_sigma": ["--default.speeddev", "0", "--end", "700"],
+    "c1_grid10_sigma": ["--end", "2000"],
     # every vehicle carries MSDevice_Emissions: default class (HBEFA4/PC_petrol_Euro-4) and an explicit HBEFA3 class
     "grid4_tls_hbefa4": ["--default.speeddev", "0", "--end", "900", "--device.emissions.probability", "1"],
     "grid4_tls_hbefa3": ["--default.speeddev", "0", "--end", "900", "--device.emissions.probability", "1"],
-    "grid5_dense_hbefa3": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "600", "--device.emissions.probability", "1"],
+    "grid5_dense_hbefa3": ["--default.speeddev", "0", "--end", "600", "--device.emissions.probability", "1"],
 }
 CASES.update({
     # explicit arrivalPos inside the last lane: vehicles arrive (and leave the lane queue) behind the front vehicle
     "grid4_tls_arrivalpos": ["--default.speeddev", "0", "--end", "1000"],
     # one district of bench.py's workload (10x10 TLS grid, 1800 resident vehicles, sigma 0.5, speedFactor deviation): same options as bench.py
-    "bench_grid10_tls_draws": ["--time-to-teleport", "-1", "--default.departspeed", "0", "--default.departlane", "first", "--end", "700"],
+    "bench_grid10_tls_draws": ["--default.departspeed", "0", "--default.departlane", "first", "--end", "700"],
     # carFollowModel IDM (MSCFModel_IDM, delta 4, 4 sub-steps)
     "grid3_small_idm": ["--default.speeddev", "0"],
-    "grid5_dense_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
-    "c1_grid10_idm": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "2500"],
+    "grid5_dense_idm": ["--default.speeddev", "0", "--end", "900"],
+    "c1_grid10_idm": ["--default.speeddev", "0", "--end", "2500"],
     # the case that exposed MSLink::blockedAtTime's LIVE foe speed under lastWasContRed (MSLink.cpp:1050) at t = 514 s: a left turner
     # waiting on the junction sees a foe whose lane the reference executes earlier in the step (executeMove pass 2, sb2_link.h)
     "grid4_tls_idm": ["--default.speeddev", "0", "--end", "1200"],
@@ -56,20 +56,20 @@ def _mixed_fleet(text):
 
 CASES.update({
     # other network shapes / junction types (netgenerate --rand, priority_stop, short traffic-light blocks with spill-back)
-    "rand_net": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
-    "grid4_stop": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
-    "grid3_tls_short": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
+    "rand_net": ["--default.speeddev", "0", "--end", "900"],
+    "grid4_stop": ["--default.speeddev", "0", "--end", "900"],
+    "grid3_tls_short": ["--default.speeddev", "0", "--end", "900"],
     # other option combinations of the reference's command line
-    "grid4_tls_step05": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--step-length", "0.5", "--end", "600"],
-    "grid5_dense_optmix": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],
+    "grid4_tls_step05": ["--default.speeddev", "0", "--step-length", "0.5", "--end", "600"],
+    "grid5_dense_optmix": ["--default.speeddev", "0", "--default.departspeed", "desired", "--time-to-impatience", "30", "--end", "600"],
     # heterogeneous fleet: length, minGap, accel, maxSpeed, tau, speedFactor, impatience differ between vehicles
-    # ends before t = 1086 s, where the advised speeds lead to a collision in the reference (which it resolves by teleporting; the
-    # engine raises SUMOB200_F_COLLISION at that very step)
-    "grid4_tls_setspeed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1050"],
-    "grid4_tls_setphase": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1200"],
-    "grid4_tls_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
-    "grid5_dense_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "900"],
-    "c1_grid10_mixed": ["--default.speeddev", "0", "--time-to-teleport", "-1", "--end", "1500"],
+    # at t = 1086 s the advised speeds lead to a collision, which the reference resolves by teleporting the collider (collision.action
+    # teleport, the default): the run goes on through it
+    "grid4_tls_setspeed": ["--default.speeddev", "0", "--end", "1300"],
+    "grid4_tls_setphase": ["--default.speeddev", "0", "--end", "1200"],
+    "grid4_tls_mixed": ["--default.speeddev", "0", "--end", "1500"],
+    "grid5_dense_mixed": ["--default.speeddev", "0", "--end", "900"],
+    "c1_grid10_mixed": ["--default.speeddev", "0", "--end", "1500"],
 })
 # per-case edits of the fixture's route file: (old, new) or a function text -> text
 ROU_EDITS = {
@@ -98,7 +98,7 @@ def tls_phase_events(base, period_s=37, end_s=1100):
     return ev
 
 
-def veh_speed_events(base, end_s=1040):
+def veh_speed_events(base, end_s=1290):
     """deterministic vehicle.setSpeed events for the case <base>_setspeed: every 5 s two vehicles get a speed advice (0 = stop,
     slow, medium, above the lane limit, or -1 = release), slow ones are released 30 s later.  Both sides skip an event whose
     vehicle is not on the road at that time.  [(time ms, vehicle id, speed)]"""

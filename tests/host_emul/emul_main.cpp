@@ -20,6 +20,7 @@
 #include "../../sumo_b200/csrc/sb2_exec.h"
 #include "../../sumo_b200/csrc/sb2_lane.h"
 #include "../../sumo_b200/csrc/sb2_insert.h"
+#include "../../sumo_b200/csrc/sb2_transfer.h"
 #include "../../sumo_b200/csrc/sb2_fcd.h"
 #include "../../sumo_b200/csrc/sb2_fcdxml.h"
 #include "../../sumo_b200/csrc/sb2_summary.h"
@@ -102,6 +103,9 @@ static void step(Model& m) {
     for (int l = 0; l < c.nL; l++) {
         lane_detect_collisions(c, l);
     }
+    for (int l = 0; l < c.nL; l++) {
+        lane_sort_partials(c, l);
+    }
     for (int i = 0; i < 3; i++) {
         c.fleet[i] = c.fleet_next[i];
     }
@@ -109,6 +113,9 @@ static void step(Model& m) {
         if (c.dq_head[l] < c.dq_begin[l + 1]) {
             lane_insertVehicles(c, l);
         }
+    }
+    if (c.counters[10] > 0) {
+        transfer_checkInsertions(c);
     }
     c.t += c.DELTA_T;
 }
@@ -271,7 +278,7 @@ int main(int argc, char** argv) {
                 summary_vehicle(c, v, t, p);
             }
             // time inserted running waiting ended arrived collisions teleports halting stopped meanWaitingTime meanTravelTime meanSpeed meanSpeedRelative
-            fprintf(fsum, "%lld %d %d %d %d %d %d %d %d %d %.17g %.17g %.17g %.17g\n", (long long)t, p.departed, p.count, p.waiting, p.ended, p.ended,
+            fprintf(fsum, "%lld %d %d %d %d %d %d %d %d %d %.17g %.17g %.17g %.17g\n", (long long)t, p.departed, p.count + p.teleporting, p.waiting, p.ended, p.ended,
                     c.counters[4], c.counters[6], p.halting, 0, p.departed != 0 ? ((double)p.delay_ms / 1000.) / (double)p.departed : -1.,
                     p.ended != 0 ? ((double)p.travel_ms / 1000.) / (double)p.ended : -1., p.count > 0 ? p.speedSum / p.count : -1.,
                     p.count > 0 ? p.relSpeedSum / p.count : -1.);

@@ -25,7 +25,8 @@ def test_engine_matches_reference(case):
             st = eng.vehicles()[order]
             on = st["lane"] >= 0
             assert r.flags == 0, "t=%d: engine raised flags 0x%x" % (t, r.flags)
-            assert r.running == int(on.sum()) == len(ids), "t=%d: running vehicles differ" % t
+            assert r.running - r.teleporting == int(on.sum()) == len(ids), "t=%d: running vehicles differ" % t
+            assert r.teleporting == int((st["lane"] == -3).sum())
             assert r.halting == int((speed < 0.1).sum()), "t=%d: halting vehicles (summary output) differ" % t
             assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
             assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
@@ -36,17 +37,20 @@ def test_engine_matches_reference(case):
     assert compared > 1000
 
 
-def test_teleport_condition_is_reported():
-    """the reference teleports a vehicle of grid5_dense at t=425 s; the engine must flag that step, not silently diverge"""
+def test_teleports_are_executed():
+    """grid5_dense under the reference's default --time-to-teleport 300: the first vehicle is teleported at t = 484 s, 51 follow
+    until t = 900 s (jam and yield teleports, re-insertions further along the route, teleports beyond the arrival edge); the
+    trajectories stay bit-identical through all of them (test_engine_matches_reference[grid5_dense]) and the counter agrees with
+    the reference's summary output"""
     from sumo_b200.engine import Engine
-    from conftest import CASES
-    CASES.setdefault("grid5_dense_teleport", ["--default.speeddev", "0", "--default.departspeed", "0", "--default.departlane", "first", "--end", "430"])
-    flat, trace = reference_case("grid5_dense_teleport".replace("_teleport", "") if False else "grid5_dense_teleport")
+    from conftest import reference_summary
+    flat, trace = reference_case("grid5_dense")
+    ref = reference_summary("grid5_dense")
     with Engine(flat) as eng:
-        r = eng.step(424)
-        assert r.flags == 0
-        r = eng.step(2)
-        assert r.flags & 16 and r.teleports >= 1
+        r = eng.step(480)
+        assert r.flags == 0 and r.teleports == int(ref[479]["teleports"]) == 0
+        r = eng.step(420)
+        assert r.flags == 0 and r.teleports == int(ref[899]["teleports"]) > 20
 
 
 @pytest.mark.parametrize("case", ["grid4_tls_sigma", "grid5_dense_sigma", "c1_grid10_sigma", "bench_grid10_tls_draws"])
