@@ -275,8 +275,8 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         CUDA_TRY(cudaMemcpyAsync(&updates, e->dUpdates, sizeof(updates), cudaMemcpyDeviceToHost, s));
         CUDA_TRY(cudaStreamSynchronize(s));
         out->time_ms = c.t;
-        out->running = counters[0] + counters[10];
-        out->teleporting = counters[10];
+        out->running = counters[0] + counters[10] + counters[11];
+        out->teleporting = counters[10] + counters[11];
         out->reserved = 0;
         out->arrived_total = counters[1];
         out->departed_total = counters[2];

@@ -63,6 +63,7 @@ __global__ void k_reset(const __grid_constant__ Ctx c) {
         c.counters[3] = 0;
         c.counters[8] = 0;
         c.counters[9] = 0;
+        c.counters[11] = 0;
     }
 }
 

@@ -182,6 +182,7 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
                 c.veh_arrival_time[v] = time;
                 c.veh_arrival_lane[v] = c.edge_lane_begin[e];
                 c.veh_moved[v] = 4;
+                c.counters[11] += 1;   // still counted as running in this step's result
                 c.veh_lane[v] = -2;
                 atomic_inc(&c.counters[1]);
                 continue;

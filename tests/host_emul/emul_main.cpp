@@ -81,6 +81,7 @@ static void step(Model& m) {
     }
     std::fill(c.lane_npartial, c.lane_npartial + c.nL, 0);
     c.counters[9] = 0;
+    c.counters[11] = 0;
     for (int i = 0; i < nOrder; i++) {
         veh_executeMove_pass1(c, i);
     }
