@@ -204,7 +204,7 @@ def make_grid(template, n, spacing=None, with_names=True):
     xy = t["shape_xy"].reshape(-1, 2)[spos].copy()
     sj = np.repeat(lane_j, scnt)
     shift = np.stack([(ix[sj] - st.jxy[tj[sj], 0]) * spacing, (iy[sj] - st.jxy[tj[sj], 1]) * spacing], axis=1)
-    g["shape_xy"] = (xy + shift).reshape(-1)
+    g["shape_xy"] = np.round(xy + shift, 2).reshape(-1)   # net.xml coordinates have 2 decimals: the nearest double, like the parser
     # ---- traffic lights: the program of the template junction, one per target junction that has one
     ttl = st.tl_of_junction[tj]
     has_tl = ttl >= 0
