@@ -35,6 +35,20 @@ namespace {
 
 thread_local std::string gLastError;
 
+// D2H of one FCD snapshot by the SMs (a few CTAs on the copy stream, concurrent with the next step's kernels): the number of
+// rows is only known on the device, so a cudaMemcpyAsync would need a host round trip to size it -- which stalled the pipeline
+// (the next step could not be enqueued before the rows were compacted).  16-byte stores into mapped pinned memory, count last.
+__global__ void __launch_bounds__(256) k_fcd_copy(const int4* __restrict__ src, int4* __restrict__ dst, const int32_t* __restrict__ dCount, int32_t* hCount) {
+    const int n = *dCount;
+    const long long n16 = (long long)n * (long long)(sizeof(sumob200_fcd_row) / 16);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) {
+        dst[i] = src[i];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *hCount = n;
+    }
+}
+
 #define CUDA_TRY(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
         gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
 
@@ -52,10 +66,10 @@ struct sumob200_engine {
     void* dSummary = nullptr;   // SummaryPart scratch of sumob200_summary_now
     double* dReplay = nullptr;
     // FCD streaming: device rows + block counts, two pinned host buffers, a copy stream (D2H overlaps the next step)
-    sumob200_fcd_row* dFcd = nullptr;
-    int32_t* dFcdBlocks = nullptr;
-    sumob200_fcd_row* hFcd[2] = {nullptr, nullptr};
-    int32_t* hFcdCount = nullptr;
+    sumob200_fcd_row* dFcd[2] = {nullptr, nullptr};
+    int32_t* dFcdBlocks[2] = {nullptr, nullptr};
+    sumob200_fcd_row* hFcd[2] = {nullptr, nullptr};   // pinned + mapped: written by k_fcd_copy on the copy stream
+    int32_t* hFcdCount = nullptr;                     // [2], pinned + mapped
     cudaStream_t copyStream = nullptr;
     cudaEvent_t fcdReady = nullptr, fcdCopied[2] = {nullptr, nullptr};
     int fcdBuf = 0, fcdPendingRows = -1;
@@ -209,9 +223,11 @@ void sumob200_destroy(sumob200_engine* e) {
     if (e->dReplay != nullptr) {
         cudaFree(e->dReplay);
     }
-    if (e->dFcd != nullptr) {
-        cudaFree(e->dFcd);
-        cudaFree(e->dFcdBlocks);
+    if (e->dFcd[0] != nullptr) {
+        cudaFree(e->dFcd[0]);
+        cudaFree(e->dFcd[1]);
+        cudaFree(e->dFcdBlocks[0]);
+        cudaFree(e->dFcdBlocks[1]);
         cudaFreeHost(e->hFcd[0]);
         cudaFreeHost(e->hFcd[1]);
         cudaFreeHost(e->hFcdCount);
@@ -571,13 +587,14 @@ int sumob200_fcd_begin(sumob200_engine* e) {
     CUDA_TRY(cudaSetDevice(e->device));
     const int nV = e->d.nV;
     const int nb = gridOf(e, nV);
-    if (e->dFcd == nullptr) {
+    if (e->dFcd[0] == nullptr) {
         const size_t bytes = sizeof(sumob200_fcd_row) * (size_t)(nV > 0 ? nV : 1);
-        CUDA_TRY(cudaMalloc(&e->dFcd, bytes));
-        CUDA_TRY(cudaMalloc(&e->dFcdBlocks, sizeof(int32_t) * (size_t)(nb + 1)));
-        CUDA_TRY(cudaHostAlloc(&e->hFcd[0], bytes, cudaHostAllocDefault));
-        CUDA_TRY(cudaHostAlloc(&e->hFcd[1], bytes, cudaHostAllocDefault));
-        CUDA_TRY(cudaHostAlloc(&e->hFcdCount, sizeof(int32_t), cudaHostAllocDefault));
+        for (int b = 0; b < 2; b++) {
+            CUDA_TRY(cudaMalloc(&e->dFcd[b], bytes));
+            CUDA_TRY(cudaMalloc(&e->dFcdBlocks[b], sizeof(int32_t) * (size_t)(nb + 1)));
+            CUDA_TRY(cudaHostAlloc(&e->hFcd[b], bytes, cudaHostAllocMapped));
+        }
+        CUDA_TRY(cudaHostAlloc(&e->hFcdCount, 2 * sizeof(int32_t), cudaHostAllocMapped));
         CUDA_TRY(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
         CUDA_TRY(cudaEventCreateWithFlags(&e->fcdReady, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&e->fcdCopied[0], cudaEventDisableTiming));
@@ -587,19 +604,19 @@ int sumob200_fcd_begin(sumob200_engine* e) {
         gLastError = "sumob200_fcd_begin: the previous snapshot was not collected with sumob200_fcd_end";
         return SUMOB200_EINVAL;
     }
+    const int b = e->fcdBuf;
     cudaStream_t s = e->stream;
-    // the previous D2H out of dFcd must be done before the rows are overwritten
-    CUDA_TRY(cudaStreamWaitEvent(s, e->fcdCopied[e->fcdBuf ^ 1], 0));
-    e->ks->fcd(&e->d, nV, e->dFcdBlocks, e->dFcd, s);
-    e->launches += 3;
-    CUDA_TRY(cudaMemcpyAsync(e->hFcdCount, e->dFcdBlocks + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    // the D2H out of dFcd[b] two snapshots ago must be done before its rows are overwritten (it is, unless the host falls behind)
+    CUDA_TRY(cudaStreamWaitEvent(s, e->fcdCopied[b], 0));
+    e->ks->fcd(&e->d, nV, e->dFcdBlocks[b], e->dFcd[b], s);
     CUDA_TRY(cudaEventRecord(e->fcdReady, s));
-    CUDA_TRY(cudaEventSynchronize(e->fcdReady));
-    const int n = *e->hFcdCount;
-    // rows travel on the copy stream into pinned memory while the caller is free to launch the next step
-    CUDA_TRY(cudaMemcpyAsync(e->hFcd[e->fcdBuf], e->dFcd, sizeof(sumob200_fcd_row) * (size_t)n, cudaMemcpyDeviceToHost, e->copyStream));
-    CUDA_TRY(cudaEventRecord(e->fcdCopied[e->fcdBuf], e->copyStream));
-    e->fcdPendingRows = n;
+    // rows + count travel on the copy stream while the caller launches the next step: no host synchronisation here
+    CUDA_TRY(cudaStreamWaitEvent(e->copyStream, e->fcdReady, 0));
+    k_fcd_copy<<<64, 256, 0, e->copyStream>>>(reinterpret_cast<const int4*>(e->dFcd[b]), reinterpret_cast<int4*>(e->hFcd[b]),
+                                              e->dFcdBlocks[b] + nb, e->hFcdCount + b);
+    e->launches += 4;
+    CUDA_TRY(cudaEventRecord(e->fcdCopied[b], e->copyStream));
+    e->fcdPendingRows = 0;
     return 0;
 }
 
@@ -611,7 +628,7 @@ int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n) 
     CUDA_TRY(cudaSetDevice(e->device));
     CUDA_TRY(cudaEventSynchronize(e->fcdCopied[e->fcdBuf]));
     *rows = e->hFcd[e->fcdBuf];
-    *n = e->fcdPendingRows;
+    *n = e->hFcdCount[e->fcdBuf];
     e->fcdPendingRows = -1;
     e->fcdBuf ^= 1;
     return 0;
