@@ -44,6 +44,8 @@ extern "C" {
 #define SUMOB200_F_LANE_ORDER 256
 #define SUMOB200_F_SEARCH_OVERFLOW 512
 #define SUMOB200_F_DEFERRED_UNRESOLVED 1024  /* executeMove pass 2 did not converge (sb2_exec.h) */
+#define SUMOB200_F_PARTITION_REACH 2048      /* a vehicle's look-ahead left the columns its rank simulates (edges too short for the ghost width) */
+#define SUMOB200_F_HALO_OVERFLOW 4096        /* a halo message needed more vehicle records than its capacity */
 
 typedef struct sumob200_engine sumob200_engine;
 
@@ -169,6 +171,30 @@ int sumob200_tls_get_phase(sumob200_engine* e, int tls, int* phase, int64_t* nex
  * MSVehicle::Influencer::influenceSpeed, MSVehicle.cpp:493-520, applied in planMove :2313-2326 and executeMove :4025-4056);
  * speeds[i] < 0 hands the vehicle back to the car-following model.  An unknown slot is SUMOB200_EINVAL. */
 int sumob200_vehicles_set_speed(sumob200_engine* e, const int32_t* slots, const double* speeds, int n);
+
+/* ---- multi-GPU: one connected network cut into strips of junction columns, one engine (process, GPU) per strip ----------------
+ * Mirrors the per-lane tasking of MSEdgeControl::planMovements / executeMovements (src/microsim/MSEdgeControl.cpp:150-167, 205-219)
+ * across GPUs; design in sumo_b200/csrc/sb2_halo.h.  Every engine is created from the WHOLE scenario (same arrays, same slot
+ * numbers) and then told its part:
+ *   lane_vis[n_lanes]  3 = own lane (simulated, authoritative), 2 = ghost (first column of a neighbour: simulated redundantly),
+ *                      1 = halo (second column: read only), 0 = not visible
+ *   exp_lanes[side] / imp_lanes[side]   side 0 = neighbour towards lower columns, 1 = higher: the lanes whose final state this rank
+ *                      sends (its own two border columns) / receives (the neighbour's); the neighbour's export list is this rank's
+ *                      import list, element for element;  n = 0 for a side without neighbour
+ *   capacity           vehicle records per message (the same on all ranks); an overflow raises SUMOB200_F_HALO_OVERFLOW
+ * After every sumob200_step(e, 1, ..) the caller runs, per side with a neighbour: sumob200_halo_pack into a device buffer of
+ * sumob200_halo_message_bytes(e, side, 1) bytes, transports it (ncclSend/ncclRecv, cudaMemcpyPeer ... on sumob200_stream's order),
+ * and sumob200_halo_unpack on the buffer received from that neighbour.  The three fleet aggregates behind MSLane::getMaximumBrakeDist
+ * (max speedFactor, -min decel, max minGap over all departed vehicles, MSVehicleControl.cpp:199-216) are network-wide:
+ * sumob200_fleet_aggregates returns their device address for a MAX all-reduce per step (the second one is stored negated
+ * only inside that call sequence: negate, all-reduce MAX, negate). */
+int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const int32_t* const* exp_lanes, const int32_t* n_exp,
+                           const int32_t* const* imp_lanes, const int32_t* n_imp, int capacity);
+int64_t sumob200_halo_message_bytes(const sumob200_engine* e, int side, int outgoing);
+int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message);
+int sumob200_halo_unpack(sumob200_engine* e, int side, const void* device_message);
+void* sumob200_stream(sumob200_engine* e);            /* the cudaStream_t every kernel of the engine is launched on */
+double* sumob200_fleet_aggregates(sumob200_engine* e);  /* device pointer, 3 doubles */
 
 int sumob200_num_vehicles(const sumob200_engine* e);
 int sumob200_num_lanes(const sumob200_engine* e);

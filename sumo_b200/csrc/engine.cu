@@ -28,6 +28,7 @@
 #include "sb2_kernelset.h"
 #include "sb2_fcdxml.h"
 #include "sb2_summary.h"
+#include "sb2_halo.h"
 
 using namespace sb2;
 
@@ -73,6 +74,12 @@ struct sumob200_engine {
     cudaStream_t copyStream = nullptr;
     cudaEvent_t fcdReady = nullptr, fcdCopied[2] = {nullptr, nullptr};
     int fcdBuf = 0, fcdPendingRows = -1;
+    // edge partition (sb2_halo.h): per side 0 = towards lower columns, 1 = towards higher columns
+    sb2::HaloSide halo[2];
+    uint8_t* dLaneVis = nullptr;
+    uint8_t* dImpMask[2] = {nullptr, nullptr};
+    std::vector<void*> haloAlloc;
+    bool partitioned = false;
     int64_t launches = 0;
     bool profiling = false;
     cudaEvent_t ev[6];
@@ -153,6 +160,15 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
 }
 
 inline int gridOf(const sumob200_engine* e, int n) { return n > 0 ? (n + e->ks->block - 1) / e->ks->block : 1; }
+
+template<class T> int uploadArray(sumob200_engine* e, const T* host, size_t n, T** dev) {
+    CUDA_TRY(cudaMalloc(dev, sizeof(T) * (n > 0 ? n : 1)));
+    e->haloAlloc.push_back(*dev);
+    if (n > 0) {
+        CUDA_TRY(cudaMemcpy(*dev, host, sizeof(T) * n, cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
 
 }  // namespace
 
@@ -235,6 +251,9 @@ void sumob200_destroy(sumob200_engine* e) {
         cudaEventDestroy(e->fcdCopied[0]);
         cudaEventDestroy(e->fcdCopied[1]);
         cudaStreamDestroy(e->copyStream);
+    }
+    for (void* p : e->haloAlloc) {
+        cudaFree(p);
     }
     if (e->stream != nullptr) {
         cudaStreamDestroy(e->stream);
@@ -421,6 +440,94 @@ int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity) {
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     return 0;
 }
+
+// ---- edge partition -------------------------------------------------------------------------------------------------------
+int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const int32_t* const* exp_lanes, const int32_t* n_exp,
+                           const int32_t* const* imp_lanes, const int32_t* n_imp, int capacity) {
+    if (e == nullptr || lane_vis == nullptr || exp_lanes == nullptr || imp_lanes == nullptr || n_exp == nullptr || n_imp == nullptr || capacity <= 0 || e->partitioned) {
+        gLastError = "sumob200_set_partition: bad argument (or called twice)";
+        return SUMOB200_EINVAL;
+    }
+    const int nL = e->d.nL;
+    for (int side = 0; side < 2; side++) {
+        for (int i = 0; i < n_exp[side]; i++) {
+            if (exp_lanes[side][i] < 0 || exp_lanes[side][i] >= nL || lane_vis[exp_lanes[side][i]] != LV_AUTH) {
+                gLastError = "sumob200_set_partition: an exported lane is not one of the rank's own lanes";
+                return SUMOB200_EINVAL;
+            }
+        }
+        for (int i = 0; i < n_imp[side]; i++) {
+            const int l = imp_lanes[side][i];
+            if (l < 0 || l >= nL || (lane_vis[l] != LV_GHOST && lane_vis[l] != LV_HALO)) {
+                gLastError = "sumob200_set_partition: an imported lane is not a ghost / halo lane";
+                return SUMOB200_EINVAL;
+            }
+        }
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (uploadArray(e, lane_vis, (size_t)nL, &e->dLaneVis) != 0) {
+        return SUMOB200_ECUDA;
+    }
+    e->d.lane_vis = e->dLaneVis;
+    for (int side = 0; side < 2; side++) {
+        sb2::HaloSide& h = e->halo[side];
+        int32_t* dExp = nullptr;
+        int32_t* dImp = nullptr;
+        if (uploadArray(e, exp_lanes[side], (size_t)n_exp[side], &dExp) != 0 || uploadArray(e, imp_lanes[side], (size_t)n_imp[side], &dImp) != 0) {
+            return SUMOB200_ECUDA;
+        }
+        std::vector<uint8_t> mask((size_t)nL, 0);
+        for (int i = 0; i < n_imp[side]; i++) {
+            mask[imp_lanes[side][i]] = 1;
+        }
+        if (uploadArray(e, mask.data(), (size_t)nL, &e->dImpMask[side]) != 0) {
+            return SUMOB200_ECUDA;
+        }
+        h.exp_lanes = dExp; h.nExp = n_exp[side];
+        h.imp_lanes = dImp; h.nImp = n_imp[side];
+        h.cap = capacity;
+        CUDA_TRY(cudaMalloc(&h.cursor, sizeof(int32_t)));
+        e->haloAlloc.push_back(h.cursor);
+        CUDA_TRY(cudaMalloc(&h.slots, sizeof(int32_t) * (size_t)capacity));
+        e->haloAlloc.push_back(h.slots);
+    }
+    e->partitioned = true;
+    return 0;
+}
+
+int64_t sumob200_halo_message_bytes(const sumob200_engine* e, int side, int outgoing) {
+    if (e == nullptr || !e->partitioned || side < 0 || side > 1) {
+        return 0;
+    }
+    const sb2::HaloSide& h = e->halo[side];
+    return (int64_t)sb2::halo_message_bytes(outgoing ? h.nExp : h.nImp, h.cap);
+}
+
+int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message) {
+    if (e == nullptr || !e->partitioned || side < 0 || side > 1 || device_message == nullptr) {
+        gLastError = "sumob200_halo_pack: bad argument / no partition set";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    e->launches += e->ks->halo_pack(&e->d, &e->halo[side], e->dImpMask[side], device_message, e->stream);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int sumob200_halo_unpack(sumob200_engine* e, int side, const void* device_message) {
+    if (e == nullptr || !e->partitioned || side < 0 || side > 1 || device_message == nullptr) {
+        gLastError = "sumob200_halo_unpack: bad argument / no partition set";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    e->launches += e->ks->halo_unpack(&e->d, &e->halo[side], device_message, e->stream);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+void* sumob200_stream(sumob200_engine* e) { return e == nullptr ? nullptr : (void*)e->stream; }
+double* sumob200_fleet_aggregates(sumob200_engine* e) { return e == nullptr ? nullptr : e->d.fleet_next; }
 
 int sumob200_num_vehicles(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nV; }
 int sumob200_num_lanes(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nL; }

@@ -41,6 +41,7 @@ namespace SB2_PASTE(sb2_kset_, SB2_KSET) {
 #include "sb2_lane.h"
 #include "sb2_insert.h"
 #include "sb2_transfer.h"
+#include "sb2_halo.h"
 #include "sb2_fcd.h"
 #include "sb2_summary.h"
 
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
     __shared__ int warpSumF[2][BLOCK / 32];
     __shared__ int blockFirsts[2];
 #endif
-    const int nveh = i < c.nL ? c.lane_nveh[i] : 0;
+    const int nveh = (i < c.nL && lane_simulated(c, i)) ? c.lane_nveh[i] : 0;   // work list: lanes this rank simulates
 #if defined(SB2_SPLIT_INTERNAL)
     const bool internal = i < c.nL && (c.lane_flags[i] & LF_INTERNAL) != 0;
 #elif !defined(SB2_NO_SPLIT_RED)
@@ -238,14 +239,14 @@ __global__ void __launch_bounds__(256) k_execute2(const __grid_constant__ Ctx c)
 
 __global__ void __launch_bounds__(BLOCK) k_remove(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
+    if (l < c.nL && lane_simulated(c, l)) {
         lane_handoff_remove(c, l);
     }
 }
 
 __global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
+    if (l < c.nL && lane_simulated(c, l)) {
         lane_handoff_integrate(c, l);
     }
 }
@@ -253,14 +254,14 @@ __global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx
 // MSEdgeControl::detectCollisions(STAGE_MOVEMENTS): a collider is teleported (collision.action teleport, the default)
 __global__ void __launch_bounds__(BLOCK) k_collide(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
+    if (l < c.nL && lane_simulated(c, l)) {
         lane_detect_collisions(c, l);
     }
 }
 
 __global__ void __launch_bounds__(BLOCK) k_partials(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL) {
+    if (l < c.nL && lane_simulated(c, l)) {
         lane_sort_partials(c, l);
     }
 }
@@ -274,7 +275,7 @@ __global__ void k_transfer(const __grid_constant__ Ctx c) {
 
 __global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c) {
     const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1]) {
+    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1] && lane_simulated(c, l)) {
         lane_insertVehicles(c, l);
     }
 }
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c)
 // running vehicles of this step -> counters[0] (overwritten) and the 64-bit vehicle-update accumulator
 __global__ void __launch_bounds__(1024) k_count(const __grid_constant__ Ctx c, unsigned long long* updates) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0 && lane_auth(c, c.veh_lane[v]);
     // MSVehicleControl::getHaltingVehicleNo (MSVehicleControl.cpp:568-580): on the road and slower than SUMO_const_haltingSpeed
     const bool halting = on && c.veh_speed[v] < SB2_HALTING_SPEED;
     // one atomic per 1024-thread block and counter: with one per warp the 3 x 31 k same-address atomics of a 1 M-vehicle step
@@ -302,7 +303,7 @@ __global__ void __launch_bounds__(1024) k_count(const __grid_constant__ Ctx c, u
 // pass 1: on-road vehicles per block
 __global__ void __launch_bounds__(BLOCK) k_fcd_count(const __grid_constant__ Ctx c, int32_t* blockCount) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0);
+    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0 && lane_auth(c, c.veh_lane[v]));
     if (threadIdx.x == 0) {
         blockCount[blockIdx.x] = n;
     }
@@ -358,7 +359,7 @@ __global__ void __launch_bounds__(1024) k_fcd_scan(int32_t* blockCount, int nb) 
 __global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx c, const int32_t* blockBase, sumob200_fcd_row* rows) {
     __shared__ int warpBase[BLOCK / 32];
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0 && lane_auth(c, c.veh_lane[v]);   // a partitioned run reports its own vehicles
     const unsigned mask = __ballot_sync(0xffffffffu, on);
     if ((threadIdx.x & 31) == 0) {
         warpBase[threadIdx.x >> 5] = __popc(mask);
@@ -477,6 +478,34 @@ __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* 
 }
 
 
+// ---- halo exchange of the edge partition (sb2_halo.h)
+__global__ void __launch_bounds__(BLOCK) k_halo_pack_lanes(const __grid_constant__ Ctx c, const HaloSide h, const uint8_t* imp_mask, void* msg) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < h.nExp) {
+        halo_pack_lane(c, h, msg, i);
+    }
+    if (i == h.nExp) {   // one extra thread: teleporting vehicles that have moved into the receiver's strip
+        halo_pack_transfers(c, h, imp_mask);
+    }
+}
+__global__ void __launch_bounds__(BLOCK) k_halo_pack_vehicles(const __grid_constant__ Ctx c, const HaloSide h, void* msg) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    halo_pack_vehicle(c, h, msg, i);
+}
+__global__ void __launch_bounds__(BLOCK) k_halo_clear(const __grid_constant__ Ctx c, const HaloSide h) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < h.nImp) {
+        halo_clear_lane(c, h, i);
+    }
+}
+__global__ void __launch_bounds__(BLOCK) k_halo_unpack(const __grid_constant__ Ctx c, const HaloSide h, const void* msg) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < h.nImp) {
+        halo_unpack_lane(c, msg, i);
+    }
+    halo_unpack_vehicle(c, msg, i);
+}
+
 inline int grid(int n) { return n > 0 ? (n + BLOCK - 1) / BLOCK : 1; }
 inline const Ctx& ctx(const void* p) { return *static_cast<const Ctx*>(p); }   // same layout as the engine's sb2::Ctx (one header)
 
@@ -508,7 +537,21 @@ void l_fcd(const void* c, int n, int32_t* blocks, sumob200_fcd_row* rows, cudaSt
     k_fcd_write<<<nb, BLOCK, 0, s>>>(ctx(c), blocks, rows);
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed};
+int l_halo_pack(const void* c, const void* side, const uint8_t* imp_mask, void* msg, cudaStream_t s) {
+    const HaloSide& h = *static_cast<const HaloSide*>(side);
+    cudaMemsetAsync(h.cursor, 0, sizeof(int32_t), s);
+    k_halo_pack_lanes<<<grid(h.nExp + 1), BLOCK, 0, s>>>(ctx(c), h, imp_mask, msg);
+    k_halo_pack_vehicles<<<grid(h.cap), BLOCK, 0, s>>>(ctx(c), h, msg);
+    return 2;
+}
+int l_halo_unpack(const void* c, const void* side, const void* msg, cudaStream_t s) {
+    const HaloSide& h = *static_cast<const HaloSide*>(side);
+    k_halo_clear<<<grid(h.nImp), BLOCK, 0, s>>>(ctx(c), h);
+    k_halo_unpack<<<grid(h.cap > h.nImp ? h.cap : h.nImp), BLOCK, 0, s>>>(ctx(c), h, msg);
+    return 2;
+}
+
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack};
 
 }  // namespace sb2_kset_<name>
 

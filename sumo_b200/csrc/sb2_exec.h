@@ -325,7 +325,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
             // emergency stop at the end of the lane (MSVehicle.cpp:4784-4796)
             (void)emergency;
             raise(c, ERR_EMERGENCY_STOP);
-            atomic_inc(&c.counters[5]);
+            count_event(c, oldLane, 5);
             pos = c.lane_length[myLane];
             speed = 0;
             accelOut = 0;
@@ -380,7 +380,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
         c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
         c.veh_arrival_lane[v] = myLane;
         c.lane_arrived[oldLane] = 1;   // its queue entry is removed by lane_handoff_remove wherever it sits; veh_lane becomes -2 there
-        atomic_inc(&c.counters[1]);
+        count_event(c, oldLane, 1);
     } else if (myLane != oldLane) {
         c.veh_moved[v] = 1;
         c.veh_lane[v] = myLane;

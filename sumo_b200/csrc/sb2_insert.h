@@ -372,7 +372,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
         atomic_max_double(&c.fleet_next[0], c.veh_speedfactor[v]);
         atomic_min_double(&c.fleet_next[1], cf.decel());
         atomic_max_double(&c.fleet_next[2], cf.minGap());
-        atomic_inc(&c.counters[2]);
+        count_event(c, l, 2);
     }
     return true;
 }

@@ -24,6 +24,9 @@ struct sb2_kernelset {
     int (*summary)(const void* ctx, int n_vehicles, void* parts, void* out, cudaStream_t s);
     void (*tls_set_phase)(const void* ctx, int tls, int phase, cudaStream_t s);
     void (*set_speed)(const void* ctx, const int32_t* slots, const double* speeds, int n, cudaStream_t s);
+    /* halo exchange of the edge partition (sb2_halo.h); `side` points at an sb2::HaloSide in host memory, msg at device memory */
+    int (*halo_pack)(const void* ctx, const void* side, const uint8_t* imp_mask, void* msg, cudaStream_t s);      /* returns the launch count */
+    int (*halo_unpack)(const void* ctx, const void* side, const void* msg, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

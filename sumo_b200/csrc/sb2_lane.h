@@ -40,7 +40,13 @@ SB2_HD void lane_patch_active(const Ctx& c, int l) {
 // orderBase = first slot of this lane in the lane-ordered work list veh_order; firstSlot >= 0: the lane's front vehicle goes
 // there instead (k_pre groups the front vehicles of a block's lanes), the followers start at orderBase
 SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1, int firstSlot = -1) {
-    lane_patch_active(c, l);
+    const int vis = lane_vis(c, l);
+    if (vis == LV_NONE) {
+        return;
+    }
+    if (vis >= LV_GHOST) {
+        lane_patch_active(c, l);   // (a halo lane's key arrives with its state)
+    }
     // front -> back (MSLane.cpp:1608-1623)
     double cum = 0.;
     int guard = 0;
@@ -50,7 +56,9 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1,
         (void)SB2_CHK(guard++, 0, c.lane_nveh[l], 13);
         c.veh_len_in_front[v] = cum;
         c.veh_qlane[v] = l;
-        if (firstSlot >= 0) {
+        if (vis < LV_GHOST) {
+            // halo lane: its vehicles are read, not moved
+        } else if (firstSlot >= 0) {
             c.veh_order[c.cur][firstSlot] = v;
             firstSlot = -1;
         } else {
@@ -91,7 +99,7 @@ SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
         c.veh_arrival_lane[v] = lane;
         c.veh_moved[v] = 2;
         c.veh_lane[v] = -2;
-        atomic_inc(&c.counters[1]);
+        count_event(c, lane, 1);
         return;
     }
     c.veh_odometer[v] += c.lane_length[lane];
@@ -102,6 +110,12 @@ SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
     c.veh_pos[v] = 0;
     c.veh_lane[v] = -3;
     c.veh_tp_proceed[v] = -1;
+    // partitioned run: the transfer entry belongs to the rank that owns the edge the vehicle now (virtually) sits on, because
+    // MSVehicleTransfer::checkInsertions tries to re-insert it there in this very step.  That rank sees the teleport itself: the
+    // lane the vehicle was taken from is its own or in its ghost column (the next route edge ends at a neighbour junction).
+    if (!lane_auth(c, c.edge_lane_begin[veh_succ_edge(c, v, 0)])) {
+        return;
+    }
 #if defined(__CUDA_ARCH__)
     const int at = atomicAdd(&c.counters[10], 1);
 #else
@@ -176,7 +190,7 @@ SB2_HDN void lane_handoff_remove(const Ctx& c, int l) {
         }
         c.lane_nveh[l] -= 1;
         c.lane_brutto[l] = c.lane_nveh[l] == 0 ? 0. : c.lane_brutto[l] - veh_length_with_gap(c, f);
-        atomic_inc(&c.counters[6]);
+        count_event(c, l, 6);
         veh_transfer_add(c, f, l);
     }
     // MSEdgeControl::executeMovements (MSEdgeControl.cpp:229-232): a lane without vehicles leaves the active list
@@ -332,8 +346,8 @@ SB2_HDN void lane_detect_collisions(const Ctx& c, int l) {
             }
             c.lane_nveh[l] -= 1;
             brutto -= veh_length_with_gap(c, x);
-            atomic_inc(&c.counters[4]);   // MSVehicleControl::countCollision(teleport = true): a collision and a teleport
-            atomic_inc(&c.counters[6]);
+            count_event(c, l, 4);   // MSVehicleControl::countCollision(teleport = true): a collision and a teleport
+            count_event(c, l, 6);
             veh_transfer_add(c, x, l);
         } else {
             ahead = x;

@@ -214,6 +214,12 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
             SB2_PUSH(di_make_nolink(vv, seen, 0));
             break;
         }
+        if (c.lane_vis != nullptr && c.lane_vis[myLane] == LV_AUTH && c.lane_vis[c.link_from[link]] < LV_GHOST) {
+            // the look-ahead of one of the rank's OWN vehicles reaches a junction whose approaching vehicles this rank does not plan:
+            // the ghost column is too narrow for this network (edges shorter than the look-ahead) -- reported, never silently wrong.
+            // (Ghost vehicles heading away from the strip do look at such links; their result is replaced by the owner's anyway.)
+            raise(c, ERR_PARTITION_REACH);
+        }
         const uint8_t lstate = c.link_state[link];
         const bool yellowOrRed = state_red(lstate) || state_yellow(lstate);
         double laneStopOffset;

@@ -166,6 +166,10 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
         const int v = list[i];
         const int e = veh_succ_edge(c, v, 0);
         const int nextEdge = veh_succ_edge(c, v, 1);
+        if (!lane_auth(c, c.edge_lane_begin[e])) {
+            list[keep++] = v;   // moved on into another rank's part of the network: handed over with the next halo exchange
+            continue;
+        }
         const int l = edge_free_lane(c, e, nextEdge);
         const double mspeed = l >= 0 ? MIN2(c.lane_speed[l], veh_max_speed(c, v)) : 0.;
         if (l >= 0 && lane_freeInsertion(c, l, v, mspeed)) {
@@ -184,7 +188,7 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
                 c.veh_moved[v] = 4;
                 c.counters[11] += 1;   // still counted as running in this step's result
                 c.veh_lane[v] = -2;
-                atomic_inc(&c.counters[1]);
+                count_event(c, c.edge_lane_begin[e], 1);
                 continue;
             }
             // leaveLane(NOTIFICATION_TELEPORT_CONTINUATION), enterLaneAtMove(first lane of the next edge, onTeleporting)

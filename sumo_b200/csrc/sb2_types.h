@@ -83,7 +83,7 @@ enum { LL_IN_THE_WAY = 1, LL_FROM_LEFT = 2, LL_SAME_SOURCE = 4, LL_SAME_TARGET =
 // error / event flags raised by kernels (never silently ignored: sumob200_step returns them)
 enum {
     ERR_DRIVE_ITEM_OVERFLOW = 1, ERR_FURTHER_OVERFLOW = 2, ERR_PARTIAL_OVERFLOW = 4, ERR_COLLISION = 8, ERR_TELEPORT = 16,
-    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512, ERR_DEFERRED_UNRESOLVED = 1024
+    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512, ERR_DEFERRED_UNRESOLVED = 1024, ERR_PARTITION_REACH = 2048, ERR_HALO_OVERFLOW = 4096
 };
 // car-following model ids = SUMO_TAG_CF_* values are remapped at load time
 enum { CF_KRAUSS = 0, CF_KRAUSS_ORIG1 = 1, CF_IDM = 2 };
@@ -198,6 +198,13 @@ struct Ctx {
     // sorted by numerical id in checkInsertions like the reference's std::sort), veh_tp_proceed = myProceedTime (-1 = not set)
     int32_t* tp_list; SUMOTime* veh_tp_proceed;
     uint8_t* edge_delayed;     // MSEdge::myAmDelayed (a vehicle has entered the edge at some time, MSEdge.h:750)
+    // ---- multi-GPU edge partition (sb2_halo.h): what this rank does with each lane.  nullptr = one partition owning everything.
+    //   LV_AUTH  lanes of the rank's own junction columns: simulated here, results authoritative (counted, reported, exported)
+    //   LV_GHOST lanes of the neighbouring rank's first column: simulated here too (so that vehicles cross the cut inside one
+    //            step without a mid-step exchange), results overwritten by the owner's at the end of the step
+    //   LV_HALO  lanes of the neighbour's second column: not simulated, only read (state received at the end of every step)
+    //   LV_NONE  everything further away: never touched
+    const uint8_t* lane_vis;
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
     // neighbouring lanes, see the same links and foes and take the same branches.  Two segments: [0, counters[7]) = lanes whose
@@ -311,6 +318,16 @@ SB2_HD int sb2_chk(const Ctx& c, long long x, long long lo, long long hi, int si
 #define SB2_CHK(x, lo, hi, site) (x)
 #endif
 
+enum { LV_NONE = 0, LV_HALO = 1, LV_GHOST = 2, LV_AUTH = 3 };
+SB2_HD int lane_vis(const Ctx& c, int l) { return c.lane_vis == nullptr ? LV_AUTH : c.lane_vis[l]; }
+SB2_HD bool lane_auth(const Ctx& c, int l) { return c.lane_vis == nullptr || c.lane_vis[l] == LV_AUTH; }
+SB2_HD bool lane_simulated(const Ctx& c, int l) { return c.lane_vis == nullptr || c.lane_vis[l] >= LV_GHOST; }
+// event counters count what happens on the rank's own lanes only (the ghost column repeats the neighbour's work)
+SB2_HD void count_event(const Ctx& c, int lane, int counter) {
+    if (lane_auth(c, lane)) {
+        atomic_inc(&c.counters[counter]);
+    }
+}
 SB2_HD bool lane_internal(const Ctx& c, int l) { return (c.lane_flags[l] & LF_INTERNAL) != 0; }
 SB2_HD bool state_priority(uint8_t s) { return s >= 'A' && s <= 'Z'; }               // MSLink.h:473
 SB2_HD bool state_red(uint8_t s) { return s == 'r' || s == 'u'; }                     // MSLink.h:484

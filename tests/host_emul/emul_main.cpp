@@ -21,6 +21,7 @@
 #include "../../sumo_b200/csrc/sb2_lane.h"
 #include "../../sumo_b200/csrc/sb2_insert.h"
 #include "../../sumo_b200/csrc/sb2_transfer.h"
+#include "../../sumo_b200/csrc/sb2_halo.h"
 #include "../../sumo_b200/csrc/sb2_fcd.h"
 #include "../../sumo_b200/csrc/sb2_fcdxml.h"
 #include "../../sumo_b200/csrc/sb2_summary.h"
@@ -68,7 +69,9 @@ static void step(Model& m) {
     int nOrder = 0;
     for (int l = 0; l < c.nL; l++) {
         lane_summary(c, l, nOrder);
-        nOrder += c.lane_nveh[l];
+        if (lane_simulated(c, l)) {
+            nOrder += c.lane_nveh[l];
+        }
     }
     c.counters[7] = nOrder;
     c.counters[3] = 0;
@@ -96,22 +99,30 @@ static void step(Model& m) {
         }
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_handoff_remove(c, l);
+        if (lane_simulated(c, l)) {
+            lane_handoff_remove(c, l);
+        }
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_handoff_integrate(c, l);
+        if (lane_simulated(c, l)) {
+            lane_handoff_integrate(c, l);
+        }
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_detect_collisions(c, l);
+        if (lane_simulated(c, l)) {
+            lane_detect_collisions(c, l);
+        }
     }
     for (int l = 0; l < c.nL; l++) {
-        lane_sort_partials(c, l);
+        if (lane_simulated(c, l)) {
+            lane_sort_partials(c, l);
+        }
     }
     for (int i = 0; i < 3; i++) {
         c.fleet[i] = c.fleet_next[i];
     }
     for (int l = 0; l < c.nL; l++) {
-        if (c.dq_head[l] < c.dq_begin[l + 1]) {
+        if (c.dq_head[l] < c.dq_begin[l + 1] && lane_simulated(c, l)) {
             lane_insertVehicles(c, l);
         }
     }
@@ -121,6 +132,185 @@ static void step(Model& m) {
     c.t += c.DELTA_T;
 }
 
+// ---- several partitions of one network stepped in one process (the multi-GPU scheme of sb2_halo.h without GPUs): every
+// partition is a full Model with its own lane_vis; after each step the halo messages are packed, handed to the neighbour
+// and unpacked exactly like sumob200_halo_pack / _unpack do on the device.  The merged trace (every vehicle reported by the
+// partition that owns its lane) must equal the single-partition trace bit for bit.
+// partition file (int32 words): P, nL, capacity, then per partition: lane_vis[nL], and per side (0, 1): nExp, exp..., nImp, imp...
+struct EmulPart {
+    Model m;
+    std::vector<uint8_t> vis;
+    std::vector<int32_t> exp[2], imp[2], slots[2];
+    std::vector<uint8_t> impMask[2];
+    int32_t cursor[2] = {0, 0};
+    HaloSide side[2];
+    std::vector<char> sendBuf[2];
+};
+
+static int runPartitioned(const char* flatPath, const std::string& partFile, long maxSteps, const std::string& traceOut) {
+    FILE* pf = fopen(partFile.c_str(), "rb");
+    if (pf == nullptr) {
+        fprintf(stderr, "cannot read %s\n", partFile.c_str());
+        return 1;
+    }
+    std::vector<int32_t> w;
+    int32_t x;
+    while (fread(&x, 4, 1, pf) == 1) {
+        w.push_back(x);
+    }
+    fclose(pf);
+    size_t at = 0;
+    const int P = w[at++], nL = w[at++], cap = w[at++];
+    FlatFile ff;
+    ff.load(flatPath);
+    std::vector<EmulPart*> parts;
+    for (int p = 0; p < P; p++) {
+        EmulPart* e = new EmulPart();
+        e->m.build(ff);
+        if (e->m.h.nL != nL) {
+            fprintf(stderr, "partition file does not match the scenario\n");
+            return 1;
+        }
+        e->vis.resize(nL);
+        for (int l = 0; l < nL; l++) {
+            e->vis[l] = (uint8_t)w[at++];
+        }
+        e->m.h.lane_vis = e->vis.data();
+        for (int sd = 0; sd < 2; sd++) {
+            const int ne = w[at++];
+            e->exp[sd].assign(w.begin() + at, w.begin() + at + ne);
+            at += ne;
+            const int ni = w[at++];
+            e->imp[sd].assign(w.begin() + at, w.begin() + at + ni);
+            at += ni;
+            e->impMask[sd].assign(nL, 0);
+            for (int l : e->imp[sd]) {
+                e->impMask[sd][l] = 1;
+            }
+            e->slots[sd].resize(cap);
+            HaloSide& h = e->side[sd];
+            h.exp_lanes = e->exp[sd].data(); h.nExp = ne; h.imp_lanes = e->imp[sd].data(); h.nImp = ni;
+            h.cursor = &e->cursor[sd]; h.slots = e->slots[sd].data(); h.cap = cap;
+            e->sendBuf[sd].resize(halo_message_bytes(ne, cap));
+        }
+        parts.push_back(e);
+    }
+    FILE* f = traceOut.empty() ? nullptr : fopen(traceOut.c_str(), "wb");
+    const Ctx& c0 = parts[0]->m.h;
+    std::vector<int> order(c0.nV);
+    for (int v = 0; v < c0.nV; v++) {
+        order[v] = v;
+    }
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return c0.veh_numid[a] < c0.veh_numid[b]; });
+    long long updates = 0;
+    int errs = 0;
+    for (long s = 0; maxSteps < 0 || s < maxSteps; s++) {
+        const SUMOTime t = parts[0]->m.h.t;
+        if (parts[0]->m.end >= 0 && t >= parts[0]->m.end) {
+            break;
+        }
+        for (EmulPart* e : parts) {
+            step(e->m);
+        }
+        // pack
+        for (EmulPart* e : parts) {
+            for (int sd = 0; sd < 2; sd++) {
+                HaloSide& h = e->side[sd];
+                if (h.nExp == 0) {
+                    continue;
+                }
+                *h.cursor = 0;
+                for (int i = 0; i < h.nExp; i++) {
+                    halo_pack_lane(e->m.h, h, e->sendBuf[sd].data(), i);
+                }
+                halo_pack_transfers(e->m.h, h, e->impMask[sd].data());
+                for (int i = 0; i < cap; i++) {
+                    halo_pack_vehicle(e->m.h, h, e->sendBuf[sd].data(), i);
+                }
+            }
+        }
+        // transport + unpack: side 0 of partition p talks to side 1 of partition p - 1
+        for (int p = 0; p < P; p++) {
+            EmulPart* e = parts[p];
+            for (int sd = 0; sd < 2; sd++) {
+                const int q = sd == 0 ? p - 1 : p + 1;
+                HaloSide& h = e->side[sd];
+                if (q < 0 || q >= P || h.nImp == 0) {
+                    continue;
+                }
+                const void* msg = parts[q]->sendBuf[sd ^ 1].data();
+                for (int i = 0; i < h.nImp; i++) {
+                    halo_clear_lane(e->m.h, h, i);
+                }
+                for (int i = 0; i < h.nImp; i++) {
+                    halo_unpack_lane(e->m.h, msg, i);
+                }
+                for (int i = 0; i < cap; i++) {
+                    halo_unpack_vehicle(e->m.h, msg, i);
+                }
+            }
+        }
+        // network-wide fleet aggregates (MSVehicleControl.cpp:199-216)
+        double agg[3] = {parts[0]->m.h.fleet_next[0], parts[0]->m.h.fleet_next[1], parts[0]->m.h.fleet_next[2]};
+        for (EmulPart* e : parts) {
+            agg[0] = MAX2(agg[0], e->m.h.fleet_next[0]);
+            agg[1] = MIN2(agg[1], e->m.h.fleet_next[1]);
+            agg[2] = MAX2(agg[2], e->m.h.fleet_next[2]);
+        }
+        for (EmulPart* e : parts) {
+            for (int k = 0; k < 3; k++) {
+                e->m.h.fleet_next[k] = agg[k];
+            }
+        }
+        // merged trace
+        std::vector<int> owner(c0.nV, -1);
+        int n = 0;
+        for (int p = 0; p < P; p++) {
+            const Ctx& c = parts[p]->m.h;
+            for (int v = 0; v < c.nV; v++) {
+                if (c.veh_lane[v] >= 0 && c.lane_vis[c.veh_lane[v]] == LV_AUTH) {
+                    if (owner[v] >= 0) {
+                        fprintf(stderr, "t=%lld: vehicle %d is owned by two partitions\n", (long long)t, v);
+                        errs++;
+                    }
+                    owner[v] = p;
+                    n++;
+                }
+            }
+            if (*c.err_flags != 0) {
+                fprintf(stderr, "t=%lld: partition %d raised flags 0x%x\n", (long long)t, p, *c.err_flags);
+                errs++;
+                *c.err_flags = 0;
+            }
+        }
+        updates += n;
+        if (f != nullptr) {
+            const int64_t hdr[2] = {(int64_t)t, (int64_t)n};
+            fwrite(hdr, 8, 2, f);
+            for (int v : order) {
+                if (owner[v] >= 0) {
+                    const Ctx& c = parts[owner[v]]->m.h;
+                    const int64_t ids[2] = {(int64_t)c.veh_numid[v], (int64_t)c.veh_lane[v]};
+                    const double st[2] = {c.veh_pos[v], c.veh_speed[v]};
+                    fwrite(ids, 8, 2, f);
+                    fwrite(st, 8, 2, f);
+                }
+            }
+        }
+    }
+    if (f != nullptr) {
+        fclose(f);
+    }
+    int inserted = 0, arrived = 0, teleports = 0;
+    for (EmulPart* e : parts) {
+        inserted += e->m.h.counters[2];
+        arrived += e->m.h.counters[1];
+        teleports += e->m.h.counters[6];
+    }
+    fprintf(stderr, "partitions=%d vehicle-updates=%lld inserted=%d arrived=%d teleports=%d errors=%d\n", P, updates, inserted, arrived, teleports, errs);
+    return errs == 0 ? 0 : 3;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
@@ -128,9 +318,13 @@ int main(int argc, char** argv) {
     }
     std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed;
     long maxSteps = -1;
-    std::string debugName;
+    std::string debugName, partFile;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
+        if (a == "--partitions" && i + 1 < argc) {
+            partFile = argv[++i];   // written by sumo_b200/partition.py:write_partition_file
+            continue;
+        }
         if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
         } else if (a == "--fcd-xml-out" && i + 1 < argc) {
@@ -153,6 +347,14 @@ int main(int argc, char** argv) {
             maxSteps = atol(argv[++i]);
         } else if (a == "--debug-veh" && i + 1 < argc) {
             debugName = argv[++i];
+        }
+    }
+    if (!partFile.empty()) {
+        try {
+            return runPartitioned(argv[1], partFile, maxSteps, traceOut);
+        } catch (const std::exception& e) {
+            fprintf(stderr, "%s\n", e.what());
+            return 1;
         }
     }
     FlatFile ff;

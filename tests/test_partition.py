@@ -1,0 +1,125 @@
+"""Edge-partitioned multi-GPU run (sumo_b200/partition.py + csrc/sb2_halo.h).
+
+CPU suite: the strip planning, the transport with world_size 2 over gloo, and -- through tests/host_emul, which steps all strips in
+one process with the very pack / unpack functions the device kernels are made of -- that a run cut into 2 or 3 strips reproduces
+the REFERENCE's trace bit for bit (so it equals the single-strip run as well), including teleports that cross the cut.
+GPU suite: the same on the device, all strips as engines of one process on one GPU (LocalPartitionedRun), and over NCCL with one
+process per GPU when the box has two."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, reference_case
+from sumo_b200 import partition
+from sumo_b200.flatfile import load_flat, load_trace
+from test_parity_host import assert_traces_identical
+
+
+def test_plan_is_a_partition_and_lists_mirror():
+    flat, _ = reference_case("c1_grid10")
+    g = load_flat(flat)
+    for world in (1, 2, 3, 5):
+        plans = [partition.plan_partition(g, r, world) for r in range(world)]
+        own = np.stack([p["lane_vis"] == partition.LV_AUTH for p in plans])
+        assert (own.sum(axis=0) == 1).all()              # every lane has exactly one owner
+        for r, p in enumerate(plans):
+            vis = p["lane_vis"]
+            assert (vis[p["exp"][0]] == partition.LV_AUTH).all() and (vis[p["exp"][1]] == partition.LV_AUTH).all()
+            assert set(vis[np.concatenate(p["imp"])]) <= {partition.LV_GHOST, partition.LV_HALO}
+            # whatever is visible but not owned is imported from exactly one side
+            seen = np.zeros(len(vis), int)
+            for side in (0, 1):
+                seen[p["imp"][side]] += 1
+            assert ((seen == 1) == ((vis == partition.LV_GHOST) | (vis == partition.LV_HALO))).all()
+            if r + 1 < world:
+                assert np.array_equal(p["exp"][1], plans[r + 1]["imp"][0]) and np.array_equal(p["imp"][1], plans[r + 1]["exp"][0])
+            assert p["capacity"] == plans[0]["capacity"]
+    with pytest.raises(ValueError):
+        partition.plan_partition(g, 0, 6)               # 10 columns: at most 5 strips of 2
+
+
+@pytest.mark.parametrize("case,world", [("c1_grid10", 2), ("c1_grid10", 3), ("grid5_dense", 2)])
+def test_partitioned_emulation_matches_reference(case, world, host_emul, tmp_path):
+    """grid5_dense: 51 teleports until t = 900 s (reference default time-to-teleport), several of them across the cut"""
+    flat, trace = reference_case(case)
+    part = str(tmp_path / "p.part")
+    partition.write_partition_file(part, load_flat(flat), world)
+    out = str(tmp_path / "p.trace")
+    ref = load_trace(trace)
+    r = subprocess.run([host_emul, flat, "--partitions", part, "--trace-out", out, "--steps", str(len(ref))], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "errors=0" in r.stderr
+    assert assert_traces_identical(ref, load_trace(out)) > 1000
+
+
+def _worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    send = [torch.full((64,), 10 * rank + side, dtype=torch.uint8) for side in (0, 1)]
+    recv = [torch.zeros(64, dtype=torch.uint8) for _ in (0, 1)]
+    for _ in range(3):
+        partition.exchange_messages(dist, rank, world, send, recv)
+    out[rank] = (int(recv[0][0]), int(recv[1][0]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_exchange_messages_gloo_world2():
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, 29641, out), nprocs=2, join=True)
+    # rank 0 has only a right neighbour (its side 1 receives rank 1's side 0 message), rank 1 only a left one
+    assert out[0] == (0, 10) and out[1] == (1, 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,world", [("c1_grid10", 2), ("c1_grid10", 3), ("grid5_dense", 2)])
+def test_partitioned_engines_match_reference_on_one_gpu(case, world):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs CUDA")
+    flat, trace = reference_case(case)
+    g = load_flat(flat)
+    ref = load_trace(trace)
+    numid = g["veh_numid"]
+    order = np.argsort(numid, kind="stable")
+    run = partition.LocalPartitionedRun(g, world)
+    compared = 0
+    try:
+        for (t, ids, lanes, pos, speed) in ref:
+            run.step()
+            st = run.vehicles()[order]
+            on = st["lane"] >= 0
+            assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
+            assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
+            assert np.array_equal(st["pos"][on].view(np.int64), pos.view(np.int64)), "t=%d: positions differ (bitwise)" % t
+            assert np.array_equal(st["speed"][on].view(np.int64), speed.view(np.int64)), "t=%d: speeds differ (bitwise)" % t
+            compared += len(ids)
+        res = run.results()
+        assert all(r.flags == 0 for r in res)
+        assert sum(r.running for r in res) == len(ref[-1][1]) + sum(r.teleporting for r in res)
+    finally:
+        run.close()
+    assert compared > 1000
+
+
+@pytest.mark.gpu
+def test_two_gpus_over_nccl_match_reference():
+    """one process per GPU (torchrun), halo exchange over NCCL: tools_dev/partition_nccl_check.py compares every rank's own
+    vehicles with the reference trace after every step"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    flat, trace = reference_case("c1_grid10")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29655", os.path.join(ROOT, "tools_dev", "partition_nccl_check.py"), flat, trace],
+                       capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    assert "PARTITION-NCCL-OK" in r.stdout
