@@ -12,8 +12,10 @@ options (time-to-teleport 300 s, collision.action teleport).  The network is gen
 validated against netgenerate + the reference loader in tests/test_gridgen.py), the demand likewise (no per-vehicle host objects).
 A "step" is one simulation step (DELTA_T = 1 s).
 
-N > 1 (torchrun): the same grid is cut into N column strips, one per GPU, with a halo exchange over NCCL every step (strong
-scaling of one network: sumo_b200/partition.py); `--replicas` runs N independent copies instead (weak scaling).
+N > 1 (torchrun): ONE connected grid cut into N column strips, one per GPU, with a halo exchange over NCCL every step
+(sumo_b200/partition.py, csrc/sb2_halo.h).  Default = weak scaling: the grid grows with N at the same density and per-GPU work
+(side 100 * sqrt(N): 141 / 200 / 283 junctions, 2 / 4 / 8 M vehicles; N = 8 is close to BASELINE.json configs[3]); `--strong` keeps
+the 100 x 100 / 1 M network for every N; `--replicas` runs N unconnected copies (no exchange).
 """
 import argparse
 import json
@@ -230,6 +232,10 @@ def run_reference(args):
     if rank != 0:
         return 0
     total = SPINUP_STEPS + 180
+    if args.gpus > 1 and not args.replicas and not args.strong:
+        g1, v1 = args.grid, args.vehicles      # the workload our arm runs at this N (weak scaling, see main)
+        args.grid = int(round(g1 * args.gpus ** 0.5))
+        args.vehicles = int(round(v1 * (args.grid * (args.grid - 1)) / float(g1 * (g1 - 1))))
     r = reference_ups(total, args.sigma)
     if r is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/sumo or oracle/_ref/netgenerate not built"}))
@@ -238,7 +244,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": "vehicle-updates/s", "value": r["ups"], "unit": "veh*steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * r["duration_s"] / total, "higher_is_better": True,
-        "scaling": "strong" if args.gpus > 1 and not args.replicas else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "strong" if args.gpus > 1 and args.strong and not args.replicas else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_text(args.grid, args.vehicles, args.sigma, args.emissions),
                    "reference_sample": "%dx%d cut per process (the full size needs ~2 s per step on one core)" % (r["grid"], r["grid"]),
                    "vehicles": r["vehicles"], "processes": r["procs"]},
@@ -259,7 +265,8 @@ def main():
     ap.add_argument("--vehicles", type=int, default=VEHICLES, help="vehicles of the whole network")
     ap.add_argument("--sigma", type=float, default=0.5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--replicas", action="store_true", help="N > 1: every rank simulates its own copy of the network (weak scaling) instead of a strip of one network")
+    ap.add_argument("--replicas", action="store_true", help="N > 1: every rank simulates its own copy of the network instead of a strip of one network")
+    ap.add_argument("--strong", action="store_true", help="N > 1: keep the N = 1 network (strong scaling) instead of growing it with N")
     ap.add_argument("--emissions", action="store_true", help="every vehicle carries the HBEFA emission device (BASELINE.json configs[4] flavour)")
     ap.add_argument("--xml", action="store_true", help="also time the e2e loop with the FCD rows formatted as XML on the host threads")
     args = ap.parse_args()
@@ -278,8 +285,13 @@ def main():
 
     from sumo_b200.engine import Engine, describe_flags
 
-    scenario = build_scenario(args.grid, args.vehicles, args.sigma, emissions=args.emissions, names=args.xml)
     partitioned = world > 1 and not args.replicas
+    if partitioned and not args.strong:
+        # weak scaling: same density, same work per GPU
+        g1, v1 = args.grid, args.vehicles
+        args.grid = int(round(g1 * world ** 0.5))
+        args.vehicles = int(round(v1 * (args.grid * (args.grid - 1)) / float(g1 * (g1 - 1))))
+    scenario = build_scenario(args.grid, args.vehicles, args.sigma, emissions=args.emissions, names=args.xml)
     if partitioned:
         from sumo_b200.partition import PartitionedEngine
         eng = PartitionedEngine(scenario, dist, rank, world, device=local_rank)
@@ -388,7 +400,7 @@ def main():
             traffic_src = tr["source"]
     except Exception:
         pass
-    scaling = "weak" if (world == 1 or args.replicas) else "strong"
+    scaling = "strong" if (partitioned and args.strong) else "weak"
     line = {
         "metric": "vehicle-updates/s", "value": value, "unit": "veh*steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",

@@ -191,7 +191,9 @@ int sumob200_vehicles_set_speed(sumob200_engine* e, const int32_t* slots, const 
 int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const int32_t* const* exp_lanes, const int32_t* n_exp,
                            const int32_t* const* imp_lanes, const int32_t* n_imp, int capacity);
 int64_t sumob200_halo_message_bytes(const sumob200_engine* e, int side, int outgoing);
-int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message);
+/* max_records > 0 limits the vehicle records of this message (<= capacity): lets both ends transport a prefix of the buffer whose
+ * size they derive from the previous step's count; more records than that raise SUMOB200_F_HALO_OVERFLOW */
+int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message, int max_records);
 int sumob200_halo_unpack(sumob200_engine* e, int side, const void* device_message);
 void* sumob200_stream(sumob200_engine* e);            /* the cudaStream_t every kernel of the engine is launched on */
 double* sumob200_fleet_aggregates(sumob200_engine* e);  /* device pointer, 3 doubles */

@@ -504,13 +504,17 @@ int64_t sumob200_halo_message_bytes(const sumob200_engine* e, int side, int outg
     return (int64_t)sb2::halo_message_bytes(outgoing ? h.nExp : h.nImp, h.cap);
 }
 
-int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message) {
+int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message, int max_records) {
     if (e == nullptr || !e->partitioned || side < 0 || side > 1 || device_message == nullptr) {
         gLastError = "sumob200_halo_pack: bad argument / no partition set";
         return SUMOB200_EINVAL;
     }
     CUDA_TRY(cudaSetDevice(e->device));
-    e->launches += e->ks->halo_pack(&e->d, &e->halo[side], e->dImpMask[side], device_message, e->stream);
+    sb2::HaloSide h = e->halo[side];
+    if (max_records > 0 && max_records < h.cap) {
+        h.cap = max_records;   // the caller transports only this many records (both ends agree on the size from the previous step's count)
+    }
+    e->launches += e->ks->halo_pack(&e->d, &h, e->dImpMask[side], device_message, e->stream);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -428,7 +428,7 @@ public:
             SB2_DYN2(double, di_avail, b, nDI, 0.);
             SB2_DYN2(int64_t, di_arrtime, b, nDI, (int64_t)0); SB2_DYN2(int64_t, di_leavetime, b, nDI, (int64_t)0);
             SB2_DYN2(double, di_regspeed, b, nDI, 0.); SB2_DYN2(int64_t, di_regwaiting, b, nDI, (int64_t)0);
-            SB2_DYN2(int32_t, di_next, b, nDI, -1);
+            SB2_DYN2(int32_t, di_next, b, nDI, -1); SB2_DYN2(int32_t, di_veh, b, nDI, -1);
         }
         h.cur = 0;
         {

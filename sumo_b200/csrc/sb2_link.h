@@ -159,7 +159,12 @@ SB2_HD int link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime
                               bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, int live = LIVE_NOW) {
     int result = OPEN_YES;
     for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        const int foe = SB2_CHK(c.veh_order[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8) % c.nV], 0, c.nV, 9);
+        // (a record without request never blocks -- MSLink::blockedByFoe starts with `if (!avi.willPass) return false` -- so it is
+        // dropped before anything of its vehicle is loaded: with queues of 20-30 vehicles per lane most records end here)
+        if (!c.di_request[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8)]) {
+            continue;
+        }
+        const int foe = SB2_CHK(c.di_veh[buf][r], 0, c.nV, 9);
         if (foe == ego || !veh_on_road(c, foe)) {
             continue;
         }
@@ -251,7 +256,7 @@ SB2_HD bool link_hasApproachingFoe(const Ctx& c, int k, int buf, SUMOTime arriva
 // find the approach record of vehicle v on link k (MSLink::getApproaching, MSLink.cpp:801-809); -1 if absent
 SB2_HD int link_getApproaching(const Ctx& c, int k, int buf, int v) {
     for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        if (c.veh_order[buf][r % c.nV] == v) {
+        if (c.di_veh[buf][r] == v) {
             return r;
         }
     }

@@ -353,6 +353,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
             c.di_leavetime[cur][r] = link_getLeaveTime(c, d.link, d.arrivalTime, d.arrivalSpeed, di_getLeaveSpeed(d), e.length);
             c.di_regspeed[cur][r] = e.speed;
             c.di_regwaiting[cur][r] = e.waiting;
+            c.di_veh[cur][r] = v;
             c.di_next[cur][r] = atomic_exch(&c.link_app_head[cur][d.link], (int32_t)r);
         }
     }

@@ -224,6 +224,7 @@ struct Ctx {
     double* di_regspeed[2];              // approach record: approaching->getSpeed() at registration
     SUMOTime* di_regwaiting[2];          // approach record: waiting time at registration
     int32_t* di_next[2];                 // next record in the link's approach list
+    int32_t* di_veh[2];                  // approach record: the approaching vehicle (saves the reader a modulo and the veh_order lookup)
     int cur;                             // buffer written by this step's planMove
     // ---- departure queues (per departure lane, in load order) ----------------------------
     const int32_t* dq_begin; const int32_t* dq_veh; int32_t* dq_head;   // [nL+1], [nV], [nL]

@@ -122,7 +122,7 @@ class PartitionedEngine:
                                                ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_int]
         lib.sumob200_halo_message_bytes.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
         lib.sumob200_halo_message_bytes.restype = ctypes.c_int64
-        lib.sumob200_halo_pack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        lib.sumob200_halo_pack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
         lib.sumob200_halo_unpack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         lib.sumob200_stream.argtypes = [ctypes.c_void_p]
         lib.sumob200_stream.restype = ctypes.c_void_p
@@ -147,19 +147,50 @@ class PartitionedEngine:
         self.num_vehicles = self.eng.num_vehicles
         self.num_lanes = self.eng.num_lanes
         self.exchanges = 0
+        self.bytes_sent = 0
 
     # ---- the step: engine step + halo exchange, all enqueued on the engine's stream
+    HEADER, LANE_REC, VEH_REC = 16, 64, 288    # sizeof HaloHeader / HaloLane / HaloVeh (static_assert in sb2_halo.h)
+
+    def _limit(self, last_count):
+        """vehicle records both ends transport in the next message, from the count of the previous one (which both know: the
+        sender packed it, the receiver read it in the header): 25 % + 512 head room, at most the capacity"""
+        if last_count is None:
+            return self.plan["capacity"]
+        return int(min(self.plan["capacity"], last_count + last_count // 4 + 512))
+
     def _exchange(self):
         from .engine import _check
         lib, h, torch = self.eng._lib, self.eng._h, self.torch
+        if not hasattr(self, "_counts"):
+            # per side: [pinned host copy of the last sent header, of the last received header, event]
+            self._counts = [{"sent": torch.zeros(4, dtype=torch.int32).pin_memory(), "recv": torch.zeros(4, dtype=torch.int32).pin_memory(),
+                             "event": None} for _ in (0, 1)]
         with torch.cuda.stream(self.stream):
+            send_v, recv_v = [None, None], [None, None]
             for side in (0, 1):
-                if self.send[side] is not None:
-                    _check(lib, lib.sumob200_halo_pack(h, side, self.send[side].data_ptr()), "sumob200_halo_pack")
-            exchange_messages(self.dist, self.rank, self.world, self.send, self.recv)
+                if self.send[side] is None:
+                    continue
+                st = self._counts[side]
+                if st["event"] is not None:
+                    st["event"].synchronize()            # recorded a whole step ago
+                    lim_s, lim_r = self._limit(int(st["sent"][1])), self._limit(int(st["recv"][1]))
+                else:
+                    lim_s = lim_r = self.plan["capacity"]
+                n_exp, n_imp = len(self._keep[side]), len(self._keep[2 + side])
+                _check(lib, lib.sumob200_halo_pack(h, side, self.send[side].data_ptr(), lim_s), "sumob200_halo_pack")
+                send_v[side] = self.send[side][:self.HEADER + self.LANE_REC * n_exp + self.VEH_REC * lim_s]
+                recv_v[side] = self.recv[side][:self.HEADER + self.LANE_REC * n_imp + self.VEH_REC * lim_r]
+                self.bytes_sent += send_v[side].numel()
+            exchange_messages(self.dist, self.rank, self.world, send_v, recv_v)
             for side in (0, 1):
                 if self.recv[side] is not None:
                     _check(lib, lib.sumob200_halo_unpack(h, side, self.recv[side].data_ptr()), "sumob200_halo_unpack")
+                    st = self._counts[side]
+                    st["sent"].copy_(self.send[side][:16].view(torch.int32), non_blocking=True)
+                    st["recv"].copy_(self.recv[side][:16].view(torch.int32), non_blocking=True)
+                    st["event"] = torch.cuda.Event()
+                    st["event"].record(self.stream)
             # fleet aggregates: max speedFactor, MIN deceleration, max minGap over the departed vehicles of the whole network
             self.fleet[1].neg_()
             self.dist.all_reduce(self.fleet, op=self.dist.ReduceOp.MAX)
@@ -196,7 +227,8 @@ class PartitionedEngine:
     def halo_stats(self):
         torch = self.torch
         self.stream.synchronize()
-        out = {"exchanges": self.exchanges, "columns": list(self.plan["columns"]), "capacity_records": self.plan["capacity"]}
+        out = {"exchanges": self.exchanges, "columns": list(self.plan["columns"]), "capacity_records": self.plan["capacity"],
+               "bytes_sent_per_step": self.bytes_sent // max(self.exchanges, 1)}
         for side, name in ((0, "left"), (1, "right")):
             if self.send[side] is not None:
                 hdr = self.send[side][:16].cpu().numpy().view(np.int32)
@@ -248,7 +280,7 @@ class LocalPartitionedRun:
                                                    ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_int]
             lib.sumob200_halo_message_bytes.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
             lib.sumob200_halo_message_bytes.restype = ctypes.c_int64
-            lib.sumob200_halo_pack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+            lib.sumob200_halo_pack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
             lib.sumob200_halo_unpack.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
             lib.sumob200_fleet_aggregates.argtypes = [ctypes.c_void_p]
             lib.sumob200_fleet_aggregates.restype = ctypes.c_void_p
@@ -275,7 +307,7 @@ class LocalPartitionedRun:
             lib, h = p["eng"]._lib, p["eng"]._h
             for side in (0, 1):
                 if p["send"][side] is not None:
-                    _check(lib, lib.sumob200_halo_pack(h, side, p["send"][side].data_ptr()), "sumob200_halo_pack")
+                    _check(lib, lib.sumob200_halo_pack(h, side, p["send"][side].data_ptr(), 0), "sumob200_halo_pack")
         torch.cuda.synchronize()
         for rank, p in enumerate(self.parts):
             lib, h = p["eng"]._lib, p["eng"]._h
