@@ -372,6 +372,7 @@ def main():
     mean_speed = float(state["speed"][on].mean()) if on.any() else 0.0
     halo = eng.halo_stats() if partitioned else None
 
+    eng.close()
     if dist is not None:
         import torch
         from sumo_b200.shard import reduce_step_metrics

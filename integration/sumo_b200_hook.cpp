@@ -1,0 +1,252 @@
+/* sumo_b200_hook.cpp -- REFERENCE-SIDE binding of the engine: what makes `sumo` drive libsumob200.so instead of MSEdgeControl.
+ *
+ * Built by oracle/build_ref.sh (target sumo_b200) into oracle/_ref/sumo_b200 = the reference's own objects, with two changes:
+ *   1. MSNet.cpp is compiled from an OVERLAY COPY generated at build time (oracle/_ref/gen/MSNet_b200.cpp, never committed):
+ *      the reference's file with one line inserted at the top of MSNet::simulationStep (src/microsim/MSNet.cpp:799)
+ *          if (sumob200_hook_step(this)) { return; }
+ *      -- the patch of INTEGRATION.md, applied by `sed`.
+ *   2. this file replaces sumo_main.cpp: the same start-up sequence (XMLSubSys, OptionsIO, NLBuilder::init, MSNet::simulate,
+ *      closeSimulation) plus the option `--b200.device N`.
+ * Everything else -- NLBuilder network / route loading, the option parser, MSFCDExport and the other output writers,
+ * libsumo -- is the reference's unchanged code.
+ *
+ * With `--b200.device N` the first step flattens the loaded scenario IN MEMORY (the walk of integration/sumo_flatten.cpp over
+ * MSEdge / MSLane / MSLink / MSTrafficLightLogic / MSVehicleType / SUMOVehicle) and hands the arrays to sumob200_create; every
+ * step then is: sumob200_step(1) on the GPU, the vehicle states mirrored back into the reference's MSVehicle objects (lane,
+ * position, speed, angle, on-road flag) and MSVehicleControl's counters, MSNet::writeOutput (so --fcd-output is written by the
+ * reference's own MSFCDExport from those objects), time += DELTA_T.  libsumo getters (Vehicle::getSpeed, getLaneID,
+ * getLanePosition ...) read the same mirrored objects.
+ *
+ * This is integration / test code on the reference's side of the boundary: it reaches MSVehicle's state through
+ * `#define private public` (sumo_flatten.cpp), which a maintainer would replace by a friend declaration or setters.
+ *
+ * `--libsumo-check K` instead of simulate(): K steps through libsumo::Simulation::step() and after each one the ids, lanes,
+ * positions and speeds as libsumo::Vehicle reports them, printed to stdout (tests/test_boundary.py compares the output of the
+ * stock run with the engine run).
+ */
+#include <config.h>
+#include <algorithm>
+#include <bitset>
+#include <list>
+#include <map>
+#include <random>
+#include <set>
+#include <sstream>
+#include <string>
+#include <vector>
+#include <memory>
+#include <iostream>
+#include <fstream>
+#include <functional>
+#include <cassert>
+#include <limits>
+#include <utils/common/StdDefs.h>
+#include <utils/common/SUMOTime.h>
+#include <utils/geom/Position.h>
+#include <utils/geom/PositionVector.h>
+// write access to the few members the mirror sets (MSVehicle: lane, state, angle, on-road flag; MSBaseVehicle: route position,
+// departure; MSVehicleControl: counters; MSNet: clock) -- see the header comment
+#define private public
+#define protected public
+#include <microsim/MSBaseVehicle.h>
+#include <microsim/MSVehicle.h>
+#include <microsim/MSVehicleControl.h>
+#include <microsim/MSNet.h>
+#undef private
+#undef protected
+#define SUMOB200_NO_MAIN
+#include "sumo_flatten.cpp"
+
+#include <libsumo/Simulation.h>
+#include <utils/geom/GeomHelper.h>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+
+#include "../include/sumob200.h"
+
+namespace {
+
+int gDevice = -1;
+
+struct Hook {
+    sumob200_engine* eng = nullptr;
+    std::vector<MSVehicle*> vehOfSlot;
+    std::vector<MSLane*> laneOfIndex;
+    std::vector<sumob200_vehicle_state> state;
+    std::vector<sumob200_fcd_row> rows;
+    std::vector<char> wasOnRoad;
+    int lastDeparted = 0, lastArrived = 0;
+
+    static Hook* create(MSNet* net) {
+        sb2::FlatFile ff;
+        flattenTo(net, ff);
+        std::vector<sumob200_array> arrays;
+        for (auto& kv : ff.arrays) {
+            sumob200_array a;
+            a.name = kv.first.c_str();
+            a.dtype = kv.second.dtype;
+            a.elem_size = kv.second.elemSize;
+            a.count = kv.second.count;
+            a.data = kv.second.bytes.data();
+            arrays.push_back(a);
+        }
+        Hook* h = new Hook();
+        if (sumob200_create(arrays.data(), (int)arrays.size(), gDevice, &h->eng) != 0) {
+            throw ProcessError(std::string("sumob200_create failed: ") + sumob200_last_error());
+        }
+        for (const MSEdge* e : MSEdge::getAllEdges()) {
+            for (MSLane* l : e->getLanes()) {
+                h->laneOfIndex.push_back(l);
+            }
+        }
+        std::map<int, MSVehicle*> byNumId;
+        MSVehicleControl& vc = net->getVehicleControl();
+        for (auto it = vc.loadedVehBegin(); it != vc.loadedVehEnd(); ++it) {
+            MSVehicle* v = dynamic_cast<MSVehicle*>(it->second);
+            if (v != nullptr) {
+                byNumId[v->getNumericalID()] = v;
+            }
+        }
+        const int32_t* numid = ff.ptr<int32_t>("veh_numid");
+        const int nV = (int)ff.count("veh_numid");
+        for (int s = 0; s < nV; s++) {
+            h->vehOfSlot.push_back(byNumId[numid[s]]);
+        }
+        h->state.resize(nV > 0 ? nV : 1);
+        h->rows.resize(nV > 0 ? nV : 1);
+        h->wasOnRoad.assign(nV, 0);
+        WRITE_MESSAGE("sumob200: " + std::string(sumob200_version()) + "; " + toString(nV) + " vehicles, " + toString(h->laneOfIndex.size()) + " lanes on CUDA device " + toString(gDevice));
+        return h;
+    }
+
+    void step(MSNet* net) {
+        sumob200_step_result r;
+        if (sumob200_step(eng, 1, &r) != 0) {
+            throw ProcessError(std::string("sumob200_step failed: ") + sumob200_last_error());
+        }
+        if (r.flags != 0) {
+            throw ProcessError("sumob200: the engine raised flags " + toString(r.flags) + " (the run left the supported path)");
+        }
+        const int nV = (int)vehOfSlot.size();
+        int nRows = 0;
+        if (sumob200_mirror_all(eng, state.data(), nV) != 0 || sumob200_fcd_snapshot(eng, rows.data(), nV, &nRows) != 0) {
+            throw ProcessError(std::string("sumob200 mirror failed: ") + sumob200_last_error());
+        }
+        // ---- mirror: what libsumo::Vehicle getters and MSFCDExport read from MSVehicle
+        for (int i = 0; i < nRows; i++) {
+            const sumob200_fcd_row& row = rows[i];
+            MSVehicle* v = vehOfSlot[row.slot];
+            if (!wasOnRoad[row.slot]) {
+                wasOnRoad[row.slot] = 1;
+                v->myDeparture = net->getCurrentTimeStep();   // (insertion time; exact value: sumob200_tripinfo_all)
+            }
+            v->myLane = laneOfIndex[row.lane];
+            v->myAmOnNet = true;
+            v->myState.myPos = row.pos;
+            v->myState.mySpeed = row.speed;
+            v->myState.myBackPos = row.pos - v->getVehicleType().getLength();
+            v->myCachedPosition = Position::INVALID;            // MSVehicle::getPosition recomputes it from lane + position
+            v->myAngle = DEG2RAD(90. - row.angle);              // inverse of GeomHelper::naviDegree
+            v->myCurrEdge = v->getRoute().begin() + state[row.slot].route_pos;
+        }
+        for (int s = 0; s < nV; s++) {
+            if (wasOnRoad[s] && state[s].lane < 0) {
+                wasOnRoad[s] = 2;
+                vehOfSlot[s]->myAmOnNet = false;   // arrived (or teleporting): not visible to the output writers
+            }
+        }
+        // ---- MSVehicleControl counters (summary output, MSNet::simulationState's termination test)
+        MSVehicleControl& vc = net->getVehicleControl();
+        vc.myRunningVehNo = r.running;
+        vc.myEndedVehNo = r.arrived_total;
+        vc.myCollisions = r.collisions;
+        vc.myTeleportsJam = r.teleports;
+        // ---- the rest of MSNet::simulationStep / postMoveStep (MSNet.cpp:919-964): outputs, clock
+        net->writeOutput();
+        net->myStep += DELTA_T;
+    }
+};
+
+Hook* gHook = nullptr;
+
+}  // namespace
+
+// called from the inserted line of the overlay MSNet::simulationStep; false = not active, run the reference's own step
+bool sumob200_hook_step(MSNet* net) {
+    if (gDevice < 0) {
+        return false;
+    }
+    if (gHook == nullptr) {
+        gHook = Hook::create(net);
+    }
+    gHook->step(net);
+    return true;
+}
+
+int
+main(int argc, char** argv) {
+    std::vector<char*> args;
+    args.push_back(argv[0]);
+    int libsumoCheck = -1;
+    for (int i = 1; i < argc; i++) {
+        const std::string a = argv[i];
+        if (a == "--b200.device" && i + 1 < argc) {
+            gDevice = atoi(argv[++i]);
+        } else if (a == "--libsumo-check" && i + 1 < argc) {
+            libsumoCheck = atoi(argv[++i]);
+        } else {
+            args.push_back(argv[i]);
+        }
+    }
+    // the engine needs the whole demand at create (incremental route loading = sumob200_add_routes, not built): load it all at start
+    static char routeSteps[] = "--route-steps";
+    static char zero[] = "0";
+    args.push_back(routeSteps);
+    args.push_back(zero);
+    OptionsCont& oc = OptionsCont::getOptions();
+    oc.setApplicationName("sumo", "Eclipse SUMO sumo " VERSION_STRING);
+    gSimulation = true;
+    int ret = 0;
+    MSNet* net = nullptr;
+    try {
+        XMLSubSys::init();
+        OptionsIO::setArgs((int)args.size(), args.data());
+        net = NLBuilder::init();
+        if (net == nullptr) {
+            return 1;
+        }
+        const SUMOTime begin = string2time(oc.getString("begin"));
+        const SUMOTime end = string2time(oc.getString("end"));
+        if (libsumoCheck >= 0) {
+            // libsumo-style stepping: Simulation::step -> MSNet::simulationStep -> (hook) ; getters read MSVehicle
+            for (int k = 0; k < libsumoCheck; k++) {
+                libsumo::Simulation::step();
+                std::vector<std::string> ids = libsumo::Vehicle::getIDList();
+                std::sort(ids.begin(), ids.end());
+                printf("t=%.2f n=%d", libsumo::Simulation::getTime(), (int)ids.size());
+                for (const std::string& id : ids) {
+                    printf(" %s:%s:%.6f:%.6f", id.c_str(), libsumo::Vehicle::getLaneID(id).c_str(), libsumo::Vehicle::getLanePosition(id), libsumo::Vehicle::getSpeed(id));
+                }
+                printf("\n");
+            }
+            net->closeSimulation(begin, "libsumo check done");
+        } else {
+            MSNet::SimulationState state = net->simulate(begin, end);
+            (void)state;
+        }
+        delete net;
+        OutputDevice::closeAll();
+        MsgHandler::cleanupOnEnd();
+    } catch (const ProcessError& e) {
+        if (std::string(e.what()) != std::string("Process Error") && std::string(e.what()) != std::string("")) {
+            WRITE_ERROR(e.what());
+        }
+        ret = 1;
+    }
+    if (gHook != nullptr && gHook->eng != nullptr) {
+        sumob200_destroy(gHook->eng);
+    }
+    SystemFrame::close();
+    return ret;
+}

@@ -123,8 +123,7 @@ int edgeFlags(const MSEdge* e) {
            | (e->isCrossing() || e->isWalkingArea() ? 16 : 0);
 }
 
-void flatten(MSNet* net, const std::string& path) {
-    sb2::FlatFile ff;
+void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     OptionsCont& oc = OptionsCont::getOptions();
     // ---------------- edges and lanes
     const MSEdgeVector& edges = MSEdge::getAllEdges();
@@ -612,6 +611,11 @@ void flatten(MSNet* net, const std::string& path) {
     ff.putScalar<int32_t>("opt_tag_cf_idm", (int)SUMO_TAG_CF_IDM);
     ff.putScalar<int32_t>("opt_default_departlane_proc", (int)MSEdge::getAllEdges().front()->getDefaultDepartLaneDefinition());
     ff.putScalar<int32_t>("opt_default_departlane", MSEdge::getAllEdges().front()->getDefaultDepartLane());
+}
+
+void flatten(MSNet* net, const std::string& path) {
+    sb2::FlatFile ff;
+    flattenTo(net, ff);
     ff.save(path);
 }
 
@@ -702,6 +706,7 @@ predictDraws(MSNet* net) {
 
 }  // namespace
 
+#ifndef SUMOB200_NO_MAIN
 int
 main(int argc, char** argv) {
     std::string flatOut, traceOut, drawsOut, emisOut, tlsSetPhase, vehSetSpeed;
@@ -855,3 +860,4 @@ main(int argc, char** argv) {
     SystemFrame::close();
     return ret;
 }
+#endif  // SUMOB200_NO_MAIN

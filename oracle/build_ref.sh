@@ -6,7 +6,7 @@
 # Flags: -O2 -ffp-contract=off and no -march, so the oracle is strict non-FMA IEEE fp64
 # (the reference sets no FP flags itself, CMakeLists.txt:147-157).
 #
-# usage: oracle/build_ref.sh [sumo|netgenerate|duarouter|flatten|all]   (default: all)
+# usage: oracle/build_ref.sh [sumo|netgenerate|duarouter|flatten|sumo_b200|all]   (default: all; sumo_b200 needs sumo_b200/libsumob200.so)
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${SUMO_REFERENCE:-/root/reference}"
@@ -57,6 +57,12 @@ SIM="$(srcs_in microsim mesosim netload traci-server) $(ls $SRC/libsumo/*.cpp | 
 NET="$(srcs_in netbuild netwrite netimport foreign/eulerspiral) $(ls $SRC/netgen/*.cpp)"
 DUA="$(srcs_in router) $(ls $SRC/duarouter/*.cpp)"
 
+# overlay copy of MSNet.cpp: declaration + one inserted line at the top of MSNet::simulationStep (src/microsim/MSNet.cpp:799)
+sed -e 's|^MSNet::simulationStep(const bool onlyMove) {$|MSNet::simulationStep(const bool onlyMove) {\n    if (sumob200_hook_step(this)) {\n        return;\n    }|' \
+    -e '0,/^#include <config.h>/s||#include <config.h>\nclass MSNet;\nbool sumob200_hook_step(MSNet* net);   // integration/sumo_b200_hook.cpp|' \
+    "$SRC/microsim/MSNet.cpp" > "$OUT/gen/MSNet_b200.cpp"
+grep -q 'sumob200_hook_step(this)' "$OUT/gen/MSNet_b200.cpp" || { echo "build_ref: could not patch MSNet::simulationStep" >&2; exit 1; }
+
 MK="$OUT/Makefile"
 {
     echo "CXX=g++"
@@ -89,6 +95,15 @@ MK="$OUT/Makefile"
     printf '\t@echo CXX integration/sumo_flatten.cpp\n\t@$(CXX) $(CXXFLAGS) -c $< -o $@\n'
     echo "$OUT/sumo_flatten: \$(OBJ)/sumo_flatten.o \$(filter-out %sumo_main.o,\$(SIM_OBJS)) \$(VEHICLE_OBJS) \$(COMMON_OBJS)"
     printf '\t@echo LINK $@\n\t@$(CXX) -o $@ $^ -l:libexpat.a -l:libz.a -lpthread -ldl\n'
+    # sumo_b200 = the reference's sumo driving libsumob200.so (integration/sumo_b200_hook.cpp): MSNet.cpp compiled from an overlay copy with
+    # the one-line hook of INTEGRATION.md inserted by sed (generated below, never committed); needs sumo_b200/libsumob200.so
+    echo "\$(OBJ)/MSNet_b200.o: $OUT/gen/MSNet_b200.cpp"
+    printf '\t@echo CXX gen/MSNet_b200.cpp\n\t@$(CXX) $(CXXFLAGS) -I%s -c $< -o $@\n' "$SRC/microsim"
+    echo "\$(OBJ)/sumo_b200_hook.o: $HERE/../integration/sumo_b200_hook.cpp $HERE/../integration/sumo_flatten.cpp $HERE/../include/sumob200_flatfile.h $HERE/../include/sumob200.h"
+    printf '\t@echo CXX integration/sumo_b200_hook.cpp\n\t@$(CXX) $(CXXFLAGS) -c $< -o $@\n'
+    echo "$OUT/sumo_b200: \$(OBJ)/sumo_b200_hook.o \$(OBJ)/MSNet_b200.o \$(filter-out %sumo_main.o %microsim_MSNet.o,\$(SIM_OBJS)) \$(VEHICLE_OBJS) \$(COMMON_OBJS)"
+    printf '\t@echo LINK $@\n\t@$(CXX) -o $@ $^ -L%s -lsumob200 -Wl,-rpath,\\$$ORIGIN/../../sumo_b200 -l:libexpat.a -l:libz.a -lpthread -ldl\n' "$HERE/../sumo_b200"
+    echo "sumo_b200: $OUT/sumo_b200"
     echo "flatten: $OUT/sumo_flatten"
     echo "sumo: $OUT/sumo"
     echo "netgenerate: $OUT/netgenerate"

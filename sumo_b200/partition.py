@@ -258,6 +258,15 @@ class PartitionedEngine:
         return self.eng.time_ms
 
     def close(self):
+        # torch buffers that were used on the engine's stream must go before the stream does (their deleter records on it)
+        torch = self.torch
+        self.stream.synchronize()
+        self.send, self.recv, self.fleet = [None, None], [None, None], None
+        if hasattr(self, "_counts"):
+            del self._counts
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        self.stream = None
         self.eng.close()
 
 

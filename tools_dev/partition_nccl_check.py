@@ -40,6 +40,7 @@ def main():
             break
         compared[0] += int(on.sum())
         compared[1] += len(ids)
+    eng.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.all_reduce(compared[:1])
