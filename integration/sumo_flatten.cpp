@@ -405,6 +405,46 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             }
             return a->getNumericalID() < b->getNumericalID();
         });
+        // ---- features of the demand the step engine does not model: refused here, never silently dropped
+        if (net->getInsertionControl().getPendingFlowCount() > 0) {
+            throw ProcessError("sumob200: <flow> definitions are not supported (expand them into <vehicle>s)");
+        }
+        if (net->hasPersons() || net->hasContainers()) {
+            throw ProcessError("sumob200: persons / containers are not supported");
+        }
+        for (const SUMOVehicle* v : vehs) {
+            const SUMOVehicleParameter& p = v->getParameter();
+            const std::string who = "sumob200: vehicle '" + v->getID() + "': ";
+            if (!p.stops.empty() || !v->getRoute().getStops().empty() || v->hasStops()) {
+                throw ProcessError(who + "<stop>s are not supported");
+            }
+            if (p.arrivalSpeedProcedure != ArrivalSpeedDefinition::DEFAULT && p.arrivalSpeedProcedure != ArrivalSpeedDefinition::CURRENT) {
+                throw ProcessError(who + "arrivalSpeed is not supported");
+            }
+            if (p.arrivalLaneProcedure != ArrivalLaneDefinition::DEFAULT && p.arrivalLaneProcedure != ArrivalLaneDefinition::CURRENT) {
+                throw ProcessError(who + "arrivalLane is not supported");
+            }
+            const SUMOVTypeParameter& tp = v->getVehicleType().getParameter();
+            if (tp.actionStepLength != 0 && tp.actionStepLength != DELTA_T) {
+                throw ProcessError(who + "actionStepLength different from the step length is not supported");
+            }
+            if (!tp.jmParameter.empty()) {
+                throw ProcessError(who + "junction model parameters (jm*) are not supported");
+            }
+            for (const MSVehicleDevice* d : v->getDevices()) {
+                const std::string dev = d->deviceName();
+                if (dev != "emissions" && dev != "tripinfo" && dev != "fcd" && dev != "vehroute") {
+                    throw ProcessError(who + "device '" + dev + "' is not supported");
+                }
+            }
+            for (const MSEdge* e : v->getRoute().getEdges()) {
+                for (const MSLane* l : e->getLanes()) {
+                    if (!l->allowsVehicleClass(v->getVClass())) {
+                        throw ProcessError(who + "lane '" + l->getID() + "' on its route does not allow its vehicle class (lane permissions are not modelled)");
+                    }
+                }
+            }
+        }
         std::map<const MSVehicleType*, int> typeIdx;
         std::vector<const MSVehicleType*> types;
         std::map<const MSRoute*, int> routeIdx;
