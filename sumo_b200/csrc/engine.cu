@@ -36,20 +36,6 @@ namespace {
 
 thread_local std::string gLastError;
 
-// D2H of one FCD snapshot by the SMs (a few CTAs on the copy stream, concurrent with the next step's kernels): the number of
-// rows is only known on the device, so a cudaMemcpyAsync would need a host round trip to size it -- which stalled the pipeline
-// (the next step could not be enqueued before the rows were compacted).  16-byte stores into mapped pinned memory, count last.
-__global__ void __launch_bounds__(256) k_fcd_copy(const int4* __restrict__ src, int4* __restrict__ dst, const int32_t* __restrict__ dCount, int32_t* hCount) {
-    const int n = *dCount;
-    const long long n16 = (long long)n * (long long)(sizeof(sumob200_fcd_row) / 16);
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) {
-        dst[i] = src[i];
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        *hCount = n;
-    }
-}
-
 #define CUDA_TRY(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
         gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
 
@@ -69,8 +55,10 @@ struct sumob200_engine {
     // FCD streaming: device rows + block counts, two pinned host buffers, a copy stream (D2H overlaps the next step)
     sumob200_fcd_row* dFcd[2] = {nullptr, nullptr};
     int32_t* dFcdBlocks[2] = {nullptr, nullptr};
-    sumob200_fcd_row* hFcd[2] = {nullptr, nullptr};   // pinned + mapped: written by k_fcd_copy on the copy stream
-    int32_t* hFcdCount = nullptr;                     // [2], pinned + mapped
+    sumob200_fcd_row* hFcd[2] = {nullptr, nullptr};   // pinned
+    int32_t* hFcdCount = nullptr;                     // [2], pinned
+    int fcdCopiedRows[2] = {0, 0};                    // rows the asynchronous copy of each buffer covered
+    int fcdLastCount = -1;                            // row count of the previous snapshot (sizes the next asynchronous copy)
     cudaStream_t copyStream = nullptr;
     cudaEvent_t fcdReady = nullptr, fcdCopied[2] = {nullptr, nullptr};
     int fcdBuf = 0, fcdPendingRows = -1;
@@ -703,9 +691,9 @@ int sumob200_fcd_begin(sumob200_engine* e) {
         for (int b = 0; b < 2; b++) {
             CUDA_TRY(cudaMalloc(&e->dFcd[b], bytes));
             CUDA_TRY(cudaMalloc(&e->dFcdBlocks[b], sizeof(int32_t) * (size_t)(nb + 1)));
-            CUDA_TRY(cudaHostAlloc(&e->hFcd[b], bytes, cudaHostAllocMapped));
+            CUDA_TRY(cudaHostAlloc(&e->hFcd[b], bytes, cudaHostAllocDefault));
         }
-        CUDA_TRY(cudaHostAlloc(&e->hFcdCount, 2 * sizeof(int32_t), cudaHostAllocMapped));
+        CUDA_TRY(cudaHostAlloc(&e->hFcdCount, 2 * sizeof(int32_t), cudaHostAllocDefault));
         CUDA_TRY(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
         CUDA_TRY(cudaEventCreateWithFlags(&e->fcdReady, cudaEventDisableTiming));
         CUDA_TRY(cudaEventCreateWithFlags(&e->fcdCopied[0], cudaEventDisableTiming));
@@ -721,11 +709,21 @@ int sumob200_fcd_begin(sumob200_engine* e) {
     CUDA_TRY(cudaStreamWaitEvent(s, e->fcdCopied[b], 0));
     e->ks->fcd(&e->d, nV, e->dFcdBlocks[b], e->dFcd[b], s);
     CUDA_TRY(cudaEventRecord(e->fcdReady, s));
-    // rows + count travel on the copy stream while the caller launches the next step: no host synchronisation here
+    // rows + count travel on the copy stream (copy engine, no SM) while the caller launches the next step.  The number of rows is
+    // only known on the device; waiting for it here would stall the pipeline (the next step could not be enqueued before this
+    // snapshot was compacted).  So the copy is sized from the PREVIOUS snapshot's count plus head room -- the number of vehicles on
+    // the road changes slowly -- and sumob200_fcd_end fetches the remainder in the rare case it was not enough.
     CUDA_TRY(cudaStreamWaitEvent(e->copyStream, e->fcdReady, 0));
-    k_fcd_copy<<<64, 256, 0, e->copyStream>>>(reinterpret_cast<const int4*>(e->dFcd[b]), reinterpret_cast<int4*>(e->hFcd[b]),
-                                              e->dFcdBlocks[b] + nb, e->hFcdCount + b);
-    e->launches += 4;
+    int guess = e->fcdLastCount < 0 ? nV : e->fcdLastCount + e->fcdLastCount / 16 + 1024;
+    if (guess > nV) {
+        guess = nV;
+    }
+    CUDA_TRY(cudaMemcpyAsync(e->hFcdCount + b, e->dFcdBlocks[b] + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, e->copyStream));
+    if (guess > 0) {
+        CUDA_TRY(cudaMemcpyAsync(e->hFcd[b], e->dFcd[b], sizeof(sumob200_fcd_row) * (size_t)guess, cudaMemcpyDeviceToHost, e->copyStream));
+    }
+    e->fcdCopiedRows[b] = guess;
+    e->launches += 3;
     CUDA_TRY(cudaEventRecord(e->fcdCopied[b], e->copyStream));
     e->fcdPendingRows = 0;
     return 0;
@@ -737,9 +735,18 @@ int sumob200_fcd_end(sumob200_engine* e, const sumob200_fcd_row** rows, int* n) 
         return SUMOB200_EINVAL;
     }
     CUDA_TRY(cudaSetDevice(e->device));
-    CUDA_TRY(cudaEventSynchronize(e->fcdCopied[e->fcdBuf]));
-    *rows = e->hFcd[e->fcdBuf];
-    *n = e->hFcdCount[e->fcdBuf];
+    const int b = e->fcdBuf;
+    CUDA_TRY(cudaEventSynchronize(e->fcdCopied[b]));
+    const int count = e->hFcdCount[b];
+    if (count > e->fcdCopiedRows[b]) {
+        // more vehicles entered the road in one step than the head room covered: fetch the rest now
+        CUDA_TRY(cudaMemcpyAsync(e->hFcd[b] + e->fcdCopiedRows[b], e->dFcd[b] + e->fcdCopiedRows[b],
+                                 sizeof(sumob200_fcd_row) * (size_t)(count - e->fcdCopiedRows[b]), cudaMemcpyDeviceToHost, e->copyStream));
+        CUDA_TRY(cudaStreamSynchronize(e->copyStream));
+    }
+    e->fcdLastCount = count;
+    *rows = e->hFcd[b];
+    *n = count;
     e->fcdPendingRows = -1;
     e->fcdBuf ^= 1;
     return 0;
