@@ -426,9 +426,13 @@ public:
             SB2_DYN2(double, di_vpass, b, nDI, 0.); SB2_DYN2(double, di_vwait, b, nDI, 0.); SB2_DYN2(double, di_arrspeed, b, nDI, 0.);
             SB2_DYN2(double, di_arrspeedbraking, b, nDI, 0.); SB2_DYN2(double, di_dist, b, nDI, 0.); SB2_DYN2(double, di_accelv, b, nDI, 0.);
             SB2_DYN2(double, di_avail, b, nDI, 0.);
-            SB2_DYN2(int64_t, di_arrtime, b, nDI, (int64_t)0); SB2_DYN2(int64_t, di_leavetime, b, nDI, (int64_t)0);
+            SB2_DYN2(int64_t, di_arrtime, b, nDI, (int64_t)0);
             SB2_DYN2(double, di_regspeed, b, nDI, 0.); SB2_DYN2(int64_t, di_regwaiting, b, nDI, (int64_t)0);
-            SB2_DYN2(int32_t, di_next, b, nDI, -1); SB2_DYN2(int32_t, di_veh, b, nDI, -1);
+            {
+                AppRec none;
+                none.next = -1; none.veh = -1; none.arrtime = 0; none.leavetime = 0; none.arrspeedbraking = 0.;
+                SB2_DYN2(AppRec, ap_rec, b, nDI, none);
+            }
         }
         h.cur = 0;
         {

@@ -5,7 +5,7 @@
  * (hasApproachingFoe), 1346-1397 (isCont, lastWasContMajor, lastWasContState), MSLink.h:730 (unsafeMergeSpeeds).
  *
  * The approach table of the reference (std::map<vehicle, ApproachingVehicleInformation> per link, MSLink.h:183) is
- * the set of drive items of one buffer, chained per link through di_next (lock-free push in k_plan).  Iteration order
+ * the set of drive items of one buffer, chained per link through AppRec::next (lock-free push in k_plan).  Iteration order
  * differs from the reference's map order, which is unobservable here: blockedAtTime is a pure OR over the foes unless
  * collectFoes is used (zipper links only; refused at load).
  */
@@ -90,15 +90,16 @@ SB2_HD SUMOTime computeFoeArrivalTimeBraking(const Ctx& c, SUMOTime arrivalTime,
 }
 
 // MSLink.cpp:1113-1221 ; `k` is the foe link whose approach record `r` (of vehicle `foe`) is tested
-SB2_HD bool link_blockedByFoe(const Ctx& c, int k, int buf, int r, int foe,
+SB2_HD bool link_blockedByFoe(const Ctx& c, int k, int buf, int r, const AppRec& a,
                               SUMOTime arrivalTime, SUMOTime leaveTime, double arrivalSpeed, double leaveSpeed,
                               bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime) {
-    if (!c.di_request[buf][r]) {   // avi.willPass
+    if (a.veh < 0) {   // !avi.willPass
         return false;
     }
+    const int foe = a.veh;
     const uint8_t state = c.link_state[k];
-    const SUMOTime aviArrival = c.di_arrtime[buf][r];
-    const SUMOTime aviLeaving = c.di_leavetime[buf][r];
+    const SUMOTime aviArrival = a.arrtime;
+    const SUMOTime aviLeaving = a.leavetime;
     if (state == 'w') {
         // action step == sim step: actionDelta = SIMSTEP - lastActionTime = 0 during executeMove
         const SUMOTime actionDelta = 0;
@@ -110,7 +111,7 @@ SB2_HD bool link_blockedByFoe(const Ctx& c, int k, int buf, int r, int foe,
         }
     }
     SUMOTime foeArrivalTime = aviArrival;
-    double foeArrivalSpeedBraking = c.di_arrspeedbraking[buf][r];
+    double foeArrivalSpeedBraking = a.arrspeedbraking;
     if (impatience > 0 && arrivalTime < aviArrival) {
         const SUMOTime fatb = computeFoeArrivalTimeBraking(c, arrivalTime, foe, aviArrival, impatience, c.di_dist[buf][r], foeArrivalSpeedBraking);
         foeArrivalTime = (SUMOTime)((1. - impatience) * (double)aviArrival + impatience * (double)fatb);
@@ -158,14 +159,21 @@ SB2_HD bool veh_executes_before(const Ctx& c, int foe, int ego) {
 SB2_HD int link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime, SUMOTime leaveTime, double arrivalSpeed, double leaveSpeed,
                               bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, int live = LIVE_NOW) {
     int result = OPEN_YES;
-    for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        // (a record without request never blocks -- MSLink::blockedByFoe starts with `if (!avi.willPass) return false` -- so it is
-        // dropped before anything of its vehicle is loaded: with queues of 20-30 vehicles per lane most records end here)
-        if (!c.di_request[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8)]) {
+    for (int r = c.link_app_head[buf][k]; r >= 0;) {
+        const AppRec a = c.ap_rec[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8)];
+        const int rec = r;
+        r = a.next;
+        // The reference tests, per approaching vehicle: not ego, (under lastWasContRed) not standing, blockedByFoe.  The tests are
+        // independent, so the cheapest comes first: most records are dismissed from their 32-byte hot part alone (no request, or
+        // their time window does not meet ego's), before anything of the vehicle itself is loaded.
+        if (a.veh < 0 || a.veh == ego) {
             continue;
         }
-        const int foe = SB2_CHK(c.di_veh[buf][r], 0, c.nV, 9);
-        if (foe == ego || !veh_on_road(c, foe)) {
+        if (!link_blockedByFoe(c, k, buf, rec, a, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
+            continue;
+        }
+        const int foe = SB2_CHK(a.veh, 0, c.nV, 9);
+        if (!veh_on_road(c, foe)) {
             continue;
         }
         if (lastWasContRed) {
@@ -173,23 +181,18 @@ SB2_HD int link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime
             if (live == LIVE_NOW) {
                 foeSpeed = c.veh_speed[foe];
             } else if (!veh_executes_before(c, foe, ego)) {
-                foeSpeed = c.di_regspeed[buf][r];
+                foeSpeed = c.di_regspeed[buf][rec];
             } else if (live == LIVE_PASS2 && !c.veh_deferred[foe]) {
                 foeSpeed = c.veh_speed[foe];
             } else {
-                // the foe's new speed is not known yet: it only matters if this record would block
-                if (link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
-                    result = OPEN_UNDETERMINED;
-                }
+                result = OPEN_UNDETERMINED;   // the foe's new speed is not known yet, and this record would block
                 continue;
             }
             if (!(foeSpeed > SB2_HALTING_SPEED)) {
                 continue;
             }
         }
-        if (link_blockedByFoe(c, k, buf, r, foe, arrivalTime, leaveTime, arrivalSpeed, leaveSpeed, sameTargetLane, impatience, decel, waitingTime)) {
-            return OPEN_NO;
-        }
+        return OPEN_NO;
     }
     return result;
 }
@@ -255,10 +258,12 @@ SB2_HD bool link_hasApproachingFoe(const Ctx& c, int k, int buf, SUMOTime arriva
 
 // find the approach record of vehicle v on link k (MSLink::getApproaching, MSLink.cpp:801-809); -1 if absent
 SB2_HD int link_getApproaching(const Ctx& c, int k, int buf, int v) {
-    for (int r = c.link_app_head[buf][k]; r >= 0; r = c.di_next[buf][r]) {
-        if (c.di_veh[buf][r] == v) {
+    for (int r = c.link_app_head[buf][k]; r >= 0;) {
+        const AppRec a = c.ap_rec[buf][r];
+        if (a.veh == v || a.veh == ~v) {
             return r;
         }
+        r = a.next;
     }
     return -1;
 }

@@ -6,27 +6,57 @@
 
 namespace sb2 {
 
+// the drive items of the vehicle at work-list position wp, as they lie in the item-major SoA of buffer c.cur (item i at i * nV + wp:
+// a warp's accesses to "item i" are coalesced).  planMove writes every item ONCE when the look-ahead has finished with it and
+// checkRewindLinkLanes edits them in place -- there is no per-thread DriveItem array (it was 640 B of local memory per thread,
+// most of the register-spill traffic of the kernel: profiles/r01_k_plan_ncu.txt)
+struct DIView {
+    const Ctx& c;
+    int buf;
+    size_t wp, nV;
+    SB2_HD size_t at(int i) const { return (size_t)i * nV + wp; }
+    SB2_HD int link(int i) const { return c.di_link[buf][at(i)]; }
+    SB2_HD bool request(int i) const { return c.di_request[buf][at(i)] != 0; }
+    SB2_HD double leaveSpeed(int i) const { const double a = c.di_accelv[buf][at(i)]; return a < 0 ? c.di_vpass[buf][at(i)] : a; }
+    SB2_HD void store(int i, const DriveItem& d) const {
+        const size_t r = at(i);
+        c.di_link[buf][r] = d.link;
+        c.di_vpass[buf][r] = d.vPass;
+        c.di_vwait[buf][r] = d.vWait;
+        c.di_request[buf][r] = d.setRequest;
+        c.di_arrtime[buf][r] = d.arrivalTime;
+        c.di_arrspeed[buf][r] = d.arrivalSpeed;
+        c.di_arrspeedbraking[buf][r] = d.arrivalSpeedBraking;
+        c.di_dist[buf][r] = d.distance;
+        c.di_accelv[buf][r] = d.accelV;
+        c.di_hadstopped[buf][r] = d.hadStoppedVehicle;
+        c.di_avail[buf][r] = d.availableSpace;
+    }
+};
+
 // MSVehicle::checkRewindLinkLanes (MSVehicle.cpp:5255-5489); tableBuf = approach table of the previous step
-SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsInFront, DriveItem* lf, int n, int tableBuf) {
+SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsInFront, const DIView& lf, int n, int tableBuf) {
     if (c.lane_flags[e.lane] & LF_ROUNDABOUT) {
         return;
     }
+    const int cur = lf.buf;
     const double lengthWithGap = e.length + e.minGap;
     double seenSpace = -lengthsInFront;
     bool foundStopped = false;
     for (int i = 0; i < n; ++i) {
-        DriveItem& item = lf[i];
-        if (item.link < 0 || foundStopped) {
+        const size_t r = lf.at(i);
+        const int link = c.di_link[cur][r];
+        if (link < 0 || foundStopped) {
             if (!foundStopped) {
-                item.availableSpace += seenSpace;
+                c.di_avail[cur][r] += seenSpace;
             } else {
-                item.availableSpace = seenSpace;
+                c.di_avail[cur][r] = seenSpace;
             }
             continue;
         }
-        int approachedLane = c.link_via[item.link];
+        int approachedLane = c.link_via[link];
         if (approachedLane >= 0) {
-            if (veh_keepClear(c, item.link)) {
+            if (veh_keepClear(c, link)) {
                 seenSpace = seenSpace - c.lane_brutto[approachedLane];
                 if (approachedLane == e.lane) {
                     seenSpace += lengthWithGap;
@@ -37,71 +67,73 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
                 }
                 seenSpace = seenSpace + c.ls_space[approachedLane];
             }
-            item.availableSpace = seenSpace;
+            c.di_avail[cur][r] = seenSpace;
             continue;
         }
-        approachedLane = c.link_to[item.link];
+        approachedLane = c.link_to[link];
         const int last = lane_last_any(c, approachedLane);
         if (last < 0 || last == e.v) {
-            if (c.lane_length[approachedLane] > e.length || veh_keepClear(c, item.link)) {
+            if (c.lane_length[approachedLane] > e.length || veh_keepClear(c, link)) {
                 seenSpace += c.lane_length[approachedLane];
             }
-            item.availableSpace = seenSpace;
+            c.di_avail[cur][r] = seenSpace;
         } else {
             const bool foundStopped2 = c.ls_found_stopped[approachedLane] != 0;
             const double spaceTillLastStanding = c.ls_space[approachedLane];
             seenSpace += spaceTillLastStanding;
             if (foundStopped2) {
                 foundStopped = true;
-                item.hadStoppedVehicle = true;
+                c.di_hadstopped[cur][r] = 1;
             }
-            item.availableSpace = seenSpace;
+            c.di_avail[cur][r] = seenSpace;
             if (c.veh_havetowait[last]) {
                 foundStopped = true;
-                item.hadStoppedVehicle = true;
+                c.di_hadstopped[cur][r] = 1;
             }
         }
     }
     // check which links allow continuation and add pass available to the previous item
     for (int i = n - 1; i > 0; --i) {
-        DriveItem& item = lf[i - 1];
-        DriveItem& nextItem = lf[i];
+        const size_t r = lf.at(i - 1), rNext = lf.at(i);
+        const int itemLink = c.di_link[cur][r];
+        const int nextLink = c.di_link[cur][rNext];
         // (the reference dereferences item.myLink before testing it; a link-less item can only be the last one)
-        const bool canLeaveJunction = item.link < 0 || c.link_via[item.link] < 0 || nextItem.link < 0 || nextItem.setRequest;
-        const bool opened = (item.link >= 0
+        const bool canLeaveJunction = itemLink < 0 || c.link_via[itemLink] < 0 || nextLink < 0 || c.di_request[cur][rNext] != 0;
+        const bool opened = (itemLink >= 0
                              && (canLeaveJunction || (
-                                     nextItem.link >= 0 && (c.link_flags[nextItem.link] & KF_INTERNAL_JUNCTION) && state_red(c.link_state[nextItem.link])))
+                                     nextLink >= 0 && (c.link_flags[nextLink] & KF_INTERNAL_JUNCTION) && state_red(c.link_state[nextLink])))
                              && (
-                                 state_priority(c.link_state[item.link])
+                                 state_priority(c.link_state[itemLink])
                                  || i == 1
-                                 || link_opened(c, item.link, tableBuf, item.arrivalTime, item.arrivalSpeed,
-                                                di_getLeaveSpeed(item), e.length,
+                                 || link_opened(c, itemLink, tableBuf, c.di_arrtime[cur][r], c.di_arrspeed[cur][r],
+                                                lf.leaveSpeed(i - 1), e.length,
                                                 veh_impatience(c, e.v), e.cf.decel(), e.waiting, false, e.v) != OPEN_NO));
-        bool allowsContinuation = (item.link < 0 || link_isCont(c, item.link) || opened) && !item.hadStoppedVehicle;
-        if (!opened && item.link >= 0) {
+        bool allowsContinuation = (itemLink < 0 || link_isCont(c, itemLink) || opened) && !c.di_hadstopped[cur][r];
+        if (!opened && itemLink >= 0) {
             foundStopped = true;
             if (i > 1) {
-                DriveItem& item2 = lf[i - 2];
-                if (item2.link >= 0 && link_isCont(c, item2.link)) {
+                const int link2 = c.di_link[cur][lf.at(i - 2)];
+                if (link2 >= 0 && link_isCont(c, link2)) {
                     allowsContinuation = true;
                 }
             }
         }
         if (allowsContinuation) {
-            item.availableSpace = nextItem.availableSpace;
+            c.di_avail[cur][r] = c.di_avail[cur][rNext];
         }
     }
     // find removalBegin
     int removalBegin = -1;
     for (int i = 0; foundStopped && i < n && removalBegin < 0; ++i) {
-        const DriveItem& item = lf[i];
-        if (item.link < 0) {
+        const size_t r = lf.at(i);
+        const int link = c.di_link[cur][r];
+        if (link < 0) {
             continue;
         }
-        const double leftSpace = item.availableSpace - lengthWithGap;
+        const double leftSpace = c.di_avail[cur][r] - lengthWithGap;
         if (leftSpace < 0) {
             double impatienceCorrection = 0;
-            if (leftSpace < -impatienceCorrection / 10. && veh_keepClear(c, item.link)) {
+            if (leftSpace < -impatienceCorrection / 10. && veh_keepClear(c, link)) {
                 removalBegin = i;
             }
         }
@@ -110,14 +142,15 @@ SB2_HD void veh_checkRewindLinkLanes(const Ctx& c, const Ego& e, double lengthsI
     if (removalBegin != -1 && !(removalBegin == 0 && lane_internal(c, e.lane))) {
         const double brakeGap = cf_brakeGap(e.cf, e.speed, e.cf.decel(), 0.);
         while (removalBegin < n) {
-            DriveItem& dpi = lf[removalBegin];
-            if (dpi.link < 0) {
+            const size_t r = lf.at(removalBegin);
+            const int link = c.di_link[cur][r];
+            if (link < 0) {
                 break;
             }
-            dpi.vPass = dpi.vWait;
-            if (dpi.distance >= brakeGap + SB2_POSITION_EPS) {
-                if (!(c.link_flags[dpi.link] & KF_EXIT) || !lf[removalBegin - 1].setRequest) {
-                    dpi.setRequest = false;
+            c.di_vpass[cur][r] = c.di_vwait[cur][r];
+            if (c.di_dist[cur][r] >= brakeGap + SB2_POSITION_EPS) {
+                if (!(c.link_flags[link] & KF_EXIT) || !c.di_request[cur][lf.at(removalBegin - 1)]) {
+                    c.di_request[cur][r] = 0;
                 }
             }
             ++removalBegin;
@@ -148,10 +181,13 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     // MSVehicle.cpp:2183
     c.veh_stopspeed[v] = cf_maxNextSpeed(cf, c.veh_stopspeed[v]);
 
-    DriveItem lf[MAX_DRIVE_ITEMS];
+    // items 0 .. n-2 are in the drive-item arrays already; item n-1 (`last`, the only one the look-ahead still edits through
+    // lastLink) stays in registers until the next one is pushed
+    const DIView lf = {c, cur, (size_t)wp, (size_t)c.nV};
+    DriveItem last;
     int n = 0;
     bool overflow = false;
-#define SB2_PUSH(item) do { if (n < MAX_DRIVE_ITEMS) { lf[n++] = (item); } else { overflow = true; } } while (0)
+#define SB2_PUSH(item) do { if (n < MAX_DRIVE_ITEMS) { if (n > 0) { lf.store(n - 1, last); } last = (item); n++; } else { overflow = true; } } while (0)
 
     // leader on the own lane (MSLane::planMovements / updateLeaderInfo, MSLane.cpp:1608-1685)
     int ahead = c.veh_ahead[v];
@@ -324,37 +360,34 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         ahead = SB2_CHK(lane_last_any(c, SB2_CHK(leaderLane, 0, c.nL, 4)), -1, c.nV, 5);   // getLastVehicleInformation(nullptr, 0)
         seen += c.lane_length[lane];
         vLinkPass = MIN2(cf_estimateSpeedAfterDistance(cf, c.lane_length[lane], vv, cf.accel()), laneMaxV);
-        lastLink = &lf[n - 1];
+        lastLink = &last;
     }
 #undef SB2_PUSH
+    if (n > 0) {
+        lf.store(n - 1, last);
+    }
     if (overflow) {
         raise(c, ERR_DRIVE_ITEM_OVERFLOW);
     }
 
     veh_checkRewindLinkLanes(c, e, c.veh_len_in_front[v], lf, n, prev);
 
-    // store items + register approaches (MSVehicle::setApproachingForAllLinks -> MSLink::setApproaching, MSLink.cpp:718-736)
+    // register approaches (MSVehicle::setApproachingForAllLinks -> MSLink::setApproaching, MSLink.cpp:718-736)
     c.veh_ndi[cur][wp] = n;
     for (int i = 0; i < n; i++) {
-        const size_t r = (size_t)i * c.nV + wp;
-        const DriveItem& d = lf[i];
-        c.di_link[cur][r] = d.link;
-        c.di_vpass[cur][r] = d.vPass;
-        c.di_vwait[cur][r] = d.vWait;
-        c.di_request[cur][r] = d.setRequest;
-        c.di_arrtime[cur][r] = d.arrivalTime;
-        c.di_arrspeed[cur][r] = d.arrivalSpeed;
-        c.di_arrspeedbraking[cur][r] = d.arrivalSpeedBraking;
-        c.di_dist[cur][r] = d.distance;
-        c.di_accelv[cur][r] = d.accelV;
-        c.di_hadstopped[cur][r] = d.hadStoppedVehicle;
-        c.di_avail[cur][r] = d.availableSpace;
-        if (d.link >= 0) {
-            c.di_leavetime[cur][r] = link_getLeaveTime(c, d.link, d.arrivalTime, d.arrivalSpeed, di_getLeaveSpeed(d), e.length);
+        const size_t r = lf.at(i);
+        const int link = c.di_link[cur][r];
+        if (link >= 0) {
+            const SUMOTime arrivalTime = c.di_arrtime[cur][r];
             c.di_regspeed[cur][r] = e.speed;
             c.di_regwaiting[cur][r] = e.waiting;
-            c.di_veh[cur][r] = v;
-            c.di_next[cur][r] = atomic_exch(&c.link_app_head[cur][d.link], (int32_t)r);
+            AppRec a;
+            a.veh = c.di_request[cur][r] ? v : ~v;
+            a.arrtime = arrivalTime;
+            a.leavetime = link_getLeaveTime(c, link, arrivalTime, c.di_arrspeed[cur][r], lf.leaveSpeed(i), e.length);
+            a.arrspeedbraking = c.di_arrspeedbraking[cur][r];
+            a.next = atomic_exch(&c.link_app_head[cur][link], (int32_t)r);
+            c.ap_rec[cur][r] = a;
         }
     }
 }

@@ -93,6 +93,17 @@ enum { DSD_DEFAULT = 0, DSD_GIVEN = 1, DSD_GIVEN_VEHROUTE = 2, DSD_RANDOM = 3, D
 enum { DPD_DEFAULT = 0, DPD_GIVEN = 1, DPD_GIVEN_VEHROUTE = 2, DPD_RANDOM = 3, DPD_FREE = 4, DPD_BASE = 5, DPD_LAST = 6, DPD_RANDOM_FREE = 7 };
 enum { DLD_DEFAULT = 0, DLD_GIVEN = 1, DLD_FIRST_ALLOWED = 7 };
 
+// hot part of one approach record (MSLink::ApproachingVehicleInformation, MSLink.h:118-165): what MSLink::blockedAtTime needs to
+// dismiss a record, in ONE 32-byte sector (the scan of a foe link's approachers is the inner loop of MSLink::opened; with the
+// fields spread over separate arrays every record cost five sectors).  The remaining fields stay in the di_* arrays.
+struct AppRec {
+    int32_t next;            // next record of the link's list, -1 = end
+    int32_t veh;             // approaching vehicle; ~vehicle (negative) if the record has no request (willPass == false)
+    int64_t arrtime;         // arrivalTime
+    int64_t leavetime;       // leavingTime (MSLink::getLeaveTime at registration)
+    double arrspeedbraking;  // arrivalSpeedBraking
+};
+
 struct Ctx {
     // ---- options (MSGlobals) -------------------------------------------------------------
     double TS;                 // step length [s]
@@ -220,11 +231,9 @@ struct Ctx {
     double* di_vpass[2]; double* di_vwait[2]; double* di_arrspeed[2]; double* di_arrspeedbraking[2];
     double* di_dist[2]; double* di_accelv[2]; double* di_avail[2];
     SUMOTime* di_arrtime[2];
-    SUMOTime* di_leavetime[2];           // approach record: MSLink::getLeaveTime at registration
     double* di_regspeed[2];              // approach record: approaching->getSpeed() at registration
     SUMOTime* di_regwaiting[2];          // approach record: waiting time at registration
-    int32_t* di_next[2];                 // next record in the link's approach list
-    int32_t* di_veh[2];                  // approach record: the approaching vehicle (saves the reader a modulo and the veh_order lookup)
+    AppRec* ap_rec[2];                   // approach record (hot part) of every drive item with a link; list head: link_app_head
     int cur;                             // buffer written by this step's planMove
     // ---- departure queues (per departure lane, in load order) ----------------------------
     const int32_t* dq_begin; const int32_t* dq_veh; int32_t* dq_head;   // [nL+1], [nV], [nL]
