@@ -85,6 +85,10 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
         if (e->ks->ctx_size != sizeof(Ctx)) {
             throw std::runtime_error("sumob200: kernel set was built with a different Ctx layout");
         }
+    } catch (const std::invalid_argument& ex) {
+        gLastError = ex.what();
+        delete e;
+        return SUMOB200_EINVAL;
     } catch (const std::exception& ex) {
         gLastError = ex.what();
         delete e;
@@ -325,16 +329,24 @@ int sumob200_step_timed(sumob200_engine* e, int n_steps, sumob200_step_result* o
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     CUDA_TRY(cudaEventRecord(a, e->stream));
     const int rc = sumob200_step(e, n_steps, nullptr);
+    float ms = 0;
+    cudaError_t err = rc == 0 ? cudaEventRecord(b, e->stream) : cudaSuccess;
+    if (rc == 0 && err == cudaSuccess) {
+        err = cudaEventSynchronize(b);
+    }
+    if (rc == 0 && err == cudaSuccess) {
+        err = cudaEventElapsedTime(&ms, a, b);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
     if (rc != 0) {
         return rc;
     }
-    CUDA_TRY(cudaEventRecord(b, e->stream));
-    CUDA_TRY(cudaEventSynchronize(b));
-    float ms = 0;
-    CUDA_TRY(cudaEventElapsedTime(&ms, a, b));
+    if (err != cudaSuccess) {
+        gLastError = std::string("sumob200_step_timed: ") + cudaGetErrorString(err);
+        return SUMOB200_ECUDA;
+    }
     *elapsed_ms = ms;
-    cudaEventDestroy(a);
-    cudaEventDestroy(b);
     return sumob200_step(e, 0, out);
 }
 

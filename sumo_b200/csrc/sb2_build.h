@@ -80,7 +80,114 @@ public:
         return out;
     }
 
+    // ---- the arrays come from outside the library (C ABI): every index and every CSR offset array is range-checked before
+    // anything is uploaded; a malformed array is std::invalid_argument (SUMOB200_EINVAL), never an out-of-bounds device access
+    static void checkIndex(const FlatFile& ff, const char* name, int64_t lo, int64_t hi) {
+        if (!ff.has(name)) {
+            return;
+        }
+        const FlatArray& a = ff.get(name);
+        if (a.elemSize != 4) {
+            throw std::invalid_argument(std::string("flat array '") + name + "' must be int32");
+        }
+        const int32_t* p = a.as<int32_t>();
+        for (uint64_t i = 0; i < a.count; i++) {
+            if (p[i] < lo || p[i] >= hi) {
+                throw std::invalid_argument(std::string("flat array '") + name + "': element " + std::to_string(i) + " = " + std::to_string(p[i]) +
+                                            " is outside [" + std::to_string(lo) + ", " + std::to_string(hi) + ")");
+            }
+        }
+    }
+    static void checkCsr(const FlatFile& ff, const char* name, uint64_t rows, uint64_t payload) {
+        const FlatArray& a = ff.get(name);
+        if (a.elemSize != 4 || a.count != rows + 1) {
+            throw std::invalid_argument(std::string("flat array '") + name + "' must have " + std::to_string(rows + 1) + " int32 offsets");
+        }
+        const int32_t* p = a.as<int32_t>();
+        if (p[0] != 0 || (uint64_t)p[rows] != payload) {
+            throw std::invalid_argument(std::string("flat array '") + name + "': offsets must run from 0 to " + std::to_string(payload));
+        }
+        for (uint64_t i = 0; i < rows; i++) {
+            if (p[i] > p[i + 1]) {
+                throw std::invalid_argument(std::string("flat array '") + name + "': offsets are not monotonic at " + std::to_string(i));
+            }
+        }
+    }
+    static void validate(const FlatFile& ff) {
+        const int64_t nL = (int64_t)ff.count("lane_length"), nE = (int64_t)ff.count("edge_flags"), nK = (int64_t)ff.count("link_from");
+        const int64_t nV = (int64_t)ff.count("veh_type"), nT = (int64_t)ff.count("vt_length"), nTL = (int64_t)ff.count("tl_cur_phase");
+        const int64_t nR = (int64_t)ff.count("route_begin") - 1, nPh = (int64_t)ff.count("phase_dur");
+        const int64_t nJ = 1 + nL;   // junction indices are only compared with each other
+        for (const char* per_lane : {"lane_speed", "lane_edge", "lane_flags", "lane_pred_logical", "lane_pred_normal", "lane_entry_link", "lane_to_junction", "lane_from_junction", "lane_geomfactor"}) {
+            if ((int64_t)ff.count(per_lane) != nL) {
+                throw std::invalid_argument(std::string("flat array '") + per_lane + "' must have one element per lane");
+            }
+        }
+        for (const char* per_link : {"link_to", "link_via", "link_state", "link_dir", "link_length", "link_foevis", "link_radius", "link_flags", "link_index", "link_tl",
+                                     "link_internal_before", "link_junction", "link_entry", "link_exit"}) {
+            if ((int64_t)ff.count(per_link) != nK) {
+                throw std::invalid_argument(std::string("flat array '") + per_link + "' must have one element per link");
+            }
+        }
+        if ((int64_t)ff.count("link_response") != 4 * nK) {
+            throw std::invalid_argument("flat array 'link_response' must have 4 words per link");
+        }
+        for (const char* per_veh : {"veh_route", "veh_numid", "veh_idrank", "veh_depart", "veh_speedfactor", "veh_arrivalpos", "veh_departpos", "veh_departpos_proc",
+                                    "veh_departspeed", "veh_departspeed_proc", "veh_departlane", "veh_departlane_proc"}) {
+            if ((int64_t)ff.count(per_veh) != nV) {
+                throw std::invalid_argument(std::string("flat array '") + per_veh + "' must have one element per vehicle");
+            }
+        }
+        checkCsr(ff, "edge_lane_begin", (uint64_t)nE, (uint64_t)nL);
+        checkCsr(ff, "lane_link_begin", (uint64_t)nL, (uint64_t)nK);
+        checkCsr(ff, "lane_inc_begin", (uint64_t)nL, ff.count("inc_lane"));
+        checkCsr(ff, "lane_shape_begin", (uint64_t)nL, ff.count("shape_xy") / 2);
+        checkCsr(ff, "link_foelink_begin", (uint64_t)nK, ff.count("foelink"));
+        checkCsr(ff, "link_foelane_begin", (uint64_t)nK, ff.count("foelane"));
+        checkCsr(ff, "route_begin", (uint64_t)nR, ff.count("route_edges"));
+        checkCsr(ff, "tl_phase_begin", (uint64_t)nTL, (uint64_t)nPh);
+        checkCsr(ff, "phase_state_begin", (uint64_t)nPh, ff.count("phase_states"));
+        checkCsr(ff, "tl_link_begin", (uint64_t)nTL, ff.count("tllink_link"));
+        if (ff.count("inc_link") != ff.count("inc_lane") || ff.count("inc_length") != ff.count("inc_lane") || ff.count("tllink_index") != ff.count("tllink_link")
+                || ff.count("conf_lbc") != ff.count("foelane") || ff.count("conf_size") != ff.count("foelane") || ff.count("conf_flag") != ff.count("foelane")
+                || ff.count("conf_foeidx") != ff.count("foelane")) {
+            throw std::invalid_argument("flat arrays: payload arrays of one CSR structure differ in length");
+        }
+        checkIndex(ff, "lane_edge", 0, nE);
+        checkIndex(ff, "lane_pred_logical", -1, nL); checkIndex(ff, "lane_pred_normal", -1, nL); checkIndex(ff, "lane_entry_link", -1, nK);
+        checkIndex(ff, "lane_to_junction", -1, nJ); checkIndex(ff, "lane_from_junction", -1, nJ);
+        checkIndex(ff, "inc_lane", 0, nL); checkIndex(ff, "inc_link", 0, nK);
+        checkIndex(ff, "link_from", 0, nL); checkIndex(ff, "link_to", 0, nL); checkIndex(ff, "link_via", -1, nL);
+        checkIndex(ff, "link_internal_before", -1, nL); checkIndex(ff, "link_entry", -1, nK); checkIndex(ff, "link_exit", -1, nK);
+        checkIndex(ff, "link_tl", -1, nTL); checkIndex(ff, "link_index", -1, 256); checkIndex(ff, "link_junction", -1, nJ);
+        checkIndex(ff, "foelink", 0, nK); checkIndex(ff, "foelane", 0, nL); checkIndex(ff, "conf_foeidx", -1, 1 << 20);
+        checkIndex(ff, "tllink_link", 0, nK); checkIndex(ff, "tl_cur_phase", 0, nPh > 0 ? nPh : 1);
+        checkIndex(ff, "route_edges", 0, nE);
+        checkIndex(ff, "veh_type", 0, nT); checkIndex(ff, "veh_route", 0, nR);
+        {
+            // a traffic light's current phase and the state index of every controlled link must lie inside its own program
+            const int32_t* pb = ff.ptr<int32_t>("tl_phase_begin");
+            const int32_t* cur = ff.ptr<int32_t>("tl_cur_phase");
+            const int32_t* sb = ff.ptr<int32_t>("phase_state_begin");
+            const int32_t* lb = ff.ptr<int32_t>("tl_link_begin");
+            const int32_t* li = ff.ptr<int32_t>("tllink_index");
+            for (int64_t t = 0; t < nTL; t++) {
+                if (pb[t + 1] > pb[t] && cur[t] >= pb[t + 1] - pb[t]) {
+                    throw std::invalid_argument("flat array 'tl_cur_phase': phase index outside the program");
+                }
+                for (int ph = pb[t]; ph < pb[t + 1]; ph++) {
+                    for (int i = lb[t]; i < lb[t + 1]; i++) {
+                        if (li[i] < 0 || li[i] >= sb[ph + 1] - sb[ph]) {
+                            throw std::invalid_argument("flat array 'tllink_index': state index outside the phase's state string");
+                        }
+                    }
+                }
+            }
+        }
+    }
+
     void build(const FlatFile& ff) {
+        validate(ff);
         // ---------------- options
         h.DELTA_T = ff.scalar<int64_t>("opt_delta_t", 1000);
         h.TS = (double)h.DELTA_T / 1000.;

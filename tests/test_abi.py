@@ -65,3 +65,30 @@ def test_unsupported_scenarios_are_refused_at_load(tmp_path):
     sc["lane_flags"] = base["lane_flags"] | 8   # LF_LANECHANGER: an edge with several lanes
     with pytest.raises(SumoB200Error):
         Engine(sc)
+
+
+def test_malformed_arrays_are_einval(tmp_path):
+    """the C ABI range-checks every index array and every CSR offset array it is handed (Model::validate): a malformed scenario
+    is SUMOB200_EINVAL with a message naming the array, before any device memory is touched"""
+    from sumo_b200.engine import Engine, SumoB200Error
+    from sumo_b200.flatfile import load_flat
+    base = load_flat(os.path.join(ROOT, "tests", "golden", "grid3_small.golden.flat"))
+    bad = []
+    for name, edit in (("link_to", lambda a: a.__setitem__(3, len(base["lane_length"]) + 5)),
+                       ("route_edges", lambda a: a.__setitem__(0, -7)),
+                       ("veh_type", lambda a: a.__setitem__(0, 99)),
+                       ("lane_link_begin", lambda a: a.__setitem__(2, a[3] + 1)),
+                       ("foelane", lambda a: a.__setitem__(0, 1 << 30)),
+                       ("tllink_link", lambda a: a.__setitem__(0, -1) if len(a) else None),
+                       ("veh_route", lambda a: a.__setitem__(1, len(base["route_begin"])))):
+        sc = dict(base)
+        arr = base[name].copy()
+        if len(arr) == 0:
+            continue
+        edit(arr)
+        sc[name] = arr
+        with pytest.raises(SumoB200Error) as ei:
+            Engine(sc)
+        assert "(-1)" in str(ei.value) and name in str(ei.value), str(ei.value)
+        bad.append(name)
+    assert len(bad) >= 5
