@@ -260,7 +260,8 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     }
     CUDA_TRY(cudaSetDevice(e->device));
     Ctx& c = e->d;
-    const int nPre = c.nL > c.nK ? (c.nL > c.nTL ? c.nL : c.nTL) : (c.nK > c.nTL ? c.nK : c.nTL);
+    const int nLv = c.lane_hi - c.lane_lo, nKv = c.link_hi - c.link_lo;   // visible lanes / links (everything unless partitioned)
+    const int nPre = nLv > nKv ? (nLv > c.nTL ? nLv : c.nTL) : (nKv > c.nTL ? nKv : c.nTL);
     cudaStream_t s = e->stream;
     for (int i = 0; i < n_steps; i++) {
         const bool prof = e->profiling;
@@ -270,13 +271,13 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         if (prof) { cudaEventRecord(e->ev[1], s); }
         e->ks->plan(&e->d, c.nV, s);
         if (prof) { cudaEventRecord(e->ev[2], s); }
-        CUDA_TRY(cudaMemsetAsync(c.lane_npartial, 0, sizeof(int32_t) * (size_t)c.nL, s));
+        CUDA_TRY(cudaMemsetAsync(c.lane_npartial + c.lane_lo, 0, sizeof(int32_t) * (size_t)nLv, s));
         e->ks->execute(&e->d, c.nV, s);
         if (prof) { cudaEventRecord(e->ev[3], s); }
-        e->ks->remove(&e->d, c.nL, s);
-        e->ks->integrate(&e->d, c.nL, s);
+        e->ks->remove(&e->d, nLv, s);
+        e->ks->integrate(&e->d, nLv, s);
         if (prof) { cudaEventRecord(e->ev[4], s); }
-        e->ks->insert(&e->d, c.nL, s);
+        e->ks->insert(&e->d, nLv, s);
         e->ks->count(&e->d, c.nV, e->dUpdates, s);
         if (prof) {
             cudaEventRecord(e->ev[5], s);
@@ -470,6 +471,23 @@ int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const in
         return SUMOB200_ECUDA;
     }
     e->d.lane_vis = e->dLaneVis;
+    {
+        int lo = nL, hi = 0;
+        for (int l = 0; l < nL; l++) {
+            if (lane_vis[l] != LV_NONE) {
+                lo = l < lo ? l : lo;
+                hi = l + 1;
+            }
+        }
+        if (lo >= hi) {
+            lo = 0;
+            hi = 0;
+        }
+        e->d.lane_lo = lo;
+        e->d.lane_hi = hi;
+        e->d.link_lo = e->model.h.lane_link_begin[lo];
+        e->d.link_hi = e->model.h.lane_link_begin[hi];
+    }
     for (int side = 0; side < 2; side++) {
         sb2::HaloSide& h = e->halo[side];
         int32_t* dExp = nullptr;

@@ -69,10 +69,12 @@ __global__ void k_reset(const __grid_constant__ Ctx c) {
 }
 
 __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < c.nTL) {
-        tls_advance(c, i);
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid < c.nTL) {
+        tls_advance(c, tid);
     }
+    // thread tid also handles lane lane_lo + tid and link link_lo + tid (the partition's visible range, sb2_types.h)
+    const int i = tid < c.lane_hi - c.lane_lo ? c.lane_lo + tid : c.nL;
     // lane-ordered work list: block-wide exclusive scan of the lanes' vehicle counts, one atomic per block for the base.
     // The list has two segments: [0, counters[7]) filled forwards and [nV - counters[3], nV) filled from the end backwards.
     // Default split: lanes whose first link is red/yellow go to the second segment (measured on B200, 1M vehicles on the
@@ -185,11 +187,11 @@ __global__ void __launch_bounds__(BLOCK) k_pre(const __grid_constant__ Ctx c) {
         }
     }
 #endif
-    if (i < c.nK) {
-        c.link_app_head[c.cur][i] = -1;
+    if (tid < c.link_hi - c.link_lo) {
+        c.link_app_head[c.cur][c.link_lo + tid] = -1;
     }
-    if (i < 3) {
-        c.fleet[i] = c.fleet_next[i];
+    if (tid < 3) {
+        c.fleet[tid] = c.fleet_next[tid];
     }
 }
 
@@ -238,30 +240,30 @@ __global__ void __launch_bounds__(256) k_execute2(const __grid_constant__ Ctx c)
 }
 
 __global__ void __launch_bounds__(BLOCK) k_remove(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && lane_simulated(c, l)) {
+    const int l = c.lane_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.lane_hi && lane_simulated(c, l)) {
         lane_handoff_remove(c, l);
     }
 }
 
 __global__ void __launch_bounds__(BLOCK) k_integrate(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && lane_simulated(c, l)) {
+    const int l = c.lane_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.lane_hi && lane_simulated(c, l)) {
         lane_handoff_integrate(c, l);
     }
 }
 
 // MSEdgeControl::detectCollisions(STAGE_MOVEMENTS): a collider is teleported (collision.action teleport, the default)
 __global__ void __launch_bounds__(BLOCK) k_collide(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && lane_simulated(c, l)) {
+    const int l = c.lane_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.lane_hi && lane_simulated(c, l)) {
         lane_detect_collisions(c, l);
     }
 }
 
 __global__ void __launch_bounds__(BLOCK) k_partials(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && lane_simulated(c, l)) {
+    const int l = c.lane_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.lane_hi && lane_simulated(c, l)) {
         lane_sort_partials(c, l);
     }
 }
@@ -274,8 +276,8 @@ __global__ void k_transfer(const __grid_constant__ Ctx c) {
 }
 
 __global__ void __launch_bounds__(BLOCK) k_insert(const __grid_constant__ Ctx c) {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l < c.nL && c.dq_head[l] < c.dq_begin[l + 1] && lane_simulated(c, l)) {
+    const int l = c.lane_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.lane_hi && c.dq_head[l] < c.dq_begin[l + 1] && lane_simulated(c, l)) {
         lane_insertVehicles(c, l);
     }
 }

@@ -218,6 +218,7 @@ public:
         h.nT = (int)ff.count("vt_length");
         h.nTL = (int)ff.count("tl_cur_phase");
         const int nL = h.nL, nK = h.nK, nV = h.nV, nT = h.nT;
+        h.lane_lo = 0; h.lane_hi = nL; h.link_lo = 0; h.link_hi = nK;
         if (ff.has("lane_names") && ff.has("veh_names")) {   // ids are only needed for diagnostics and output writers
             lane_names = names(ff, "lane");
             veh_names = names(ff, "veh");

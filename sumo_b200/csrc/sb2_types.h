@@ -216,6 +216,9 @@ struct Ctx {
     //   LV_HALO  lanes of the neighbour's second column: not simulated, only read (state received at the end of every step)
     //   LV_NONE  everything further away: never touched
     const uint8_t* lane_vis;
+    // the visible lanes / links of a partition form one index range (lanes are numbered junction block by junction block, column by
+    // column): the per-lane kernels are launched over [lane_lo, lane_hi) only.  One partition: the whole network.
+    int lane_lo, lane_hi, link_lo, link_hi;
     // lane-ordered work list of this step: the vehicles on the road, lane by lane, front -> back (rebuilt by k_pre).
     // k_plan / k_execute give thread i the vehicle veh_order[i], so the 32 threads of a warp work on the same or on
     // neighbouring lanes, see the same links and foes and take the same branches.  Two segments: [0, counters[7]) = lanes whose

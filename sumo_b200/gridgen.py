@@ -371,6 +371,17 @@ def make_demand(g, n_vehicles, route_edges, depart_end_s, seed=42, sigma=None, s
         g["veh_idrank"] = _decimal_string_rank(n_vehicles)
     if sigma is not None:
         g["vt_sigma"] = np.full(g["vt_sigma"].shape, float(sigma))
+    # slot order: by departure lane, then departure time.  The slot is only the index of the vehicle's state in HBM (identity =
+    # veh_numid / veh_idrank, both kept); vehicles that start on the same lane drive near each other for a long time, so their state
+    # shares sectors, and in a partitioned run the slots a rank touches are (initially) one contiguous range instead of every N-th.
+    # Per departure lane the order stays the load order, which is all MSInsertionControl's semantics need (sb2_build.h dq_*).
+    perm = np.argsort(routes[:, 0], kind="stable")
+    for k in list(g):
+        if k.startswith("veh_") and k not in ("veh_names", "veh_name_begin") and len(g[k]) == n_vehicles:
+            g[k] = g[k][perm]
+    if names:
+        vn = [vn[i] for i in perm]
+        g["veh_name_begin"], g["veh_names"] = _pack_names(vn)
     return g
 
 
@@ -398,7 +409,8 @@ def write_routes_xml(g, path, vtype_attrs='sigma="0.5"'):
     re_ = g["route_edges"]
     with open(path, "w") as f:
         f.write('<routes>\n    <vType id="car" %s/>\n' % vtype_attrs)
-        for v in range(len(g["veh_type"])):
+        for v in np.argsort(g["veh_numid"], kind="stable"):      # load order = departure order (the slots are sorted by lane)
+            r = g["veh_route"][v]
             f.write('    <vehicle id="v%d" type="car" depart="%.3f"><route edges="%s"/></vehicle>\n' % (
-                v, g["veh_depart"][v] / 1000., " ".join(en[e] for e in re_[rb[v]:rb[v + 1]])))
+                g["veh_numid"][v], g["veh_depart"][v] / 1000., " ".join(en[e] for e in re_[rb[r]:rb[r + 1]])))
         f.write("</routes>\n")
