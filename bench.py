@@ -268,6 +268,7 @@ def main():
     ap.add_argument("--replicas", action="store_true", help="N > 1: every rank simulates its own copy of the network instead of a strip of one network")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the N = 1 network (strong scaling) instead of growing it with N")
     ap.add_argument("--emissions", action="store_true", help="every vehicle carries the HBEFA emission device (BASELINE.json configs[4] flavour)")
+    ap.add_argument("--reslot", type=int, default=32, help="single GPU: renumber the on-road vehicles in lane order every this many steps (0 = never)")
     ap.add_argument("--xml", action="store_true", help="also time the e2e loop with the FCD rows formatted as XML on the host threads")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -297,6 +298,7 @@ def main():
         eng = PartitionedEngine(scenario, dist, rank, world, device=local_rank)
     else:
         eng = Engine(scenario, device=local_rank)
+        eng.set_reslot_period(args.reslot)
     del scenario
     nV = eng.num_vehicles
     eng.step(SPINUP_STEPS, result=False)

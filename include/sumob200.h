@@ -212,6 +212,11 @@ int64_t sumob200_kernel_launches(const sumob200_engine* e);
  * since the last call with reset != 0.  phases: 0 pre (tls, lane summary) 1 plan 2 execute 3 hand-off 4 insert */
 int sumob200_phase_times(sumob200_engine* e, double* ms, int n_phases, int reset);
 int sumob200_set_profiling(sumob200_engine* e, int enabled);
+/* memory layout tuning: every `steps` steps (0 = never, the default) the engine renumbers the on-road vehicles in lane order, so
+ * that vehicles that are neighbours on the road are neighbours in HBM.  Results are unchanged; the vehicle indices of this API
+ * ("slot") stay the load-order indices.  With it on, sumob200_fcd_* rows come in memory order instead of slot order.  Ignored in
+ * partitioned runs (all ranks share one numbering). */
+int sumob200_set_reslot_period(sumob200_engine* e, int steps);
 
 const char* sumob200_last_error(void);
 const char* sumob200_version(void);

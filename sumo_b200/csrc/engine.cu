@@ -36,6 +36,14 @@ namespace {
 
 thread_local std::string gLastError;
 
+// dst[i] = src[oldOfNew[i]] for one per-vehicle array (re-slotting)
+template<class T> __global__ void __launch_bounds__(256) k_permute(T* __restrict__ dst, const T* __restrict__ src, const int32_t* __restrict__ oldOfNew, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        dst[i] = src[oldOfNew[i]];
+    }
+}
+
 #define CUDA_TRY(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { \
         gLastError = std::string(#call) + ": " + cudaGetErrorString(_e); return SUMOB200_ECUDA; } } while (0)
 
@@ -68,6 +76,11 @@ struct sumob200_engine {
     uint8_t* dImpMask[2] = {nullptr, nullptr};
     std::vector<void*> haloAlloc;
     bool partitioned = false;
+    // re-slotting: every reslotPeriod steps the on-road vehicles are renumbered in lane order (0 = never)
+    int reslotPeriod = 0;
+    long long reslots = 0;
+    int32_t* rsScratch = nullptr;   // blocksA, blocksB, order, sorted, newOfOld, oldOfNew
+    void* rsTmp = nullptr;          // one permuted array (16 B per vehicle)
     int64_t launches = 0;
     bool profiling = false;
     cudaEvent_t ev[6];
@@ -153,6 +166,66 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
 
 inline int gridOf(const sumob200_engine* e, int n) { return n > 0 ? (n + e->ks->block - 1) / e->ks->block : 1; }
 
+// Re-slotting: renumber the on-road vehicles in (lane, front -> back) order so that vehicles that are neighbours on the road are
+// neighbours in HBM (the per-vehicle kernels walk the lane-ordered work list: their state gathers become nearly coalesced).
+// Every per-vehicle array -- static and dynamic alike, so no kernel needs an extra indirection -- is permuted, every stored slot
+// number follows; veh_ext / ext2slot keep the external (load-order) index the C ABI speaks.  Nothing in the step depends on the
+// slot number (ties are broken by numerical id / id rank, random draws are keyed by the external index): results are unchanged.
+int reslot(sumob200_engine* e) {
+    Ctx& c = e->d;
+    const int nV = c.nV, nL = c.nL;
+    const int nbL = gridOf(e, nL), nbV = gridOf(e, nV);
+    cudaStream_t s = e->stream;
+    if (e->rsScratch == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->rsScratch, sizeof(int32_t) * ((size_t)nbL + nbV + 4 + 4 * (size_t)(nV > 0 ? nV : 1))));
+        CUDA_TRY(cudaMalloc(&e->rsTmp, 16 * (size_t)(nV > 0 ? nV : 1)));
+    }
+    int32_t* blocksA = e->rsScratch;
+    int32_t* blocksB = blocksA + nbL + 2;
+    int32_t* order = blocksB + nbV + 2;
+    int32_t* sorted = order + nV;
+    int32_t* newOfOld = sorted + nV;
+    int32_t* oldOfNew = newOfOld + nV;
+    e->launches += e->ks->reslot_maps(&e->d, nL, nV, blocksA, blocksB, order, sorted, newOfOld, oldOfNew, s);
+    const int nb = (nV + 255) / 256;
+    for (size_t i = 0; i < e->model.buffers.size(); i++) {
+        const Buffer* b = e->model.buffers[i];
+        if (b->name.compare(0, 4, "veh_") != 0 || b->name == "veh_order" || b->name == "veh_ndi") {
+            continue;
+        }
+        char* base = static_cast<char*>(e->dev[i]);
+        size_t rows = 1, bytes = b->elem;
+        if (b->count == (size_t)nV) {
+            // one element per vehicle
+        } else if (b->name == "veh_further" && b->count == (size_t)nV * MAX_FURTHER) {
+            bytes = b->elem * MAX_FURTHER;          // vehicle-major rows
+        } else if (b->name == "veh_em" && b->count == (size_t)nV * 7) {
+            rows = 7;                               // pollutant-major: seven arrays of nV
+        } else {
+            continue;                               // (veh_em of a scenario without emission devices: one dummy element)
+        }
+        for (size_t r = 0; r < rows; r++) {
+            char* a = base + r * (size_t)nV * bytes;
+            switch (bytes) {
+                case 1: k_permute<uint8_t><<<nb, 256, 0, s>>>(static_cast<uint8_t*>(e->rsTmp), reinterpret_cast<const uint8_t*>(a), oldOfNew, nV); break;
+                case 4: k_permute<int32_t><<<nb, 256, 0, s>>>(static_cast<int32_t*>(e->rsTmp), reinterpret_cast<const int32_t*>(a), oldOfNew, nV); break;
+                case 8: k_permute<int64_t><<<nb, 256, 0, s>>>(static_cast<int64_t*>(e->rsTmp), reinterpret_cast<const int64_t*>(a), oldOfNew, nV); break;
+                case 16: k_permute<int4><<<nb, 256, 0, s>>>(static_cast<int4*>(e->rsTmp), reinterpret_cast<const int4*>(a), oldOfNew, nV); break;
+                default:
+                    gLastError = "reslot: unexpected element size of " + b->name;
+                    return SUMOB200_EINVAL;
+            }
+            CUDA_TRY(cudaMemcpyAsync(a, e->rsTmp, (size_t)nV * bytes, cudaMemcpyDeviceToDevice, s));
+            e->launches += 1;
+        }
+    }
+    // the approach table the next step reads is the one the last step wrote: buffer cur ^ 1 (cur was flipped at the end of the step)
+    e->launches += e->ks->reslot_remap(&e->d, nL, nV, newOfOld, c.cur ^ 1, s);
+    e->reslots++;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
 template<class T> int uploadArray(sumob200_engine* e, const T* host, size_t n, T** dev) {
     CUDA_TRY(cudaMalloc(dev, sizeof(T) * (n > 0 ? n : 1)));
     e->haloAlloc.push_back(*dev);
@@ -221,6 +294,10 @@ void sumob200_destroy(sumob200_engine* e) {
     }
     if (e->dUpdates != nullptr) {
         cudaFree(e->dUpdates);
+    }
+    if (e->rsScratch != nullptr) {
+        cudaFree(e->rsScratch);
+        cudaFree(e->rsTmp);
     }
     if (e->dSummary != nullptr) {
         cudaFree(e->dSummary);
@@ -292,6 +369,12 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         c.t += c.DELTA_T;
         c.cur ^= 1;
         e->stepsDone++;
+        if (e->reslotPeriod > 0 && !e->partitioned && e->stepsDone % e->reslotPeriod == 0) {
+            const int rc = reslot(e);
+            if (rc != 0) {
+                return rc;
+            }
+        }
     }
     CUDA_TRY(cudaGetLastError());
     if (out != nullptr) {
@@ -439,6 +522,20 @@ int sumob200_emissions(sumob200_engine* e, double* out, int64_t capacity) {
     CUDA_TRY(cudaSetDevice(e->device));
     CUDA_TRY(cudaMemcpyAsync(out, e->d.veh_em, sizeof(double) * 7 * (size_t)e->d.nV, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (e->reslots > 0) {
+        // the device array is in memory (slot) order: hand it out in load order like everything else of this API
+        const size_t nV = (size_t)e->d.nV;
+        std::vector<int32_t> ext(nV);
+        std::vector<double> tmp(nV);
+        CUDA_TRY(cudaMemcpy(ext.data(), e->d.veh_ext, sizeof(int32_t) * nV, cudaMemcpyDeviceToHost));
+        for (int p = 0; p < 7; p++) {
+            double* row = out + (size_t)p * nV;
+            for (size_t v = 0; v < nV; v++) {
+                tmp[ext[v]] = row[v];
+            }
+            memcpy(row, tmp.data(), sizeof(double) * nV);
+        }
+    }
     return 0;
 }
 
@@ -656,6 +753,15 @@ int sumob200_set_random_mode(sumob200_engine* e, int mode) {
         return SUMOB200_EINVAL;
     }
     e->d.rng_mode = mode;
+    return 0;
+}
+
+int sumob200_set_reslot_period(sumob200_engine* e, int steps) {
+    if (e == nullptr || steps < 0) {
+        gLastError = "sumob200_set_reslot_period: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    e->reslotPeriod = steps;
     return 0;
 }
 

@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(BLOCK) k_fcd_write(const __grid_constant__ Ctx
         const int at = base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1u));
         const Pos2 p = veh_position(c, v);
         sumob200_fcd_row r;
-        r.slot = v;
+        r.slot = c.veh_ext[v];
         r.lane = c.veh_lane[v];
         r.pos = c.veh_pos[v];
         r.speed = c.veh_speed[v];
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(BLOCK) k_tripinfo(const __grid_constant__ Ctx 
         r.arrival_speed = c.veh_speed[v];
         r.route_length = c.veh_trip_routelen[v] + (arrived ? c.veh_arrivalpos[v] : (departed ? c.veh_pos[v] : 0.));
         r.speed_factor = c.veh_speedfactor[v];
-        out[v] = r;
+        out[c.veh_ext[v]] = r;
     }
 }
 
@@ -463,7 +463,7 @@ __global__ void k_tls_set_phase(const __grid_constant__ Ctx c, int tl, int phase
 __global__ void k_set_speed(const __grid_constant__ Ctx c, const int32_t* slots, const double* speeds, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && slots[i] >= 0 && slots[i] < c.nV) {
-        c.veh_traci_speed[slots[i]] = speeds[i] >= 0. ? speeds[i] : -1.;
+        c.veh_traci_speed[c.ext2slot[slots[i]]] = speeds[i] >= 0. ? speeds[i] : -1.;
     }
 }
 
@@ -475,7 +475,7 @@ __global__ void k_mirror(const __grid_constant__ Ctx c, sumob200_vehicle_state* 
         s.route_pos = c.veh_routepos[v];
         s.pos = c.veh_pos[v];
         s.speed = c.veh_speed[v];
-        out[v] = s;
+        out[c.veh_ext[v]] = s;
     }
 }
 
@@ -506,6 +506,126 @@ __global__ void __launch_bounds__(BLOCK) k_halo_unpack(const __grid_constant__ C
         halo_unpack_lane(c, msg, i);
     }
     halo_unpack_vehicle(c, msg, i);
+}
+
+// ---- re-slotting (engine.cu reslot): renumber the on-road vehicles in lane order ------------------------------------------------
+// per block of lanes: number of vehicles on them
+__global__ void __launch_bounds__(BLOCK) k_rs_lanecount(const __grid_constant__ Ctx c, int32_t* blockCount) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    int n = l < c.nL ? c.lane_nveh[l] : 0;
+    for (int d = 16; d > 0; d >>= 1) {
+        n += __shfl_down_sync(0xffffffffu, n, d);
+    }
+    __shared__ int w[BLOCK / 32];
+    if ((threadIdx.x & 31) == 0) {
+        w[threadIdx.x >> 5] = n;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int i = 0; i < BLOCK / 32; i++) {
+            t += w[i];
+        }
+        blockCount[blockIdx.x] = t;
+    }
+}
+// order[j] = the j-th vehicle in (lane index, front -> back) order; blockBase = exclusive scan of k_rs_lanecount's counts
+__global__ void __launch_bounds__(BLOCK) k_rs_laneorder(const __grid_constant__ Ctx c, const int32_t* blockBase, int32_t* order) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = l < c.nL ? c.lane_nveh[l] : 0;
+    int incl = n;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((threadIdx.x & 31) >= d) {
+            incl += o;
+        }
+    }
+    __shared__ int w[BLOCK / 32];
+    if ((threadIdx.x & 31) == 31) {
+        w[threadIdx.x >> 5] = incl;
+    }
+    __syncthreads();
+    int base = blockBase[blockIdx.x] + incl - n;
+    for (int i = 0; i < (int)(threadIdx.x >> 5); i++) {
+        base += w[i];
+    }
+    if (l < c.nL) {
+        for (int v = c.lane_first[l]; v >= 0; v = c.veh_behind[v]) {
+            order[base++] = v;
+        }
+    }
+}
+// slots of the on-road vehicles, ascending (compaction; blockBase = exclusive scan of k_fcd_count-style counts)
+__global__ void __launch_bounds__(BLOCK) k_rs_slotcount(const __grid_constant__ Ctx c, int32_t* blockCount) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = __syncthreads_count(v < c.nV && c.veh_lane[v] >= 0);
+    if (threadIdx.x == 0) {
+        blockCount[blockIdx.x] = n;
+    }
+}
+__global__ void __launch_bounds__(BLOCK) k_rs_slotlist(const __grid_constant__ Ctx c, const int32_t* blockBase, int32_t* sorted) {
+    __shared__ int warpBase[BLOCK / 32];
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool on = v < c.nV && c.veh_lane[v] >= 0;
+    const unsigned mask = __ballot_sync(0xffffffffu, on);
+    if ((threadIdx.x & 31) == 0) {
+        warpBase[threadIdx.x >> 5] = __popc(mask);
+    }
+    __syncthreads();
+    int base = blockBase[blockIdx.x];
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
+        base += warpBase[w];
+    }
+    if (on) {
+        sorted[base + __popc(mask & ((1u << (threadIdx.x & 31)) - 1u))] = v;
+    }
+}
+// the permutation: the j-th vehicle in lane order gets the j-th smallest on-road slot
+__global__ void __launch_bounds__(BLOCK) k_rs_identity(int32_t* newOfOld, int32_t* oldOfNew, int n) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) {
+        newOfOld[v] = v;
+        oldOfNew[v] = v;
+    }
+}
+__global__ void __launch_bounds__(BLOCK) k_rs_maps(const int32_t* order, const int32_t* sorted, const int32_t* count, int32_t* newOfOld, int32_t* oldOfNew) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < *count) {
+        newOfOld[order[j]] = sorted[j];
+        oldOfNew[sorted[j]] = order[j];
+    }
+}
+// after the per-vehicle arrays have been permuted: every stored slot number follows
+__global__ void __launch_bounds__(BLOCK) k_rs_remap(const __grid_constant__ Ctx c, const int32_t* newOfOld, int appBuf) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (size_t)c.nV) {
+        const int a = c.veh_ahead[i], b = c.veh_behind[i];
+        if (a >= 0) {
+            c.veh_ahead[i] = newOfOld[a];
+        }
+        if (b >= 0) {
+            c.veh_behind[i] = newOfOld[b];
+        }
+        c.ext2slot[c.veh_ext[i]] = (int32_t)i;
+    }
+    if (i < (size_t)c.nL) {
+        if (c.lane_first[i] >= 0) {
+            c.lane_first[i] = newOfOld[c.lane_first[i]];
+            c.lane_last[i] = newOfOld[c.lane_last[i]];
+        }
+        for (int k = 0; k < c.lane_npartial[i] && k < MAX_PARTIAL; k++) {
+            c.lane_partial[i * MAX_PARTIAL + k] = newOfOld[c.lane_partial[i * MAX_PARTIAL + k]];
+        }
+    }
+    if (i < (size_t)c.nV * MAX_DRIVE_ITEMS) {
+        // the approach table the next planMove reads (records of unused items hold stale but valid slot numbers)
+        const int v = c.ap_rec[appBuf][i].veh;
+        const int dec = v < 0 ? ~v : v;
+        if (dec >= 0 && dec < c.nV) {
+            const int nw = newOfOld[dec];
+            c.ap_rec[appBuf][i].veh = v < 0 ? ~nw : nw;
+        }
+    }
 }
 
 inline int grid(int n) { return n > 0 ? (n + BLOCK - 1) / BLOCK : 1; }
@@ -553,7 +673,26 @@ int l_halo_unpack(const void* c, const void* side, const void* msg, cudaStream_t
     return 2;
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack};
+// renumber the on-road vehicles in lane order: fills newOfOld / oldOfNew (scratch: blocks >= grid(nL) + grid(nV) + 2 ints, order / sorted nV ints)
+int l_reslot_maps(const void* c, int nL, int nV, int32_t* blocksA, int32_t* blocksB, int32_t* order, int32_t* sorted, int32_t* newOfOld, int32_t* oldOfNew, cudaStream_t s) {
+    const int nbL = grid(nL), nbV = grid(nV);
+    k_rs_lanecount<<<nbL, BLOCK, 0, s>>>(ctx(c), blocksA);
+    k_fcd_scan<<<1, 1024, 0, s>>>(blocksA, nbL);
+    k_rs_laneorder<<<nbL, BLOCK, 0, s>>>(ctx(c), blocksA, order);
+    k_rs_slotcount<<<nbV, BLOCK, 0, s>>>(ctx(c), blocksB);
+    k_fcd_scan<<<1, 1024, 0, s>>>(blocksB, nbV);
+    k_rs_slotlist<<<nbV, BLOCK, 0, s>>>(ctx(c), blocksB, sorted);
+    k_rs_identity<<<nbV, BLOCK, 0, s>>>(newOfOld, oldOfNew, nV);
+    k_rs_maps<<<nbV, BLOCK, 0, s>>>(order, sorted, blocksB + nbV, newOfOld, oldOfNew);
+    return 8;
+}
+int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int appBuf, cudaStream_t s) {
+    const size_t n = (size_t)nV * MAX_DRIVE_ITEMS > (size_t)nL ? (size_t)nV * MAX_DRIVE_ITEMS : (size_t)nL;
+    k_rs_remap<<<(unsigned)((n + BLOCK - 1) / BLOCK), BLOCK, 0, s>>>(ctx(c), newOfOld, appBuf);
+    return 1;
+}
+
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap};
 
 }  // namespace sb2_kset_<name>
 

@@ -22,6 +22,7 @@ struct Buffer {
     size_t offset;       // offset of the pointer inside Ctx
     std::vector<uint8_t> host;
     bool dynamic;        // written by kernels (state); static buffers are read-only after load
+    size_t elem = 0, count = 0;   // element size and number of elements
 };
 
 class Model {
@@ -41,7 +42,7 @@ public:
 
     template<class T> T* add(const char* name, size_t offset, size_t count, bool dynamic, T fill) {
         Buffer* b = new Buffer();
-        b->name = name; b->offset = offset; b->dynamic = dynamic;
+        b->name = name; b->offset = offset; b->dynamic = dynamic; b->elem = sizeof(T); b->count = count;
         b->host.resize(std::max<size_t>(count, 1) * sizeof(T));
         T* p = reinterpret_cast<T*>(b->host.data());
         for (size_t i = 0; i < std::max<size_t>(count, 1); i++) {
@@ -502,6 +503,14 @@ public:
         SB2_DYN(double, veh_len_in_front, nV, 0.);
         SB2_DYN(int32_t, tp_list, nV, -1); SB2_DYN(SUMOTime, veh_tp_proceed, nV, (SUMOTime)-1);
         SB2_DYN(uint8_t, edge_delayed, h.nE, (uint8_t)0);
+        {
+            int32_t* ext = SB2_DYN(int32_t, veh_ext, nV, 0);
+            int32_t* inv = SB2_DYN(int32_t, ext2slot, nV, 0);
+            for (int v = 0; v < nV; v++) {
+                ext[v] = v;
+                inv[v] = v;
+            }
+        }
         SB2_DYN(int32_t, veh_qlane, nV, -1); SB2_DYN(uint8_t, veh_deferred, nV, (uint8_t)0); SB2_DYN(int32_t, deferred_list, nV, -1);
         SB2_DYN(int32_t, lane_arrived, nL, 0);
         SB2_DYN(SUMOTime, veh_trip_wait, nV, 0); SB2_DYN(int32_t, veh_trip_waitcount, nV, 0); SB2_DYN(uint8_t, veh_trip_amwaiting, nV, 0);

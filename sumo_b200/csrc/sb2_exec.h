@@ -159,10 +159,11 @@ SB2_HD double veh_random(const Ctx& c, int v) {
     if (c.rng_mode == 0) {
         return 0.;
     }
+    const int ext = c.veh_ext[v];   // keyed by the vehicle's external index: independent of where its state currently lies
     if (c.rng_mode == 2) {
-        return c.rng_replay[v];
+        return c.rng_replay[ext];
     }
-    uint64_t z = c.rng_seed + 0x9E3779B97F4A7C15ull * ((uint64_t)v + 1) + 0xD1B54A32D192ED03ull * (uint64_t)(c.t / c.DELTA_T + 1);
+    uint64_t z = c.rng_seed + 0x9E3779B97F4A7C15ull * ((uint64_t)ext + 1) + 0xD1B54A32D192ED03ull * (uint64_t)(c.t / c.DELTA_T + 1);
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     z = z ^ (z >> 31);

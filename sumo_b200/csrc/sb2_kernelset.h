@@ -27,6 +27,10 @@ struct sb2_kernelset {
     /* halo exchange of the edge partition (sb2_halo.h); `side` points at an sb2::HaloSide in host memory, msg at device memory */
     int (*halo_pack)(const void* ctx, const void* side, const uint8_t* imp_mask, void* msg, cudaStream_t s);      /* returns the launch count */
     int (*halo_unpack)(const void* ctx, const void* side, const void* msg, cudaStream_t s);
+    /* re-slotting (engine.cu reslot): the permutation of the on-road vehicles into lane order, and the fix-up of every stored slot number */
+    int (*reslot_maps)(const void* ctx, int n_lanes, int n_vehicles, int32_t* blocks_a, int32_t* blocks_b, int32_t* order, int32_t* sorted,
+                       int32_t* new_of_old, int32_t* old_of_new, cudaStream_t s);
+    int (*reslot_remap)(const void* ctx, int n_lanes, int n_vehicles, const int32_t* new_of_old, int app_buf, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

@@ -286,8 +286,8 @@ SB2_HDN void lane_sort_partials(const Ctx& c, int l) {
         int j = i - 1;
         while (j >= 0) {
             const double py = veh_back_pos_on_lane(c, p[j], l);
-            // equal back positions: lower vehicle index first (the reference order is then the push order)
-            if (py < px || (py == px && p[j] < x)) {
+            // equal back positions: lower numerical id first (the reference order is then the push order)
+            if (py < px || (py == px && c.veh_numid[p[j]] < c.veh_numid[x])) {
                 break;
             }
             p[j + 1] = p[j];

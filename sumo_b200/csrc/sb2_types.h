@@ -204,6 +204,10 @@ struct Ctx {
     // executeMove pass 2 (sb2_exec.h): vehicles whose right of way depends on the NEW speed of a foe that the reference executes
     // earlier (MSLink::blockedAtTime reads the live speed, MSLink.cpp:1050): veh_deferred 1 = waiting, list + counters[9]
     uint8_t* veh_deferred; int32_t* deferred_list;
+    // re-slotting (engine.cu reslot): the slot is where a vehicle's state lies in HBM; every few steps the on-road vehicles are
+    // renumbered in lane order so that neighbours on the road are neighbours in memory.  veh_ext[slot] = the vehicle's EXTERNAL index
+    // (load order: what the C ABI calls a slot -- mirror, FCD rows, set_speed, replayed draws), ext2slot the inverse.
+    int32_t* veh_ext; int32_t* ext2slot;
     // MSVehicleTransfer (src/microsim/MSVehicleTransfer.cpp): vehicles that were teleported (jam / collision) wait off the road on
     // route edge veh_routepos until they fit on a lane again.  tp_list[0 .. counters[10]) = their slots (appended with an atomic,
     // sorted by numerical id in checkInsertions like the reference's std::sort), veh_tp_proceed = myProceedTime (-1 = not set)

@@ -91,6 +91,7 @@ def load_library(path=None):
     lib.sumob200_set_random_draws.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_set_random_mode.argtypes = [ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_set_profiling.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_set_reslot_period.argtypes = [ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_phase_times.argtypes = [ctypes.c_void_p, P(ctypes.c_double), ctypes.c_int, ctypes.c_int]
     lib.sumob200_last_error.restype = ctypes.c_char_p
     lib.sumob200_version.restype = ctypes.c_char_p
@@ -256,6 +257,10 @@ class Engine:
 
     def set_random_mode(self, mode):
         _check(self._lib, self._lib.sumob200_set_random_mode(self._h, mode), "sumob200_set_random_mode")
+
+    def set_reslot_period(self, steps):
+        """renumber the on-road vehicles in lane order every `steps` steps (memory locality; results unchanged; 0 = never)"""
+        _check(self._lib, self._lib.sumob200_set_reslot_period(self._h, int(steps)), "sumob200_set_reslot_period")
 
     def set_profiling(self, enabled):
         _check(self._lib, self._lib.sumob200_set_profiling(self._h, 1 if enabled else 0), "sumob200_set_profiling")

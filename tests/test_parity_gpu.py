@@ -36,6 +36,40 @@ def test_engine_matches_reference(case):
     assert compared > 1000
 
 
+@pytest.mark.parametrize("case,period", [("c1_grid10", 7), ("grid5_dense", 3), ("grid4_tls_mixed", 1), ("grid4_tls_hbefa4", 4)])
+def test_reslotting_changes_nothing(case, period):
+    """sumob200_set_reslot_period: the on-road vehicles are renumbered in lane order every few steps (memory locality); positions,
+    speeds, lanes (and the emission sums) stay bit-identical to the reference, the API keeps speaking load-order indices"""
+    from sumo_b200.engine import Engine
+    flat, trace = reference_case(case)
+    ref = load_trace(trace)
+    numid = load_flat(flat)["veh_numid"]
+    order = np.argsort(numid, kind="stable")
+    compared = 0
+    with Engine(flat) as eng:
+        eng.set_reslot_period(period)
+        for (t, ids, lanes, pos, speed) in ref:
+            r = eng.step(1)
+            st = eng.vehicles()[order]
+            on = st["lane"] >= 0
+            assert r.flags == 0, "t=%d: engine raised flags 0x%x" % (t, r.flags)
+            assert np.array_equal(numid[order][on], ids), "t=%d: sets of vehicles on the road differ" % t
+            assert np.array_equal(st["lane"][on], lanes), "t=%d: lanes differ" % t
+            assert np.array_equal(st["pos"][on].view(np.int64), pos.view(np.int64)), "t=%d: positions differ (bitwise)" % t
+            assert np.array_equal(st["speed"][on].view(np.int64), speed.view(np.int64)), "t=%d: speeds differ (bitwise)" % t
+            compared += len(ids)
+        if "hbefa" in case:
+            from conftest import emissions_path, load_emissions
+            te, eids, evals = load_emissions(emissions_path(case))[len(ref) - 1]
+            got = eng.emissions()
+            slot = {int(n): i for i, n in enumerate(numid)}
+            idx = [slot[int(i)] for i in eids]
+            assert np.array_equal(np.ascontiguousarray(got[:, idx].T).view(np.int64), evals.view(np.int64))
+        rows = eng.fcd()
+        assert sorted(rows["slot"].tolist()) == sorted(np.nonzero(eng.vehicles()["lane"] >= 0)[0].tolist())
+    assert compared > 1000
+
+
 def test_teleports_are_executed():
     """grid5_dense under the reference's default --time-to-teleport 300: the first vehicle is teleported at t = 484 s, 51 follow
     until t = 900 s (jam and yield teleports, re-insertions further along the route, teleports beyond the arrival edge); the
