@@ -268,7 +268,7 @@ def main():
     ap.add_argument("--replicas", action="store_true", help="N > 1: every rank simulates its own copy of the network instead of a strip of one network")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the N = 1 network (strong scaling) instead of growing it with N")
     ap.add_argument("--emissions", action="store_true", help="every vehicle carries the HBEFA emission device (BASELINE.json configs[4] flavour)")
-    ap.add_argument("--reslot", type=int, default=32, help="single GPU: renumber the on-road vehicles in lane order every this many steps (0 = never)")
+    ap.add_argument("--reslot", type=int, default=64, help="single GPU: renumber the on-road vehicles in lane order every this many steps (0 = never)")
     ap.add_argument("--xml", action="store_true", help="also time the e2e loop with the FCD rows formatted as XML on the host threads")
     args = ap.parse_args()
     if args.impl == "reference":
