@@ -25,12 +25,13 @@
  * constant-bank operands (a noinline callee would get a generic pointer to the parameter space instead) */
 #define SB2_HDN __host__ __device__ __forceinline__
 /* pure scalar arithmetic cores that are used from dozens of call sites (fp64 division / sqrt expand to long instruction
- * sequences): real calls, arguments in registers.  profiles/r01b: with everything inlined k_plan is ~8 k instructions and
- * its divergent warps stall on instruction fetch as often as on memory. */
-#if defined(SB2_CORE_INLINE)
-#define SB2_CORE __host__ __device__ __forceinline__
-#else
+ * sequences).  Round 1 measured real calls as faster (k_plan was ~8 k instructions with a 1.1 KB stack); with the per-thread
+ * DriveItem array gone (round 2) inlining wins again: k_plan 1.295 -> 1.248 ms (profiles/r02_occupancy_sweep.txt).
+ * -DSB2_CORE_CALL brings the calls back. */
+#if defined(SB2_CORE_CALL)
 #define SB2_CORE __host__ __device__ __noinline__
+#else
+#define SB2_CORE __host__ __device__ __forceinline__
 #endif
 /* rarely executed, register-hungry blocks (right-of-way check against the approach tables): out of line, so that their
  * register demand does not set the allocation of the whole kernel; they get the Ctx by reference (generic loads) */

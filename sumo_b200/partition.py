@@ -148,6 +148,10 @@ class PartitionedEngine:
         self.num_lanes = self.eng.num_lanes
         self.exchanges = 0
         self.bytes_sent = 0
+        import os as _os
+        self._prof = [] if _os.environ.get("SUMOB200_HALO_PROF") else None
+        self._prof_ms, self._prof_n = {}, 0
+        self._skip_fleet = bool(_os.environ.get("SUMOB200_NO_FLEET_SYNC"))   # measurement only: results are then not exact
 
     # ---- the step: engine step + halo exchange, all enqueued on the engine's stream
     HEADER, LANE_REC, VEH_REC = 16, 64, 288    # sizeof HaloHeader / HaloLane / HaloVeh (static_assert in sb2_halo.h)
@@ -159,6 +163,14 @@ class PartitionedEngine:
             return self.plan["capacity"]
         return int(min(self.plan["capacity"], last_count + last_count // 4 + 512))
 
+    def _mark(self, name):
+        """SUMOB200_HALO_PROF=1: CUDA events between the parts of the exchange (summed in halo_stats()['ms_per_step'])"""
+        if self._prof is None:
+            return
+        ev = self.torch.cuda.Event(enable_timing=True)
+        ev.record(self.stream)
+        self._prof.append((name, ev))
+
     def _exchange(self):
         from .engine import _check
         lib, h, torch = self.eng._lib, self.eng._h, self.torch
@@ -167,6 +179,7 @@ class PartitionedEngine:
             self._counts = [{"sent": torch.zeros(4, dtype=torch.int32).pin_memory(), "recv": torch.zeros(4, dtype=torch.int32).pin_memory(),
                              "event": None} for _ in (0, 1)]
         with torch.cuda.stream(self.stream):
+            self._mark("step")
             send_v, recv_v = [None, None], [None, None]
             for side in (0, 1):
                 if self.send[side] is None:
@@ -182,7 +195,9 @@ class PartitionedEngine:
                 send_v[side] = self.send[side][:self.HEADER + self.LANE_REC * n_exp + self.VEH_REC * lim_s]
                 recv_v[side] = self.recv[side][:self.HEADER + self.LANE_REC * n_imp + self.VEH_REC * lim_r]
                 self.bytes_sent += send_v[side].numel()
+            self._mark("pack")
             exchange_messages(self.dist, self.rank, self.world, send_v, recv_v)
+            self._mark("transfer")
             for side in (0, 1):
                 if self.recv[side] is not None:
                     _check(lib, lib.sumob200_halo_unpack(h, side, self.recv[side].data_ptr()), "sumob200_halo_unpack")
@@ -192,10 +207,27 @@ class PartitionedEngine:
                     st["event"] = torch.cuda.Event()
                     st["event"].record(self.stream)
             # fleet aggregates: max speedFactor, MIN deceleration, max minGap over the departed vehicles of the whole network
-            self.fleet[1].neg_()
-            self.dist.all_reduce(self.fleet, op=self.dist.ReduceOp.MAX)
-            self.fleet[1].neg_()
+            self._mark("unpack")
+            if not self._skip_fleet:
+                self.fleet[1].neg_()
+                self.dist.all_reduce(self.fleet, op=self.dist.ReduceOp.MAX)
+                self.fleet[1].neg_()
+            self._mark("allreduce")
         self.exchanges += 1
+        if self._prof is not None and len(self._prof) >= 5 * 64:
+            self._fold_prof()
+
+    def _fold_prof(self):
+        self.stream.synchronize()
+        prev = None
+        for name, ev in self._prof:
+            if prev is not None and name != "step":
+                self._prof_ms[name] = self._prof_ms.get(name, 0.) + prev.elapsed_time(ev)
+            elif prev is not None:
+                self._prof_ms["step"] = self._prof_ms.get("step", 0.) + prev.elapsed_time(ev)
+            prev = ev
+        self._prof_n += sum(1 for name, _ in self._prof if name == "step")
+        self._prof = []
 
     def step(self, n=1, result=True):
         for _ in range(n):
@@ -229,6 +261,9 @@ class PartitionedEngine:
         self.stream.synchronize()
         out = {"exchanges": self.exchanges, "columns": list(self.plan["columns"]), "capacity_records": self.plan["capacity"],
                "bytes_sent_per_step": self.bytes_sent // max(self.exchanges, 1)}
+        if self._prof is not None:
+            self._fold_prof()
+            out["ms_per_step"] = {k: v / max(self._prof_n, 1) for k, v in self._prof_ms.items()}
         for side, name in ((0, "left"), (1, "right")):
             if self.send[side] is not None:
                 hdr = self.send[side][:16].cpu().numpy().view(np.int32)
