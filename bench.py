@@ -42,6 +42,28 @@ SPINUP_STEPS = 420          # all departures are due within 300 s; the backlog o
 PROF_STEPS = 60             # window of the per-kernel (roofline) timing
 TLS_CYCLE_S = 90
 REF_GRID = 12               # the reference arm simulates a 12 x 12 cut of the same workload per process (same density, same options)
+# --config c4: BASELINE.json configs[3] as SURVEY.md section 8d defines it (C4): 1000 x 1000 grid at 100 m, priority junctions,
+# 10 M vehicles (25 veh/lane-km), Krauss sigma 0; fixed size for every N (edge-partitioned across the GPUs: strong scaling)
+WORKLOADS = {
+    "c2": {"template": "grid5_tls800", "grid": GRID, "vehicles": VEHICLES, "route_edges": 40, "depart_end": 300, "spinup": 420, "length": 800,
+           "jtype": "traffic_light", "ref_grid": 12, "sigma": 0.5, "tls": True},
+    "c4": {"template": "grid5_prio100", "grid": 1000, "vehicles": 10000000, "route_edges": 48, "depart_end": 100, "spinup": 200, "length": 100,
+           "jtype": "priority", "ref_grid": 40, "sigma": 0.0, "tls": False},
+}
+
+
+def use_workload(name):
+    """selects the workload constants (module globals: the functions below read them)"""
+    global TEMPLATE, ROUTE_EDGES, DEPART_END_S, SPINUP_STEPS, REF_GRID, GRID_LENGTH, JUNCTION_TYPE, HAS_TLS
+    w = WORKLOADS[name]
+    TEMPLATE = os.path.join(ROOT, "tests", "golden", w["template"] + ".flat")
+    ROUTE_EDGES, DEPART_END_S, SPINUP_STEPS, REF_GRID = w["route_edges"], w["depart_end"], w["spinup"], w["ref_grid"]
+    GRID_LENGTH, JUNCTION_TYPE, HAS_TLS = w["length"], w["jtype"], w["tls"]
+    return w
+
+
+GRID_LENGTH, JUNCTION_TYPE, HAS_TLS = 800, "traffic_light", True
+REF_DENSITY_GRID, REF_DENSITY_VEHICLES = GRID, VEHICLES
 # algorithmic bytes per vehicle-update (SURVEY.md section 8d / DESIGN.md "roofline"): whole step, and the plan kernel alone
 BYTES_PER_UPDATE_STEP = 576
 BYTES_PER_UPDATE_PLAN = 320
@@ -65,7 +87,8 @@ def build_scenario(grid, vehicles, sigma, emissions=False, names=False, seed=1):
     from sumo_b200 import gridgen
     from sumo_b200.flatfile import load_flat
     g = gridgen.make_grid(load_flat(TEMPLATE), grid, with_names=grid <= 200)
-    gridgen.set_tls_offsets(g, tls_offsets(len(g["tl_cur_phase"])))
+    if HAS_TLS:
+        gridgen.set_tls_offsets(g, tls_offsets(len(g["tl_cur_phase"])))
     gridgen.make_demand(g, vehicles, ROUTE_EDGES, DEPART_END_S, seed=seed, sigma=sigma, speeddev=0.1, names=names)
     if emissions:
         g["veh_emissions"] = np.ones(vehicles, np.uint8)
@@ -167,7 +190,7 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(self.sm), "source": self.source}
 
 
-def reference_ups(total_steps, sigma, procs=None, grid=REF_GRID):
+def reference_ups(total_steps, sigma, procs=None, grid=None):
     """the reference's own CPU implementation (oracle/_ref/sumo: the unmodified sources, oracle/build_ref.sh) on a `grid` x `grid`
     cut of the bench workload: the same netgenerate options, density (32 veh/lane-km), route length, departure window, vType,
     per-junction signal offsets and default sumo options; the net comes from oracle/_ref/netgenerate, the demand from the same
@@ -181,17 +204,19 @@ def reference_ups(total_steps, sigma, procs=None, grid=REF_GRID):
     if not (os.path.exists(exe) and os.path.exists(netgen)):
         return None
     procs = procs or max(1, os.cpu_count() or 1)
+    grid = grid or REF_GRID
     tmp = tempfile.mkdtemp(prefix="sumob200_ref_")
     try:
         net = os.path.join(tmp, "ref.net.xml")
-        subprocess.check_call([netgen, "--grid", "--grid.number=%d" % grid, "--grid.length=800", "--default-junction-type", "traffic_light",
+        subprocess.check_call([netgen, "--grid", "--grid.number=%d" % grid, "--grid.length=%d" % GRID_LENGTH, "--default-junction-type", JUNCTION_TYPE,
                                "-o", net, "--no-warnings"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         g = gridgen.make_grid(load_flat(TEMPLATE), grid)
-        off = dict(zip(names(g, "tl"), tls_offsets(len(g["tl_cur_phase"])) // 1000))
-        text = re.sub(r'<tlLogic id="([^"]+)" type="static" programID="0" offset="0">',
-                      lambda m: '<tlLogic id="%s" type="static" programID="0" offset="%d">' % (m.group(1), off[m.group(1)]), open(net).read())
-        open(net, "w").write(text)
-        vehicles = int(round(VEHICLES * (2 * grid * (grid - 1) * 2) / (2 * GRID * (GRID - 1) * 2)))
+        if HAS_TLS:
+            off = dict(zip(names(g, "tl"), tls_offsets(len(g["tl_cur_phase"])) // 1000))
+            text = re.sub(r'<tlLogic id="([^"]+)" type="static" programID="0" offset="0">',
+                          lambda m: '<tlLogic id="%s" type="static" programID="0" offset="%d">' % (m.group(1), off[m.group(1)]), open(net).read())
+            open(net, "w").write(text)
+        vehicles = int(round(REF_DENSITY_VEHICLES * (grid * (grid - 1)) / float(REF_DENSITY_GRID * (REF_DENSITY_GRID - 1))))
         gridgen.make_demand(g, vehicles, ROUTE_EDGES, DEPART_END_S, seed=1, sigma=sigma, speeddev=0.1)
         rou = os.path.join(tmp, "ref.rou.xml")
         # speedFactor: the reference samples its own normc(1, 0.1, 0.2, 2) values from the vType distribution
@@ -222,9 +247,10 @@ def reference_sample_text(r):
 
 
 def workload_text(grid, vehicles, sigma, emissions):
-    return ("netgenerate %dx%d grid, 800 m, static traffic lights with per-junction offsets, %d vehicles on ONE connected network, Krauss sigma=%.1f, "
+    return ("netgenerate %dx%d grid, %d m, %s, %d vehicles on ONE connected network, Krauss sigma=%.1f, "
             "speedFactor normc(1,0.1), random-walk routes of %d edges, step-length 1 s, default teleport/collision options%s"
-            % (grid, grid, vehicles, sigma, ROUTE_EDGES, ", HBEFA4 emission device on every vehicle" if emissions else ""))
+            % (grid, grid, GRID_LENGTH, "static traffic lights with per-junction offsets" if HAS_TLS else "priority junctions", vehicles, sigma, ROUTE_EDGES,
+               ", HBEFA4 emission device on every vehicle" if emissions else ""))
 
 
 def run_reference(args):
@@ -261,9 +287,10 @@ def main():
     ap.add_argument("--steps", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--grid", type=int, default=GRID, help="junctions per side of the connected grid")
-    ap.add_argument("--vehicles", type=int, default=VEHICLES, help="vehicles of the whole network")
-    ap.add_argument("--sigma", type=float, default=0.5)
+    ap.add_argument("--config", default="c2", choices=sorted(WORKLOADS), help="c2 = BASELINE configs[1] (default), c4 = configs[3] (1000x1000 / 100 m / 10 M vehicles)")
+    ap.add_argument("--grid", type=int, default=None, help="junctions per side of the connected grid")
+    ap.add_argument("--vehicles", type=int, default=None, help="vehicles of the whole network")
+    ap.add_argument("--sigma", type=float, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--replicas", action="store_true", help="N > 1: every rank simulates its own copy of the network instead of a strip of one network")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the N = 1 network (strong scaling) instead of growing it with N")
@@ -271,6 +298,14 @@ def main():
     ap.add_argument("--reslot", type=int, default=64, help="single GPU: renumber the on-road vehicles in lane order every this many steps (0 = never)")
     ap.add_argument("--xml", action="store_true", help="also time the e2e loop with the FCD rows formatted as XML on the host threads")
     args = ap.parse_args()
+    global REF_DENSITY_GRID, REF_DENSITY_VEHICLES
+    w = use_workload(args.config)
+    args.grid = args.grid or w["grid"]
+    args.vehicles = args.vehicles or w["vehicles"]
+    args.sigma = w["sigma"] if args.sigma is None else args.sigma
+    REF_DENSITY_GRID, REF_DENSITY_VEHICLES = args.grid, args.vehicles
+    if args.config == "c4":
+        args.strong = True      # configs[3] is one fixed network partitioned across the GPUs
     if args.impl == "reference":
         return run_reference(args)
 
