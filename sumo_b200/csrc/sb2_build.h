@@ -372,14 +372,12 @@ public:
                     m[i] = CF_KRAUSS;
                 } else if (tag[i] == tagOrig) {
                     m[i] = CF_KRAUSS_ORIG1;
+                    anyIDM = true;   // (selects the `full` kernel set: the `krauss` set is compiled without the other models)
                 } else if (tag[i] == tagIDM) {
                     m[i] = CF_IDM;
                     anyIDM = true;
                 } else {
-                    throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss, IDM)");
-                }
-                if (m[i] == CF_KRAUSS_ORIG1) {
-                    throw std::runtime_error("sumob200: carFollowModel KraussOrig1 is not implemented (supported: Krauss, IDM)");
+                    throw std::runtime_error("sumob200: unsupported car-following model (supported: Krauss, KraussOrig1, IDM)");
                 }
             }
             SB2_COPY(double, vt_collision_mingap_factor);

@@ -15,8 +15,10 @@ namespace sb2 {
 
 #if defined(SB2_NO_IDM)
 #define SB2_IS_IDM(m) false
+#define SB2_IS_ORIG1(m) false
 #else
 #define SB2_IS_IDM(m) ((m).model() == CF_IDM)
+#define SB2_IS_ORIG1(m) ((m).model() == CF_KRAUSS_ORIG1)
 #endif
 
 // The car-following parameters of one vehicle type.  With -DSB2_CF_TABLE a VIEW of the vType table (vType index + context): every use
@@ -338,6 +340,17 @@ SB2_HD double cf_idm_freeSpeed(const CF& m, double speed, double seen, double ma
     return vSafe;
 }
 
+// MSCFModel_KraussOrig1::vsafe (MSCFModel_KraussOrig1.cpp:96-113): the SK safe speed; myTauDecel = decel * tau
+SB2_HD double cf_orig1_vsafe(const CF& m, double gap, double predSpeed) {
+    if (predSpeed == 0 && gap < 0.01) {
+        return 0;
+    } else if (predSpeed == 0 && gap <= m.decel() * m.TS()) {
+        return MIN2(m.decel() * m.TS(), gap / m.TS());
+    }
+    const double tauDecel = m.decel() * m.tau();
+    return (double)(-1. * tauDecel + sqrt(tauDecel * tauDecel + (predSpeed * predSpeed) + (2. * m.decel() * gap)));
+}
+
 // ---- model dispatch -----------------------------------------------------------------------------
 // stopSpeed(veh, speed, gap, decel, usage): MSCFModel_Krauss.cpp:127-134 ; relaxEmergency = (usage != FUTURE)
 // IDM: MSCFModel_IDM.cpp:178-194
@@ -355,6 +368,9 @@ SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap, double decel, 
         }
         return result;
     }
+    if (SB2_IS_ORIG1(m)) {   // MSCFModel_KraussOrig1.cpp:70-79
+        return MIN2(cf_orig1_vsafe(m, gap, 0.), cf_maxNextSpeed(m, speed));
+    }
     return MIN2(cf_maximumSafeStopSpeed(m, gap, decel, speed, false, m.TS() /* actionStepLengthSecs */, !future), cf_maxNextSpeed(m, speed));
 }
 SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_stopSpeed(m, speed, gap, m.decel(), false); }
@@ -364,6 +380,9 @@ SB2_HD double cf_stopSpeed(const CF& m, double speed, double gap) { return cf_st
 SB2_HD double cf_followSpeed(const CF& m, double speed, double gap, double predSpeed, double predMaxDecel, bool computeLC = false) {
     if (SB2_IS_IDM(m)) {
         return cf_idm_v(m, speed, gap, predSpeed, m.desSpeed, true);
+    }
+    if (SB2_IS_ORIG1(m)) {   // MSCFModel_KraussOrig1.cpp:59-66
+        return MIN2(cf_orig1_vsafe(m, gap, predSpeed), cf_maxNextSpeed(m, speed));
     }
     const double vsafe = cf_maximumSafeFollowSpeed(m, gap, speed, predSpeed, predMaxDecel, false, computeLC);
     const double vmax = cf_maxNextSpeed(m, speed);
@@ -417,6 +436,9 @@ SB2_HD double cf_getSecureGap(const CF& m, double speed, double leaderSpeed, dou
 SB2_HD double cf_dawdle2(const CF& m, double speed, double sigma, double random) {
     if (SB2_IS_IDM(m)) {
         return speed;   // MSCFModel::patchSpeedBeforeLC (MSCFModel.h) returns vMax: no dawdling, no draw
+    }
+    if (SB2_IS_ORIG1(m)) {   // MSCFModel_KraussOrig1::dawdle (MSCFModel_KraussOrig1.cpp:82-93)
+        return MAX2(0., speed - (sigma * m.accel() * random) * m.TS());
     }
     if (speed < m.accel()) {
         speed -= (sigma * speed * random) * m.TS();

@@ -42,6 +42,10 @@ CASES.update({
     # the case that exposed MSLink::blockedAtTime's LIVE foe speed under lastWasContRed (MSLink.cpp:1050) at t = 514 s: a left turner
     # waiting on the junction sees a foe whose lane the reference executes earlier in the step (executeMove pass 2, sb2_link.h)
     "grid4_tls_idm": ["--default.speeddev", "0", "--end", "1200"],
+    # carFollowModel KraussOrig1 (MSCFModel_KraussOrig1: the SK safe speed): not collision free -- 20 resp. 58 rear-end collisions, each
+    # resolved by teleporting the collider like the reference does (collision.action teleport)
+    "grid4_tls_orig1": ["--default.speeddev", "0", "--end", "900"],
+    "grid5_dense_orig1": ["--default.speeddev", "0", "--end", "900"],
 })
 def _mixed_fleet(text):
     """three vTypes (default car, long slow truck, short quick car with impatience), assigned pseudo-randomly but reproducibly"""
@@ -77,6 +81,7 @@ ROU_EDITS = {
     "_arrivalpos": ('<vehicle ', '<vehicle arrivalPos="60" '),
     "_idm": ('sigma="0"', 'sigma="0" carFollowModel="IDM"'),
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
+    "_orig1": ('sigma="0"', 'sigma="0" carFollowModel="KraussOrig1"'),
     "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
 }
 
@@ -174,7 +179,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase", "_setspeed"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_orig1", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase", "_setspeed"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []
