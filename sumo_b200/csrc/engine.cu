@@ -19,6 +19,7 @@
  */
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -80,6 +81,7 @@ struct sumob200_engine {
     int reslotPeriod = 0;
     long long reslots = 0;
     int32_t* rsScratch = nullptr;   // blocksA, blocksB, order, sorted, newOfOld, oldOfNew
+    bool debugSync = getenv("SUMOB200_DEBUG_SYNC") != nullptr;
     void* rsTmp = nullptr;          // one permuted array (16 B per vehicle)
     int64_t launches = 0;
     bool profiling = false;
@@ -240,7 +242,7 @@ template<class T> int uploadArray(sumob200_engine* e, const T* host, size_t n, T
 extern "C" {
 
 const char* sumob200_last_error(void) { return gLastError.c_str(); }
-const char* sumob200_version(void) { return "sumob200 0.2 (sm_100a; Krauss + IDM, single-lane edges, static TLS, HBEFA3/4, FCD streaming; kernel sets: full, krauss)"; }
+const char* sumob200_version(void) { return "sumob200 0.2 (sm_100a; Krauss + KraussOrig1 + IDM, single-lane edges, static TLS, teleports + collisions, HBEFA3/4, FCD streaming; kernel sets: full, krauss)"; }
 
 int sumob200_create(const sumob200_array* arrays, int n_arrays, int device, sumob200_engine** out) {
     if (arrays == nullptr || out == nullptr || n_arrays <= 0) {
@@ -343,19 +345,29 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
     for (int i = 0; i < n_steps; i++) {
         const bool prof = e->profiling;
         if (prof) { cudaEventRecord(e->ev[0], s); }
+        // SUMOB200_DEBUG_SYNC=1 (debugging only): wait after every launch group and name the one that failed
+#define SB2_DBG(name) do { if (e->debugSync) { cudaError_t _d = cudaStreamSynchronize(s); if (_d != cudaSuccess) { \
+        gLastError = std::string("step ") + std::to_string((long long)e->stepsDone) + ", after " name ": " + cudaGetErrorString(_d); return SUMOB200_ECUDA; } } } while (0)
         e->ks->reset(&e->d, s);   // counters[0] = running vehicles of this step, counters[7] = length of the work list
         e->ks->pre(&e->d, nPre, s);
+        SB2_DBG("k_pre");
         if (prof) { cudaEventRecord(e->ev[1], s); }
         e->ks->plan(&e->d, c.nV, s);
+        SB2_DBG("k_plan");
         if (prof) { cudaEventRecord(e->ev[2], s); }
         CUDA_TRY(cudaMemsetAsync(c.lane_npartial + c.lane_lo, 0, sizeof(int32_t) * (size_t)nLv, s));
         e->ks->execute(&e->d, c.nV, s);
+        SB2_DBG("k_execute / k_execute2");
         if (prof) { cudaEventRecord(e->ev[3], s); }
         e->ks->remove(&e->d, nLv, s);
+        SB2_DBG("k_remove");
         e->ks->integrate(&e->d, nLv, s);
+        SB2_DBG("k_integrate / k_collide / k_partials");
         if (prof) { cudaEventRecord(e->ev[4], s); }
         e->ks->insert(&e->d, nLv, s);
+        SB2_DBG("k_insert / k_transfer");
         e->ks->count(&e->d, c.nV, e->dUpdates, s);
+        SB2_DBG("k_count");
         if (prof) {
             cudaEventRecord(e->ev[5], s);
             CUDA_TRY(cudaEventSynchronize(e->ev[5]));
@@ -630,6 +642,7 @@ int sumob200_halo_pack(sumob200_engine* e, int side, void* device_message, int m
         h.cap = max_records;   // the caller transports only this many records (both ends agree on the size from the previous step's count)
     }
     e->launches += e->ks->halo_pack(&e->d, &h, e->dImpMask[side], device_message, e->stream);
+    if (e->debugSync) { CUDA_TRY(cudaStreamSynchronize(e->stream)); }
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -641,6 +654,7 @@ int sumob200_halo_unpack(sumob200_engine* e, int side, const void* device_messag
     }
     CUDA_TRY(cudaSetDevice(e->device));
     e->launches += e->ks->halo_unpack(&e->d, &e->halo[side], device_message, e->stream);
+    if (e->debugSync) { CUDA_TRY(cudaStreamSynchronize(e->stream)); }
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
