@@ -152,6 +152,18 @@ typedef struct sumob200_summary {
 } sumob200_summary;
 int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out);
 
+/* sumob200_summary_now without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs,
+ * same output, same result as sumob200_summary_now, but the kernel's scratch (the per-block partial sums and the reduced result)
+ * lies in a file-scope `static __device__` array of the library instead of a lazily allocated buffer: 917,560 bytes that every GPU
+ * which loads the library holds until exit.  The call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: engines with more than SUMOB200_SUMMARY_STATIC_MAX_VEHICLES vehicle slots are rejected with SUMOB200_EINVAL and a message
+ * in sumob200_last_error().  All calls on one GPU share the array (it keeps the last call's contents; nothing in it needs to
+ * start at zero, the result slot is cleared anyway): calls that overlap on the GPU -- two engines on one device called from two
+ * threads -- race and must be serialised by the caller. */
+#define SUMOB200_SUMMARY_STATIC_MAX_VEHICLES 2097152
+int sumob200_summary_now_static(sumob200_engine* e, sumob200_summary* out);
+
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],
  * p = 0 CO2, 1 CO, 2 HC, 3 fuel, 4 NOx, 5 PMx, 6 electricity [mg resp. ml resp. Wh], n = sumob200_num_vehicles.

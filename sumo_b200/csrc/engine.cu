@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -921,3 +922,86 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
 }
 
 }  // extern "C"
+
+// ---- sumob200_summary_now_static: sumob200_summary_now without any allocation --------------------------------------------------
+// No counterpart in the reference; added for callers that must not allocate device memory
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The per-block partial sums of k_summary and the
+// reduced result live in ONE file-scope device array of a fixed size instead of the lazily cudaMalloc'ed e->dSummary: every GPU
+// that loads the library holds its 917,560 bytes until exit, every call (of every engine on that GPU) shares it.  Calls that
+// overlap on one GPU race on it; one engine's calls are ordered by its stream, different engines' calls must not run concurrently.
+// Nothing in it has to start at zero: k_summary overwrites parts [0, nb), k_summary_final overwrites the result slot, and nothing
+// else is read -- the result slot is cleared all the same, so that a launch that did not run cannot hand back the last call's sums.
+namespace {
+
+enum { SUMMARY_STATIC_MAX_PARTS = SUMOB200_SUMMARY_STATIC_MAX_VEHICLES / 128, SUMMARY_STATIC_MAX_DEVICES = 64 };
+static __device__ __align__(256) unsigned char gSummaryScratch[sizeof(sb2::SummaryPart) * (SUMMARY_STATIC_MAX_PARTS + 1)];
+// device address of gSummaryScratch per device (in host code the symbol's name is only a host-side stand-in, not a device address)
+void* gSummaryScratchPtr[SUMMARY_STATIC_MAX_DEVICES];
+std::mutex gSummaryScratchMutex;
+
+// the array's address on `device` (which must be current); looked up once per device
+int summaryScratchAddress(int device, void** out) {
+    if (device < 0 || device >= SUMMARY_STATIC_MAX_DEVICES) {
+        gLastError = "sumob200_summary_now_static: device index beyond " + std::to_string((int)SUMMARY_STATIC_MAX_DEVICES);
+        return SUMOB200_EINVAL;
+    }
+    std::lock_guard<std::mutex> lock(gSummaryScratchMutex);
+    if (gSummaryScratchPtr[device] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t err = cudaGetSymbolAddress(&p, gSummaryScratch);
+        if (err != cudaSuccess || p == nullptr) {
+            gLastError = std::string("sumob200_summary_now_static: cudaGetSymbolAddress: ") + cudaGetErrorString(err);
+            return SUMOB200_ECUDA;
+        }
+        gSummaryScratchPtr[device] = p;
+    }
+    *out = gSummaryScratchPtr[device];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int sumob200_summary_now_static(sumob200_engine* e, sumob200_summary* out) {
+    if (e == nullptr || out == nullptr) {
+        gLastError = "sumob200_summary_now_static: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int nV = e->d.nV;
+    const int bytes = e->ks->summary(&e->d, nV, nullptr, nullptr, e->stream);   // (size query: launches nothing)
+    if (nV > SUMOB200_SUMMARY_STATIC_MAX_VEHICLES || (size_t)bytes > sizeof(gSummaryScratch)) {
+        gLastError = "sumob200_summary_now_static: " + std::to_string(nV) + " vehicle slots exceed the static scratch array's limit of "
+                     + std::to_string((int)SUMOB200_SUMMARY_STATIC_MAX_VEHICLES) + " (use sumob200_summary_now)";
+        return SUMOB200_EINVAL;
+    }
+    void* scratch = nullptr;
+    const int rc = summaryScratchAddress(e->device, &scratch);
+    if (rc != 0) {
+        return rc;
+    }
+    sb2::SummaryPart* res = reinterpret_cast<sb2::SummaryPart*>(static_cast<char*>(scratch) + bytes) - 1;
+    CUDA_TRY(cudaMemsetAsync(res, 0, sizeof(sb2::SummaryPart), e->stream));
+    e->launches += e->ks->summary(&e->d, nV, scratch, res, e->stream);
+    CUDA_TRY(cudaGetLastError());
+    sb2::SummaryPart p;
+    int32_t counters[16];
+    CUDA_TRY(cudaMemcpyAsync(&p, res, sizeof(p), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    out->time_ms = e->d.t - e->d.DELTA_T;
+    out->inserted = p.departed;
+    out->running = p.count + p.teleporting;
+    out->waiting = p.waiting;
+    out->ended = p.ended;
+    out->arrived = p.ended;
+    out->collisions = counters[4];
+    out->teleports = counters[6];
+    out->halting = p.halting;
+    out->stopped = 0;
+    out->reserved = 0;
+    out->mean_waiting_time = p.departed != 0 ? ((double)p.delay_ms / 1000.) / (double)p.departed : -1.;
+    out->mean_travel_time = p.ended != 0 ? ((double)p.travel_ms / 1000.) / (double)p.ended : -1.;
+    out->mean_speed = p.count > 0 ? p.speedSum / p.count : -1.;
+    out->mean_speed_relative = p.count > 0 ? p.relSpeedSum / p.count : -1.;
+    return 0;
+}

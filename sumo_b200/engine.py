@@ -77,6 +77,7 @@ def load_library(path=None):
     lib.sumob200_fcd_end.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_int)]
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.sumob200_summary_now_static.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_tls.argtypes = [ctypes.c_void_p]
     lib.sumob200_vehicles_set_speed.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
@@ -222,6 +223,13 @@ class Engine:
         """the attributes of the <step> line MSNet::writeSummaryOutput writes for the step executed last (record of dtype SUMMARY)"""
         out = np.zeros(1, dtype=SUMMARY)
         _check(self._lib, self._lib.sumob200_summary_now(self._h, out.ctypes.data), "sumob200_summary_now")
+        return out[0]
+
+    def summary_static(self):
+        """summary() through sumob200_summary_now_static: the same record, computed without any device allocation (scratch in a
+        static device array of the library; at most SUMOB200_SUMMARY_STATIC_MAX_VEHICLES = 2,097,152 vehicle slots)"""
+        out = np.zeros(1, dtype=SUMMARY)
+        _check(self._lib, self._lib.sumob200_summary_now_static(self._h, out.ctypes.data), "sumob200_summary_now_static")
         return out[0]
 
     def emissions(self):
