@@ -105,14 +105,14 @@ SB2_HD FollowerInfo lane_followers_on_consecutive(const Ctx& c, int l, int ego, 
         }
         while (nEx != 0) {
             for (int q = 0; q < nEx; q++) {
-                const int next = toExamine[q].lane;
+                const int next = SB2_CHK(toExamine[q].lane, 0, c.nL, 38);
                 const double ilen = toExamine[q].length;
                 searchDist = MIN2(searchDist, lane_max_brake_dist(c, next) - backOffset);
                 // getFirstVehicleInformation: front-most of vehicles and partial occupators / front-most vehicle with front on lane
                 const int np = c.lane_npartial[next];
-                const int firstFront = ins_lane_first(c, next, snapshot);
+                const int firstFront = SB2_CHK(ins_lane_first(c, next, snapshot), -1, c.nV, 39);
                 int first = np > 0 ? c.lane_partial[(size_t)next * MAX_PARTIAL + np - 1] : firstFront;
-                int v = first == ego ? firstFront : first;
+                int v = SB2_CHK(first == ego ? firstFront : first, -1, c.nV, 40);
                 double agap = 0;
                 if (v >= 0 && v != ego) {
                     if (!veh_front_on_lane(c, v, next)) {
@@ -216,6 +216,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
             }
         }
     }
+    leader = SB2_CHK(leader, -1, c.nV, 32);
     const double nspeed = lane_safeInsertionSpeed(c, l, cf, -pos, leader, speed);
     if (nspeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nspeed, patchSpeed)) {
         return false;
@@ -232,7 +233,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
     int guard = 0;
     while (seen < dist && guard++ < 32) {
         const int nextEdge = routePos0 + nRouteSuccs < routeLen ? c.route_edges[c.route_begin[r] + routePos0 + nRouteSuccs] : -1;
-        const int link = lane_succ_link(c, currentLane, nextEdge);
+        const int link = SB2_CHK(lane_succ_link(c, SB2_CHK(currentLane, 0, c.nL, 33), SB2_CHK(nextEdge, -1, c.nE, 34)), -1, c.nK, 35);
         if (link < 0) {
             if (c.lane_edge[currentLane] == c.route_edges[c.route_begin[r + 1] - 1]) {
                 // reached the end of the route (arrivalSpeed not given; mayContinue: no further route)
@@ -243,7 +244,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
             }
             break;
         }
-        const int nextLane = c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link];
+        const int nextLane = SB2_CHK(c.link_via[link] >= 0 ? c.link_via[link] : c.link_to[link], 0, c.nL, 36);
         const uint8_t state = c.link_state[link];
         if (link_opened(c, link, c.cur, arrivalTime, speed, speed, cf.length(), veh_impatience(c, v), cf.decel(), 0, false, v) == OPEN_NO
                 || !state_priority(state)
@@ -265,7 +266,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
             }
         }
         // leader on next lane: getLastVehicleInformation(aVehicle, 0, 0)
-        const int nextLeader = ins_lane_last_any(c, nextLane, !teleport);
+        const int nextLeader = SB2_CHK(ins_lane_last_any(c, nextLane, !teleport), -1, c.nV, 37);
         if (nextLeader >= 0 && nextLeader != v) {
             const double nextLaneSpeed = lane_safeInsertionSpeed(c, nextLane, cf, seen, nextLeader, speed);
             if (nextLaneSpeed == SB2_INVALID_SPEED || ins_checkFailure(cf, speed, dist, nextLaneSpeed, patchSpeed)) {
@@ -299,7 +300,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
     // followers
     const double backOffset = pos - cf.length();
     const FollowerInfo fi = lane_followers_on_consecutive(c, l, v, cf.length(), cf.decel(), backOffset, egoSpeed, !teleport);
-    if (fi.veh >= 0) {
+    if (SB2_CHK(fi.veh, -1, c.nV, 41) >= 0) {
         const CF fcf = make_cf(c, c.veh_type[fi.veh]);
         const double backGapNeeded = cf_getSecureGap(fcf, c.veh_speed[fi.veh], speed, cf.decel());
         if (fi.dist < backGapNeeded) {
@@ -440,7 +441,7 @@ SB2_HDN void lane_insertVehicles(const Ctx& c, int l) {
     int head = c.dq_head[l];
     const int end = c.dq_begin[l + 1];
     while (head < end) {
-        const int v = c.dq_veh[head];
+        const int v = SB2_CHK(c.dq_veh[SB2_CHK(head, 0, c.nV, 30)], 0, c.nV, 31);
         if (c.veh_depart[v] > c.t) {
             break;
         }
