@@ -21,12 +21,16 @@ namespace sb2 {
 // queue here skips entries with veh_depart_time == now.  (Teleporting vehicles re-enter afterwards, one by one, and see everything: snapshot == false.  The reference inserts sequentially in load order, so there the later
 // vehicle sees the earlier one; that only matters when two vehicles depart in the same step on lanes closer to each other than
 // the insertion look-ahead -- brake gap downstream, getMaximumBrakeDist upstream.)
-SB2_HD bool ins_is_new(const Ctx& c, int v) { return c.veh_depart_time[v] == c.t; }
+// The queue heads and the fields of a possibly new vehicle are read past the L1 (ld_coherent): the SM may hold the cache line of
+// veh_depart_time / veh_ahead / veh_behind from BEFORE the other thread's insertion (slots are sorted by departure lane, so
+// neighbouring lanes' vehicles share lines) -- a stale -1 there made a new vehicle look like an old one whose state (veh_lane
+// == -1) was then used: one wrong read in ~3e5 insertions on the 1000 x 1000 / 100 m grid, a fault where lane_edge[-1] is unmapped.
+SB2_HD bool ins_is_new(const Ctx& c, int v) { return ld_coherent(&c.veh_depart_time[v]) == c.t; }
 // getLastAnyVehicle of another lane, without this step's departures
 SB2_HD int ins_lane_last_any(const Ctx& c, int l, bool snapshot) {
-    int last = c.lane_last[l];
+    int last = snapshot ? ld_coherent(&c.lane_last[l]) : c.lane_last[l];
     while (snapshot && last >= 0 && ins_is_new(c, last)) {
-        last = c.veh_ahead[last];
+        last = ld_coherent(&c.veh_ahead[last]);
     }
     if (last >= 0) {
         return last;
@@ -35,9 +39,9 @@ SB2_HD int ins_lane_last_any(const Ctx& c, int l, bool snapshot) {
 }
 // front-most vehicle of another lane, without this step's departures
 SB2_HD int ins_lane_first(const Ctx& c, int l, bool snapshot) {
-    int first = c.lane_first[l];
+    int first = snapshot ? ld_coherent(&c.lane_first[l]) : c.lane_first[l];
     while (snapshot && first >= 0 && ins_is_new(c, first)) {
-        first = c.veh_behind[first];
+        first = ld_coherent(&c.veh_behind[first]);
     }
     return first;
 }

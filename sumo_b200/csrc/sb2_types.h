@@ -282,6 +282,15 @@ SB2_HD int32_t atomic_exch(int32_t* p, int32_t v) {
     const int32_t old = *p; *p = v; return old;
 #endif
 }
+// Load that bypasses the (non-coherent) L1: for data another thread of the SAME kernel may have written, published with a
+// __threadfence().  A plain load may hit a line this SM cached before the write and return the old contents.
+template<class T> SB2_HD T ld_coherent(const T* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldcg(p);
+#else
+    return *p;
+#endif
+}
 SB2_HD void atomic_inc(int32_t* p) {
 #if defined(__CUDA_ARCH__)
     atomicAdd(p, 1);
