@@ -46,6 +46,7 @@ extern "C" {
 #define SUMOB200_F_DEFERRED_UNRESOLVED 1024  /* executeMove pass 2 did not converge (sb2_exec.h) */
 #define SUMOB200_F_PARTITION_REACH 2048      /* a vehicle's look-ahead left the columns its rank simulates (edges too short for the ghost width) */
 #define SUMOB200_F_HALO_OVERFLOW 4096        /* a halo message needed more vehicle records than its capacity */
+#define SUMOB200_F_DETECTOR_OVERFLOW 8192    /* more E1 passages in one output interval than the event list holds, or > 4 detectors under one vehicle */
 
 typedef struct sumob200_engine sumob200_engine;
 
@@ -163,6 +164,27 @@ int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out);
  * threads -- race and must be serialised by the caller. */
 #define SUMOB200_SUMMARY_STATIC_MAX_VEHICLES 2097152
 int sumob200_summary_now_static(sumob200_engine* e, sumob200_summary* out);
+
+/* E1 induction loops (src/microsim/output/MSInductLoop.cpp; row f4).  Detectors are part of the scenario: optional arrays
+ * e1_lane (int32, lane index), e1_pos (float64, metres from the lane's start; negative = from its end, as
+ * NLDetectorBuilder::getPositionChecking does), e1_length (float64, optional; 0) -- what <inductionLoop lane= pos= length=/> of an
+ * additional file declares.  Vehicles notify the detectors during sumob200_step exactly as MSInductLoop::notifyEnter / notifyMove /
+ * notifyLeave do (entry and leave times interpolated inside the step by MSCFModel::passingTime).
+ * sumob200_e1_interval = MSInductLoop::writeXMLOutput (MSInductLoop.cpp:456-493) for every detector at once: the aggregates of the
+ * interval [begin_ms, end_ms) that ends NOW (end_ms must be the engine's time: call it after the step that completes the period,
+ * where MSDetectorControl::writeOutput(step + DELTA_T) fires), written to out[detector]; then MSInductLoop::reset.  The XML line
+ * stays with the reference's writer.  Not supported together with sumob200_set_partition (SUMOB200_EUNSUPPORTED). */
+typedef struct sumob200_e1_interval_t {
+    int32_t n_veh_contrib;        /* nVehContrib: vehicles that passed completely */
+    int32_t n_veh_entered;        /* nVehEntered */
+    double flow;                  /* veh/h */
+    double occupancy;             /* % */
+    double speed;                 /* mean of the passages' speeds, -1 if none */
+    double harmonic_mean_speed;   /* -1 if none */
+    double length;                /* mean vehicle length, -1 if none */
+} sumob200_e1_interval_t;
+int sumob200_e1_count(const sumob200_engine* e);
+int sumob200_e1_interval(sumob200_engine* e, int64_t begin_ms, int64_t end_ms, sumob200_e1_interval_t* out, int capacity);
 
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],

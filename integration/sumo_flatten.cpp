@@ -61,6 +61,8 @@
 #include <utils/iodevices/OutputDevice_String.h>
 #include <utils/common/StringTokenizer.h>
 #include <microsim/MSEdgeControl.h>
+#include <microsim/output/MSDetectorControl.h>
+#include <microsim/output/MSInductLoop.h>
 #include <random>
 #include <list>
 #include <set>
@@ -622,6 +624,38 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         }
         ff.put("route_begin", routeBegin);
         ff.put("route_edges", routeEdges);
+    }
+    // ---------------- E1 induction loops (NLDetectorBuilder::buildInductLoop; row f4): lane, position, length, in id order (the
+    // order MSDetectorControl::writeOutput visits them).  Other detector types are not modelled by the engine: refused.
+    {
+        MSDetectorControl& dc = net->getDetectorControl();
+        for (const SumoXMLTag tag : dc.getAvailableTypes()) {
+            if (tag != SUMO_TAG_INDUCTION_LOOP && dc.getTypedDetectors(tag).size() > 0) {
+                throw ProcessError("sumob200: detectors of type '" + toString(tag) + "' are not supported (only inductionLoop / e1Detector)");
+            }
+        }
+        std::vector<int32_t> e1Lane;
+        std::vector<double> e1Pos, e1Length;
+        NameTable e1Names;
+        for (const auto& item : dc.getTypedDetectors(SUMO_TAG_INDUCTION_LOOP)) {
+            const MSInductLoop* loop = dynamic_cast<const MSInductLoop*>(item.second);
+            if (loop == nullptr) {
+                throw ProcessError("sumob200: unexpected detector object '" + item.first + "'");
+            }
+            if (!loop->getVehicleTypes().empty() || loop->detectsPersons()) {
+                throw ProcessError("sumob200: detector '" + item.first + "': vTypes / detectPersons filters are not supported");
+            }
+            e1Lane.push_back(lIdx(loop->getLane()));
+            e1Pos.push_back(loop->getPosition());
+            e1Length.push_back(loop->getEndPosition() - loop->getPosition());
+            e1Names.add(item.first);
+        }
+        if (!e1Lane.empty()) {
+            ff.put("e1_lane", e1Lane);
+            ff.put("e1_pos", e1Pos);
+            ff.put("e1_length", e1Length);
+            e1Names.put(ff, "e1");
+        }
     }
     // ---------------- options the step depends on (MSFrame::setMSGlobals, MSFrame.cpp:1172-1283)
     ff.putScalar<int64_t>("opt_delta_t", DELTA_T);

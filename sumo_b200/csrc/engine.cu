@@ -30,6 +30,7 @@
 #include "sb2_kernelset.h"
 #include "sb2_fcdxml.h"
 #include "sb2_summary.h"
+#include "sb2_e1_host.h"
 #include "sb2_halo.h"
 
 using namespace sb2;
@@ -204,6 +205,8 @@ int reslot(sumob200_engine* e) {
             bytes = b->elem * MAX_FURTHER;          // vehicle-major rows
         } else if (b->name == "veh_em" && b->count == (size_t)nV * 7) {
             rows = 7;                               // pollutant-major: seven arrays of nV
+        } else if (b->name.compare(0, 7, "veh_e1_") == 0 && b->count == (size_t)nV * MAX_E1_REMINDERS) {
+            rows = MAX_E1_REMINDERS;                // reminder-slot-major
         } else {
             continue;                               // (veh_em of a scenario without emission devices: one dummy element)
         }
@@ -558,6 +561,10 @@ int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const in
     if (e == nullptr || lane_vis == nullptr || exp_lanes == nullptr || imp_lanes == nullptr || n_exp == nullptr || n_imp == nullptr || capacity <= 0 || e->partitioned) {
         gLastError = "sumob200_set_partition: bad argument (or called twice)";
         return SUMOB200_EINVAL;
+    }
+    if (e->d.nE1 > 0) {
+        gLastError = "sumob200_set_partition: E1 detectors are not carried across partitions yet";
+        return SUMOB200_EUNSUPPORTED;
     }
     const int nL = e->d.nL;
     for (int side = 0; side < 2; side++) {
@@ -922,6 +929,45 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
 }
 
 }  // extern "C"
+
+// ---- E1 induction loops (sb2_e1.h) ---------------------------------------------------------------------------------------
+extern "C" int sumob200_e1_count(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nE1; }
+
+extern "C" int sumob200_e1_interval(sumob200_engine* e, int64_t begin_ms, int64_t end_ms, sumob200_e1_interval_t* out, int capacity) {
+    static_assert(sizeof(sumob200_e1_interval_t) == sizeof(sb2::E1Result), "public and internal E1 record differ");
+    if (e == nullptr || out == nullptr || capacity < e->d.nE1 || end_ms <= begin_ms) {
+        gLastError = "sumob200_e1_interval: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    if (end_ms != e->d.t) {
+        gLastError = "sumob200_e1_interval: the interval must end at the engine's current time";
+        return SUMOB200_EINVAL;
+    }
+    const int nD = e->d.nE1;
+    if (nD == 0) {
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    cudaStream_t s = e->stream;
+    e->ks->e1_collect(&e->d, e->d.nV, s);
+    e->launches += 1;
+    int32_t counters[16];
+    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
+    std::vector<int32_t> entered((size_t)nD);
+    CUDA_TRY(cudaMemcpyAsync(entered.data(), e->d.e1_entered, sizeof(int32_t) * (size_t)nD, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    const int n = counters[12] < e->d.e1_event_cap ? counters[12] : e->d.e1_event_cap;   // (an overflow has raised its flag)
+    std::vector<sb2::E1Event> ev((size_t)n);
+    if (n > 0) {
+        CUDA_TRY(cudaMemcpyAsync(ev.data(), e->d.e1_events, sizeof(sb2::E1Event) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    }
+    // MSInductLoop::reset
+    CUDA_TRY(cudaMemsetAsync(e->d.counters + 12, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaMemsetAsync(e->d.e1_entered, 0, sizeof(int32_t) * (size_t)nD, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    sb2::e1_reduce(ev, entered.data(), nD, e->model.h.e1_pos, e->model.h.e1_end, begin_ms, end_ms, reinterpret_cast<sb2::E1Result*>(out));
+    return 0;
+}
 
 // ---- sumob200_summary_now_static: sumob200_summary_now without any allocation --------------------------------------------------
 // No counterpart in the reference; added for callers that must not allocate device memory

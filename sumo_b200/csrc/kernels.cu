@@ -508,6 +508,14 @@ __global__ void __launch_bounds__(BLOCK) k_halo_unpack(const __grid_constant__ C
     halo_unpack_vehicle(c, msg, i);
 }
 
+// E1 detectors: the vehicles on a detector at the end of an output interval (sb2_e1.h)
+__global__ void __launch_bounds__(BLOCK) k_e1_collect(const __grid_constant__ Ctx c) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < c.nV && c.nE1 > 0) {
+        veh_e1_collect_on_detector(c, v);
+    }
+}
+
 // ---- re-slotting (engine.cu reslot): renumber the on-road vehicles in lane order ------------------------------------------------
 // per block of lanes: number of vehicles on them
 __global__ void __launch_bounds__(BLOCK) k_rs_lanecount(const __grid_constant__ Ctx c, int32_t* blockCount) {
@@ -686,13 +694,14 @@ int l_reslot_maps(const void* c, int nL, int nV, int32_t* blocksA, int32_t* bloc
     k_rs_maps<<<nbV, BLOCK, 0, s>>>(order, sorted, blocksB + nbV, newOfOld, oldOfNew);
     return 8;
 }
+void l_e1_collect(const void* c, int n, cudaStream_t s) { k_e1_collect<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
 int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int appBuf, cudaStream_t s) {
     const size_t n = (size_t)nV * MAX_DRIVE_ITEMS > (size_t)nL ? (size_t)nV * MAX_DRIVE_ITEMS : (size_t)nL;
     k_rs_remap<<<(unsigned)((n + BLOCK - 1) / BLOCK), BLOCK, 0, s>>>(ctx(c), newOfOld, appBuf);
     return 1;
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap, l_e1_collect};
 
 }  // namespace sb2_kset_<name>
 

@@ -557,6 +557,57 @@ public:
             f[1] = g[1] = ff.scalar<double>("opt_min_deceleration", 4.5);
             f[2] = g[2] = ff.scalar<double>("opt_max_mingap", 0.);
         }
+        // ---------------- E1 induction loops (optional arrays e1_lane, e1_pos, e1_length; sb2_e1.h)
+        {
+            const int nD = ff.has("e1_lane") ? (int)ff.count("e1_lane") : 0;
+            if (nD > 0 && (!ff.has("e1_pos") || (int)ff.count("e1_pos") != nD || (ff.has("e1_length") && (int)ff.count("e1_length") != nD))) {
+                throw std::invalid_argument("sumob200: e1_lane / e1_pos / e1_length must have the same length");
+            }
+            h.nE1 = nD;
+            int32_t* lb = add<int32_t>("lane_e1_begin", SB2_OFF(lane_e1_begin), (size_t)nL + 1, false, 0);
+            int32_t* of = add<int32_t>("e1_of_lane", SB2_OFF(e1_of_lane), (size_t)nD, false, 0);
+            double* dp = add<double>("e1_pos", SB2_OFF(e1_pos), (size_t)nD, false, 0.);
+            double* de = add<double>("e1_end", SB2_OFF(e1_end), (size_t)nD, false, 0.);
+            if (nD > 0) {
+                checkIndex(ff, "e1_lane", 0, nL);
+                const int32_t* dl = ff.ptr<int32_t>("e1_lane");
+                const double* pp = ff.ptr<double>("e1_pos");
+                const double* pl = ff.has("e1_length") ? ff.ptr<double>("e1_length") : nullptr;
+                for (int d = 0; d < nD; d++) {
+                    // NLDetectorBuilder::getPositionChecking: a negative position counts from the lane's end
+                    double pos = pp[d];
+                    if (pos < 0) {
+                        pos += h.lane_length[dl[d]];
+                    }
+                    const double len = pl != nullptr ? pl[d] : 0.;
+                    if (pos < 0 || len < 0 || pos + len > h.lane_length[dl[d]]) {
+                        throw std::invalid_argument("sumob200: an E1 detector does not lie on its lane");
+                    }
+                    dp[d] = pos;
+                    de[d] = pos + len;
+                    lb[dl[d] + 1]++;
+                }
+                for (int l = 0; l < nL; l++) {
+                    lb[l + 1] += lb[l];
+                }
+                std::vector<int32_t> fill(lb, lb + nL);
+                for (int d = 0; d < nD; d++) {
+                    of[fill[dl[d]]++] = d;
+                }
+            }
+            const size_t nR = nD > 0 ? (size_t)nV * MAX_E1_REMINDERS : 1;
+            SB2_DYN(int32_t, veh_e1_det, nR, -1); SB2_DYN(double, veh_e1_off, nR, 0.); SB2_DYN(double, veh_e1_entry, nR, E1_NOT_ON);
+            SB2_DYN(int32_t, e1_entered, (size_t)nD, 0);
+            // room for the passages of one output interval: every vehicle over a few detectors, or every detector a few thousand times
+            h.e1_event_cap = nD > 0 ? (int)std::min<size_t>((size_t)1 << 26, std::max<size_t>((size_t)4 * nV + 65536, (size_t)64 * nD))
+                                    : 1;
+            if (ff.has("e1_event_capacity")) {
+                h.e1_event_cap = std::max(1, ff.scalar<int32_t>("e1_event_capacity", 1));
+            }
+            E1Event none;
+            none.det = -1; none.veh = -1; none.entry = 0; none.leave = 0; none.length = 0; none.leftEarly = 0; none.pad = 0;
+            SB2_DYN(E1Event, e1_events, (size_t)h.e1_event_cap, none);
+        }
         SB2_DYN(int32_t, err_flags, 1, 0);
         SB2_DYN(int32_t, counters, 16, 0);
     }

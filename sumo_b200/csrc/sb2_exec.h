@@ -16,6 +16,7 @@
 #include "sb2_veh.h"
 #include "sb2_link.h"
 #include "sb2_emis.h"
+#include "sb2_e1.h"
 
 namespace sb2 {
 
@@ -278,6 +279,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
                     odometer += c.lane_length[myLane];
                     pos -= c.lane_length[myLane];
                     // enterLaneAtMove
+                    veh_e1_enter_at_move(c, v, myLane, approachedLane);
                     myLane = approachedLane;
                     if (!lane_internal(c, myLane)) {
                         ++routePos;
@@ -376,7 +378,9 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
         c.veh_trip_amwaiting[v] = 0;
     }
     veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
+    veh_e1_move(c, v, pos - lastDist, pos, speed);     //                                          -> MSInductLoop::notifyMove
     if (arrived) {
+        veh_e1_leave_net(c, v);        // onRemovalFromNet(NOTIFICATION_ARRIVED) -> leaveLane -> notifyLeave
         c.veh_moved[v] = 2;
         c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
         c.veh_arrival_lane[v] = myLane;

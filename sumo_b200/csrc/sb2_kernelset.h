@@ -31,6 +31,8 @@ struct sb2_kernelset {
     int (*reslot_maps)(const void* ctx, int n_lanes, int n_vehicles, int32_t* blocks_a, int32_t* blocks_b, int32_t* order, int32_t* sorted,
                        int32_t* new_of_old, int32_t* old_of_new, cudaStream_t s);
     int (*reslot_remap)(const void* ctx, int n_lanes, int n_vehicles, const int32_t* new_of_old, int app_buf, cudaStream_t s);
+    /* E1 detectors (sb2_e1.h): append the vehicles that are on a detector right now to the event list */
+    void (*e1_collect)(const void* ctx, int n_vehicles, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

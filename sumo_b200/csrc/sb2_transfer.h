@@ -183,6 +183,7 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
                 // "teleports beyond arrival edge": leaveLane(NOTIFICATION_TELEPORT_ARRIVED), scheduleVehicleRemoval
                 // (MSVehicleControl::removePending runs in the NEXT step's executeMovements: until then the vehicle still counts as
                 // running in the summary output -- veh_moved 4, see summary_vehicle)
+                veh_e1_leave_net(c, v);
                 c.veh_arrival_time[v] = time;
                 c.veh_arrival_lane[v] = c.edge_lane_begin[e];
                 c.veh_moved[v] = 4;
@@ -197,6 +198,8 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
             c.veh_trip_routelen[v] += c.lane_length[cl];
             c.veh_routepos[v] += 1;
             c.veh_tp_proceed[v] = time + TIME2STEPS(edge_current_travel_time(c, e, 1.));
+            veh_e1_leave_net(c, v);
+            veh_e1_add_lane(c, v, c.edge_lane_begin[nextEdge], false, 0., 0.);
         }
         list[keep++] = v;
     }

@@ -68,7 +68,7 @@ typedef int64_t SUMOTime;
 #define SB2_NO_INTERSECTION 10000.0              /* MSLink.cpp:76 */
 #define SB2_EMERGENCY_DECEL_AMPLIFIER 1.2        /* MSCFModel.h:35 */
 
-enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4 };
+enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4, MAX_E1_REMINDERS = 4 };
 
 // lane_flags / edge_flags bits (include/sumob200_flatfile.h)
 enum { LF_INTERNAL = 1, LF_ROUNDABOUT = 2, LF_FRINGE = 4, LF_LANECHANGER = 8 };
@@ -84,7 +84,7 @@ enum { LL_IN_THE_WAY = 1, LL_FROM_LEFT = 2, LL_SAME_SOURCE = 4, LL_SAME_TARGET =
 // error / event flags raised by kernels (never silently ignored: sumob200_step returns them)
 enum {
     ERR_DRIVE_ITEM_OVERFLOW = 1, ERR_FURTHER_OVERFLOW = 2, ERR_PARTIAL_OVERFLOW = 4, ERR_COLLISION = 8, ERR_TELEPORT = 16,
-    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512, ERR_DEFERRED_UNRESOLVED = 1024, ERR_PARTITION_REACH = 2048, ERR_HALO_OVERFLOW = 4096
+    ERR_EMERGENCY_STOP = 32, ERR_NO_CONNECTION = 64, ERR_UNSUPPORTED_LINKSTATE = 128, ERR_LANE_ORDER = 256, ERR_LINKLEADER_OVERFLOW = 512, ERR_DEFERRED_UNRESOLVED = 1024, ERR_PARTITION_REACH = 2048, ERR_HALO_OVERFLOW = 4096, ERR_DETECTOR_OVERFLOW = 8192
 };
 // car-following model ids = SUMO_TAG_CF_* values are remapped at load time
 enum { CF_KRAUSS = 0, CF_KRAUSS_ORIG1 = 1, CF_IDM = 2 };
@@ -104,6 +104,19 @@ struct AppRec {
     int64_t leavetime;       // leavingTime (MSLink::getLeaveTime at registration)
     double arrspeedbraking;  // arrivalSpeedBraking
 };
+
+// one entry of MSInductLoop::myVehicleDataCont (VehicleData, MSInductLoop.cpp:561-565) -- or, with leave == E1_STILL_ON, one entry of
+// myVehiclesOnDet at the time the interval was collected
+struct E1Event {
+    int32_t det;
+    int32_t veh;         // external index (load order)
+    double entry, leave; // seconds
+    double length;       // vehicle length
+    int32_t leftEarly;
+    int32_t pad;
+};
+#define E1_NOT_ON (-1e300)
+#define E1_STILL_ON (-1e300)
 
 struct Ctx {
     // ---- options (MSGlobals) -------------------------------------------------------------
@@ -213,6 +226,17 @@ struct Ctx {
     // route edge veh_routepos until they fit on a lane again.  tp_list[0 .. counters[10]) = their slots (appended with an atomic,
     // sorted by numerical id in checkInsertions like the reference's std::sort), veh_tp_proceed = myProceedTime (-1 = not set)
     int32_t* tp_list; SUMOTime* veh_tp_proceed;
+    // ---- E1 induction loops (MSInductLoop as a move reminder, sb2_e1.h); nE1 == 0: every array has one dummy element
+    int nE1, e1_event_cap;
+    const int32_t* lane_e1_begin;    // [nL+1] CSR: detectors of a lane = e1_of_lane[lane_e1_begin[l] .. lane_e1_begin[l+1])
+    const int32_t* e1_of_lane;       // [nE1] detector indices sorted by lane (load order within a lane)
+    const double* e1_pos;            // [nE1] myPosition
+    const double* e1_end;            // [nE1] myEndPosition = position + length
+    int32_t* veh_e1_det;             // [MAX_E1_REMINDERS][nV] the vehicle's active reminders (MSBaseVehicle::myMoveReminders): detector or -1
+    double* veh_e1_off;              // [MAX_E1_REMINDERS][nV] rem->second: length of the lanes left since the detector's lane
+    double* veh_e1_entry;            // [MAX_E1_REMINDERS][nV] myVehiclesOnDet[veh] (entry time in s), E1_NOT_ON if not on the detector
+    int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
+    struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
     uint8_t* edge_delayed;     // MSEdge::myAmDelayed (a vehicle has entered the edge at some time, MSEdge.h:750)
     // ---- multi-GPU edge partition (sb2_halo.h): what this rank does with each lane.  nullptr = one partition owning everything.
     //   LV_AUTH  lanes of the rank's own junction columns: simulated here, results authoritative (counted, reported, exported)
@@ -254,7 +278,7 @@ struct Ctx {
     int traci_speed_used; double* veh_traci_speed;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
-    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step
+    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step, 12 length of e1_events
 };
 
 SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }

@@ -17,7 +17,8 @@ LIB_PATH = os.environ.get("SUMOB200_LIB") or os.path.join(_HERE, "libsumob200.so
 
 FLAGS = {
     1: "drive item overflow", 2: "further-lane overflow", 4: "partial occupator overflow", 8: "collision", 16: "teleport",
-    32: "emergency stop", 64: "no connection", 128: "unsupported link state", 256: "lane order", 512: "search overflow", 1024: "executeMove pass 2 unresolved",
+    32: "emergency stop", 64: "no connection", 128: "unsupported link state", 256: "lane order", 512: "search overflow", 1024: "executeMove pass 2 unresolved", 2048: "look-ahead beyond the partition's ghost column", 4096: "halo message overflow",
+    8192: "detector event list / reminder overflow",
 }
 
 
@@ -46,6 +47,8 @@ SUMMARY = np.dtype([("time_ms", np.int64), ("inserted", np.int32), ("running", n
                     ("arrived", np.int32), ("collisions", np.int32), ("teleports", np.int32), ("halting", np.int32), ("stopped", np.int32),
                     ("reserved", np.int32), ("mean_waiting_time", np.float64), ("mean_travel_time", np.float64), ("mean_speed", np.float64),
                     ("mean_speed_relative", np.float64)])
+E1_INTERVAL = np.dtype([("n_veh_contrib", np.int32), ("n_veh_entered", np.int32), ("flow", np.float64), ("occupancy", np.float64),
+                        ("speed", np.float64), ("harmonic_mean_speed", np.float64), ("length", np.float64)])
 FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
                     ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
 
@@ -78,6 +81,8 @@ def load_library(path=None):
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_summary_now_static.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.sumob200_e1_count.argtypes = [ctypes.c_void_p]
+    lib.sumob200_e1_interval.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_tls.argtypes = [ctypes.c_void_p]
     lib.sumob200_vehicles_set_speed.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
@@ -231,6 +236,14 @@ class Engine:
         out = np.zeros(1, dtype=SUMMARY)
         _check(self._lib, self._lib.sumob200_summary_now_static(self._h, out.ctypes.data), "sumob200_summary_now_static")
         return out[0]
+
+    def e1_interval(self, begin_ms, end_ms):
+        """MSInductLoop::writeXMLOutput for every E1 detector of the scenario: the aggregates of [begin_ms, end_ms) -- end_ms must be
+        the engine's current time --, then the detectors are reset (array of dtype E1_INTERVAL, one record per detector)"""
+        n = self._lib.sumob200_e1_count(self._h)
+        out = np.zeros(max(n, 1), dtype=E1_INTERVAL)
+        _check(self._lib, self._lib.sumob200_e1_interval(self._h, int(begin_ms), int(end_ms), out.ctypes.data, out.shape[0]), "sumob200_e1_interval")
+        return out[:n]
 
     def emissions(self):
         """[7, num_vehicles] accumulated CO2, CO, HC, fuel, NOx, PMx, electricity of every vehicle slot"""

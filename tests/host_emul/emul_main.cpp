@@ -25,6 +25,7 @@
 #include "../../sumo_b200/csrc/sb2_fcd.h"
 #include "../../sumo_b200/csrc/sb2_fcdxml.h"
 #include "../../sumo_b200/csrc/sb2_summary.h"
+#include "../../sumo_b200/csrc/sb2_e1_host.h"
 
 using namespace sb2;
 
@@ -316,7 +317,8 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out;
+    long long e1Period = 60000;
     long maxSteps = -1;
     std::string debugName, partFile;
     for (int i = 2; i < argc; i++) {
@@ -333,6 +335,10 @@ int main(int argc, char** argv) {
             tlsSetPhase = argv[++i];   // "timeMs:tlsIndex:phase;..." applied before the step at that time (sumob200_tls_set_phase)
         } else if (a == "--veh-set-speed" && i + 1 < argc) {
             vehSetSpeed = argv[++i];   // "timeMs:slot:speed;..." applied before the step at that time if the vehicle is on the road (sumob200_vehicles_set_speed)
+        } else if (a == "--e1-out" && i + 1 < argc) {
+            e1Out = argv[++i];   // text, one line per detector and interval: the attributes of the reference's E1 output (sumob200_e1_interval)
+        } else if (a == "--e1-period" && i + 1 < argc) {
+            e1Period = atoll(argv[++i]);   // ms
         } else if (a == "--summary-out" && i + 1 < argc) {
             summaryOut = argv[++i];   // text, one line per step: the attributes of the reference's --summary-output
         } else if (a == "--tripinfo-out" && i + 1 < argc) {
@@ -380,6 +386,7 @@ int main(int argc, char** argv) {
     std::sort(order.begin(), order.end(), [&](int a, int b) { return c.veh_numid[a] < c.veh_numid[b]; });
     FILE* ffcdxml = fcdXmlOut.empty() ? nullptr : fopen(fcdXmlOut.c_str(), "w");
     FILE* fsum = summaryOut.empty() ? nullptr : fopen(summaryOut.c_str(), "w");
+    FILE* fe1 = e1Out.empty() ? nullptr : fopen(e1Out.c_str(), "w");
     FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
     FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
@@ -486,6 +493,23 @@ int main(int argc, char** argv) {
                     p.ended != 0 ? ((double)p.travel_ms / 1000.) / (double)p.ended : -1., p.count > 0 ? p.speedSum / p.count : -1.,
                     p.count > 0 ? p.relSpeedSum / p.count : -1.);
         }
+        if (fe1 != nullptr && c.nE1 > 0 && (t + c.DELTA_T) % e1Period == 0) {
+            // MSDetectorControl::writeOutput(step + DELTA_T): the interval [t + DELTA_T - period, t + DELTA_T)
+            for (int v = 0; v < c.nV; v++) {
+                veh_e1_collect_on_detector(c, v);
+            }
+            const int n = std::min(c.counters[12], c.e1_event_cap);
+            std::vector<E1Event> ev(c.e1_events, c.e1_events + n);
+            std::vector<E1Result> res((size_t)c.nE1);
+            e1_reduce(ev, c.e1_entered, c.nE1, c.e1_pos, c.e1_end, t + c.DELTA_T - e1Period, t + c.DELTA_T, res.data());
+            c.counters[12] = 0;
+            for (int d = 0; d < c.nE1; d++) {
+                c.e1_entered[d] = 0;
+                // begin end detector nVehContrib flow occupancy speed harmonicMeanSpeed length nVehEntered
+                fprintf(fe1, "%lld %lld %d %d %.17g %.17g %.17g %.17g %.17g %d\n", (long long)(t + c.DELTA_T - e1Period), (long long)(t + c.DELTA_T), d,
+                        res[d].nVehContrib, res[d].flow, res[d].occupancy, res[d].speed, res[d].harmonicMeanSpeed, res[d].length, res[d].nVehEntered);
+            }
+        }
         if (femis != nullptr) {
             int64_t ne = 0;
             for (int v : order) {
@@ -526,6 +550,9 @@ int main(int argc, char** argv) {
     }
     if (ffcd != nullptr) {
         fclose(ffcd);
+    }
+    if (fe1 != nullptr) {
+        fclose(fe1);
     }
     if (fsum != nullptr) {
         fclose(fsum);
