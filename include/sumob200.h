@@ -185,6 +185,21 @@ typedef struct sumob200_e1_interval_t {
 } sumob200_e1_interval_t;
 int sumob200_e1_count(const sumob200_engine* e);
 int sumob200_e1_interval(sumob200_engine* e, int64_t begin_ms, int64_t end_ms, sumob200_e1_interval_t* out, int capacity);
+/* The raw passages instead of the aggregates, for a caller that keeps the reference's MSInductLoop objects (the hook of
+ * integration/sumo_b200_hook.cpp fills their myVehicleDataCont / myVehiclesOnDet with them, so that the reference's own
+ * writeXMLOutput and the libsumo getters work): everything since the last drain / interval call, sorted by (detector, leave time,
+ * vehicle), the vehicles that are on a detector right now last per detector with leave_s = SUMOB200_E1_STILL_ON; entered[detector]
+ * = vehicles that entered since the last call (may be NULL).  Resets the device-side lists like sumob200_e1_interval. */
+#define SUMOB200_E1_STILL_ON (-1e300)
+typedef struct sumob200_e1_event {
+    int32_t detector;
+    int32_t vehicle;          /* slot (load order) */
+    double entry_s, leave_s;  /* simulation seconds, interpolated inside the step */
+    double vehicle_length;
+    int32_t left_early;       /* 1: arrived / teleported while on the detector (MSInductLoop::notifyLeave) */
+    int32_t reserved;
+} sumob200_e1_event;
+int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, int capacity, int* n, int32_t* entered);
 
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],

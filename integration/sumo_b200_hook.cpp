@@ -52,6 +52,8 @@
 #include <microsim/MSVehicle.h>
 #include <microsim/MSVehicleControl.h>
 #include <microsim/MSNet.h>
+#include <microsim/output/MSDetectorControl.h>
+#include <microsim/output/MSInductLoop.h>
 #undef private
 #undef protected
 #define SUMOB200_NO_MAIN
@@ -76,6 +78,9 @@ struct Hook {
     std::vector<sumob200_vehicle_state> state;
     std::vector<sumob200_fcd_row> rows;
     std::vector<char> wasOnRoad;
+    std::vector<MSInductLoop*> loops;                 // the E1 detectors in the order the flatten walk exported them (id order)
+    std::vector<sumob200_e1_event> e1Events;
+    std::vector<int32_t> e1Entered;
     int lastDeparted = 0, lastArrived = 0;
 
     static Hook* create(MSNet* net) {
@@ -113,6 +118,14 @@ struct Hook {
         for (int s = 0; s < nV; s++) {
             h->vehOfSlot.push_back(byNumId[numid[s]]);
         }
+        for (const auto& item : net->getDetectorControl().getTypedDetectors(SUMO_TAG_INDUCTION_LOOP)) {
+            h->loops.push_back(dynamic_cast<MSInductLoop*>(item.second));
+        }
+        if ((int)h->loops.size() != sumob200_e1_count(h->eng)) {
+            throw ProcessError("sumob200: detector lists of the reference and the engine differ");
+        }
+        h->e1Entered.resize(h->loops.size() + 1);
+        h->e1Events.resize(4 * (size_t)nV + 65536);
         h->state.resize(nV > 0 ? nV : 1);
         h->rows.resize(nV > 0 ? nV : 1);
         h->wasOnRoad.assign(nV, 0);
@@ -154,6 +167,32 @@ struct Hook {
             if (wasOnRoad[s] && state[s].lane < 0) {
                 wasOnRoad[s] = 2;
                 vehOfSlot[s]->myAmOnNet = false;   // arrived (or teleporting): not visible to the output writers
+            }
+        }
+        // ---- E1 detectors: this step's passages into the reference's own MSInductLoop objects (their writeXMLOutput, called by
+        // MSDetectorControl::writeOutput below, and the libsumo::InductionLoop getters then work unchanged)
+        if (!loops.empty()) {
+            int nEv = 0;
+            if (sumob200_e1_drain(eng, e1Events.data(), (int)e1Events.size(), &nEv, e1Entered.data()) != 0) {
+                throw ProcessError(std::string("sumob200_e1_drain failed: ") + sumob200_last_error());
+            }
+            for (size_t d = 0; d < loops.size(); d++) {
+                loops[d]->myVehiclesOnDet.clear();
+                loops[d]->myEnteredVehicleNumber += e1Entered[d];
+            }
+            for (int i = 0; i < nEv; i++) {
+                const sumob200_e1_event& ev = e1Events[i];
+                MSInductLoop* loop = loops[ev.detector];
+                MSVehicle* v = vehOfSlot[ev.vehicle];
+                if (ev.leave_s == SUMOB200_E1_STILL_ON) {
+                    loop->myVehiclesOnDet[v] = ev.entry_s;
+                } else if (ev.left_early) {
+                    loop->myVehicleDataCont.push_back(MSInductLoop::VehicleData(*v, ev.entry_s, ev.leave_s, true));
+                    loop->myLastLeaveTime = ev.leave_s;
+                } else {
+                    loop->myVehicleDataCont.push_back(MSInductLoop::VehicleData(*v, ev.entry_s, ev.leave_s, false, loop->myEndPosition - loop->myPosition));
+                    loop->myLastLeaveTime = ev.leave_s;
+                }
             }
         }
         // ---- MSVehicleControl counters (summary output, MSNet::simulationState's termination test)

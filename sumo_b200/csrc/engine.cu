@@ -933,6 +933,34 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
 // ---- E1 induction loops (sb2_e1.h) ---------------------------------------------------------------------------------------
 extern "C" int sumob200_e1_count(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nE1; }
 
+namespace {
+
+// the event list of the running interval (+ pseudo events of the vehicles on a detector right now) and the entered counters,
+// copied to the host; the device side starts a new interval (MSInductLoop::reset)
+int e1Fetch(sumob200_engine* e, std::vector<sb2::E1Event>& ev, std::vector<int32_t>& entered) {
+    const int nD = e->d.nE1;
+    CUDA_TRY(cudaSetDevice(e->device));
+    cudaStream_t s = e->stream;
+    e->ks->e1_collect(&e->d, e->d.nV, s);
+    e->launches += 1;
+    int32_t counters[16];
+    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
+    entered.assign((size_t)nD, 0);
+    CUDA_TRY(cudaMemcpyAsync(entered.data(), e->d.e1_entered, sizeof(int32_t) * (size_t)nD, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    const int n = counters[12] < e->d.e1_event_cap ? counters[12] : e->d.e1_event_cap;   // (an overflow has raised its flag)
+    ev.resize((size_t)n);
+    if (n > 0) {
+        CUDA_TRY(cudaMemcpyAsync(ev.data(), e->d.e1_events, sizeof(sb2::E1Event) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    }
+    CUDA_TRY(cudaMemsetAsync(e->d.counters + 12, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaMemsetAsync(e->d.e1_entered, 0, sizeof(int32_t) * (size_t)nD, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return 0;
+}
+
+}  // namespace
+
 extern "C" int sumob200_e1_interval(sumob200_engine* e, int64_t begin_ms, int64_t end_ms, sumob200_e1_interval_t* out, int capacity) {
     static_assert(sizeof(sumob200_e1_interval_t) == sizeof(sb2::E1Result), "public and internal E1 record differ");
     if (e == nullptr || out == nullptr || capacity < e->d.nE1 || end_ms <= begin_ms) {
@@ -943,29 +971,45 @@ extern "C" int sumob200_e1_interval(sumob200_engine* e, int64_t begin_ms, int64_
         gLastError = "sumob200_e1_interval: the interval must end at the engine's current time";
         return SUMOB200_EINVAL;
     }
-    const int nD = e->d.nE1;
-    if (nD == 0) {
+    if (e->d.nE1 == 0) {
         return 0;
     }
-    CUDA_TRY(cudaSetDevice(e->device));
-    cudaStream_t s = e->stream;
-    e->ks->e1_collect(&e->d, e->d.nV, s);
-    e->launches += 1;
-    int32_t counters[16];
-    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
-    std::vector<int32_t> entered((size_t)nD);
-    CUDA_TRY(cudaMemcpyAsync(entered.data(), e->d.e1_entered, sizeof(int32_t) * (size_t)nD, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    const int n = counters[12] < e->d.e1_event_cap ? counters[12] : e->d.e1_event_cap;   // (an overflow has raised its flag)
-    std::vector<sb2::E1Event> ev((size_t)n);
-    if (n > 0) {
-        CUDA_TRY(cudaMemcpyAsync(ev.data(), e->d.e1_events, sizeof(sb2::E1Event) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    std::vector<sb2::E1Event> ev;
+    std::vector<int32_t> entered;
+    const int rc = e1Fetch(e, ev, entered);
+    if (rc != 0) {
+        return rc;
     }
-    // MSInductLoop::reset
-    CUDA_TRY(cudaMemsetAsync(e->d.counters + 12, 0, sizeof(int32_t), s));
-    CUDA_TRY(cudaMemsetAsync(e->d.e1_entered, 0, sizeof(int32_t) * (size_t)nD, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    sb2::e1_reduce(ev, entered.data(), nD, e->model.h.e1_pos, e->model.h.e1_end, begin_ms, end_ms, reinterpret_cast<sb2::E1Result*>(out));
+    sb2::e1_reduce(ev, entered.data(), e->d.nE1, e->model.h.e1_pos, e->model.h.e1_end, begin_ms, end_ms, reinterpret_cast<sb2::E1Result*>(out));
+    return 0;
+}
+
+extern "C" int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, int capacity, int* n, int32_t* entered_out) {
+    static_assert(sizeof(sumob200_e1_event) == sizeof(sb2::E1Event), "public and internal E1 event differ");
+    if (e == nullptr || events == nullptr || n == nullptr || capacity < 0) {
+        gLastError = "sumob200_e1_drain: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    *n = 0;
+    if (e->d.nE1 == 0) {
+        return 0;
+    }
+    std::vector<sb2::E1Event> ev;
+    std::vector<int32_t> entered;
+    const int rc = e1Fetch(e, ev, entered);
+    if (rc != 0) {
+        return rc;
+    }
+    if ((int)ev.size() > capacity) {
+        gLastError = "sumob200_e1_drain: " + std::to_string(ev.size()) + " events do not fit the caller's buffer (they are lost)";
+        return SUMOB200_EINVAL;
+    }
+    sb2::e1_sort(ev);
+    memcpy(events, ev.data(), sizeof(sb2::E1Event) * ev.size());
+    *n = (int)ev.size();
+    if (entered_out != nullptr) {
+        memcpy(entered_out, entered.data(), sizeof(int32_t) * entered.size());
+    }
     return 0;
 }
 

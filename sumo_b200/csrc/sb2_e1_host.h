@@ -13,8 +13,7 @@ struct E1Result {   // == sumob200_e1_interval
     int32_t nVehContrib, nVehEntered;
     double flow, occupancy, speed, harmonicMeanSpeed, length;
 };
-inline void e1_reduce(std::vector<E1Event>& ev, const int32_t* entered, int nD, const double* e1_pos, const double* e1_end,
-                      SUMOTime startTime, SUMOTime stopTime, E1Result* out) {
+inline void e1_sort(std::vector<E1Event>& ev) {
     std::sort(ev.begin(), ev.end(), [](const E1Event& a, const E1Event& b) {
         if (a.det != b.det) {
             return a.det < b.det;
@@ -28,6 +27,11 @@ inline void e1_reduce(std::vector<E1Event>& ev, const int32_t* entered, int nD, 
         }
         return a.veh < b.veh;
     });
+}
+
+inline void e1_reduce(std::vector<E1Event>& ev, const int32_t* entered, int nD, const double* e1_pos, const double* e1_end,
+                      SUMOTime startTime, SUMOTime stopTime, E1Result* out) {
+    e1_sort(ev);
     const double t = (double)(stopTime - startTime) / 1000.;
     const double start = (double)startTime / 1000., stop = (double)stopTime / 1000.;
     size_t at = 0;
