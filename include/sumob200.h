@@ -201,6 +201,22 @@ typedef struct sumob200_e1_event {
 } sumob200_e1_event;
 int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, int capacity, int* n, int32_t* entered);
 
+/* edgeData / laneData (src/microsim/output/MSMeanData.cpp:87-253, MSMeanData_Net.cpp:131-246; row f4).  Enabled by the scenario
+ * scalar md_enabled = 1 (optional md_halt_speed = haltingSpeedThreshold, default 0.1): every vehicle then reports the part of each
+ * step it spends on each non-internal lane exactly as MSMeanData::MeanDataValues::notifyMove does, and the engine accumulates per
+ * lane the raw members of MSMeanData_Net::MSLaneMeanDataValues.  sumob200_meandata_interval copies them out for ALL lanes
+ * (out[lane]; internal lanes stay zero) and starts a new interval (MSLaneMeanDataValues::reset).  The derived attributes of the
+ * <edge .../> line (density, traveltime, speed, flow, ...) are MSLaneMeanDataValues::write's business and stay with the reference's
+ * writer; edges with several lanes are summed by MSLaneMeanDataValues::addTo there.  The sums are accumulated with atomics: their
+ * last bits depend on the order of additions (the reference's differ too: it adds in lane execution order). */
+typedef struct sumob200_lane_meandata {
+    double sample_seconds, travelled_distance, wait_seconds, time_loss;
+    double front_sample_seconds, front_travelled_distance, veh_length_sum, occupation_sum;
+    double minimal_vehicle_length;   /* < 0: no vehicle seen (INVALID_DOUBLE) */
+    int32_t departed, arrived, entered, left, teleported, reserved;
+} sumob200_lane_meandata;
+int sumob200_meandata_interval(sumob200_engine* e, sumob200_lane_meandata* out, int capacity);
+
 /* accumulated emissions of every vehicle slot since its departure (MSDevice_Emissions::myEmissions, what tripinfo's
  * <emissions .../> and --emission-output report; src/microsim/devices/MSDevice_Emissions.cpp:122-135): out[p * n + slot],
  * p = 0 CO2, 1 CO, 2 HC, 3 fuel, 4 NOx, 5 PMx, 6 electricity [mg resp. ml resp. Wh], n = sumob200_num_vehicles.

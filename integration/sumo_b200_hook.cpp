@@ -52,6 +52,8 @@
 #include <microsim/MSVehicle.h>
 #include <microsim/MSVehicleControl.h>
 #include <microsim/MSNet.h>
+#include <microsim/output/MSMeanData.h>
+#include <microsim/output/MSMeanData_Net.h>
 #include <microsim/output/MSDetectorControl.h>
 #include <microsim/output/MSInductLoop.h>
 #undef private
@@ -81,6 +83,8 @@ struct Hook {
     std::vector<MSInductLoop*> loops;                 // the E1 detectors in the order the flatten walk exported them (id order)
     std::vector<sumob200_e1_event> e1Events;
     std::vector<int32_t> e1Entered;
+    std::vector<std::vector<MSMeanData_Net::MSLaneMeanDataValues*> > mdOfLane;   // per lane index: its values object in every <edgeData> / <laneData>
+    std::vector<sumob200_lane_meandata> mdBuf;
     int lastDeparted = 0, lastArrived = 0;
 
     static Hook* create(MSNet* net) {
@@ -123,6 +127,33 @@ struct Hook {
         }
         if ((int)h->loops.size() != sumob200_e1_count(h->eng)) {
             throw ProcessError("sumob200: detector lists of the reference and the engine differ");
+        }
+        {
+            std::map<const MSLane*, int> indexOfLane;
+            for (size_t i = 0; i < h->laneOfIndex.size(); i++) {
+                indexOfLane[h->laneOfIndex[i]] = (int)i;
+            }
+            bool any = false;
+            h->mdOfLane.resize(h->laneOfIndex.size());
+            for (const auto& item : net->getDetectorControl().getMeanData()) {
+                for (MSMeanData* md : item.second) {
+                    for (auto& edgeValues : md->myMeasures) {
+                        for (MSMeanData::MeanDataValues* v : edgeValues) {
+                            MSMeanData_Net::MSLaneMeanDataValues* lv = dynamic_cast<MSMeanData_Net::MSLaneMeanDataValues*>(v);
+                            if (lv == nullptr || lv->getLane() == nullptr) {
+                                throw ProcessError("sumob200: unexpected mean data container in '" + item.first + "'");
+                            }
+                            h->mdOfLane[indexOfLane[lv->getLane()]].push_back(lv);
+                            any = true;
+                        }
+                    }
+                }
+            }
+            if (any) {
+                h->mdBuf.resize(h->laneOfIndex.size());
+            } else {
+                h->mdOfLane.clear();
+            }
         }
         h->e1Entered.resize(h->loops.size() + 1);
         h->e1Events.resize(4 * (size_t)nV + 65536);
@@ -192,6 +223,37 @@ struct Hook {
                 } else {
                     loop->myVehicleDataCont.push_back(MSInductLoop::VehicleData(*v, ev.entry_s, ev.leave_s, false, loop->myEndPosition - loop->myPosition));
                     loop->myLastLeaveTime = ev.leave_s;
+                }
+            }
+        }
+        // ---- edgeData / laneData: this step's contributions added to the reference's MSLaneMeanDataValues objects, whose own
+        // write() / reset() (MSMeanData::writeXMLOutput, driven by MSDetectorControl::writeOutput below) then do the rest
+        if (!mdOfLane.empty()) {
+            if (sumob200_meandata_interval(eng, mdBuf.data(), (int)mdBuf.size()) != 0) {
+                throw ProcessError(std::string("sumob200_meandata_interval failed: ") + sumob200_last_error());
+            }
+            for (size_t l = 0; l < mdOfLane.size(); l++) {
+                const sumob200_lane_meandata& m = mdBuf[l];
+                if (m.sample_seconds == 0 && m.departed == 0 && m.arrived == 0 && m.entered == 0 && m.left == 0) {
+                    continue;
+                }
+                for (MSMeanData_Net::MSLaneMeanDataValues* lv : mdOfLane[l]) {
+                    lv->sampleSeconds += m.sample_seconds;
+                    lv->travelledDistance += m.travelled_distance;
+                    lv->waitSeconds += m.wait_seconds;
+                    lv->timeLoss += m.time_loss;
+                    lv->frontSampleSeconds += m.front_sample_seconds;
+                    lv->frontTravelledDistance += m.front_travelled_distance;
+                    lv->vehLengthSum += m.veh_length_sum;
+                    lv->occupationSum += m.occupation_sum;
+                    if (m.minimal_vehicle_length >= 0) {
+                        lv->minimalVehicleLength = lv->minimalVehicleLength == INVALID_DOUBLE ? m.minimal_vehicle_length : MIN2(lv->minimalVehicleLength, m.minimal_vehicle_length);
+                    }
+                    lv->nVehDeparted += m.departed;
+                    lv->nVehArrived += m.arrived;
+                    lv->nVehEntered += m.entered;
+                    lv->nVehLeft += m.left;
+                    lv->nVehTeleported += m.teleported;
                 }
             }
         }

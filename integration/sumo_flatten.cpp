@@ -63,6 +63,7 @@
 #include <microsim/MSEdgeControl.h>
 #include <microsim/output/MSDetectorControl.h>
 #include <microsim/output/MSInductLoop.h>
+#include <microsim/output/MSMeanData_Net.h>
 #include <random>
 #include <list>
 #include <set>
@@ -106,6 +107,26 @@ struct PedFoeTag {
     friend type get(PedFoeTag);
 };
 template struct Rob<PedFoeTag, &MSLink::myHavePedestrianCrossingFoe>;
+struct MdHaltTag {
+    typedef const double MSMeanData_Net::* type;
+    friend type get(MdHaltTag);
+};
+template struct Rob<MdHaltTag, &MSMeanData_Net::myHaltSpeed>;
+struct MdHaltRelTag {
+    typedef const double MSMeanData_Net::* type;
+    friend type get(MdHaltRelTag);
+};
+template struct Rob<MdHaltRelTag, &MSMeanData_Net::myHaltSpeedRel>;
+struct MdTrackTag {
+    typedef const bool MSMeanData::* type;
+    friend type get(MdTrackTag);
+};
+template struct Rob<MdTrackTag, &MSMeanData::myTrackVehicles>;
+struct MdInternalTag {
+    typedef const bool MSMeanData::* type;
+    friend type get(MdInternalTag);
+};
+template struct Rob<MdInternalTag, &MSMeanData::myDumpInternal>;
 
 struct NameTable {
     std::vector<int32_t> begin{0};
@@ -655,6 +676,32 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             ff.put("e1_pos", e1Pos);
             ff.put("e1_length", e1Length);
             e1Names.put(ff, "e1");
+        }
+    }
+    // ---------------- edgeData / laneData (MSMeanData_Net; row f4): the engine accumulates the raw per-lane members, the writer stays here
+    {
+        bool any = false;
+        double halt = 0;
+        for (const auto& item : net->getDetectorControl().getMeanData()) {
+            for (const MSMeanData* md : item.second) {
+                const MSMeanData_Net* mdn = dynamic_cast<const MSMeanData_Net*>(md);
+                if (mdn == nullptr) {
+                    throw ProcessError("sumob200: mean data '" + item.first + "' is not of type edgeData / laneData (emissions, harmonoise, ... are not supported)");
+                }
+                if (md->*get(MdTrackTag()) || md->*get(MdInternalTag()) || mdn->*get(MdHaltRelTag()) > 0 || !md->getVehicleTypes().empty()) {
+                    throw ProcessError("sumob200: mean data '" + item.first + "': trackVehicles, withInternal, speedThresholdRelative and vTypes are not supported");
+                }
+                const double hs = mdn->*get(MdHaltTag());
+                if (any && hs != halt) {
+                    throw ProcessError("sumob200: mean data definitions with different speedThreshold values are not supported");
+                }
+                any = true;
+                halt = hs;
+            }
+        }
+        if (any) {
+            ff.putScalar<int32_t>("md_enabled", 1);
+            ff.putScalar<double>("md_halt_speed", halt);
         }
     }
     // ---------------- options the step depends on (MSFrame::setMSGlobals, MSFrame.cpp:1172-1283)

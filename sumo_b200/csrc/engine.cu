@@ -84,6 +84,7 @@ struct sumob200_engine {
     long long reslots = 0;
     int32_t* rsScratch = nullptr;   // blocksA, blocksB, order, sorted, newOfOld, oldOfNew
     bool debugSync = getenv("SUMOB200_DEBUG_SYNC") != nullptr;
+    std::vector<double> mdMinlenInit;   // SB2_DBL_MAX per lane: what md_minlen is reset to
     void* rsTmp = nullptr;          // one permuted array (16 B per vehicle)
     int64_t launches = 0;
     bool profiling = false;
@@ -1009,6 +1010,43 @@ extern "C" int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, 
     *n = (int)ev.size();
     if (entered_out != nullptr) {
         memcpy(entered_out, entered.data(), sizeof(int32_t) * entered.size());
+    }
+    return 0;
+}
+
+// ---- edgeData / laneData accumulators (sb2_meandata.h) -----------------------------------------------------------------
+extern "C" int sumob200_meandata_interval(sumob200_engine* e, sumob200_lane_meandata* out, int capacity) {
+    if (e == nullptr || out == nullptr || capacity < e->d.nL) {
+        gLastError = "sumob200_meandata_interval: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    if (!e->d.md_on) {
+        gLastError = "sumob200_meandata_interval: the scenario does not enable mean data (md_enabled)";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const size_t nL = (size_t)e->d.nL;
+    cudaStream_t s = e->stream;
+    std::vector<double> sums(nL * MD_NSUMS), minlen(nL);
+    std::vector<int32_t> counts(nL * MD_NCOUNTS);
+    CUDA_TRY(cudaMemcpyAsync(sums.data(), e->d.md_sums, sizeof(double) * sums.size(), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(minlen.data(), e->d.md_minlen, sizeof(double) * nL, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(counts.data(), e->d.md_counts, sizeof(int32_t) * counts.size(), cudaMemcpyDeviceToHost, s));
+    // MSLaneMeanDataValues::reset
+    CUDA_TRY(cudaMemsetAsync(e->d.md_sums, 0, sizeof(double) * sums.size(), s));
+    CUDA_TRY(cudaMemsetAsync(e->d.md_counts, 0, sizeof(int32_t) * counts.size(), s));
+    e->mdMinlenInit.resize(nL, SB2_DBL_MAX);
+    CUDA_TRY(cudaMemcpyAsync(e->d.md_minlen, e->mdMinlenInit.data(), sizeof(double) * nL, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    for (size_t l = 0; l < nL; l++) {
+        sumob200_lane_meandata& o = out[l];
+        o.sample_seconds = sums[MD_SAMPLE * nL + l]; o.travelled_distance = sums[MD_DIST * nL + l];
+        o.wait_seconds = sums[MD_WAIT * nL + l]; o.time_loss = sums[MD_TIMELOSS * nL + l];
+        o.front_sample_seconds = sums[MD_FRONT_SAMPLE * nL + l]; o.front_travelled_distance = sums[MD_FRONT_DIST * nL + l];
+        o.veh_length_sum = sums[MD_LENGTH_SUM * nL + l]; o.occupation_sum = sums[MD_OCCUPATION * nL + l];
+        o.minimal_vehicle_length = minlen[l] == SB2_DBL_MAX ? -1. : minlen[l];
+        o.departed = counts[MD_DEPARTED * nL + l]; o.arrived = counts[MD_ARRIVED * nL + l]; o.entered = counts[MD_ENTERED * nL + l];
+        o.left = counts[MD_LEFT * nL + l]; o.teleported = counts[MD_TELEPORTED * nL + l]; o.reserved = 0;
     }
     return 0;
 }

@@ -608,6 +608,15 @@ public:
             none.det = -1; none.veh = -1; none.entry = 0; none.leave = 0; none.length = 0; none.leftEarly = 0; none.pad = 0;
             SB2_DYN(E1Event, e1_events, (size_t)h.e1_event_cap, none);
         }
+        // ---------------- edgeData / laneData accumulators (optional scalar md_enabled; sb2_meandata.h)
+        {
+            h.md_on = ff.scalar<int32_t>("md_enabled", 0) != 0 ? 1 : 0;
+            h.md_halt_speed = ff.scalar<double>("md_halt_speed", SB2_POSITION_EPS);
+            const size_t n = h.md_on ? (size_t)nL : 1;
+            SB2_DYN(double, md_sums, n * MD_NSUMS, 0.);
+            SB2_DYN(double, md_minlen, n, SB2_DBL_MAX);
+            SB2_DYN(int32_t, md_counts, n * MD_NCOUNTS, 0);
+        }
         SB2_DYN(int32_t, err_flags, 1, 0);
         SB2_DYN(int32_t, counters, 16, 0);
     }

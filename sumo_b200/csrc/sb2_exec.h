@@ -17,6 +17,7 @@
 #include "sb2_link.h"
 #include "sb2_emis.h"
 #include "sb2_e1.h"
+#include "sb2_meandata.h"
 
 namespace sb2 {
 
@@ -250,6 +251,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
     double tripRouteLen = c.veh_trip_routelen[v];
     bool arrived = false;
     bool emergency = false;
+    int arrivalLaneEntered = -1;
     if (pos > c.lane_length[myLane]) {
         if (routePos != routeLen - 1) {
             int approachedLane = myLane;
@@ -280,6 +282,8 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
                     pos -= c.lane_length[myLane];
                     // enterLaneAtMove
                     veh_e1_enter_at_move(c, v, myLane, approachedLane);
+                    md_count(c, myLane, MD_LEFT);               // leaveLane(NOTIFICATION_JUNCTION) -> notifyLeave of the lane that is left
+                    md_count(c, approachedLane, MD_ENTERED);    // activateReminders(NOTIFICATION_JUNCTION) -> notifyEnter of the entered lane
                     myLane = approachedLane;
                     if (!lane_internal(c, myLane)) {
                         ++routePos;
@@ -300,6 +304,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
                     }
                     // hasArrivedInternal
                     if (routePos == routeLen - 1 && pos > MIN2(c.lane_length[myLane], c.veh_arrivalpos[v]) - SB2_POSITION_EPS) {
+                        arrivalLaneEntered = approachedLane;   // (not a "passed" lane, but its move reminders were activated)
                         break;
                     }
                     if (np < MAX_FURTHER + MAX_DRIVE_ITEMS + 2) {
@@ -379,6 +384,22 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
     }
     veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
     veh_e1_move(c, v, pos - lastDist, pos, speed);     //                                          -> MSInductLoop::notifyMove
+    if (c.md_on) {
+        // -> MeanDataValues::notifyMove of every lane the vehicle's body was on or entered; rem->second = lengths of the lanes left since
+        const double vmaxNow = lane_vehicle_max_speed(c, myLane, v);
+        const int nChain = np + (arrivalLaneEntered >= 0 ? 1 : 0);
+        for (int k = 0; k < nChain; k++) {
+            double off = 0.;
+            for (int j = k; j < nChain - 1; j++) {
+                off += c.lane_length[passed[j]];
+            }
+            const int lane = k < np ? passed[k] : arrivalLaneEntered;
+            md_notifyMove(c, v, lane, (pos - lastDist) + off, pos + off, MAX2(0., speed), vmaxNow);
+        }
+        if (arrived) {
+            md_count(c, myLane, MD_ARRIVED);
+        }
+    }
     if (arrived) {
         veh_e1_leave_net(c, v);        // onRemovalFromNet(NOTIFICATION_ARRIVED) -> leaveLane -> notifyLeave
         c.veh_moved[v] = 2;

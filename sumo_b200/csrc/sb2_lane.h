@@ -13,6 +13,7 @@
 #include "sb2_cf.h"
 #include "sb2_veh.h"
 #include "sb2_e1.h"
+#include "sb2_meandata.h"
 
 namespace sb2 {
 
@@ -95,6 +96,8 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1,
 // table but every reader skips vehicles that are not on the road; partial occupations are dropped in lane_handoff_integrate.
 SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
     veh_e1_leave_net(c, v);   // leaveLane(NOTIFICATION_TELEPORT / _TELEPORT_ARRIVED) -> notifyLeave of every move reminder
+    md_count(c, lane, MD_LEFT);
+    md_count(c, lane, MD_TELEPORTED);
     if (c.veh_routepos[v] + 1 >= veh_route_len(c, v)) {
         // "teleports beyond arrival edge": removed from the simulation (NOTIFICATION_TELEPORT_ARRIVED)
         c.veh_arrival_time[v] = c.t;
@@ -111,7 +114,9 @@ SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
     c.veh_routepos[v] += 1;
     c.veh_pos[v] = 0;
     c.veh_lane[v] = -3;
-    veh_e1_add_lane(c, v, c.edge_lane_begin[veh_succ_edge(c, v, 0)], false, 0., 0.);   // enterLaneAtMove(.., onTeleporting): reminders only
+    // enterLaneAtMove(.., onTeleporting): myPos = 0, activateReminders(NOTIFICATION_TELEPORT) (MSVehicle.cpp:5613-5618)
+    veh_e1_add_lane(c, v, c.edge_lane_begin[veh_succ_edge(c, v, 0)], true, 0., -veh_length(c, v));
+    md_count(c, c.edge_lane_begin[veh_succ_edge(c, v, 0)], MD_ENTERED);
     c.veh_tp_proceed[v] = -1;
     // partitioned run: the transfer entry belongs to the rank that owns the edge the vehicle now (virtually) sits on, because
     // MSVehicleTransfer::checkInsertions tries to re-insert it there in this very step.  That rank sees the teleport itself: the

@@ -69,6 +69,9 @@ typedef int64_t SUMOTime;
 #define SB2_EMERGENCY_DECEL_AMPLIFIER 1.2        /* MSCFModel.h:35 */
 
 enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4, MAX_E1_REMINDERS = 4 };
+// rows of Ctx::md_sums / md_counts (sb2_meandata.h)
+enum { MD_SAMPLE = 0, MD_DIST = 1, MD_WAIT = 2, MD_TIMELOSS = 3, MD_FRONT_SAMPLE = 4, MD_FRONT_DIST = 5, MD_LENGTH_SUM = 6, MD_OCCUPATION = 7, MD_NSUMS = 8 };
+enum { MD_DEPARTED = 0, MD_ARRIVED = 1, MD_ENTERED = 2, MD_LEFT = 3, MD_TELEPORTED = 4, MD_NCOUNTS = 5 };
 
 // lane_flags / edge_flags bits (include/sumob200_flatfile.h)
 enum { LF_INTERNAL = 1, LF_ROUNDABOUT = 2, LF_FRINGE = 4, LF_LANECHANGER = 8 };
@@ -237,6 +240,12 @@ struct Ctx {
     double* veh_e1_entry;            // [MAX_E1_REMINDERS][nV] myVehiclesOnDet[veh] (entry time in s), E1_NOT_ON if not on the detector
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
+    // ---- edgeData / laneData (MSMeanData_Net, sb2_meandata.h); md_on == 0: one dummy element each
+    int md_on;
+    double md_halt_speed;            // haltingSpeedThreshold of the <edgeData> definition (default POSITION_EPS)
+    double* md_sums;                 // [MD_NSUMS][nL] sampleSeconds, travelledDistance, waitSeconds, timeLoss, frontSampleSeconds, frontTravelledDistance, vehLengthSum, occupationSum
+    double* md_minlen;               // [nL] minimalVehicleLength (SB2_DBL_MAX = INVALID_DOUBLE)
+    int32_t* md_counts;              // [MD_NCOUNTS][nL] nVehDeparted, nVehArrived, nVehEntered, nVehLeft, nVehTeleported
     uint8_t* edge_delayed;     // MSEdge::myAmDelayed (a vehicle has entered the edge at some time, MSEdge.h:750)
     // ---- multi-GPU edge partition (sb2_halo.h): what this rank does with each lane.  nullptr = one partition owning everything.
     //   LV_AUTH  lanes of the rank's own junction columns: simulated here, results authoritative (counted, reported, exported)

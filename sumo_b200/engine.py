@@ -49,6 +49,10 @@ SUMMARY = np.dtype([("time_ms", np.int64), ("inserted", np.int32), ("running", n
                     ("mean_speed_relative", np.float64)])
 E1_INTERVAL = np.dtype([("n_veh_contrib", np.int32), ("n_veh_entered", np.int32), ("flow", np.float64), ("occupancy", np.float64),
                         ("speed", np.float64), ("harmonic_mean_speed", np.float64), ("length", np.float64)])
+LANE_MEANDATA = np.dtype([("sample_seconds", np.float64), ("travelled_distance", np.float64), ("wait_seconds", np.float64), ("time_loss", np.float64),
+                          ("front_sample_seconds", np.float64), ("front_travelled_distance", np.float64), ("veh_length_sum", np.float64),
+                          ("occupation_sum", np.float64), ("minimal_vehicle_length", np.float64), ("departed", np.int32), ("arrived", np.int32),
+                          ("entered", np.int32), ("left", np.int32), ("teleported", np.int32), ("reserved", np.int32)])
 FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
                     ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
 
@@ -81,6 +85,7 @@ def load_library(path=None):
     lib.sumob200_tripinfo_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_summary_now_static.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.sumob200_meandata_interval.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_e1_count.argtypes = [ctypes.c_void_p]
     lib.sumob200_e1_interval.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
@@ -236,6 +241,12 @@ class Engine:
         out = np.zeros(1, dtype=SUMMARY)
         _check(self._lib, self._lib.sumob200_summary_now_static(self._h, out.ctypes.data), "sumob200_summary_now_static")
         return out[0]
+
+    def meandata_interval(self):
+        """the raw MSLaneMeanDataValues members of every lane since the last call (dtype LANE_MEANDATA, indexed by lane); resets them"""
+        out = np.zeros(max(self.num_lanes, 1), dtype=LANE_MEANDATA)
+        _check(self._lib, self._lib.sumob200_meandata_interval(self._h, out.ctypes.data, out.shape[0]), "sumob200_meandata_interval")
+        return out[:self.num_lanes]
 
     def e1_interval(self, begin_ms, end_ms):
         """MSInductLoop::writeXMLOutput for every E1 detector of the scenario: the aggregates of [begin_ms, end_ms) -- end_ms must be

@@ -317,8 +317,8 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out;
-    long long e1Period = 60000;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out, mdOut;
+    long long e1Period = 60000, mdPeriod = 60000;
     long maxSteps = -1;
     std::string debugName, partFile;
     for (int i = 2; i < argc; i++) {
@@ -335,6 +335,10 @@ int main(int argc, char** argv) {
             tlsSetPhase = argv[++i];   // "timeMs:tlsIndex:phase;..." applied before the step at that time (sumob200_tls_set_phase)
         } else if (a == "--veh-set-speed" && i + 1 < argc) {
             vehSetSpeed = argv[++i];   // "timeMs:slot:speed;..." applied before the step at that time if the vehicle is on the road (sumob200_vehicles_set_speed)
+        } else if (a == "--md-out" && i + 1 < argc) {
+            mdOut = argv[++i];   // text, one line per non-internal lane and interval: the raw members of MSLaneMeanDataValues (sumob200_meandata_interval)
+        } else if (a == "--md-period" && i + 1 < argc) {
+            mdPeriod = atoll(argv[++i]);   // ms
         } else if (a == "--e1-out" && i + 1 < argc) {
             e1Out = argv[++i];   // text, one line per detector and interval: the attributes of the reference's E1 output (sumob200_e1_interval)
         } else if (a == "--e1-period" && i + 1 < argc) {
@@ -387,6 +391,7 @@ int main(int argc, char** argv) {
     FILE* ffcdxml = fcdXmlOut.empty() ? nullptr : fopen(fcdXmlOut.c_str(), "w");
     FILE* fsum = summaryOut.empty() ? nullptr : fopen(summaryOut.c_str(), "w");
     FILE* fe1 = e1Out.empty() ? nullptr : fopen(e1Out.c_str(), "w");
+    FILE* fmd = mdOut.empty() ? nullptr : fopen(mdOut.c_str(), "w");
     FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
     FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
@@ -510,6 +515,27 @@ int main(int argc, char** argv) {
                         res[d].nVehContrib, res[d].flow, res[d].occupancy, res[d].speed, res[d].harmonicMeanSpeed, res[d].length, res[d].nVehEntered);
             }
         }
+        if (fmd != nullptr && c.md_on && (t + c.DELTA_T) % mdPeriod == 0) {
+            for (int l = 0; l < c.nL; l++) {
+                if (lane_internal(c, l)) {
+                    continue;
+                }
+                // begin lane sampleSeconds travelledDistance waitSeconds timeLoss frontSampleSeconds frontTravelledDistance vehLengthSum occupationSum
+                // minimalVehicleLength departed arrived entered left teleported
+                fprintf(fmd, "%lld %d", (long long)(t + c.DELTA_T - mdPeriod), l);
+                for (int k = 0; k < MD_NSUMS; k++) {
+                    fprintf(fmd, " %.17g", c.md_sums[(size_t)k * c.nL + l]);
+                    c.md_sums[(size_t)k * c.nL + l] = 0.;
+                }
+                fprintf(fmd, " %.17g", c.md_minlen[l] == SB2_DBL_MAX ? -1. : c.md_minlen[l]);
+                c.md_minlen[l] = SB2_DBL_MAX;
+                for (int k = 0; k < MD_NCOUNTS; k++) {
+                    fprintf(fmd, " %d", c.md_counts[(size_t)k * c.nL + l]);
+                    c.md_counts[(size_t)k * c.nL + l] = 0;
+                }
+                fprintf(fmd, "\n");
+            }
+        }
         if (femis != nullptr) {
             int64_t ne = 0;
             for (int v : order) {
@@ -553,6 +579,9 @@ int main(int argc, char** argv) {
     }
     if (fe1 != nullptr) {
         fclose(fe1);
+    }
+    if (fmd != nullptr) {
+        fclose(fmd);
     }
     if (fsum != nullptr) {
         fclose(fsum);
