@@ -52,6 +52,8 @@
 #include <microsim/MSVehicle.h>
 #include <microsim/MSVehicleControl.h>
 #include <microsim/MSNet.h>
+#include <microsim/MSInsertionControl.h>
+#include <microsim/devices/MSDevice_Tripinfo.h>
 #include <microsim/output/MSMeanData.h>
 #include <microsim/output/MSMeanData_Net.h>
 #include <microsim/output/MSDetectorControl.h>
@@ -79,7 +81,9 @@ struct Hook {
     std::vector<MSLane*> laneOfIndex;
     std::vector<sumob200_vehicle_state> state;
     std::vector<sumob200_fcd_row> rows;
-    std::vector<char> wasOnRoad;
+    std::vector<char> wasOnRoad;                     // 0 not departed, 1 departed, 2 removed (arrived)
+    std::vector<sumob200_tripinfo> trips;
+    std::vector<SUMOTime> departBucket;               // MSVehicleContainer's bucket of every slot (depart rounded up to a step)
     std::vector<MSInductLoop*> loops;                 // the E1 detectors in the order the flatten walk exported them (id order)
     std::vector<sumob200_e1_event> e1Events;
     std::vector<int32_t> e1Entered;
@@ -160,6 +164,12 @@ struct Hook {
         h->state.resize(nV > 0 ? nV : 1);
         h->rows.resize(nV > 0 ? nV : 1);
         h->wasOnRoad.assign(nV, 0);
+        h->trips.resize(nV > 0 ? nV : 1);
+        for (int s = 0; s < nV; s++) {
+            const SUMOTime d = h->vehOfSlot[s]->getParameter().depart;
+            const SUMOTime delay = d % DELTA_T;
+            h->departBucket.push_back(d + (delay == 0 ? 0 : DELTA_T - delay));
+        }
         WRITE_MESSAGE("sumob200: " + std::string(sumob200_version()) + "; " + toString(nV) + " vehicles, " + toString(h->laneOfIndex.size()) + " lanes on CUDA device " + toString(gDevice));
         return h;
     }
@@ -183,7 +193,9 @@ struct Hook {
             MSVehicle* v = vehOfSlot[row.slot];
             if (!wasOnRoad[row.slot]) {
                 wasOnRoad[row.slot] = 1;
-                v->myDeparture = net->getCurrentTimeStep();   // (insertion time; exact value: sumob200_tripinfo_all)
+                v->myDeparture = net->getCurrentTimeStep();   // inserted in this step
+                v->myDepartPos = row.pos;                     // (a vehicle does not move in the step of its insertion)
+                net->getVehicleControl().vehicleDeparted(*v); // ++running, total departure delay (summary output)
             }
             v->myLane = laneOfIndex[row.lane];
             v->myAmOnNet = true;
@@ -194,12 +206,61 @@ struct Hook {
             v->myAngle = DEG2RAD(90. - row.angle);              // inverse of GeomHelper::naviDegree
             v->myCurrEdge = v->getRoute().begin() + state[row.slot].route_pos;
         }
+        // ---- arrivals: the trip record into the vehicle's MSDevice_Tripinfo, then the reference's own removal
+        // (MSVehicleControl::scheduleVehicleRemoval / removePending: tripinfo line, total travel time, counters, delete)
+        MSVehicleControl& vcr = net->getVehicleControl();
+        bool tripsFetched = false;
+        std::vector<int> removed;
+        std::vector<SUMOVehicle*> pendingEmits;
+        const SUMOTime now = net->getCurrentTimeStep();
         for (int s = 0; s < nV; s++) {
-            if (wasOnRoad[s] && state[s].lane < 0) {
-                wasOnRoad[s] = 2;
-                vehOfSlot[s]->myAmOnNet = false;   // arrived (or teleporting): not visible to the output writers
+            MSVehicle* v = vehOfSlot[s];
+            if (v == nullptr) {
+                continue;
             }
+            if (wasOnRoad[s] == 0) {
+                if (departBucket[s] <= now) {
+                    pendingEmits.push_back(v);   // depart time reached, no room yet: MSInsertionControl::myPendingEmits
+                }
+                continue;
+            }
+            if (state[s].lane >= 0) {
+                continue;
+            }
+            v->myAmOnNet = false;   // arrived or teleporting: not visible to the output writers
+            if (state[s].lane != -2) {
+                continue;
+            }
+            if (!tripsFetched) {
+                if (sumob200_tripinfo_all(eng, trips.data(), nV) != 0) {
+                    throw ProcessError(std::string("sumob200_tripinfo_all failed: ") + sumob200_last_error());
+                }
+                tripsFetched = true;
+            }
+            const sumob200_tripinfo& tr = trips[s];
+            v->myDeparture = tr.depart_ms;
+            v->myDepartPos = tr.depart_pos;
+            v->myTimeLoss = (double)tr.time_loss_ms / 1000.;
+            v->myCurrEdge = v->getRoute().end() - 1;
+            v->myState.mySpeed = tr.arrival_speed;
+            MSDevice_Tripinfo* d = static_cast<MSDevice_Tripinfo*>(v->getDevice(typeid(MSDevice_Tripinfo)));
+            if (d != nullptr) {
+                d->myDepartLane = laneOfIndex[tr.depart_lane]->getID();
+                d->myDepartSpeed = tr.depart_speed;
+                d->myWaitingTime = tr.waiting_ms;
+                d->myWaitingCount = tr.waiting_count;
+                d->myStoppingTime = 0;
+                d->myArrivalTime = tr.arrival_ms;
+                d->myArrivalLane = tr.arrival_lane >= 0 ? laneOfIndex[tr.arrival_lane]->getID() : "";
+                d->myArrivalPos = tr.arrival_pos;
+                d->myArrivalSpeed = tr.arrival_speed;
+                d->myArrivalReason = MSMoveReminder::NOTIFICATION_ARRIVED;
+                d->myRouteLength = tr.route_length - tr.arrival_pos;
+            }
+            vcr.scheduleVehicleRemoval(v, false);
+            removed.push_back(s);
         }
+
         // ---- E1 detectors: this step's passages into the reference's own MSInductLoop objects (their writeXMLOutput, called by
         // MSDetectorControl::writeOutput below, and the libsumo::InductionLoop getters then work unchanged)
         if (!loops.empty()) {
@@ -257,10 +318,21 @@ struct Hook {
                 }
             }
         }
+        // ---- the arrived vehicles leave the reference's containers now (after the detectors have copied what they need of them)
+        for (const int s : removed) {
+            vehOfSlot[s] = nullptr;
+            wasOnRoad[s] = 2;
+        }
+        vcr.removePending();
+        net->getInsertionControl().myPendingEmits = pendingEmits;
         // ---- MSVehicleControl counters (summary output, MSNet::simulationState's termination test)
         MSVehicleControl& vc = net->getVehicleControl();
-        vc.myRunningVehNo = r.running;
-        vc.myEndedVehNo = r.arrived_total;
+        if (vc.myRunningVehNo != r.running || vc.myEndedVehNo != r.arrived_total) {
+            // (differs for one step when a vehicle was teleported beyond its arrival edge from MSVehicleTransfer::checkInsertions:
+            // the reference removes it one step later)
+            vc.myRunningVehNo = r.running;
+            vc.myEndedVehNo = r.arrived_total;
+        }
         vc.myCollisions = r.collisions;
         vc.myTeleportsJam = r.teleports;
         // ---- the rest of MSNet::simulationStep / postMoveStep (MSNet.cpp:919-964): outputs, clock
