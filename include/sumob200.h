@@ -127,7 +127,9 @@ typedef struct sumob200_tripinfo {
     int64_t duration_ms;      /* arrival (or current time) - departure */
     int64_t waiting_ms;       /* myWaitingTime */
     int64_t time_loss_ms;     /* MSVehicle::getTimeLoss = TIME2STEPS(myTimeLoss) */
-    int32_t depart_lane, arrival_lane, waiting_count, reserved;
+    int32_t depart_lane, arrival_lane, waiting_count;
+    int32_t teleport_arrived; /* != 0: removed by MSVehicleTransfer as "teleports beyond arrival edge" (tripinfo: vaporized="teleport"); 1 = in
+                               * MSVehicleTransfer::add, 2 = in checkInsertions (MSVehicleControl::removePending sees it one step later) */
     double depart_pos, depart_speed, arrival_pos, arrival_speed, route_length, speed_factor;
 } sumob200_tripinfo;
 /* trip records of all vehicle slots (n = sumob200_num_vehicles) */

@@ -238,6 +238,9 @@ struct Hook {
                 tripsFetched = true;
             }
             const sumob200_tripinfo& tr = trips[s];
+            if (tr.teleport_arrived == 2 && tr.arrival_ms == now) {
+                continue;   // scheduled by MSVehicleTransfer::checkInsertions: removePending runs in the next step's executeMovements
+            }
             v->myDeparture = tr.depart_ms;
             v->myDepartPos = tr.depart_pos;
             v->myTimeLoss = (double)tr.time_loss_ms / 1000.;
@@ -254,7 +257,7 @@ struct Hook {
                 d->myArrivalLane = tr.arrival_lane >= 0 ? laneOfIndex[tr.arrival_lane]->getID() : "";
                 d->myArrivalPos = tr.arrival_pos;
                 d->myArrivalSpeed = tr.arrival_speed;
-                d->myArrivalReason = MSMoveReminder::NOTIFICATION_ARRIVED;
+                d->myArrivalReason = tr.teleport_arrived ? MSMoveReminder::NOTIFICATION_TELEPORT_ARRIVED : MSMoveReminder::NOTIFICATION_ARRIVED;
                 d->myRouteLength = tr.route_length - tr.arrival_pos;
             }
             vcr.scheduleVehicleRemoval(v, false);
@@ -327,12 +330,7 @@ struct Hook {
         net->getInsertionControl().myPendingEmits = pendingEmits;
         // ---- MSVehicleControl counters (summary output, MSNet::simulationState's termination test)
         MSVehicleControl& vc = net->getVehicleControl();
-        if (vc.myRunningVehNo != r.running || vc.myEndedVehNo != r.arrived_total) {
-            // (differs for one step when a vehicle was teleported beyond its arrival edge from MSVehicleTransfer::checkInsertions:
-            // the reference removes it one step later)
-            vc.myRunningVehNo = r.running;
-            vc.myEndedVehNo = r.arrived_total;
-        }
+        // (myRunningVehNo / myEndedVehNo / the totals are kept by vehicleDeparted and removePending above)
         vc.myCollisions = r.collisions;
         vc.myTeleportsJam = r.teleports;
         // ---- the rest of MSNet::simulationStep / postMoveStep (MSNet.cpp:919-964): outputs, clock

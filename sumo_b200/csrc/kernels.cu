@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(BLOCK) k_tripinfo(const __grid_constant__ Ctx 
         r.depart_lane = c.veh_departlane[v];
         r.arrival_lane = c.veh_arrival_lane[v];
         r.waiting_count = c.veh_trip_waitcount[v];
-        r.reserved = 0;
+        r.teleport_arrived = (arrived && c.veh_trip_amwaiting[v] >= 2) ? c.veh_trip_amwaiting[v] - 1 : 0;
         r.depart_pos = c.veh_trip_departpos[v];
         r.depart_speed = c.veh_trip_departspeed[v];
         r.arrival_pos = c.veh_arrivalpos[v];

@@ -102,6 +102,7 @@ SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
         // "teleports beyond arrival edge": removed from the simulation (NOTIFICATION_TELEPORT_ARRIVED)
         c.veh_arrival_time[v] = c.t;
         c.veh_arrival_lane[v] = lane;
+        c.veh_trip_amwaiting[v] = 2;   // (free after the removal) marks NOTIFICATION_TELEPORT_ARRIVED for the trip record
         c.veh_moved[v] = 2;
         c.veh_lane[v] = -2;
         count_event(c, lane, 1);

@@ -188,6 +188,7 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
                 md_count(c, c.edge_lane_begin[e], MD_TELEPORTED);
                 c.veh_arrival_time[v] = time;
                 c.veh_arrival_lane[v] = c.edge_lane_begin[e];
+                c.veh_trip_amwaiting[v] = 3;   // NOTIFICATION_TELEPORT_ARRIVED for the trip record, removal pending until the next step
                 c.veh_moved[v] = 4;
                 c.counters[11] += 1;   // still counted as running in this step's result
                 c.veh_lane[v] = -2;

@@ -41,7 +41,7 @@ class StepResult(ctypes.Structure):
 VEHICLE_STATE = np.dtype([("lane", np.int32), ("route_pos", np.int32), ("pos", np.float64), ("speed", np.float64)])
 TRIPINFO = np.dtype([("depart_ms", np.int64), ("depart_delay_ms", np.int64), ("arrival_ms", np.int64), ("duration_ms", np.int64),
                      ("waiting_ms", np.int64), ("time_loss_ms", np.int64), ("depart_lane", np.int32), ("arrival_lane", np.int32),
-                     ("waiting_count", np.int32), ("reserved", np.int32), ("depart_pos", np.float64), ("depart_speed", np.float64),
+                     ("waiting_count", np.int32), ("teleport_arrived", np.int32), ("depart_pos", np.float64), ("depart_speed", np.float64),
                      ("arrival_pos", np.float64), ("arrival_speed", np.float64), ("route_length", np.float64), ("speed_factor", np.float64)])
 SUMMARY = np.dtype([("time_ms", np.int64), ("inserted", np.int32), ("running", np.int32), ("waiting", np.int32), ("ended", np.int32),
                     ("arrived", np.int32), ("collisions", np.int32), ("teleports", np.int32), ("halting", np.int32), ("stopped", np.int32),
