@@ -464,6 +464,17 @@ public:
                     throw std::runtime_error("sumob200: departLane index out of range");
                 }
                 dl[v] = h.edge_lane_begin[e0] + idx;
+                // a vehicle inserted with its back behind the lane's start laps into the predecessor lanes
+                // (MSVehicle::computeFurtherLanes at insertion, MSVehicle.cpp:5823): not modelled
+                if (h.veh_departpos_proc[v] == DPD_GIVEN) {
+                    double pos = h.veh_departpos[v];
+                    if (pos < 0.) {
+                        pos += h.lane_length[dl[v]];
+                    }
+                    if (pos < h.vt_length[h.veh_type[v]]) {
+                        throw std::runtime_error("sumob200: departPos closer to the lane's start than the vehicle is long is not supported");
+                    }
+                }
             }
             // departure queues per lane, in load order
             int32_t* qb = add<int32_t>("dq_begin", SB2_OFF(dq_begin), (size_t)nL + 1, false, 0);

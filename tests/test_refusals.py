@@ -59,3 +59,20 @@ def test_plain_scenario_is_accepted(tmp_path):
     r = subprocess.run([exe, "--flat-out", str(tmp_path / "x.flat"), "-n", NET, "-r", os.path.join(GOLDEN, "grid3_small.rou.xml"), "--no-step-log"],
                        capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and os.path.exists(str(tmp_path / "x.flat"))
+
+
+def test_depart_position_inside_the_first_vehicle_length_is_refused_by_the_engine(tmp_path, host_emul):
+    """departPos < vehicle length: the vehicle would lap into the predecessor lanes at insertion (MSVehicle::computeFurtherLanes) --
+    refused when the engine's model is built (sb2_build.h; the host emulation runs the same builder); 6 m (> 5 m) is accepted"""
+    exe = ensure_reference()
+    edges = first_route()
+    for pos, ok in (("2", False), ("6", True)):
+        rou = str(tmp_path / ("r%s.rou.xml" % pos))
+        open(rou, "w").write('<routes><vType id="car" sigma="0"/><vehicle id="a" type="car" depart="0" departPos="%s"><route edges="%s"/></vehicle></routes>' % (pos, edges))
+        flat = str(tmp_path / ("x%s.flat" % pos))
+        subprocess.run([exe, "--flat-out", flat, "-n", NET, "-r", rou, "--no-step-log", "--end", "20"], check=True, capture_output=True, timeout=120)
+        r = subprocess.run([host_emul, flat, "--steps", "5"], capture_output=True, text=True, timeout=120)
+        if ok:
+            assert r.returncode == 0, r.stderr[-500:]
+        else:
+            assert r.returncode != 0 and "departPos closer to the lane's start" in r.stderr
