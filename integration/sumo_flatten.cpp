@@ -441,8 +441,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             if (!p.stops.empty() || !v->getRoute().getStops().empty() || v->hasStops()) {
                 throw ProcessError(who + "<stop>s are not supported");
             }
-            if (p.arrivalSpeedProcedure != ArrivalSpeedDefinition::DEFAULT && p.arrivalSpeedProcedure != ArrivalSpeedDefinition::CURRENT) {
-                throw ProcessError(who + "arrivalSpeed is not supported");
+            if (p.arrivalSpeedProcedure != ArrivalSpeedDefinition::DEFAULT && p.arrivalSpeedProcedure != ArrivalSpeedDefinition::CURRENT
+                    && p.arrivalSpeedProcedure != ArrivalSpeedDefinition::GIVEN) {
+                throw ProcessError(who + "arrivalSpeed must be 'current' or a number");
             }
             if (p.arrivalLaneProcedure != ArrivalLaneDefinition::DEFAULT && p.arrivalLaneProcedure != ArrivalLaneDefinition::CURRENT) {
                 throw ProcessError(who + "arrivalLane is not supported");
@@ -475,7 +476,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         std::vector<int32_t> numid, vtype, vroute, dpp, dsp, dlp, dlane, idrank(vehs.size(), 0);
         std::vector<uint8_t> hasEmissions;   // vehicle carries MSDevice_Emissions (--device.emissions.probability / explicit)
         std::vector<int64_t> depart;
-        std::vector<double> sf, arrpos, dpos, dspeed;
+        std::vector<double> sf, arrpos, arrspeed, dpos, dspeed;
         NameTable vehNames;
         for (const SUMOVehicle* v : vehs) {
             const MSVehicleType* t = &v->getVehicleType();
@@ -495,6 +496,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             depart.push_back(p.depart);
             sf.push_back(v->getChosenSpeedFactor());
             arrpos.push_back(v->getArrivalPos());
+            arrspeed.push_back(p.arrivalSpeedProcedure == ArrivalSpeedDefinition::GIVEN ? p.arrivalSpeed : -1.);
             dpp.push_back((int)p.departPosProcedure);
             dpos.push_back(p.departPos);
             dsp.push_back((int)p.departSpeedProcedure);
@@ -523,6 +525,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         ff.put("veh_depart", depart);
         ff.put("veh_speedfactor", sf);
         ff.put("veh_arrivalpos", arrpos);
+        ff.put("veh_arrivalspeed", arrspeed);
         ff.put("veh_departpos_proc", dpp);
         ff.put("veh_departpos", dpos);
         ff.put("veh_departspeed_proc", dsp);

@@ -404,6 +404,14 @@ public:
         SB2_COPY(int32_t, route_begin); SB2_COPY(int32_t, route_edges);
         SB2_COPY(int32_t, veh_type); SB2_COPY(int32_t, veh_route); SB2_COPY(int32_t, veh_numid); SB2_COPY(int32_t, veh_idrank);
         SB2_COPY(double, veh_speedfactor); SB2_COPY(double, veh_arrivalpos);
+        if (ff.has("veh_arrivalspeed")) {
+            if ((int)ff.count("veh_arrivalspeed") != nV) {
+                throw std::invalid_argument("sumob200: veh_arrivalspeed must have one element per vehicle");
+            }
+            SB2_COPY(double, veh_arrivalspeed);
+        } else {
+            add<double>("veh_arrivalspeed", SB2_OFF(veh_arrivalspeed), nV, false, -1.);
+        }
         SB2_COPY(double, veh_departpos); SB2_COPY(int32_t, veh_departpos_proc);
         {
             // depart time = MSVehicleContainer bucket (rounded up to the step grid, MSVehicleContainer.cpp:80-81)

@@ -240,7 +240,14 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
         const int link = SB2_CHK(lane_succ_link(c, SB2_CHK(currentLane, 0, c.nL, 33), SB2_CHK(nextEdge, -1, c.nE, 34)), -1, c.nK, 35);
         if (link < 0) {
             if (c.lane_edge[currentLane] == c.route_edges[c.route_begin[r + 1] - 1]) {
-                // reached the end of the route (arrivalSpeed not given; mayContinue: no further route)
+                // reached the end of the route (mayContinue: no further route)
+                if (c.veh_arrivalspeed[v] >= 0.) {
+                    const double remaining = seen + c.veh_arrivalpos[v] - c.lane_length[currentLane];
+                    const double fspeed = cf_freeSpeed(cf, speed, remaining, c.veh_arrivalspeed[v], true);
+                    if (ins_checkFailure(cf, speed, dist, fspeed, patchSpeedSpecial)) {
+                        return false;   // "arrival speed too low"
+                    }
+                }
             } else {
                 if (ins_checkFailure(cf, speed, dist, cf_insertionStopSpeed(cf, speed, seen), patchSpeedSpecial)) {
                     return false;

@@ -230,7 +230,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
         const int link = lane_succ_link(c, lane, veh_succ_edge(c, v, view + 1));
         // check whether the vehicle is on its final edge
         if (routePos + view + 1 == routeLen) {
-            const double arrivalSpeed = laneMaxV;
+            const double arrivalSpeed = c.veh_arrivalspeed[v] >= 0. ? c.veh_arrivalspeed[v] : laneMaxV;   // ArrivalSpeedDefinition::GIVEN
             const double distToArrival = seen + c.veh_arrivalpos[v] - c.lane_length[lane] - arrivalSpeed * c.TS;
             const double va = MAX2(SB2_NUMERICAL_EPS, cf_freeSpeed(cf, e.speed, distToArrival, arrivalSpeed, false));
             vv = MIN2(vv, va);

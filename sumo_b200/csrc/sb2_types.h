@@ -192,7 +192,7 @@ struct Ctx {
     const int32_t* route_begin; const int32_t* route_edges;
     // ---- vehicles (static) ---------------------------------------------------------------
     const int32_t* veh_type; const int32_t* veh_route; const int32_t* veh_numid; const int32_t* veh_idrank;
-    const SUMOTime* veh_depart; const SUMOTime* veh_depart_param; /* as given (tripinfo departDelay) */ const double* veh_speedfactor; const double* veh_arrivalpos;
+    const SUMOTime* veh_depart; const SUMOTime* veh_depart_param; /* as given (tripinfo departDelay) */ const double* veh_speedfactor; const double* veh_arrivalpos; const double* veh_arrivalspeed; /* arrivalSpeed if given, else < 0 */
     const int32_t* veh_departlane;                   // resolved departure lane index
     const double* veh_departpos; const int32_t* veh_departpos_proc;
     const double* veh_departspeed; const int32_t* veh_departspeed_proc;

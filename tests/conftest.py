@@ -44,6 +44,7 @@ CASES.update({
     "grid4_tls_idm": ["--default.speeddev", "0", "--end", "1200"],
     # carFollowModel KraussOrig1 (MSCFModel_KraussOrig1: the SK safe speed): not collision free -- 20 resp. 58 rear-end collisions, each
     # resolved by teleporting the collider like the reference does (collision.action teleport)
+    "grid4_tls_arrivalspeed": ["--default.speeddev", "0", "--end", "900"],
     "grid4_tls_orig1": ["--default.speeddev", "0", "--end", "900"],
     "grid5_dense_orig1": ["--default.speeddev", "0", "--end", "900"],
 })
@@ -82,6 +83,8 @@ ROU_EDITS = {
     "_idm": ('sigma="0"', 'sigma="0" carFollowModel="IDM"'),
     "_sigma": ('sigma="0"', 'sigma="0.5"'),
     "_orig1": ('sigma="0"', 'sigma="0" carFollowModel="KraussOrig1"'),
+    # arrivalSpeed given: the vehicle brakes down to it towards its arrival position (MSVehicle.cpp:2752-2757; insertion: MSLane.cpp "arrival speed too low")
+    "_arrivalspeed": ("<vehicle ", '<vehicle arrivalSpeed="3" '),
     "_hbefa3": ('sigma="0"', 'sigma="0" emissionClass="HBEFA3/PC_G_EU4"'),
 }
 
@@ -179,7 +182,7 @@ def reference_case(name):
     trace = os.path.join(CACHE, name + ".trace")
     if not (os.path.exists(flat) and os.path.exists(trace) and os.path.getmtime(flat) >= os.path.getmtime(exe)):
         base = name
-        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_orig1", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase", "_setspeed"):
+        for suffix in ("_depart0", "_speeddev", "_teleport", "_sigma", "_hbefa4", "_hbefa3", "_idm", "_orig1", "_arrivalspeed", "_draws", "_arrivalpos", "_mixed", "_step05", "_optmix", "_setphase", "_setspeed"):
             base = base.replace(suffix, "")
         rou = os.path.join(GOLDEN, base + ".rou.xml")
         extra = []

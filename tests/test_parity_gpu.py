@@ -8,7 +8,7 @@ from sumo_b200.flatfile import load_flat, load_trace
 pytestmark = pytest.mark.gpu
 
 GPU_CASES = ["grid3_small", "grid3_small_depart0", "c1_grid10", "c1_grid10_depart0", "grid4_tls", "grid5_dense", "grid4_tls_speeddev", "grid4_tls_arrivalpos", "grid4_tls_mixed", "grid5_dense_mixed", "c1_grid10_mixed", "grid4_tls_step05", "grid5_dense_optmix", "rand_net", "grid4_stop", "grid3_tls_short",
-             "grid4_tls_orig1", "grid5_dense_orig1"]
+             "grid4_tls_orig1", "grid5_dense_orig1", "grid4_tls_arrivalspeed"]
 
 
 @pytest.mark.parametrize("case", GPU_CASES)

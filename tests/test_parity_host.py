@@ -12,7 +12,7 @@ from sumo_b200.flatfile import load_trace
 HOST_CASES = ["grid3_small", "grid3_small_depart0", "c1_grid10", "grid4_tls", "grid5_dense", "grid4_tls_speeddev", "grid4_tls_arrivalpos", "grid4_tls_mixed", "grid5_dense_mixed", "c1_grid10_mixed", "grid4_tls_step05", "grid5_dense_optmix", "rand_net", "grid4_stop", "grid3_tls_short",
               # IDM: the host build calls glibc's pow like the reference, so it is bit-exact here (the GPU suite checks IDM with a tolerance)
               "grid3_small_idm", "grid5_dense_idm", "c1_grid10_idm", "grid4_tls_idm",
-              "grid4_tls_orig1", "grid5_dense_orig1"]
+              "grid4_tls_orig1", "grid5_dense_orig1", "grid4_tls_arrivalspeed"]
 
 
 def assert_traces_identical(ref, got):

@@ -111,6 +111,46 @@ def test_partitioned_engines_match_reference_on_one_gpu(case, world):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_partitioned_edgedata_sums_to_the_single_engine(world):
+    """edgeData accumulators (sb2_meandata.h) under the edge partition: every rank reports its OWN lanes only (the vehicles of its
+    ghost column are executed redundantly, their lanes are the neighbour's); merged by lane they equal one engine over the whole
+    network -- counters exactly, the real sums to 1e-9 (atomics: order of additions)."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs CUDA")
+    from test_meandata import meandata_case
+    from sumo_b200.engine import Engine
+    flat, trace, _ = meandata_case("c1_grid10")
+    g = load_flat(flat)
+    steps = 900
+    with Engine(flat) as one:
+        one.step(steps, result=False)
+        want = one.meandata_interval().copy()
+    run = partition.LocalPartitionedRun(g, world)
+    try:
+        for _ in range(steps):
+            run.step()
+        merged = np.zeros_like(want)
+        seen = np.zeros(len(want), int)
+        for p in run.parts:
+            md = p["eng"].meandata_interval()
+            own = p["plan"]["lane_vis"] == partition.LV_AUTH
+            assert (md["sample_seconds"][~own] == 0).all() and (md["entered"][~own] == 0).all() and (md["departed"][~own] == 0).all()
+            merged[own] = md[own]
+            seen[own] += 1
+        assert (seen == 1).all()
+    finally:
+        run.close()
+    for k in ("departed", "arrived", "entered", "left", "teleported"):
+        assert np.array_equal(merged[k], want[k]), k
+    assert want["entered"].sum() > 2000 and want["arrived"].sum() > 100
+    for k in ("sample_seconds", "travelled_distance", "wait_seconds", "time_loss", "front_sample_seconds", "front_travelled_distance",
+              "veh_length_sum", "occupation_sum", "minimal_vehicle_length"):
+        assert np.allclose(merged[k], want[k], rtol=1e-9, atol=1e-9), k
+
+
+@pytest.mark.gpu
 def test_two_gpus_over_nccl_match_reference():
     """one process per GPU (torchrun), halo exchange over NCCL: tools_dev/partition_nccl_check.py compares every rank's own
     vehicles with the reference trace after every step"""

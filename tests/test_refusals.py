@@ -24,8 +24,8 @@ ROUTE_FILES = {
              "<flow> definitions are not supported"),
     "person": ('<routes><vType id="car" sigma="0"/><vehicle id="a" type="car" depart="0"><route edges="%(edges)s"/></vehicle>'
                '<person id="p" depart="0"><walk edges="%(first)s"/></person></routes>', "persons / containers are not supported"),
-    "arrivalSpeed": ('<routes><vType id="car" sigma="0"/><vehicle id="a" type="car" depart="0" arrivalSpeed="3"><route edges="%(edges)s"/></vehicle></routes>',
-                     "arrivalSpeed is not supported"),
+    "arrivalLane": ('<routes><vType id="car" sigma="0"/><vehicle id="a" type="car" depart="0" arrivalLane="0"><route edges="%(edges)s"/></vehicle></routes>',
+                    "arrivalLane is not supported"),
     "actionStepLength": ('<routes><vType id="car" sigma="0" actionStepLength="2"/><vehicle id="a" type="car" depart="0"><route edges="%(edges)s"/></vehicle></routes>',
                          "actionStepLength"),
     "jm": ('<routes><vType id="car" sigma="0" jmIgnoreFoeProb="0.5"/><vehicle id="a" type="car" depart="0"><route edges="%(edges)s"/></vehicle></routes>',
