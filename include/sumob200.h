@@ -167,6 +167,16 @@ int sumob200_summary_now(sumob200_engine* e, sumob200_summary* out);
 #define SUMOB200_SUMMARY_STATIC_MAX_VEHICLES 2097152
 int sumob200_summary_now_static(sumob200_engine* e, sumob200_summary* out);
 
+/* What libsumo::Lane::getLastStepVehicleNumber / getLastStepHaltingNumber / getLastStepMeanSpeed / getLastStepOccupancy /
+ * getWaitingTime return (src/libsumo/Lane.cpp:209-272), for every lane at once (the observation vector of RL tooling): out[lane].
+ * mean_speed of an empty lane is its speed limit (MSLane::getMeanSpeed); occupancy is the netto occupancy in [0, 1] incl. the part of
+ * vehicles lapping in from the next lanes. */
+typedef struct sumob200_lane_stats {
+    int32_t vehicle_number, halting_number;
+    double mean_speed, occupancy, waiting_time;
+} sumob200_lane_stats;
+int sumob200_lane_stats_all(sumob200_engine* e, sumob200_lane_stats* out, int capacity);
+
 /* E1 induction loops (src/microsim/output/MSInductLoop.cpp; row f4).  Detectors are part of the scenario: optional arrays
  * e1_lane (int32, lane index), e1_pos (float64, metres from the lane's start; negative = from its end, as
  * NLDetectorBuilder::getPositionChecking does), e1_length (float64, optional; 0) -- what <inductionLoop lane= pos= length=/> of an

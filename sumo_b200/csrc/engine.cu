@@ -84,6 +84,7 @@ struct sumob200_engine {
     long long reslots = 0;
     int32_t* rsScratch = nullptr;   // blocksA, blocksB, order, sorted, newOfOld, oldOfNew
     bool debugSync = getenv("SUMOB200_DEBUG_SYNC") != nullptr;
+    sumob200_lane_stats* dLaneStats = nullptr;
     std::vector<double> mdMinlenInit;   // SB2_DBL_MAX per lane: what md_minlen is reset to
     void* rsTmp = nullptr;          // one permuted array (16 B per vehicle)
     int64_t launches = 0;
@@ -305,6 +306,7 @@ void sumob200_destroy(sumob200_engine* e) {
     if (e->rsScratch != nullptr) {
         cudaFree(e->rsScratch);
         cudaFree(e->rsTmp);
+        cudaFree(e->dLaneStats);
     }
     if (e->dSummary != nullptr) {
         cudaFree(e->dSummary);
@@ -1011,6 +1013,24 @@ extern "C" int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, 
     if (entered_out != nullptr) {
         memcpy(entered_out, entered.data(), sizeof(int32_t) * entered.size());
     }
+    return 0;
+}
+
+// ---- libsumo::Lane::getLastStep* for all lanes ---------------------------------------------------------------------------------
+extern "C" int sumob200_lane_stats_all(sumob200_engine* e, sumob200_lane_stats* out, int capacity) {
+    if (e == nullptr || out == nullptr || capacity < e->d.nL) {
+        gLastError = "sumob200_lane_stats_all: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const size_t nL = (size_t)e->d.nL;
+    if (e->dLaneStats == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->dLaneStats, sizeof(sumob200_lane_stats) * (nL > 0 ? nL : 1)));
+    }
+    e->ks->lane_stats(&e->d, e->d.nL, e->dLaneStats, e->stream);
+    e->launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(out, e->dLaneStats, sizeof(sumob200_lane_stats) * nL, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
     return 0;
 }
 

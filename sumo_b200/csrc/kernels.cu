@@ -508,6 +508,18 @@ __global__ void __launch_bounds__(BLOCK) k_halo_unpack(const __grid_constant__ C
     halo_unpack_vehicle(c, msg, i);
 }
 
+// libsumo::Lane::getLastStep* of every lane (sb2_transfer.h:lane_stats)
+__global__ void __launch_bounds__(BLOCK) k_lane_stats(const __grid_constant__ Ctx c, sumob200_lane_stats* out) {
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < c.nL) {
+        const LaneStats r = lane_stats(c, l);
+        sumob200_lane_stats o;
+        o.vehicle_number = r.vehicleNumber; o.halting_number = r.haltingNumber;
+        o.mean_speed = r.meanSpeed; o.occupancy = r.occupancy; o.waiting_time = r.waitingTime;
+        out[l] = o;
+    }
+}
+
 // E1 detectors: the vehicles on a detector at the end of an output interval (sb2_e1.h)
 __global__ void __launch_bounds__(BLOCK) k_e1_collect(const __grid_constant__ Ctx c) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -695,13 +707,14 @@ int l_reslot_maps(const void* c, int nL, int nV, int32_t* blocksA, int32_t* bloc
     return 8;
 }
 void l_e1_collect(const void* c, int n, cudaStream_t s) { k_e1_collect<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_lane_stats(const void* c, int n, sumob200_lane_stats* out, cudaStream_t s) { k_lane_stats<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int appBuf, cudaStream_t s) {
     const size_t n = (size_t)nV * MAX_DRIVE_ITEMS > (size_t)nL ? (size_t)nV * MAX_DRIVE_ITEMS : (size_t)nL;
     k_rs_remap<<<(unsigned)((n + BLOCK - 1) / BLOCK), BLOCK, 0, s>>>(ctx(c), newOfOld, appBuf);
     return 1;
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap, l_e1_collect};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap, l_e1_collect, l_lane_stats};
 
 }  // namespace sb2_kset_<name>
 

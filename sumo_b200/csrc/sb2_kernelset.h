@@ -33,6 +33,8 @@ struct sb2_kernelset {
     int (*reslot_remap)(const void* ctx, int n_lanes, int n_vehicles, const int32_t* new_of_old, int app_buf, cudaStream_t s);
     /* E1 detectors (sb2_e1.h): append the vehicles that are on a detector right now to the event list */
     void (*e1_collect)(const void* ctx, int n_vehicles, cudaStream_t s);
+    /* libsumo::Lane::getLastStep* of every lane */
+    void (*lane_stats)(const void* ctx, int n_lanes, sumob200_lane_stats* out, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

@@ -27,6 +27,39 @@ SB2_HD double lane_mean_speed(const Ctx& c, int l) {
     return v / num;
 }
 
+// what libsumo::Lane::getLastStepVehicleNumber / HaltingNumber / MeanSpeed / Occupancy / getWaitingTime return for lane l
+// (src/libsumo/Lane.cpp:209-272, MSLane::getMeanSpeed / getNettoOccupancy / getFractionalVehicleLength, MSLane.cpp:3415-3494).
+// The reference keeps the netto length sum incrementally; here the lengths of the queue are added rear to front.
+struct LaneStats {   // == sumob200_lane_stats
+    int32_t vehicleNumber, haltingNumber;
+    double meanSpeed, occupancy, waitingTime;
+};
+SB2_HD LaneStats lane_stats(const Ctx& c, int l) {
+    LaneStats r;
+    r.vehicleNumber = 0; r.haltingNumber = 0; r.waitingTime = 0.;
+    double netto = 0.;
+    for (int x = c.lane_last[l]; x >= 0; x = c.veh_ahead[x]) {
+        r.vehicleNumber++;
+        if (c.veh_speed[x] < SB2_HALTING_SPEED) {
+            r.haltingNumber++;
+        }
+        netto += veh_length(c, x);
+        r.waitingTime += STEPS2TIME(c.veh_waiting[x]);
+    }
+    r.meanSpeed = lane_mean_speed(c, l);
+    double fractions = 0;
+    for (int i = 0; i < c.lane_npartial[l]; i++) {
+        const int p = c.lane_partial[(size_t)l * MAX_PARTIAL + i];
+        fractions += c.lane_length[l] - veh_back_pos_on_lane(c, p, l);   // getFractionalVehicleLength(false)
+    }
+    const int last = c.lane_last[l];
+    if (last >= 0 && c.veh_pos[last] < veh_length(c, last)) {
+        fractions -= veh_length(c, last) - c.veh_pos[last];
+    }
+    r.occupancy = (netto + fractions) / c.lane_length[l];
+    return r;
+}
+
 // MSEdge::getCurrentTravelTime(minSpeed)
 SB2_HD double edge_current_travel_time(const Ctx& c, int e, double minSpeed) {
     const int l0 = c.edge_lane_begin[e];

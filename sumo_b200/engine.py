@@ -53,6 +53,8 @@ LANE_MEANDATA = np.dtype([("sample_seconds", np.float64), ("travelled_distance",
                           ("front_sample_seconds", np.float64), ("front_travelled_distance", np.float64), ("veh_length_sum", np.float64),
                           ("occupation_sum", np.float64), ("minimal_vehicle_length", np.float64), ("departed", np.int32), ("arrived", np.int32),
                           ("entered", np.int32), ("left", np.int32), ("teleported", np.int32), ("reserved", np.int32)])
+LANE_STATS = np.dtype([("vehicle_number", np.int32), ("halting_number", np.int32), ("mean_speed", np.float64), ("occupancy", np.float64),
+                       ("waiting_time", np.float64)])
 FCD_ROW = np.dtype([("slot", np.int32), ("lane", np.int32), ("pos", np.float64), ("speed", np.float64),
                     ("x", np.float64), ("y", np.float64), ("angle", np.float64)])
 
@@ -86,6 +88,7 @@ def load_library(path=None):
     lib.sumob200_summary_now.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_summary_now_static.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     lib.sumob200_meandata_interval.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    lib.sumob200_lane_stats_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_e1_count.argtypes = [ctypes.c_void_p]
     lib.sumob200_e1_interval.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
@@ -241,6 +244,12 @@ class Engine:
         out = np.zeros(1, dtype=SUMMARY)
         _check(self._lib, self._lib.sumob200_summary_now_static(self._h, out.ctypes.data), "sumob200_summary_now_static")
         return out[0]
+
+    def lane_stats(self):
+        """libsumo.lane.getLastStepVehicleNumber / HaltingNumber / MeanSpeed / Occupancy / getWaitingTime of every lane (dtype LANE_STATS)"""
+        out = np.zeros(max(self.num_lanes, 1), dtype=LANE_STATS)
+        _check(self._lib, self._lib.sumob200_lane_stats_all(self._h, out.ctypes.data, out.shape[0]), "sumob200_lane_stats_all")
+        return out[:self.num_lanes]
 
     def meandata_interval(self):
         """the raw MSLaneMeanDataValues members of every lane since the last call (dtype LANE_MEANDATA, indexed by lane); resets them"""
