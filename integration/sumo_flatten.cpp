@@ -64,6 +64,9 @@
 #include <microsim/output/MSDetectorControl.h>
 #include <microsim/output/MSInductLoop.h>
 #include <microsim/output/MSMeanData_Net.h>
+#include <microsim/trigger/MSLaneSpeedTrigger.h>
+#include <microsim/trigger/MSTriggeredRerouter.h>
+#include <microsim/trigger/MSCalibrator.h>
 #include <random>
 #include <list>
 #include <set>
@@ -648,6 +651,16 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         }
         ff.put("route_begin", routeBegin);
         ff.put("route_edges", routeEdges);
+    }
+    // ---------------- triggers of additional files change lane speeds, routes or flows during the run: not modelled, refused
+    if (!MSLaneSpeedTrigger::getInstances().empty()) {
+        throw ProcessError("sumob200: variableSpeedSigns are not supported");
+    }
+    if (!MSTriggeredRerouter::getInstances().empty()) {
+        throw ProcessError("sumob200: rerouters are not supported");
+    }
+    if (!MSCalibrator::getInstances().empty()) {
+        throw ProcessError("sumob200: calibrators are not supported");
     }
     // ---------------- E1 induction loops (NLDetectorBuilder::buildInductLoop; row f4): lane, position, length, in id order (the
     // order MSDetectorControl::writeOutput visits them).  Other detector types are not modelled by the engine: refused.

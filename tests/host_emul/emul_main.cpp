@@ -392,6 +392,45 @@ int main(int argc, char** argv) {
     FILE* fsum = summaryOut.empty() ? nullptr : fopen(summaryOut.c_str(), "w");
     FILE* fe1 = e1Out.empty() ? nullptr : fopen(e1Out.c_str(), "w");
     FILE* fmd = mdOut.empty() ? nullptr : fopen(mdOut.c_str(), "w");
+    SUMOTime e1LastFlush = c.t;
+    SUMOTime mdLastFlush = c.t;
+    auto flushMd = [&](SUMOTime from) {
+        for (int l = 0; l < c.nL; l++) {
+            if (lane_internal(c, l)) {
+                continue;
+            }
+            // begin lane sampleSeconds travelledDistance waitSeconds timeLoss frontSampleSeconds frontTravelledDistance vehLengthSum occupationSum
+            // minimalVehicleLength departed arrived entered left teleported
+            fprintf(fmd, "%lld %d", (long long)from, l);
+            for (int k = 0; k < MD_NSUMS; k++) {
+                fprintf(fmd, " %.17g", c.md_sums[(size_t)k * c.nL + l]);
+                c.md_sums[(size_t)k * c.nL + l] = 0.;
+            }
+            fprintf(fmd, " %.17g", c.md_minlen[l] == SB2_DBL_MAX ? -1. : c.md_minlen[l]);
+            c.md_minlen[l] = SB2_DBL_MAX;
+            for (int k = 0; k < MD_NCOUNTS; k++) {
+                fprintf(fmd, " %d", c.md_counts[(size_t)k * c.nL + l]);
+                c.md_counts[(size_t)k * c.nL + l] = 0;
+            }
+            fprintf(fmd, "\n");
+        }
+    };
+    auto flushE1 = [&](SUMOTime from, SUMOTime to) {
+        for (int v = 0; v < c.nV; v++) {
+            veh_e1_collect_on_detector(c, v);
+        }
+        const int n = std::min(c.counters[12], c.e1_event_cap);
+        std::vector<E1Event> ev(c.e1_events, c.e1_events + n);
+        std::vector<E1Result> res((size_t)c.nE1);
+        e1_reduce(ev, c.e1_entered, c.nE1, c.e1_pos, c.e1_end, from, to, res.data());
+        c.counters[12] = 0;
+        for (int d = 0; d < c.nE1; d++) {
+            c.e1_entered[d] = 0;
+            // begin end detector nVehContrib flow occupancy speed harmonicMeanSpeed length nVehEntered
+            fprintf(fe1, "%lld %lld %d %d %.17g %.17g %.17g %.17g %.17g %d\n", (long long)from, (long long)to, d,
+                    res[d].nVehContrib, res[d].flow, res[d].occupancy, res[d].speed, res[d].harmonicMeanSpeed, res[d].length, res[d].nVehEntered);
+        }
+    };
     FILE* femis = emisOut.empty() ? nullptr : fopen(emisOut.c_str(), "wb");
     FILE* ffcd = fcdOut.empty() ? nullptr : fopen(fcdOut.c_str(), "w");
     FILE* fdraws = drawsIn.empty() ? nullptr : fopen(drawsIn.c_str(), "rb");
@@ -500,41 +539,12 @@ int main(int argc, char** argv) {
         }
         if (fe1 != nullptr && c.nE1 > 0 && (t + c.DELTA_T) % e1Period == 0) {
             // MSDetectorControl::writeOutput(step + DELTA_T): the interval [t + DELTA_T - period, t + DELTA_T)
-            for (int v = 0; v < c.nV; v++) {
-                veh_e1_collect_on_detector(c, v);
-            }
-            const int n = std::min(c.counters[12], c.e1_event_cap);
-            std::vector<E1Event> ev(c.e1_events, c.e1_events + n);
-            std::vector<E1Result> res((size_t)c.nE1);
-            e1_reduce(ev, c.e1_entered, c.nE1, c.e1_pos, c.e1_end, t + c.DELTA_T - e1Period, t + c.DELTA_T, res.data());
-            c.counters[12] = 0;
-            for (int d = 0; d < c.nE1; d++) {
-                c.e1_entered[d] = 0;
-                // begin end detector nVehContrib flow occupancy speed harmonicMeanSpeed length nVehEntered
-                fprintf(fe1, "%lld %lld %d %d %.17g %.17g %.17g %.17g %.17g %d\n", (long long)(t + c.DELTA_T - e1Period), (long long)(t + c.DELTA_T), d,
-                        res[d].nVehContrib, res[d].flow, res[d].occupancy, res[d].speed, res[d].harmonicMeanSpeed, res[d].length, res[d].nVehEntered);
-            }
+            flushE1(t + c.DELTA_T - e1Period, t + c.DELTA_T);
+            e1LastFlush = t + c.DELTA_T;
         }
         if (fmd != nullptr && c.md_on && (t + c.DELTA_T) % mdPeriod == 0) {
-            for (int l = 0; l < c.nL; l++) {
-                if (lane_internal(c, l)) {
-                    continue;
-                }
-                // begin lane sampleSeconds travelledDistance waitSeconds timeLoss frontSampleSeconds frontTravelledDistance vehLengthSum occupationSum
-                // minimalVehicleLength departed arrived entered left teleported
-                fprintf(fmd, "%lld %d", (long long)(t + c.DELTA_T - mdPeriod), l);
-                for (int k = 0; k < MD_NSUMS; k++) {
-                    fprintf(fmd, " %.17g", c.md_sums[(size_t)k * c.nL + l]);
-                    c.md_sums[(size_t)k * c.nL + l] = 0.;
-                }
-                fprintf(fmd, " %.17g", c.md_minlen[l] == SB2_DBL_MAX ? -1. : c.md_minlen[l]);
-                c.md_minlen[l] = SB2_DBL_MAX;
-                for (int k = 0; k < MD_NCOUNTS; k++) {
-                    fprintf(fmd, " %d", c.md_counts[(size_t)k * c.nL + l]);
-                    c.md_counts[(size_t)k * c.nL + l] = 0;
-                }
-                fprintf(fmd, "\n");
-            }
+            flushMd(t + c.DELTA_T - mdPeriod);
+            mdLastFlush = t + c.DELTA_T;
         }
         if (femis != nullptr) {
             int64_t ne = 0;
@@ -578,9 +588,15 @@ int main(int argc, char** argv) {
         fclose(ffcd);
     }
     if (fe1 != nullptr) {
+        if (c.nE1 > 0 && c.t > e1LastFlush) {
+            flushE1(e1LastFlush, c.t);   // MSDetectorControl::close: the partial interval at the end of the simulation
+        }
         fclose(fe1);
     }
     if (fmd != nullptr) {
+        if (c.md_on && c.t > mdLastFlush) {
+            flushMd(mdLastFlush);   // the partial interval MSDetectorControl::close writes at the end of the simulation
+        }
         fclose(fmd);
     }
     if (fsum != nullptr) {

@@ -40,20 +40,20 @@ def meandata_case(name):
     return flat, trace, out
 
 
-def derive(r, lane_len, speed_limit):
+def derive(r, lane_len, speed_limit, period=PERIOD_S):
     """MSLaneMeanDataValues::write (MSMeanData_Net.cpp:253-358) for one lane = one single-lane edge, default <edgeData> options"""
     sample, dist, wait, tloss, fsample, fdist, lensum, occ, minlen = (float(x) for x in r[:9])
     dep, arr, ent, left, tele = (int(x) for x in r[9:14])
     out = {"sampledSeconds": sample}
     cap = 1000. / max(minlen if minlen >= 0 else 1.7976931348623157e308, EPS)
-    density = min(fsample / PERIOD_S * 1000. / lane_len, cap)
-    overlap_density = min(sample / PERIOD_S * 1000. / lane_len, cap)
+    density = min(fsample / period * 1000. / lane_len, cap)
+    overlap_density = min(sample / period * 1000. / lane_len, cap)
     if sample > 0:
         if fdist > EPS:
             out["traveltime"] = min(MAX_TT, lane_len * fsample / fdist)
         out["overlapTraveltime"] = min(MAX_TT, (lane_len + lensum / sample) * sample / dist) if dist > 0 else MAX_TT
         out["density"] = out["laneDensity"] = density
-        out["occupancy"] = occ / PERIOD_S / lane_len * 100.
+        out["occupancy"] = occ / period / lane_len * 100.
         out["waitingTime"], out["timeLoss"] = wait, tloss
         out["speed"] = dist / sample
         out["speedRelative"] = 0. if speed_limit == 0 else dist / sample / speed_limit
