@@ -829,7 +829,7 @@ int sumob200_fcd_format_xml(sumob200_engine* e, const sumob200_fcd_row* rows, in
             return SUMOB200_EINVAL;
         }
     }
-    const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, m.h.veh_type, m.h.veh_idrank};
+    const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, m.h.veh_type, m.h.veh_idrank, fcdxml_precision(m.h.DELTA_T)};
     std::string out;
     fcdxml_timestep(nm, rows, n, time_ms, out);
     *length = out.size();

@@ -20,11 +20,18 @@
 
 namespace sb2 {
 
-inline std::string fcdxml_time2string(int64_t t) {
+// gPrecision: 2 unless the step length is not a multiple of 10 ms, then 3 (MSFrame.cpp:1051-1053; --precision itself is not modelled)
+inline int fcdxml_precision(int64_t delta_t_ms) { return delta_t_ms % 10 != 0 ? 3 : 2; }
+
+inline std::string fcdxml_time2string(int64_t t, int precision = 2) {
     const bool neg = t < 0;
     unsigned long long a = (unsigned long long)(neg ? -t : t);
-    a = (a + 5) / 10;   // scale = 10^(3 - gPrecision)
     char buf[48];
+    if (precision >= 3) {
+        snprintf(buf, sizeof(buf), "%s%llu.%03llu", neg ? "-" : "", a / 1000, a % 1000);
+        return buf;
+    }
+    a = (a + 5) / 10;   // scale = 10^(3 - gPrecision)
     snprintf(buf, sizeof(buf), "%s%llu.%02llu", neg ? "-" : "", a / 100, a % 100);
     return buf;
 }
@@ -35,12 +42,14 @@ struct FcdXmlNames {
     const std::vector<std::string>* vtype;   // by vType index
     const int32_t* veh_type;                 // by slot
     const int32_t* veh_idrank;               // by slot
+    int precision = 2;                       // fcdxml_precision(DELTA_T)
 };
 
 // appends one <timestep> element for `rows` (any order) to `out`
 inline void fcdxml_timestep(const FcdXmlNames& nm, const sumob200_fcd_row* rows, int n, int64_t time_ms, std::string& out, int max_threads = 0) {
+    const int prec = nm.precision >= 3 ? 3 : 2;
     if (n <= 0) {
-        out += "    <timestep time=\"" + fcdxml_time2string(time_ms) + "\"/>\n";
+        out += "    <timestep time=\"" + fcdxml_time2string(time_ms, prec) + "\"/>\n";
         return;
     }
     std::vector<int> order(n);
@@ -58,11 +67,11 @@ inline void fcdxml_timestep(const FcdXmlNames& nm, const sumob200_fcd_row* rows,
         char num[6][40];
         for (int i = b; i < e; i++) {
             const sumob200_fcd_row& r = rows[order[i]];
-            snprintf(num[0], 40, "%.2f", r.x);
-            snprintf(num[1], 40, "%.2f", r.y);
-            snprintf(num[2], 40, "%.2f", r.angle);
-            snprintf(num[3], 40, "%.2f", r.speed);
-            snprintf(num[4], 40, "%.2f", r.pos);
+            snprintf(num[0], 40, "%.*f", prec, r.x);
+            snprintf(num[1], 40, "%.*f", prec, r.y);
+            snprintf(num[2], 40, "%.*f", prec, r.angle);
+            snprintf(num[3], 40, "%.*f", prec, r.speed);
+            snprintf(num[4], 40, "%.*f", prec, r.pos);
             s += "        <vehicle id=\"";
             s += (*nm.veh)[r.slot];
             s += "\" x=\""; s += num[0];
@@ -72,7 +81,7 @@ inline void fcdxml_timestep(const FcdXmlNames& nm, const sumob200_fcd_row* rows,
             s += "\" speed=\""; s += num[3];
             s += "\" pos=\""; s += num[4];
             s += "\" lane=\""; s += (*nm.lane)[r.lane];
-            s += "\" slope=\"0.00\"/>\n";
+            s += prec >= 3 ? "\" slope=\"0.000\"/>\n" : "\" slope=\"0.00\"/>\n";
         }
     };
     if (nt == 1) {
@@ -86,7 +95,7 @@ inline void fcdxml_timestep(const FcdXmlNames& nm, const sumob200_fcd_row* rows,
             t.join();
         }
     }
-    out += "    <timestep time=\"" + fcdxml_time2string(time_ms) + "\">\n";
+    out += "    <timestep time=\"" + fcdxml_time2string(time_ms, prec) + "\">\n";
     for (const std::string& p : parts) {
         out += p;
     }

@@ -520,7 +520,7 @@ int main(int argc, char** argv) {
                     rows.push_back(r);
                 }
             }
-            const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, c.veh_type, c.veh_idrank};
+            const FcdXmlNames nm = {&m.veh_names, &m.lane_names, &m.vt_names, c.veh_type, c.veh_idrank, fcdxml_precision(c.DELTA_T)};
             std::string xml;
             fcdxml_timestep(nm, rows.data(), (int)rows.size(), t, xml, 2);
             fwrite(xml.data(), 1, xml.size(), ffcdxml);

@@ -1,5 +1,6 @@
-"""The engine against the reference's OWN texttest goldens for E1 detectors and edge-based mean data (tests/sumo/output/e1/**/detector.sumo,
-tests/sumo/output/meandata_edgebased/**/aggregated*.sumo: files the reference's maintainers committed): the test's inputs and options
+"""The engine against the reference's OWN texttest goldens: FCD output (tests/sumo/output/fcd-output/*/fcd.sumo), E1 detectors
+(tests/sumo/output/e1/**/detector.sumo) and edge-based mean data (tests/sumo/output/meandata_edgebased/**/aggregated*.sumo) -- files
+the reference's maintainers committed from a stock build: the test's inputs and options
 are flattened by the reference's loader (oracle/_ref/sumo_flatten), the step runs in tests/host_emul (the device functions compiled
 for the host), and the intervals it reports must be the committed lines -- every attribute as printed.
 
@@ -163,3 +164,41 @@ def test_engine_reproduces_the_reference_edgedata_golden(rel, golden, period, ho
 
 def np_count(begin):
     return [int(begin[i + 1]) - int(begin[i]) for i in range(len(begin) - 1)]
+
+
+FCD_TESTS = ["begin", "period", "period_begin", "subsecond", "precision", "angle"]
+
+
+@pytest.mark.parametrize("name", FCD_TESTS)
+def test_engine_reproduces_the_reference_fcd_golden(name, host_emul, tmp_path):
+    """every <timestep> of the committed fcd.sumo (the device.fcd.begin / period options only select which steps are written): the
+    <vehicle .../> lines of the engine's formatter (sb2_fcdxml.h) for that step must be the same strings -- positions, speeds and
+    angles of the engine's trajectories printed like MSFCDExport does, incl. 5 ms and 25 ms step lengths (3 decimals)"""
+    rel = "output/fcd-output/" + name
+    if not os.path.isdir(os.path.join(TT_ROOT, rel)):
+        pytest.skip("reference sources (tests/sumo) are not available on this machine")
+    options = stage(rel, tmp_path)
+    flat = str(tmp_path / "x.flat")
+    r = subprocess.run([os.path.join(REF, "sumo_flatten"), "--flat-out", flat, "--trace-out", str(tmp_path / "x.trace"),
+                        "--draws-out", str(tmp_path / "x.draws")] + options, cwd=str(tmp_path), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-2000:]
+    steps = len(load_trace(str(tmp_path / "x.trace")))
+    out = str(tmp_path / "engine.xml")
+    subprocess.run([host_emul, flat, "--fcd-xml-out", out, "--draws", str(tmp_path / "x.draws"), "--steps", str(steps)], check=True, timeout=900,
+                   stderr=subprocess.DEVNULL)
+
+    def blocks(path):
+        res, cur = {}, None
+        for line in open(path):
+            m = re.search(r'<timestep time="([^"]*)"', line)
+            if m:
+                cur = m.group(1)
+                res[cur] = []
+            elif "<vehicle" in line and cur is not None:
+                res[cur].append(line.strip())
+        return res
+
+    golden, mine = blocks(os.path.join(TT_ROOT, rel, "fcd.sumo")), blocks(out)
+    assert len(golden) >= 1 and sum(len(v) for v in golden.values()) >= 1
+    for t, lines in golden.items():
+        assert mine.get(t) == lines, (t, lines[:2], (mine.get(t) or [])[:2])
