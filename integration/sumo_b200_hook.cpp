@@ -175,6 +175,11 @@ struct Hook {
     }
 
     void step(MSNet* net) {
+        for (const MSEdge* e : MSEdge::getAllEdges()) {
+            if (e->isVaporizing()) {   // (<vaporizer> starts as an event, nothing at load time tells)
+                throw ProcessError("sumob200: vaporizers are not supported (edge '" + e->getID() + "')");
+            }
+        }
         sumob200_step_result r;
         if (sumob200_step(eng, 1, &r) != 0) {
             throw ProcessError(std::string("sumob200_step failed: ") + sumob200_last_error());

@@ -614,6 +614,10 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
                 temMass.push_back(mass);
                 temIncl.push_back(ep->getDouble(SUMO_ATTR_FRONTSURFACEAREA) / mass * -9.05337017 + -0.00017774);
             }
+            if (TIME2STEPS(t->getParameter().getCFParam(SUMO_ATTR_SIGMA_STEP, TS)) > DELTA_T) {
+                // MSCFModel_Krauss::myDawdleStep: the dawdle draw is kept for several steps (MSCFModel_Krauss.cpp:51-60, 96-113)
+                throw ProcessError("sumob200: vType '" + t->getID() + "': sigmaStep longer than the step length is not supported");
+            }
             idmDelta.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_DELTA, 4.));
             idmStep.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_STEPPING, .25));
         }
@@ -651,6 +655,17 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         }
         ff.put("route_begin", routeBegin);
         ff.put("route_edges", routeEdges);
+    }
+    // ---------------- other things the step engine does not model
+    if (oc.isSet("load-state")) {
+        throw ProcessError("sumob200: --load-state is not supported");
+    }
+    for (const MSEdge* e : MSEdge::getAllEdges()) {
+        for (const MSLane* l : e->getLanes()) {
+            if (l->getBidiLane() != nullptr) {
+                throw ProcessError("sumob200: bidirectional lanes (bidi) are not supported");
+            }
+        }
     }
     // ---------------- triggers of additional files change lane speeds, routes or flows during the run: not modelled, refused
     if (!MSLaneSpeedTrigger::getInstances().empty()) {
@@ -934,6 +949,11 @@ main(int argc, char** argv) {
                 net->simulationStep();
                 if (fd != nullptr) {
                     pred.checkAndWrite(t, fd);
+                }
+                for (const MSEdge* e : MSEdge::getAllEdges()) {
+                    if (e->isVaporizing()) {   // (<vaporizer> starts as an event, nothing at load time tells)
+                        throw ProcessError("sumob200: vaporizers are not supported (edge '" + e->getID() + "')");
+                    }
                 }
                 std::vector<const MSVehicle*> on;
                 MSVehicleControl& vc = net->getVehicleControl();

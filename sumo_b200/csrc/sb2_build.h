@@ -118,7 +118,7 @@ public:
         const int64_t nL = (int64_t)ff.count("lane_length"), nE = (int64_t)ff.count("edge_flags"), nK = (int64_t)ff.count("link_from");
         const int64_t nV = (int64_t)ff.count("veh_type"), nT = (int64_t)ff.count("vt_length"), nTL = (int64_t)ff.count("tl_cur_phase");
         const int64_t nR = (int64_t)ff.count("route_begin") - 1, nPh = (int64_t)ff.count("phase_dur");
-        const int64_t nJ = 1 + nL;   // junction indices are only compared with each other
+        const int64_t nJ = 2 * (int64_t)nL + 2;   // junction indices are only compared with each other; an edge has two ends
         for (const char* per_lane : {"lane_speed", "lane_edge", "lane_flags", "lane_pred_logical", "lane_pred_normal", "lane_entry_link", "lane_to_junction", "lane_from_junction", "lane_geomfactor"}) {
             if ((int64_t)ff.count(per_lane) != nL) {
                 throw std::invalid_argument(std::string("flat array '") + per_lane + "' must have one element per lane");
