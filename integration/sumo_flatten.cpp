@@ -316,8 +316,10 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             foeLinkBegin.push_back((int32_t)foeLink.size());
             const std::vector<const MSLane*>& fls = k->getFoeLanes();
             const std::vector<MSLink::ConflictInfo>& cis = k->getConflicts();
-            for (int i = 0; i < (int)fls.size(); i++) {
-                foeLane.push_back(lIdx(fls[i]));
+            // (MSLink::recheckSetRequestInformation, MSLink.cpp:614, appends conflict records WITHOUT a foe lane: they are only reached
+            // through the foeConflictIndex of the other link's record -- exported with foe lane -1)
+            for (int i = 0; i < (int)std::max(fls.size(), cis.size()); i++) {
+                foeLane.push_back(i < (int)fls.size() ? lIdx(fls[i]) : -1);
                 if (i < (int)cis.size()) {
                     lbc.push_back(cis[i].lengthBehindCrossing);
                     csize.push_back(cis[i].conflictSize);

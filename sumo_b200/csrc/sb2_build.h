@@ -161,7 +161,7 @@ public:
         checkIndex(ff, "link_from", 0, nL); checkIndex(ff, "link_to", 0, nL); checkIndex(ff, "link_via", -1, nL);
         checkIndex(ff, "link_internal_before", -1, nL); checkIndex(ff, "link_entry", -1, nK); checkIndex(ff, "link_exit", -1, nK);
         checkIndex(ff, "link_tl", -1, nTL); checkIndex(ff, "link_index", -1, 256); checkIndex(ff, "link_junction", -1, nJ);
-        checkIndex(ff, "foelink", 0, nK); checkIndex(ff, "foelane", 0, nL); checkIndex(ff, "conf_foeidx", -1, 1 << 20);
+        checkIndex(ff, "foelink", 0, nK); checkIndex(ff, "foelane", -1, nL); checkIndex(ff, "conf_foeidx", -1, 1 << 20);
         checkIndex(ff, "tllink_link", 0, nK); checkIndex(ff, "tl_cur_phase", 0, nPh > 0 ? nPh : 1);
         checkIndex(ff, "route_edges", 0, nE);
         checkIndex(ff, "veh_type", 0, nT); checkIndex(ff, "veh_route", 0, nR);

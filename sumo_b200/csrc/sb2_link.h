@@ -249,7 +249,7 @@ SB2_HD bool link_hasApproachingFoe(const Ctx& c, int k, int buf, SUMOTime arriva
         }
     }
     for (int i = c.link_foelane_begin[k]; i < c.link_foelane_begin[k + 1]; i++) {
-        if (lane_nveh_with_partials(c, c.foelane[i]) > 0) {
+        if (c.foelane[i] >= 0 && lane_nveh_with_partials(c, c.foelane[i]) > 0) {
             return true;
         }
     }

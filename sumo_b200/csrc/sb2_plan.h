@@ -250,6 +250,9 @@ SB2_HD void veh_checkLinkLeader(const Ctx& c, const Ego& e, int link, int lane, 
         const double radius = c.link_radius[link];
         for (int i = c.link_foelane_begin[link]; i < c.link_foelane_begin[link + 1]; ++i) {
             const int foeLane = c.foelane[i];
+            if (foeLane < 0) {
+                continue;   // a conflict record without foe lane (only addressed through conf_foeidx, MSLink.cpp:614)
+            }
             if (c.lane_last[foeLane] < 0 && c.lane_npartial[foeLane] == 0) {
                 continue;   // nobody on the foe lane: the AnyVehicleIterator loop below would not run (nothing above it has side effects)
             }
