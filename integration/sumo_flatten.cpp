@@ -662,6 +662,12 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     if (oc.isSet("load-state")) {
         throw ProcessError("sumob200: --load-state is not supported");
     }
+    if (oc.getBool("ignore-route-errors")) {
+        throw ProcessError("sumob200: --ignore-route-errors is not supported (insertion with impossible depart speeds)");
+    }
+    if (string2time(oc.getString("max-depart-delay")) >= 0) {
+        throw ProcessError("sumob200: --max-depart-delay is not supported");
+    }
     for (const MSEdge* e : MSEdge::getAllEdges()) {
         for (const MSLane* l : e->getLanes()) {
             if (l->getBidiLane() != nullptr) {
