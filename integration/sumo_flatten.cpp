@@ -383,6 +383,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         NameTable tlNames;
         for (MSTrafficLightLogic* logic : tls) {
             tlNames.add(logic->getID());
+            if (dynamic_cast<MSSimpleTrafficLightLogic*>(logic) == nullptr || logic->getLogicType() != TrafficLightType::STATIC) {
+                throw ProcessError("sumob200: traffic light '" + logic->getID() + "' is of type '" + toString(logic->getLogicType()) + "' (only static programs are supported)");
+            }
             tlStatic.push_back(dynamic_cast<MSSimpleTrafficLightLogic*>(logic) != nullptr && logic->getLogicType() == TrafficLightType::STATIC ? 1 : 0);
             for (const MSPhaseDefinition* p : logic->getPhases()) {
                 dur.push_back(p->duration);
@@ -672,6 +675,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         for (const MSLane* l : e->getLanes()) {
             if (l->getBidiLane() != nullptr) {
                 throw ProcessError("sumob200: bidirectional lanes (bidi) are not supported");
+            }
+            if (l->getOpposite() != nullptr) {
+                throw ProcessError("sumob200: opposite-direction driving (<neigh> lanes) is not supported");
             }
         }
     }

@@ -38,6 +38,7 @@ def stage(rel, tmp):
 
 
 def run_one(rel):
+    os.makedirs("/tmp/w", exist_ok=True)
     tmp = tempfile.mkdtemp(prefix="tt_", dir="/tmp/w")
     try:
         options = stage(rel, tmp)
