@@ -662,6 +662,32 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         ff.put("route_edges", routeEdges);
     }
     // ---------------- other things the step engine does not model
+    // ---- options: everything of the "Processing" and "Mesoscopic" topics that is not at its default must be one the engine is known to
+    // honour (exported below, or applied by the reference's loader to the objects that are exported) -- never silently ignored
+    {
+        static const std::set<std::string> honoured = {
+            "route-steps", "scale", "scale-suffix",  // loader only (the hook loads everything at once; --scale has been applied to the loaded vehicles)
+            "default.speeddev", "default.departspeed", "default.departlane", "default.carfollowmodel", "default.emergencydecel",   // in the exported vTypes / scalars
+            "collision.mingap-factor",               // MSVehicleType::getCollisionMinGapFactor, exported per vType
+            "time-to-teleport", "time-to-impatience", "ignore-junction-blocker", "startup-wait-threshold", "tls.yellow.min-decel",
+            "emergencydecel.warning-threshold",      // exported scalars
+            "step-method.ballistic", "lateral-resolution", "no-internal-links", "lanechange.duration", "ignore-route-errors", "max-depart-delay",   // refused with their own message
+            "waiting-time-memory", "lanechange.overtake-right", "pedestrian.model", "keep-after-arrival", "insertion-checks",
+            "tls.actuated.show-detectors", "tls.actuated.detector-length", "tls.actuated.jam-threshold", "parking.maneuver",
+            "weights.reversal-penalty", "weights.turnaround-penalty", "mapmatch.distance", "mapmatch.junctions", "mapmatch.taz", "slope-centered",
+            "persontrip.walk-opposite-factor", "ride.stop-tolerance", "railsignal-moving-block", "railsignal.max-block-length",
+            "railsignal.default-classes", "railsignal.moving-block.default-classes", "railsignal.moving-block.max-dist",
+            // (lane changing, persons, rail, actuated lights, stops, routing: the objects they act on are refused)
+        };
+        for (const std::string& topic : {std::string("Processing"), std::string("Mesoscopic")}) {
+            for (const std::string& name : oc.getSubTopicsEntries(topic)) {
+                if (oc.isSet(name) && !oc.isDefault(name) && honoured.count(name) == 0 && name.compare(0, 11, "pedestrian.") != 0
+                        && name.compare(0, 14, "overhead-wire.") != 0) {
+                    throw ProcessError("sumob200: option --" + name + " is not modelled by the engine (only its default is supported)");
+                }
+            }
+        }
+    }
     if (oc.isSet("load-state")) {
         throw ProcessError("sumob200: --load-state is not supported");
     }

@@ -1,5 +1,5 @@
 """The reference's own texttest scenarios through the engine, in bulk (tools_dev/texttest_sweep.py; results of the full sweep over 4585
-test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 266 -- reproduces the reference's trajectories
+test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 261 -- reproduces the reference's trajectories
 bit for bit, everything else is refused with a message, rejected by the reference itself, or has no vehicles).
 
 This test re-runs every fourth of the accepted scenarios: the reference's loader flattens the scenario and records the reference's
@@ -27,6 +27,8 @@ REFUSED = {
     "opposite_direction_driving/bugs/ticket9721": "opposite-direction driving",
     "rail/slow_fast_slow": "only static programs are supported",
     "output/meandata_edgebased/jam1": "variableSpeedSigns are not supported",
+    "bugs/12xxx/ticket12721c": "option --collision.action is not modelled",
+    "junction_model/opposite_left_turn/small_junction": "option --collision.check-junctions is not modelled",
 }
 
 
