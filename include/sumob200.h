@@ -46,7 +46,7 @@ extern "C" {
 #define SUMOB200_F_DEFERRED_UNRESOLVED 1024  /* executeMove pass 2 did not converge (sb2_exec.h) */
 #define SUMOB200_F_PARTITION_REACH 2048      /* a vehicle's look-ahead left the columns its rank simulates (edges too short for the ghost width) */
 #define SUMOB200_F_HALO_OVERFLOW 4096        /* a halo message needed more vehicle records than its capacity */
-#define SUMOB200_F_DETECTOR_OVERFLOW 8192    /* more E1 passages in one output interval than the event list holds, or > 4 detectors under one vehicle */
+#define SUMOB200_F_DETECTOR_OVERFLOW 8192    /* more E1 passages in one output interval than the event list holds, or > 4 E1 (or > 8 E2) detectors under one vehicle, or more E2 notifications in a step than 2 per vehicle + 65536 */
 
 typedef struct sumob200_engine sumob200_engine;
 
@@ -212,6 +212,41 @@ typedef struct sumob200_e1_event {
     int32_t reserved;
 } sumob200_e1_event;
 int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, int capacity, int* n, int32_t* entered);
+
+/* E2 lane area detectors (src/microsim/output/MSE2Collector.cpp; row f4).  Part of the scenario: arrays e2_lane (int32), e2_start,
+ * e2_length (float64, metres: myStartPos, myDetectorLength of the built detector), e2_jam_time (int64 ms), e2_jam_speed, e2_jam_dist
+ * (float64: the timeThreshold / speedThreshold / jamThreshold attributes of <laneAreaDetector>).  One lane per detector.  Vehicles
+ * notify the detectors during sumob200_step as MSE2Collector::notifyEnter / notifyMove / notifyLeave do; after every step the engine
+ * runs MSE2Collector::detectorUpdate on the device (notifications sorted by distance to the detector's end, sums added in that order,
+ * halting durations, jams).  sumob200_e2_interval = MSE2Collector::writeXMLOutput for every detector (the attributes of one
+ * <interval .../>, durations in seconds), then MSE2Collector::reset.  Call it after the step that completes the period.
+ * Not supported together with sumob200_set_partition (SUMOB200_EUNSUPPORTED). */
+typedef struct sumob200_e2_interval_t {
+    double sampled_seconds;
+    int32_t n_veh_entered, n_veh_left, n_veh_seen, max_jam_length_in_vehicles;
+    double mean_speed, mean_time_loss, mean_occupancy, max_occupancy, mean_max_jam_length_in_vehicles, mean_max_jam_length_in_meters,
+           max_jam_length_in_meters;
+    int32_t jam_length_in_vehicles_sum, started_halts;
+    double jam_length_in_meters_sum;
+    double mean_halting_duration, max_halting_duration, halting_duration_sum;
+    double mean_interval_halting_duration, max_interval_halting_duration, interval_halting_duration_sum;
+    double mean_vehicle_number;
+    int32_t max_vehicle_number, reserved;
+} sumob200_e2_interval_t;
+int sumob200_e2_count(const sumob200_engine* e);
+int sumob200_e2_interval(sumob200_engine* e, sumob200_e2_interval_t* out, int capacity);
+/* The raw notifications of the LAST step instead of the aggregates, for a caller that keeps the reference's MSE2Collector objects
+ * (the hook of integration/sumo_b200_hook.cpp puts them into myMoveNotifications, so that the reference's own detectorUpdate,
+ * writeXMLOutput and the libsumo::LaneArea getters work): one record per (vehicle, detector) that MSE2Collector::notifyMove would
+ * have stored in that step, in no particular order; counts[3 * detector + {0, 1, 2}] = vehicles entered / left / seen since the
+ * engine was created or sumob200_e2_interval was last called (running totals; may be NULL).  Changes nothing on the device. */
+typedef struct sumob200_e2_note {
+    int32_t detector;
+    int32_t vehicle;                 /* slot (load order) */
+    double dist_to_detector_end;
+    double time_on_detector, length_on_detector, time_loss, speed;
+} sumob200_e2_note;
+int sumob200_e2_notes(sumob200_engine* e, sumob200_e2_note* notes, int capacity, int* n, int32_t* counts);
 
 /* edgeData / laneData (src/microsim/output/MSMeanData.cpp:87-253, MSMeanData_Net.cpp:131-246; row f4).  Enabled by the scenario
  * scalar md_enabled = 1 (optional md_halt_speed = haltingSpeedThreshold, default 0.1): every vehicle then reports the part of each

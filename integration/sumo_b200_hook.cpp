@@ -58,6 +58,7 @@
 #include <microsim/output/MSMeanData_Net.h>
 #include <microsim/output/MSDetectorControl.h>
 #include <microsim/output/MSInductLoop.h>
+#include <microsim/output/MSE2Collector.h>
 #undef private
 #undef protected
 #define SUMOB200_NO_MAIN
@@ -86,6 +87,9 @@ struct Hook {
     std::vector<SUMOTime> departBucket;               // MSVehicleContainer's bucket of every slot (depart rounded up to a step)
     std::vector<MSInductLoop*> loops;                 // the E1 detectors in the order the flatten walk exported them (id order)
     std::vector<sumob200_e1_event> e1Events;
+    std::vector<MSE2Collector*> areas;                // the E2 detectors, same order as the engine's
+    std::vector<sumob200_e2_note> e2Notes;
+    std::vector<int32_t> e2Counts, e2CountsLast;
     std::vector<int32_t> e1Entered;
     std::vector<std::vector<MSMeanData_Net::MSLaneMeanDataValues*> > mdOfLane;   // per lane index: its values object in every <edgeData> / <laneData>
     std::vector<sumob200_lane_meandata> mdBuf;
@@ -132,6 +136,15 @@ struct Hook {
         if ((int)h->loops.size() != sumob200_e1_count(h->eng)) {
             throw ProcessError("sumob200: detector lists of the reference and the engine differ");
         }
+        for (const auto& item : net->getDetectorControl().getTypedDetectors(SUMO_TAG_LANE_AREA_DETECTOR)) {
+            h->areas.push_back(dynamic_cast<MSE2Collector*>(item.second));
+        }
+        if ((int)h->areas.size() != sumob200_e2_count(h->eng)) {
+            throw ProcessError("sumob200: lane area detector lists of the reference and the engine differ");
+        }
+        h->e2Notes.resize(h->areas.empty() ? 1 : 2 * (size_t)nV + 65536);
+        h->e2Counts.assign(3 * h->areas.size() + 1, 0);
+        h->e2CountsLast.assign(3 * h->areas.size() + 1, 0);
         {
             std::map<const MSLane*, int> indexOfLane;
             for (size_t i = 0; i < h->laneOfIndex.size(); i++) {
@@ -294,6 +307,25 @@ struct Hook {
                     loop->myLastLeaveTime = ev.leave_s;
                 }
             }
+        }
+        // ---- E2 detectors: this step's notifications into the reference's MSE2Collector::myMoveNotifications; its own detectorUpdate
+        // (MSDetectorControl::updateDetectors in writeOutput below) sorts and aggregates them, its writeXMLOutput prints them
+        if (!areas.empty()) {
+            int nNotes = 0;
+            if (sumob200_e2_notes(eng, e2Notes.data(), (int)e2Notes.size(), &nNotes, e2Counts.data()) != 0) {
+                throw ProcessError(std::string("sumob200_e2_notes failed: ") + sumob200_last_error());
+            }
+            for (int i = 0; i < nNotes; i++) {
+                const sumob200_e2_note& n = e2Notes[i];
+                areas[n.detector]->myMoveNotifications.push_back(new MSE2Collector::MoveNotificationInfo(vehOfSlot[n.vehicle]->getID(), 0., 0., n.speed, 0.,
+                        n.dist_to_detector_end, n.time_on_detector, n.length_on_detector, n.time_loss, 0., true));
+            }
+            for (size_t d = 0; d < areas.size(); d++) {
+                areas[d]->myNumberOfEnteredVehicles += e2Counts[3 * d] - e2CountsLast[3 * d];
+                areas[d]->myNumberOfLeftVehicles += e2Counts[3 * d + 1] - e2CountsLast[3 * d + 1];
+                areas[d]->myNumberOfSeenVehicles += e2Counts[3 * d + 2] - e2CountsLast[3 * d + 2];
+            }
+            e2CountsLast = e2Counts;
         }
         // ---- edgeData / laneData: this step's contributions added to the reference's MSLaneMeanDataValues objects, whose own
         // write() / reset() (MSMeanData::writeXMLOutput, driven by MSDetectorControl::writeOutput below) then do the rest

@@ -31,6 +31,11 @@
 #include <utils/emissions/HelpersHBEFA3.h>
 #include <utils/emissions/HelpersHBEFA4.h>
 #include <microsim/devices/MSDevice_Emissions.h>
+#include <microsim/MSInsertionControl.h>   // (expandFlows files myPendingEmits back into myAllVeh)
+#define protected public
+#include <microsim/output/MSDetectorControl.h>   // (myIntervals: which detectors write periodically)
+#include <microsim/output/MSE2Collector.h>       // (jam thresholds, lane list, nextEdges filter)
+#undef protected
 #undef private
 #include <utils/emissions/EnergyParams.h>
 #include <microsim/MSLink.h>
@@ -45,6 +50,7 @@
 #include <microsim/MSVehicleType.h>
 #include <microsim/MSVehicleControl.h>
 #include <microsim/MSInsertionControl.h>
+#include <microsim/devices/MSRoutingEngine.h>
 #include <microsim/cfmodels/MSCFModel.h>
 #include <microsim/traffic_lights/MSTLLogicControl.h>
 #include <microsim/traffic_lights/MSTrafficLightLogic.h>
@@ -453,7 +459,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
                     && p.arrivalSpeedProcedure != ArrivalSpeedDefinition::GIVEN) {
                 throw ProcessError(who + "arrivalSpeed must be 'current' or a number");
             }
-            if (p.arrivalLaneProcedure != ArrivalLaneDefinition::DEFAULT && p.arrivalLaneProcedure != ArrivalLaneDefinition::CURRENT) {
+            // (edges have one lane: a given or first-allowed arrival lane is lane 0, where the vehicle is anyway; MSVehicle::updateBestLanes
+            // then treats the arrival like a stop, which only shortens the LaneQ lengths lane changing would use.  random draws.)
+            if (p.arrivalLaneProcedure == ArrivalLaneDefinition::RANDOM) {
                 throw ProcessError(who + "arrivalLane is not supported");
             }
             const SUMOVTypeParameter& tp = v->getVehicleType().getParameter();
@@ -722,8 +730,8 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     {
         MSDetectorControl& dc = net->getDetectorControl();
         for (const SumoXMLTag tag : dc.getAvailableTypes()) {
-            if (tag != SUMO_TAG_INDUCTION_LOOP && dc.getTypedDetectors(tag).size() > 0) {
-                throw ProcessError("sumob200: detectors of type '" + toString(tag) + "' are not supported (only inductionLoop / e1Detector)");
+            if (tag != SUMO_TAG_INDUCTION_LOOP && tag != SUMO_TAG_LANE_AREA_DETECTOR && dc.getTypedDetectors(tag).size() > 0) {
+                throw ProcessError("sumob200: detectors of type '" + toString(tag) + "' are not supported (only inductionLoop / e1Detector and laneAreaDetector / e2Detector)");
             }
         }
         std::vector<int32_t> e1Lane;
@@ -747,6 +755,51 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             ff.put("e1_pos", e1Pos);
             ff.put("e1_length", e1Length);
             e1Names.put(ff, "e1");
+        }
+        // ---- E2 lane area detectors (NLDetectorBuilder::buildE2Detector; row f4): the built detector's lane, start, length and jam
+        // thresholds, in id order.  Refused: detectors over several lanes, filters, detectors coupled to a traffic light (they write
+        // when the light switches, not periodically).
+        std::set<const MSDetectorFileOutput*> periodic;
+        for (const auto& iv : dc.myIntervals) {
+            for (const auto& df : iv.second) {
+                periodic.insert(df.first);
+            }
+        }
+        std::vector<int32_t> e2Lane;
+        std::vector<double> e2Start, e2Length, e2JamSpeed, e2JamDist;
+        std::vector<int64_t> e2JamTime;
+        NameTable e2Names;
+        for (const auto& item : dc.getTypedDetectors(SUMO_TAG_LANE_AREA_DETECTOR)) {
+            MSE2Collector* det = dynamic_cast<MSE2Collector*>(item.second);
+            if (det == nullptr) {
+                throw ProcessError("sumob200: unexpected detector object '" + item.first + "'");
+            }
+            const std::string who = "sumob200: detector '" + item.first + "': ";
+            if (det->myLanes.size() != 1) {
+                throw ProcessError(who + "lane area detectors over several lanes are not supported");
+            }
+            if (!det->getVehicleTypes().empty() || det->detectsPersons() || !det->myNextEdges.empty()) {
+                throw ProcessError(who + "vTypes / nextEdges / detectPersons filters are not supported");
+            }
+            if (periodic.count(det) == 0) {
+                throw ProcessError(who + "lane area detectors coupled to a traffic light are not supported");
+            }
+            e2Lane.push_back(lIdx(det->getLane()));
+            e2Start.push_back(det->getStartPos());
+            e2Length.push_back(det->getLength());
+            e2JamSpeed.push_back(det->myJamHaltingSpeedThreshold);
+            e2JamDist.push_back(det->myJamDistanceThreshold);
+            e2JamTime.push_back((int64_t)det->myJamHaltingTimeThreshold);
+            e2Names.add(item.first);
+        }
+        if (!e2Lane.empty()) {
+            ff.put("e2_lane", e2Lane);
+            ff.put("e2_start", e2Start);
+            ff.put("e2_length", e2Length);
+            ff.put("e2_jam_speed", e2JamSpeed);
+            ff.put("e2_jam_dist", e2JamDist);
+            ff.put("e2_jam_time", e2JamTime);
+            e2Names.put(ff, "e2");
         }
     }
     // ---------------- edgeData / laneData (MSMeanData_Net; row f4): the engine accumulates the raw per-lane members, the writer stays here
@@ -809,6 +862,53 @@ void flatten(MSNet* net, const std::string& path) {
     sb2::FlatFile ff;
     flattenTo(net, ff);
     ff.save(path);
+}
+
+// ---- <flow>s (parity harness only; the hook refuses them).  The reference turns a flow into vehicles step by step:
+// MSNet::simulationStep calls MSInsertionControl::determineCandidates(time) (MSInsertionControl.cpp:219-301), which builds the
+// vehicles due at `time` (ids "flow.N", type / speedFactor drawn from the route parser's RNG, departure of probabilistic flows
+// from myFlowRNG), files them in MSVehicleContainer's bucket of their depart time and moves the buckets that are due to
+// myPendingEmits.  The engine wants every vehicle up front, so the harness makes the reference's own code do the expansion
+// BEFORE the run: the same calls, in the same order (time ascending), hence the same draws from both RNGs, the same numerical ids
+// and the same order inside each depart bucket (loaded vehicles first, then the flows' in flow order).  What checkCandidates
+// moved to myPendingEmits on the way is filed back (MSVehicleContainer::add appends to the bucket, the order is kept), so the run
+// that follows sees ordinary pre-loaded vehicles.  tools_dev/texttest_sweep.py pins this against the untouched reference: the
+// trace of a run without --flat-out (no expansion) must equal the trace of the expanded run byte by byte.
+// Returns the time of the step in which the reference would have dropped its last flow (a run without --end goes on until then even
+// if the road is empty), -1 without flows.
+SUMOTime expandFlows(MSNet* net, SUMOTime begin, SUMOTime end) {
+    MSInsertionControl& ic = net->getInsertionControl();
+    if (ic.getPendingFlowCount() == 0) {
+        return -1;
+    }
+    if (MSRoutingEngine::isEnabled()) {
+        throw ProcessError("sumob200: <flow>s with the routing engine enabled are not supported");
+    }
+    if (!ic.myPendingEmits.empty()) {
+        throw ProcessError("sumob200: <flow> expansion: insertion backlog before the first step");
+    }
+    const SUMOTime horizon = end >= 0 ? end : begin + 1000000 * DELTA_T;
+    SUMOTime last = -1;
+    for (SUMOTime t = begin; t < horizon && ic.getPendingFlowCount() > 0; t += DELTA_T) {
+        ic.determineCandidates(t);
+        last = t;
+    }
+    if (ic.getPendingFlowCount() > 0) {
+        if (end < 0) {
+            throw ProcessError("sumob200: <flow> without an end in a simulation without --end");
+        }
+        // flows that outlive --end: nothing more of them departs in this run (probabilistic ones would draw again)
+        for (MSInsertionControl::Flow& f : ic.myFlows) {
+            delete f.pars;
+        }
+        ic.myFlows.clear();
+    }
+    MSVehicleContainer::VehicleVector due;
+    due.swap(ic.myPendingEmits);
+    for (SUMOVehicle* v : due) {
+        ic.myAllVeh.add(v);
+    }
+    return last;
 }
 
 // ---- per-vehicle dawdle draws of the coming step (sigma > 0 parity, BASELINE north_star "replaying the reference's
@@ -931,6 +1031,7 @@ main(int argc, char** argv) {
     gSimulation = true;
     int ret = 0;
     MSNet* net = nullptr;
+    SUMOTime flowsUntil = -1;
     try {
         XMLSubSys::init();
         OptionsIO::setArgs((int)args.size(), args.data());
@@ -939,6 +1040,7 @@ main(int argc, char** argv) {
             return 1;
         }
         if (!flatOut.empty()) {
+            flowsUntil = expandFlows(net, string2time(oc.getString("begin")), string2time(oc.getString("end")));
             flatten(net, flatOut);
         }
         if (!traceOut.empty()) {
@@ -1034,6 +1136,9 @@ main(int argc, char** argv) {
                 state = net->simulationState(end);
                 if (state == MSNet::SIMSTATE_LOADING) {
                     state = MSNet::SIMSTATE_RUNNING;
+                }
+                if (state == MSNet::SIMSTATE_NO_FURTHER_VEHICLES && net->getCurrentTimeStep() <= flowsUntil) {
+                    state = MSNet::SIMSTATE_RUNNING;   // the unexpanded run still has a pending flow here (expandFlows)
                 }
             }
             fclose(f);

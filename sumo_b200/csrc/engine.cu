@@ -85,6 +85,7 @@ struct sumob200_engine {
     int32_t* rsScratch = nullptr;   // blocksA, blocksB, order, sorted, newOfOld, oldOfNew
     bool debugSync = getenv("SUMOB200_DEBUG_SYNC") != nullptr;
     sumob200_lane_stats* dLaneStats = nullptr;
+    sb2::E2Result* dE2Out = nullptr;
     std::vector<double> mdMinlenInit;   // SB2_DBL_MAX per lane: what md_minlen is reset to
     void* rsTmp = nullptr;          // one permuted array (16 B per vehicle)
     int64_t launches = 0;
@@ -209,6 +210,8 @@ int reslot(sumob200_engine* e) {
             rows = 7;                               // pollutant-major: seven arrays of nV
         } else if (b->name.compare(0, 7, "veh_e1_") == 0 && b->count == (size_t)nV * MAX_E1_REMINDERS) {
             rows = MAX_E1_REMINDERS;                // reminder-slot-major
+        } else if (b->name.compare(0, 7, "veh_e2_") == 0 && b->count == (size_t)nV * MAX_E2_REMINDERS) {
+            rows = MAX_E2_REMINDERS;
         } else {
             continue;                               // (veh_em of a scenario without emission devices: one dummy element)
         }
@@ -307,6 +310,7 @@ void sumob200_destroy(sumob200_engine* e) {
         cudaFree(e->rsScratch);
         cudaFree(e->rsTmp);
         cudaFree(e->dLaneStats);
+        cudaFree(e->dE2Out);
     }
     if (e->dSummary != nullptr) {
         cudaFree(e->dSummary);
@@ -375,6 +379,11 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         SB2_DBG("k_insert / k_transfer");
         e->ks->count(&e->d, c.nV, e->dUpdates, s);
         SB2_DBG("k_count");
+        if (c.nE2 > 0) {
+            e->ks->e2_update(&e->d, c.nE2, s);   // MSDetectorControl::updateDetectors -> MSE2Collector::detectorUpdate
+            SB2_DBG("k_e2_update");
+            e->launches += 1;
+        }
         if (prof) {
             cudaEventRecord(e->ev[5], s);
             CUDA_TRY(cudaEventSynchronize(e->ev[5]));
@@ -565,8 +574,8 @@ int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const in
         gLastError = "sumob200_set_partition: bad argument (or called twice)";
         return SUMOB200_EINVAL;
     }
-    if (e->d.nE1 > 0) {
-        gLastError = "sumob200_set_partition: E1 detectors are not carried across partitions yet";
+    if (e->d.nE1 > 0 || e->d.nE2 > 0) {
+        gLastError = "sumob200_set_partition: E1 / E2 detectors are not carried across partitions yet";
         return SUMOB200_EUNSUPPORTED;
     }
     const int nL = e->d.nL;
@@ -932,6 +941,81 @@ int sumob200_fcd_snapshot(sumob200_engine* e, sumob200_fcd_row* rows, int capaci
 }
 
 }  // extern "C"
+
+// ---- E2 lane area detectors (sb2_e2.h) -----------------------------------------------------------------------------------
+extern "C" int sumob200_e2_count(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nE2; }
+
+extern "C" int sumob200_e2_interval(sumob200_engine* e, sumob200_e2_interval_t* out, int capacity) {
+    static_assert(sizeof(sumob200_e2_interval_t) == sizeof(sb2::E2Result), "public and internal E2 record differ");
+    if (e == nullptr || out == nullptr || capacity < e->d.nE2) {
+        gLastError = "sumob200_e2_interval: bad argument / capacity too small";
+        return SUMOB200_EINVAL;
+    }
+    const int nD = e->d.nE2;
+    if (nD == 0) {
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    if (e->dE2Out == nullptr) {
+        CUDA_TRY(cudaMalloc(&e->dE2Out, sizeof(sb2::E2Result) * (size_t)nD));
+    }
+    // the notes of the last step that ran are in the buffer the step loop has flipped away from
+    e->ks->e2_readout(&e->d, nD, e->d.cur ^ 1, e->dE2Out, e->stream);
+    e->launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(out, e->dE2Out, sizeof(sb2::E2Result) * (size_t)nD, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+extern "C" int sumob200_e2_notes(sumob200_engine* e, sumob200_e2_note* notes, int capacity, int* n, int32_t* counts) {
+    if (e == nullptr || notes == nullptr || n == nullptr || capacity < 0) {
+        gLastError = "sumob200_e2_notes: bad argument";
+        return SUMOB200_EINVAL;
+    }
+    *n = 0;
+    const int nD = e->d.nE2;
+    if (nD == 0) {
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    cudaStream_t s = e->stream;
+    const int buf = e->d.cur ^ 1;   // the buffer of the last step that ran
+    int32_t counters[16];
+    std::vector<int32_t> head((size_t)nD), cnt((size_t)nD * sb2::E2C_N);
+    CUDA_TRY(cudaMemcpyAsync(counters, e->d.counters, sizeof(counters), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(head.data(), e->d.e2_head[buf], sizeof(int32_t) * (size_t)nD, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(cnt.data(), e->d.e2_cnt, sizeof(int32_t) * cnt.size(), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    const int nN = counters[13 + buf] < e->d.e2_note_cap ? counters[13 + buf] : e->d.e2_note_cap;
+    std::vector<sb2::E2Note> raw((size_t)nN);
+    if (nN > 0) {
+        CUDA_TRY(cudaMemcpyAsync(raw.data(), e->d.e2_notes[buf], sizeof(sb2::E2Note) * (size_t)nN, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+    }
+    int k = 0;
+    for (int d = 0; d < nD; d++) {
+        for (int i = head[(size_t)d]; i >= 0 && i < nN; i = raw[(size_t)i].next) {
+            if (k >= capacity) {
+                gLastError = "sumob200_e2_notes: the notifications do not fit the caller's buffer";
+                return SUMOB200_EINVAL;
+            }
+            const sb2::E2Note& r = raw[(size_t)i];
+            sumob200_e2_note o;
+            o.detector = d; o.vehicle = r.veh; o.dist_to_detector_end = r.dist; o.time_on_detector = r.timeOn;
+            o.length_on_detector = r.lenOn; o.time_loss = r.timeLoss; o.speed = r.speed;
+            notes[k++] = o;
+        }
+    }
+    *n = k;
+    if (counts != nullptr) {
+        for (int d = 0; d < nD; d++) {
+            for (int j = 0; j < 3; j++) {
+                counts[3 * d + j] = cnt[(size_t)j * nD + d];
+            }
+        }
+    }
+    return 0;
+}
 
 // ---- E1 induction loops (sb2_e1.h) ---------------------------------------------------------------------------------------
 extern "C" int sumob200_e1_count(const sumob200_engine* e) { return e == nullptr ? 0 : e->d.nE1; }

@@ -528,6 +528,20 @@ __global__ void __launch_bounds__(BLOCK) k_e1_collect(const __grid_constant__ Ct
     }
 }
 
+// E2 detectors: MSE2Collector::detectorUpdate after the step / writeXMLOutput + reset at the end of an interval (sb2_e2.h)
+__global__ void __launch_bounds__(BLOCK) k_e2_update(const __grid_constant__ Ctx c) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d < c.nE2) {
+        e2_detector_update(c, d);
+    }
+}
+__global__ void __launch_bounds__(BLOCK) k_e2_readout(const __grid_constant__ Ctx c, int buf, E2Result* out) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d < c.nE2) {
+        e2_detector_readout(c, d, buf, out);
+    }
+}
+
 // ---- re-slotting (engine.cu reslot): renumber the on-road vehicles in lane order ------------------------------------------------
 // per block of lanes: number of vehicles on them
 __global__ void __launch_bounds__(BLOCK) k_rs_lanecount(const __grid_constant__ Ctx c, int32_t* blockCount) {
@@ -707,6 +721,8 @@ int l_reslot_maps(const void* c, int nL, int nV, int32_t* blocksA, int32_t* bloc
     return 8;
 }
 void l_e1_collect(const void* c, int n, cudaStream_t s) { k_e1_collect<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_e2_update(const void* c, int n, cudaStream_t s) { k_e2_update<<<grid(n), BLOCK, 0, s>>>(ctx(c)); }
+void l_e2_readout(const void* c, int n, int buf, void* out, cudaStream_t s) { k_e2_readout<<<grid(n), BLOCK, 0, s>>>(ctx(c), buf, static_cast<E2Result*>(out)); }
 void l_lane_stats(const void* c, int n, sumob200_lane_stats* out, cudaStream_t s) { k_lane_stats<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int appBuf, cudaStream_t s) {
     const size_t n = (size_t)nV * MAX_DRIVE_ITEMS > (size_t)nL ? (size_t)nV * MAX_DRIVE_ITEMS : (size_t)nL;
@@ -714,7 +730,7 @@ int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int a
     return 1;
 }
 
-const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap, l_e1_collect, l_lane_stats};
+const sb2_kernelset kSet = {SB2_STR(SB2_KSET), BLOCK, sizeof(Ctx), l_reset, l_pre, l_plan, l_execute, l_remove, l_integrate, l_insert, l_count, l_mirror, l_fcd, l_tripinfo, l_summary, l_tls_set_phase, l_set_speed, l_halo_pack, l_halo_unpack, l_reslot_maps, l_reslot_remap, l_e1_collect, l_lane_stats, l_e2_update, l_e2_readout};
 
 }  // namespace sb2_kset_<name>
 

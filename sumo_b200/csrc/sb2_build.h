@@ -627,6 +627,64 @@ public:
             none.det = -1; none.veh = -1; none.entry = 0; none.leave = 0; none.length = 0; none.leftEarly = 0; none.pad = 0;
             SB2_DYN(E1Event, e1_events, (size_t)h.e1_event_cap, none);
         }
+        // ---------------- E2 lane area detectors on one lane (optional arrays e2_lane, e2_start, e2_length, e2_jam_*; sb2_e2.h)
+        {
+            const int nD = ff.has("e2_lane") ? (int)ff.count("e2_lane") : 0;
+            for (const char* name : {"e2_start", "e2_length", "e2_jam_time", "e2_jam_speed", "e2_jam_dist"}) {
+                if (nD > 0 && (!ff.has(name) || (int)ff.count(name) != nD)) {
+                    throw std::invalid_argument(std::string("sumob200: ") + name + " must be given for every E2 detector");
+                }
+            }
+            h.nE2 = nD;
+            const size_t n1 = nD > 0 ? (size_t)nD : 1;
+            int32_t* lb = add<int32_t>("lane_e2_begin", SB2_OFF(lane_e2_begin), (size_t)nL + 1, false, 0);
+            int32_t* of = add<int32_t>("e2_of_lane", SB2_OFF(e2_of_lane), n1, false, 0);
+            int32_t* la = add<int32_t>("e2_lane", SB2_OFF(e2_lane), n1, false, 0);
+            double* ds = add<double>("e2_start", SB2_OFF(e2_start), n1, false, 0.);
+            double* dl = add<double>("e2_length", SB2_OFF(e2_length), n1, false, 1.);
+            double* js = add<double>("e2_jam_speed", SB2_OFF(e2_jam_speed), n1, false, 0.);
+            double* jd = add<double>("e2_jam_dist", SB2_OFF(e2_jam_dist), n1, false, 0.);
+            int64_t* jt = add<int64_t>("e2_jam_time", SB2_OFF(e2_jam_time), n1, false, (int64_t)0);
+            if (nD > 0) {
+                checkIndex(ff, "e2_lane", 0, nL);
+                const int32_t* fl = ff.ptr<int32_t>("e2_lane");
+                for (int d = 0; d < nD; d++) {
+                    la[d] = fl[d];
+                    ds[d] = ff.ptr<double>("e2_start")[d];
+                    dl[d] = ff.ptr<double>("e2_length")[d];
+                    js[d] = ff.ptr<double>("e2_jam_speed")[d];
+                    jd[d] = ff.ptr<double>("e2_jam_dist")[d];
+                    jt[d] = ff.ptr<int64_t>("e2_jam_time")[d];
+                    if (ds[d] < 0 || dl[d] <= 0 || ds[d] + dl[d] > h.lane_length[la[d]] + SB2_NUMERICAL_EPS) {
+                        throw std::invalid_argument("sumob200: an E2 detector does not lie on its lane");
+                    }
+                    lb[la[d] + 1]++;
+                }
+                for (int l = 0; l < nL; l++) {
+                    lb[l + 1] += lb[l];
+                }
+                std::vector<int32_t> fill(lb, lb + nL);
+                for (int d = 0; d < nD; d++) {
+                    of[fill[la[d]]++] = d;
+                }
+            }
+            const size_t nR = nD > 0 ? (size_t)nV * MAX_E2_REMINDERS : 1;
+            SB2_DYN(int32_t, veh_e2_det, nR, -1); SB2_DYN(double, veh_e2_off, nR, 0.); SB2_DYN(int32_t, veh_e2_entered, nR, 0);
+            // one note per vehicle, detector and step; a vehicle is rarely on more than two detectors at once (overflow raises the flag)
+            h.e2_note_cap = nD > 0 ? (int)std::min<size_t>((size_t)1 << 26, std::min((size_t)nV * MAX_E2_REMINDERS, (size_t)2 * nV + 65536)) : 1;
+            if (ff.has("e2_note_capacity")) {
+                h.e2_note_cap = std::max(1, ff.scalar<int32_t>("e2_note_capacity", 1));
+            }
+            E2Note none;
+            none.next = -1; none.veh = -1; none.dist = 0; none.timeOn = 0; none.lenOn = 0; none.timeLoss = 0; none.speed = 0; none.halt = 0; none.ihalt = 0;
+            for (int b = 0; b < 2; b++) {
+                SB2_DYN2(E2Note, e2_notes, b, (size_t)h.e2_note_cap, none);
+                SB2_DYN2(int32_t, e2_head, b, n1, -1);
+            }
+            SB2_DYN(double, e2_acc_d, n1 * E2D_N, 0.);
+            SB2_DYN(int64_t, e2_acc_i, n1 * E2I_N, (int64_t)0);
+            SB2_DYN(int32_t, e2_cnt, n1 * E2C_N, 0);
+        }
         // ---------------- edgeData / laneData accumulators (optional scalar md_enabled; sb2_meandata.h)
         {
             h.md_on = ff.scalar<int32_t>("md_enabled", 0) != 0 ? 1 : 0;

@@ -17,6 +17,7 @@
 #include "sb2_link.h"
 #include "sb2_emis.h"
 #include "sb2_e1.h"
+#include "sb2_e2.h"
 #include "sb2_meandata.h"
 
 namespace sb2 {
@@ -282,6 +283,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
                     pos -= c.lane_length[myLane];
                     // enterLaneAtMove
                     veh_e1_enter_at_move(c, v, myLane, approachedLane);
+                    veh_e2_enter_at_move(c, v, myLane, approachedLane);
                     md_count(c, myLane, MD_LEFT);               // leaveLane(NOTIFICATION_JUNCTION) -> notifyLeave of the lane that is left
                     md_count(c, approachedLane, MD_ENTERED);    // activateReminders(NOTIFICATION_JUNCTION) -> notifyEnter of the entered lane
                     myLane = approachedLane;
@@ -384,6 +386,9 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
     }
     veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
     veh_e1_move(c, v, pos - lastDist, pos, speed);     //                                          -> MSInductLoop::notifyMove
+    if (c.nE2 > 0) {
+        veh_e2_move(c, v, pos - lastDist, pos, speed, lane_vehicle_max_speed(c, myLane, v));   //       -> MSE2Collector::notifyMove
+    }
     if (c.md_on) {
         // -> MeanDataValues::notifyMove of every lane the vehicle's body was on or entered; rem->second = lengths of the lanes left since
         const double vmaxNow = lane_vehicle_max_speed(c, myLane, v);
@@ -402,6 +407,7 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
     }
     if (arrived) {
         veh_e1_leave_net(c, v);        // onRemovalFromNet(NOTIFICATION_ARRIVED) -> leaveLane -> notifyLeave
+        veh_e2_leave_net(c, v);
         c.veh_moved[v] = 2;
         c.veh_arrival_time[v] = c.t;   // MSDevice_Tripinfo::notifyLeave(NOTIFICATION_ARRIVED): getCurrentTimeStep()
         c.veh_arrival_lane[v] = myLane;

@@ -339,6 +339,7 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
         c.veh_odometer[v] = 0;
         c.veh_timeloss[v] = 0;
         veh_e1_add_lane(c, v, l, true, pos, pos - cf.length());   // addReminder + activateReminders(NOTIFICATION_DEPARTED)
+        veh_e2_add_lane(c, v, l, true, pos - cf.length());
         md_count(c, l, MD_DEPARTED);
     } else {
         // MSVehicle::enterLaneAtInsertion(NOTIFICATION_TELEPORT) (MSVehicle.cpp:5793-5858): "avoid startup-effects after teleport"

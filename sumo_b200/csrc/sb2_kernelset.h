@@ -35,6 +35,9 @@ struct sb2_kernelset {
     void (*e1_collect)(const void* ctx, int n_vehicles, cudaStream_t s);
     /* libsumo::Lane::getLastStep* of every lane */
     void (*lane_stats)(const void* ctx, int n_lanes, sumob200_lane_stats* out, cudaStream_t s);
+    /* E2 detectors (sb2_e2.h): detectorUpdate after a step; the interval's attributes (sb2::E2Result per detector) + reset */
+    void (*e2_update)(const void* ctx, int n_detectors, cudaStream_t s);
+    void (*e2_readout)(const void* ctx, int n_detectors, int buf, void* out, cudaStream_t s);
 };
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);

@@ -13,6 +13,7 @@
 #include "sb2_cf.h"
 #include "sb2_veh.h"
 #include "sb2_e1.h"
+#include "sb2_e2.h"
 #include "sb2_meandata.h"
 
 namespace sb2 {
@@ -96,6 +97,7 @@ SB2_HDN void lane_summary(const Ctx& c, int l, int orderBase, int orderStep = 1,
 // table but every reader skips vehicles that are not on the road; partial occupations are dropped in lane_handoff_integrate.
 SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
     veh_e1_leave_net(c, v);   // leaveLane(NOTIFICATION_TELEPORT / _TELEPORT_ARRIVED) -> notifyLeave of every move reminder
+    veh_e2_leave_net(c, v);
     md_count(c, lane, MD_LEFT);
     md_count(c, lane, MD_TELEPORTED);
     if (c.veh_routepos[v] + 1 >= veh_route_len(c, v)) {
@@ -117,6 +119,7 @@ SB2_HD void veh_transfer_add(const Ctx& c, int v, int lane) {
     c.veh_lane[v] = -3;
     // enterLaneAtMove(.., onTeleporting): myPos = 0, activateReminders(NOTIFICATION_TELEPORT) (MSVehicle.cpp:5613-5618)
     veh_e1_add_lane(c, v, c.edge_lane_begin[veh_succ_edge(c, v, 0)], true, 0., -veh_length(c, v));
+    veh_e2_add_lane(c, v, c.edge_lane_begin[veh_succ_edge(c, v, 0)], true, -veh_length(c, v));
     md_count(c, c.edge_lane_begin[veh_succ_edge(c, v, 0)], MD_ENTERED);
     c.veh_tp_proceed[v] = -1;
     // partitioned run: the transfer entry belongs to the rank that owns the edge the vehicle now (virtually) sits on, because

@@ -217,6 +217,7 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
                 // (MSVehicleControl::removePending runs in the NEXT step's executeMovements: until then the vehicle still counts as
                 // running in the summary output -- veh_moved 4, see summary_vehicle)
                 veh_e1_leave_net(c, v);
+                veh_e2_leave_net(c, v);
                 md_count(c, c.edge_lane_begin[e], MD_LEFT);        // leaveLane(NOTIFICATION_TELEPORT_ARRIVED)
                 md_count(c, c.edge_lane_begin[e], MD_TELEPORTED);
                 c.veh_arrival_time[v] = time;
@@ -236,6 +237,8 @@ SB2_HDN void transfer_checkInsertions(const Ctx& c) {
             c.veh_tp_proceed[v] = time + TIME2STEPS(edge_current_travel_time(c, e, 1.));
             veh_e1_leave_net(c, v);
             veh_e1_add_lane(c, v, c.edge_lane_begin[nextEdge], true, 0., -veh_length(c, v));
+            veh_e2_leave_net(c, v);
+            veh_e2_add_lane(c, v, c.edge_lane_begin[nextEdge], true, -veh_length(c, v));
             md_count(c, cl, MD_LEFT);                              // leaveLane(NOTIFICATION_TELEPORT_CONTINUATION)
             md_count(c, c.edge_lane_begin[nextEdge], MD_ENTERED);  // enterLaneAtMove(.., onTeleporting) -> notifyEnter(NOTIFICATION_TELEPORT)
         }

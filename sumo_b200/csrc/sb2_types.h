@@ -68,7 +68,7 @@ typedef int64_t SUMOTime;
 #define SB2_NO_INTERSECTION 10000.0              /* MSLink.cpp:76 */
 #define SB2_EMERGENCY_DECEL_AMPLIFIER 1.2        /* MSCFModel.h:35 */
 
-enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4, MAX_E1_REMINDERS = 4 };
+enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4, MAX_E1_REMINDERS = 4, MAX_E2_REMINDERS = 8 };
 // rows of Ctx::md_sums / md_counts (sb2_meandata.h)
 enum { MD_SAMPLE = 0, MD_DIST = 1, MD_WAIT = 2, MD_TIMELOSS = 3, MD_FRONT_SAMPLE = 4, MD_FRONT_DIST = 5, MD_LENGTH_SUM = 6, MD_OCCUPATION = 7, MD_NSUMS = 8 };
 enum { MD_DEPARTED = 0, MD_ARRIVED = 1, MD_ENTERED = 2, MD_LEFT = 3, MD_TELEPORTED = 4, MD_NCOUNTS = 5 };
@@ -120,6 +120,37 @@ struct E1Event {
 };
 #define E1_NOT_ON (-1e300)
 #define E1_STILL_ON (-1e300)
+
+// one MSE2Collector::MoveNotificationInfo (MSE2Collector.h:164-217) of a step, chained per detector; halt / ihalt = the vehicle's entries
+// of myHaltingVehicleDurations / myIntervalHaltingVehicleDurations after the step (halt == 0: not in the maps)
+struct E2Note {
+    int32_t next;          // next note of the same detector, -1 = end
+    int32_t veh;           // external vehicle index
+    double dist;           // distToDetectorEnd
+    double timeOn;         // timeOnDetector
+    double lenOn;          // lengthOnDetector
+    double timeLoss;
+    double speed;
+    int64_t halt, ihalt;   // ms
+};
+// per-detector accumulators of MSE2Collector (MSE2Collector.h:700-790): fp64 members [E2D_N][nE2], integer members [E2I_N][nE2],
+// counters the vehicles' threads bump [E2C_N][nE2]
+enum { E2D_SAMPLES = 0, E2D_TIMELOSS, E2D_SPEEDSUM, E2D_OCCSUM, E2D_MAXOCC, E2D_MEANMAXJAM_M, E2D_MAXJAM_M, E2D_JAMSUM_M, E2D_N };
+enum { E2I_MEANMAXJAM_V = 0, E2I_MAXJAM_V, E2I_JAMSUM_V, E2I_TIMESAMPLES, E2I_MEANVEHNUM, E2I_MAXVEHNUM, E2I_STARTEDHALTS,
+       E2I_PAST_SUM, E2I_PAST_MAX, E2I_PAST_N, E2I_IPAST_SUM, E2I_IPAST_MAX, E2I_IPAST_N, E2I_N };
+enum { E2C_ENTERED = 0, E2C_LEFT, E2C_SEEN, E2C_N };
+// the attributes of one <interval> of an e2 output file (MSE2Collector::writeXMLOutput); = sumob200_e2_interval_t of the C ABI
+struct E2Result {
+    double sampledSeconds;
+    int32_t nVehEntered, nVehLeft, nVehSeen, maxJamLengthInVehicles;
+    double meanSpeed, meanTimeLoss, meanOccupancy, maxOccupancy, meanMaxJamLengthInVehicles, meanMaxJamLengthInMeters, maxJamLengthInMeters;
+    int32_t jamLengthInVehiclesSum, startedHalts;
+    double jamLengthInMetersSum;
+    double meanHaltingDuration, maxHaltingDuration, haltingDurationSum;
+    double meanIntervalHaltingDuration, maxIntervalHaltingDuration, intervalHaltingDurationSum;
+    double meanVehicleNumber;
+    int32_t maxVehicleNumber, pad;
+};
 
 struct Ctx {
     // ---- options (MSGlobals) -------------------------------------------------------------
@@ -240,6 +271,24 @@ struct Ctx {
     double* veh_e1_entry;            // [MAX_E1_REMINDERS][nV] myVehiclesOnDet[veh] (entry time in s), E1_NOT_ON if not on the detector
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
+    // ---- E2 lane area detectors on one lane (MSE2Collector as a move reminder, sb2_e2.h); nE2 == 0: one dummy element each
+    int nE2, e2_note_cap;
+    const int32_t* lane_e2_begin;    // [nL+1] CSR like lane_e1_begin
+    const int32_t* e2_of_lane;       // [nE2]
+    const int32_t* e2_lane;          // [nE2] the detector's lane
+    const double* e2_start;          // [nE2] myStartPos
+    const double* e2_length;         // [nE2] myDetectorLength
+    const double* e2_jam_speed;      // [nE2] myJamHaltingSpeedThreshold
+    const double* e2_jam_dist;       // [nE2] myJamDistanceThreshold
+    const int64_t* e2_jam_time;      // [nE2] myJamHaltingTimeThreshold (ms)
+    int32_t* veh_e2_det;             // [MAX_E2_REMINDERS][nV] detector of the reminder or -1 (myVehicleInfos[veh] exists)
+    double* veh_e2_off;              // [MAX_E2_REMINDERS][nV] rem->second
+    int32_t* veh_e2_entered;         // [MAX_E2_REMINDERS][nV] VehicleInfo::hasEntered
+    struct E2Note* e2_notes[2];      // [e2_note_cap] myMoveNotifications of all detectors, of this step ([cur]) and the previous one;
+    int32_t* e2_head[2];             // [nE2] first note of the detector per buffer; number of notes per buffer = counters[13 + buffer]
+    double* e2_acc_d;                // [E2D_N][nE2]
+    int64_t* e2_acc_i;               // [E2I_N][nE2]
+    int32_t* e2_cnt;                 // [E2C_N][nE2]
     // ---- edgeData / laneData (MSMeanData_Net, sb2_meandata.h); md_on == 0: one dummy element each
     int md_on;
     double md_halt_speed;            // haltingSpeedThreshold of the <edgeData> definition (default POSITION_EPS)
@@ -287,7 +336,7 @@ struct Ctx {
     int traci_speed_used; double* veh_traci_speed;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
-    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step, 12 length of e1_events
+    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step, 12 length of e1_events, 13 / 14 notes in e2_notes[0] / [1]
 };
 
 SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }

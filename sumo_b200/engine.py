@@ -49,6 +49,15 @@ SUMMARY = np.dtype([("time_ms", np.int64), ("inserted", np.int32), ("running", n
                     ("mean_speed_relative", np.float64)])
 E1_INTERVAL = np.dtype([("n_veh_contrib", np.int32), ("n_veh_entered", np.int32), ("flow", np.float64), ("occupancy", np.float64),
                         ("speed", np.float64), ("harmonic_mean_speed", np.float64), ("length", np.float64)])
+E2_INTERVAL = np.dtype([("sampled_seconds", np.float64), ("n_veh_entered", np.int32), ("n_veh_left", np.int32), ("n_veh_seen", np.int32),
+                        ("max_jam_length_in_vehicles", np.int32), ("mean_speed", np.float64), ("mean_time_loss", np.float64),
+                        ("mean_occupancy", np.float64), ("max_occupancy", np.float64), ("mean_max_jam_length_in_vehicles", np.float64),
+                        ("mean_max_jam_length_in_meters", np.float64), ("max_jam_length_in_meters", np.float64),
+                        ("jam_length_in_vehicles_sum", np.int32), ("started_halts", np.int32), ("jam_length_in_meters_sum", np.float64),
+                        ("mean_halting_duration", np.float64), ("max_halting_duration", np.float64), ("halting_duration_sum", np.float64),
+                        ("mean_interval_halting_duration", np.float64), ("max_interval_halting_duration", np.float64),
+                        ("interval_halting_duration_sum", np.float64), ("mean_vehicle_number", np.float64),
+                        ("max_vehicle_number", np.int32), ("reserved", np.int32)])
 LANE_MEANDATA = np.dtype([("sample_seconds", np.float64), ("travelled_distance", np.float64), ("wait_seconds", np.float64), ("time_loss", np.float64),
                           ("front_sample_seconds", np.float64), ("front_travelled_distance", np.float64), ("veh_length_sum", np.float64),
                           ("occupation_sum", np.float64), ("minimal_vehicle_length", np.float64), ("departed", np.int32), ("arrived", np.int32),
@@ -90,6 +99,8 @@ def load_library(path=None):
     lib.sumob200_meandata_interval.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_lane_stats_all.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_e1_count.argtypes = [ctypes.c_void_p]
+    lib.sumob200_e2_count.argtypes = [ctypes.c_void_p]
+    lib.sumob200_e2_interval.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_e1_interval.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int]
     lib.sumob200_emissions.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     lib.sumob200_num_tls.argtypes = [ctypes.c_void_p]
@@ -263,6 +274,14 @@ class Engine:
         n = self._lib.sumob200_e1_count(self._h)
         out = np.zeros(max(n, 1), dtype=E1_INTERVAL)
         _check(self._lib, self._lib.sumob200_e1_interval(self._h, int(begin_ms), int(end_ms), out.ctypes.data, out.shape[0]), "sumob200_e1_interval")
+        return out[:n]
+
+    def e2_interval(self):
+        """MSE2Collector::writeXMLOutput for every E2 detector of the scenario (the interval that ends now), then the detectors are
+        reset (array of dtype E2_INTERVAL, one record per detector)"""
+        n = self._lib.sumob200_e2_count(self._h)
+        out = np.zeros(max(n, 1), dtype=E2_INTERVAL)
+        _check(self._lib, self._lib.sumob200_e2_interval(self._h, out.ctypes.data, out.shape[0]), "sumob200_e2_interval")
         return out[:n]
 
     def emissions(self):

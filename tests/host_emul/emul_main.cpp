@@ -130,6 +130,9 @@ static void step(Model& m) {
     if (c.counters[10] > 0) {
         transfer_checkInsertions(c);
     }
+    for (int d = 0; d < c.nE2; d++) {
+        e2_detector_update(c, d);   // MSDetectorControl::updateDetectors
+    }
     c.t += c.DELTA_T;
 }
 
@@ -317,8 +320,8 @@ int main(int argc, char** argv) {
         fprintf(stderr, "usage: host_emul X.flat [--trace-out X.trace] [--steps N]\n");
         return 2;
     }
-    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out, mdOut;
-    long long e1Period = 60000, mdPeriod = 60000;
+    std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out, mdOut, e2Out;
+    long long e1Period = 60000, mdPeriod = 60000, e2Period = 60000;
     long maxSteps = -1;
     std::string debugName, partFile;
     for (int i = 2; i < argc; i++) {
@@ -339,6 +342,10 @@ int main(int argc, char** argv) {
             mdOut = argv[++i];   // text, one line per non-internal lane and interval: the raw members of MSLaneMeanDataValues (sumob200_meandata_interval)
         } else if (a == "--md-period" && i + 1 < argc) {
             mdPeriod = atoll(argv[++i]);   // ms
+        } else if (a == "--e2-out" && i + 1 < argc) {
+            e2Out = argv[++i];   // text, one line per detector and interval: the attributes of the reference's E2 output (sumob200_e2_interval)
+        } else if (a == "--e2-period" && i + 1 < argc) {
+            e2Period = atoll(argv[++i]);   // ms
         } else if (a == "--e1-out" && i + 1 < argc) {
             e1Out = argv[++i];   // text, one line per detector and interval: the attributes of the reference's E1 output (sumob200_e1_interval)
         } else if (a == "--e1-period" && i + 1 < argc) {
@@ -393,6 +400,21 @@ int main(int argc, char** argv) {
     FILE* fe1 = e1Out.empty() ? nullptr : fopen(e1Out.c_str(), "w");
     FILE* fmd = mdOut.empty() ? nullptr : fopen(mdOut.c_str(), "w");
     SUMOTime e1LastFlush = c.t;
+    FILE* fe2 = e2Out.empty() ? nullptr : fopen(e2Out.c_str(), "w");
+    SUMOTime e2LastFlush = c.t;
+    auto flushE2 = [&](SUMOTime from, SUMOTime to) {
+        std::vector<E2Result> res((size_t)c.nE2);
+        for (int d = 0; d < c.nE2; d++) {
+            e2_detector_readout(c, d, c.cur, res.data());   // (the emulation flips the buffers at the start of a step)
+            const E2Result& r = res[d];
+            fprintf(fe2, "%lld %lld %d %.17g %d %d %d %.17g %.17g %.17g %.17g %.17g %.17g %d %.17g %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g %d %.17g %d\n",
+                    (long long)from, (long long)to, d, r.sampledSeconds, r.nVehEntered, r.nVehLeft, r.nVehSeen, r.meanSpeed, r.meanTimeLoss, r.meanOccupancy,
+                    r.maxOccupancy, r.meanMaxJamLengthInVehicles, r.meanMaxJamLengthInMeters, r.maxJamLengthInVehicles, r.maxJamLengthInMeters,
+                    r.jamLengthInVehiclesSum, r.jamLengthInMetersSum, r.meanHaltingDuration, r.maxHaltingDuration, r.haltingDurationSum,
+                    r.meanIntervalHaltingDuration, r.maxIntervalHaltingDuration, r.intervalHaltingDurationSum, r.startedHalts, r.meanVehicleNumber,
+                    r.maxVehicleNumber);
+        }
+    };
     SUMOTime mdLastFlush = c.t;
     auto flushMd = [&](SUMOTime from) {
         for (int l = 0; l < c.nL; l++) {
@@ -542,6 +564,10 @@ int main(int argc, char** argv) {
             flushE1(t + c.DELTA_T - e1Period, t + c.DELTA_T);
             e1LastFlush = t + c.DELTA_T;
         }
+        if (fe2 != nullptr && c.nE2 > 0 && (t + c.DELTA_T) % e2Period == 0) {
+            flushE2(t + c.DELTA_T - e2Period, t + c.DELTA_T);
+            e2LastFlush = t + c.DELTA_T;
+        }
         if (fmd != nullptr && c.md_on && (t + c.DELTA_T) % mdPeriod == 0) {
             flushMd(t + c.DELTA_T - mdPeriod);
             mdLastFlush = t + c.DELTA_T;
@@ -592,6 +618,12 @@ int main(int argc, char** argv) {
             flushE1(e1LastFlush, c.t);   // MSDetectorControl::close: the partial interval at the end of the simulation
         }
         fclose(fe1);
+    }
+    if (fe2 != nullptr) {
+        if (c.nE2 > 0 && c.t > e2LastFlush) {
+            flushE2(e2LastFlush, c.t);
+        }
+        fclose(fe2);
     }
     if (fmd != nullptr) {
         if (c.md_on && c.t > mdLastFlush) {

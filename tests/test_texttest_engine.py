@@ -1,5 +1,5 @@
 """The engine against the reference's OWN texttest goldens: FCD output (tests/sumo/output/fcd-output/*/fcd.sumo), E1 detectors
-(tests/sumo/output/e1/**/detector.sumo) and edge-based mean data (tests/sumo/output/meandata_edgebased/**/aggregated*.sumo) -- files
+(tests/sumo/output/e1/**/detector.sumo), E2 lane area detectors (tests/sumo/output/e2/**/detector.sumo) and edge-based mean data (tests/sumo/output/meandata_edgebased/**/aggregated*.sumo) -- files
 the reference's maintainers committed from a stock build: the test's inputs and options
 are flattened by the reference's loader (oracle/_ref/sumo_flatten), the step runs in tests/host_emul (the device functions compiled
 for the host), and the intervals it reports must be the committed lines -- every attribute as printed.
@@ -82,6 +82,54 @@ def test_engine_reproduces_the_reference_e1_golden(rel, host_emul, tmp_path):
         assert mine == want, (rel, key, mine, want)
         passages += int(w["nVehContrib"])
     assert passages >= 1 or any(int(w["nVehEntered"]) for w in golden)
+
+
+E2_TESTS = ["output/e2/jam_test__preliminary/" + t for t in ("one1s", "one10s", "one100s")] + ["output/e2/one_vehicle/leave_early"]
+for group, subsecond in (("one_vehicle", ""), ("one_vehicle_subsecond", ""), ("two_same_vehicles", ""), ("two_vehicles_diff_length", ""),
+                         ("two_vehicles_diff_speed", "")):
+    E2_TESTS += ["output/e2/%s/%s" % (group, t) for t in ("one1s_1vehicle_10m_s", "one10s_1vehicle_10m_s", "one100s_1vehicle_10m_s",
+                                                           "two1s_1vehicle_10m_s", "two10s_1vehicle_10m_s", "two100s_1vehicle_10m_s")]
+E2_TESTS.append("output/e2/one_vehicle_subsecond/one.1s_1vehicle_10m_s")
+
+
+@pytest.mark.parametrize("rel", E2_TESTS)
+def test_engine_reproduces_the_reference_e2_golden(rel, host_emul, tmp_path):
+    """all 23 attributes of every <interval> of the committed lane area detector output (jams, halting durations, occupancy, ...)"""
+    if not os.path.isdir(os.path.join(TT_ROOT, rel)):
+        pytest.skip("reference sources (tests/sumo) are not available on this machine")
+    import test_e2_detectors
+    options = stage(rel, tmp_path)
+    flat = str(tmp_path / "x.flat")
+    r = subprocess.run([os.path.join(REF, "sumo_flatten"), "--flat-out", flat, "--trace-out", str(tmp_path / "x.trace"),
+                        "--draws-out", str(tmp_path / "x.draws")] + options, cwd=str(tmp_path), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-2000:]
+    add = open(str(tmp_path / "input_additional.add.xml")).read()
+    freqs = set(re.findall(r'<(?:e2Detector|laneAreaDetector)[^>]* (?:freq|period)="([^"]*)"', add))
+    assert len(freqs) == 1
+    period_ms = int(round(float(freqs.pop()) * 1000))
+    g = load_flat(flat)
+    nb, names = g["e2_name_begin"], bytes(g["e2_names"]).decode()
+    ids = [names[nb[i]:nb[i + 1]] for i in range(len(nb) - 1)]
+    out = str(tmp_path / "e2.txt")
+    steps = len(load_trace(str(tmp_path / "x.trace")))
+    subprocess.run([host_emul, flat, "--e2-out", out, "--e2-period", str(period_ms), "--draws", str(tmp_path / "x.draws"), "--steps", str(steps)],
+                   check=True, timeout=600, stderr=subprocess.DEVNULL)
+    got = {}
+    for line in open(out):
+        f = line.split()
+        got[("%.2f" % (int(f[0]) / 1000.), ids[int(f[2])])] = {a: test_e2_detectors.fmt(a, float(x)) for a, x in zip(test_e2_detectors.ATTRS, f[3:])}
+    golden = [attrs(l) for l in open(os.path.join(TT_ROOT, rel, "detector.sumo")) if "<interval" in l]
+    assert len(golden) >= 1
+    seen = 0
+    for w in golden:
+        key = (w["begin"], w["id"])
+        assert key in got, key
+        for a in test_e2_detectors.ATTRS:
+            # (the committed files print the count startedHalts as "3.00", this tree's writer as "3": counts are compared as numbers)
+            same = float(got[key][a]) == float(w[a]) if a in test_e2_detectors.INTEGER else got[key][a] == w[a]
+            assert same, (rel, key, a, got[key][a], w[a])
+        seen += int(w["nVehEntered"])
+    assert seen >= 1
 
 
 # (test directory, committed golden, period in s)

@@ -3,8 +3,9 @@ sub-trees of /root/reference/tests/sumo (a directory with an options.sumo and no
 inheritance, the reference's loader flattens the scenario and records the reference's trajectories (oracle/_ref/sumo_flatten
 --trace-out, --draws-out), tests/host_emul runs the same steps with the draws replayed, the two traces are compared byte by byte.
 Outcomes: SAME, DIFF (first differing step), REFUSED (the message), LOADFAIL (the reference itself rejects the options, e.g. tests of
-error messages), EMPTY (no vehicle ever on the road).
-Usage: texttest_sweep.py OUT.tsv SUBTREE [SUBTREE ...]     e.g.  basic cf_model junction_model tls"""
+error messages), EMPTY (no vehicle ever on the road), FLAGGED (the engine raised one of its capacity flags during the run).
+FLOWDIFF would mean the harness's up-front <flow> expansion changed the reference's own trajectories (never seen).
+Usage: texttest_sweep.py OUT.tsv SUBTREE|@LISTFILE [...]     e.g.  basic cf_model junction_model tls"""
 import os
 import shlex
 import shutil
@@ -37,6 +38,15 @@ def stage(rel, tmp):
     return options
 
 
+def has_flows(tmp):
+    for fn in os.listdir(tmp):
+        if fn.endswith(".xml"):
+            with open(os.path.join(tmp, fn), "rb") as f:
+                if b"<flow" in f.read():
+                    return True
+    return False
+
+
 def run_one(rel):
     os.makedirs("/tmp/w", exist_ok=True)
     tmp = tempfile.mkdtemp(prefix="tt_", dir="/tmp/w")
@@ -56,6 +66,12 @@ def run_one(rel):
         if not os.path.exists(os.path.join(tmp, "x.trace")):
             return rel, "LOADFAIL", "no trace"
         ref = load_trace(os.path.join(tmp, "x.trace"))
+        if has_flows(tmp):
+            # the harness expanded <flow>s before the run (integration/sumo_flatten.cpp expandFlows): the untouched reference,
+            # which expands them step by step, must give the same trace
+            n = subprocess.run([os.path.join(REF, "sumo_flatten"), "--trace-out", "n.trace"] + options, cwd=tmp, capture_output=True, text=True, timeout=120)
+            if n.returncode != 0 or open(os.path.join(tmp, "x.trace"), "rb").read() != open(os.path.join(tmp, "n.trace"), "rb").read():
+                return rel, "FLOWDIFF", "expanded flows change the reference's own run"
         if sum(len(s[1]) for s in ref) == 0:
             return rel, "EMPTY", ""
         try:
@@ -68,6 +84,11 @@ def run_one(rel):
             return rel, ("REFUSED" if "sumob200" in msg else "EMULFAIL"), msg[:160]
         if open(os.path.join(tmp, "x.trace"), "rb").read() == open(os.path.join(tmp, "e.trace"), "rb").read():
             return rel, "SAME", "%d steps, %d vehicle-steps" % (len(ref), sum(len(s[1]) for s in ref))
+        flags = int(e.stderr.strip().splitlines()[-1].rsplit("err=", 1)[-1], 16) if "err=" in e.stderr else 0
+        if flags & (1 | 2 | 4 | 512 | 8192):
+            # a fixed capacity of the engine was exceeded (drive items, further lanes, partial occupators, link leaders, detector slots):
+            # the run is void by contract (SUMOB200_F_*_OVERFLOW), a refusal at run time
+            return rel, "FLAGGED", "capacity flag 0x%x" % flags
         mine = load_trace(os.path.join(tmp, "e.trace"))
         for i, (a, b) in enumerate(zip(ref, mine)):
             if len(a[1]) != len(b[1]) or (a[1] != b[1]).any() or (a[2] != b[2]).any() or (a[3] != b[3]).any() or (a[4] != b[4]).any():
@@ -83,6 +104,9 @@ def main():
     out = sys.argv[1]
     tests = []
     for sub in sys.argv[2:]:
+        if sub.startswith("@"):      # a file with one test directory per line
+            tests += [l.strip() for l in open(sub[1:]) if l.strip()]
+            continue
         for d, subdirs, files in os.walk(os.path.join(TT_ROOT, sub)):
             if "options.sumo" in files and not any(os.path.exists(os.path.join(d, s, "options.sumo")) for s in subdirs):
                 tests.append(os.path.relpath(d, TT_ROOT))
