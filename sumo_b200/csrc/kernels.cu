@@ -651,7 +651,7 @@ __global__ void __launch_bounds__(BLOCK) k_rs_remap(const __grid_constant__ Ctx 
             c.lane_partial[i * MAX_PARTIAL + k] = newOfOld[c.lane_partial[i * MAX_PARTIAL + k]];
         }
     }
-    if (i < (size_t)c.nV * MAX_DRIVE_ITEMS) {
+    if (i < (size_t)c.nV * c.max_items) {
         // the approach table the next planMove reads (records of unused items hold stale but valid slot numbers)
         const int v = c.ap_rec[appBuf][i].veh;
         const int dec = v < 0 ? ~v : v;
@@ -725,7 +725,8 @@ void l_e2_update(const void* c, int n, cudaStream_t s) { k_e2_update<<<grid(n), 
 void l_e2_readout(const void* c, int n, int buf, void* out, cudaStream_t s) { k_e2_readout<<<grid(n), BLOCK, 0, s>>>(ctx(c), buf, static_cast<E2Result*>(out)); }
 void l_lane_stats(const void* c, int n, sumob200_lane_stats* out, cudaStream_t s) { k_lane_stats<<<grid(n), BLOCK, 0, s>>>(ctx(c), out); }
 int l_reslot_remap(const void* c, int nL, int nV, const int32_t* newOfOld, int appBuf, cudaStream_t s) {
-    const size_t n = (size_t)nV * MAX_DRIVE_ITEMS > (size_t)nL ? (size_t)nV * MAX_DRIVE_ITEMS : (size_t)nL;
+    const size_t nDI = (size_t)nV * ctx(c).max_items;
+    const size_t n = nDI > (size_t)nL ? nDI : (size_t)nL;
     k_rs_remap<<<(unsigned)((n + BLOCK - 1) / BLOCK), BLOCK, 0, s>>>(ctx(c), newOfOld, appBuf);
     return 1;
 }

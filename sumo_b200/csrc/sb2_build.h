@@ -552,7 +552,11 @@ public:
             }
             SB2_DYN(double, veh_em, anyDevice ? (size_t)nV * 7 : 1, 0.);
         }
-        const size_t nDI = (size_t)nV * MAX_DRIVE_ITEMS;
+        // drive items per vehicle: 8 covers the look-ahead on ordinary networks (and keeps the 1 M-vehicle bench at 2.2 GB); a network
+        // of very short lanes (more than 8 links inside the braking distance) raises SUMOB200_F_DRIVE_ITEM_OVERFLOW -- the scenario
+        // can then ask for more with the scalar drive_item_capacity (<= 64)
+        h.max_items = std::min(64, std::max(2, ff.scalar<int32_t>("drive_item_capacity", MAX_DRIVE_ITEMS)));
+        const size_t nDI = (size_t)nV * h.max_items;
         for (int b = 0; b < 2; b++) {
             SB2_DYN2(int32_t, veh_ndi, b, nV, 0);
             SB2_DYN2(int32_t, veh_order, b, nV, -1);

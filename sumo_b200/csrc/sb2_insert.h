@@ -352,7 +352,9 @@ SB2_HD bool lane_isInsertionSuccess(const Ctx& c, int l, int v, double speed, do
     c.veh_backpos[v] = pos - cf.length();
     c.veh_accel[v] = 0;
     c.veh_lastdist[v] = 0;
-    c.veh_havetowait[v] = 0;
+    if (!teleport) {
+        c.veh_havetowait[v] = 0;   // (myHaveToWaitOnNextLink is a member the constructor clears: a vehicle that ends a teleport keeps the
+    }                              // value of its last executeMove, and checkRewindLinkLanes of its followers reads it, MSVehicle.cpp:5356)
     c.veh_moved[v] = 0;
     c.veh_nfurther[v] = 0;
     c.veh_stopspeed[v] = SB2_DBL_MAX;

@@ -160,7 +160,7 @@ SB2_HD int link_blockedAtTime(const Ctx& c, int k, int buf, SUMOTime arrivalTime
                               bool sameTargetLane, double impatience, double decel, SUMOTime waitingTime, int ego, bool lastWasContRed, int live = LIVE_NOW) {
     int result = OPEN_YES;
     for (int r = c.link_app_head[buf][k]; r >= 0;) {
-        const AppRec a = c.ap_rec[buf][SB2_CHK(r, 0, (long long)c.nV * MAX_DRIVE_ITEMS, 8)];
+        const AppRec a = c.ap_rec[buf][SB2_CHK(r, 0, (long long)c.nV * c.max_items, 8)];
         const int rec = r;
         r = a.next;
         // The reference tests, per approaching vehicle: not ego, (under lastWasContRed) not standing, blockedByFoe.  The tests are

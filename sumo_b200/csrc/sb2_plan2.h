@@ -187,7 +187,7 @@ SB2_HDN void veh_planMove(const Ctx& c, int v, int wp) {
     DriveItem last;
     int n = 0;
     bool overflow = false;
-#define SB2_PUSH(item) do { if (n < MAX_DRIVE_ITEMS) { if (n > 0) { lf.store(n - 1, last); } last = (item); n++; } else { overflow = true; } } while (0)
+#define SB2_PUSH(item) do { if (n < c.max_items) { if (n > 0) { lf.store(n - 1, last); } last = (item); n++; } else { overflow = true; } } while (0)
 
     // leader on the own lane (MSLane::planMovements / updateLeaderInfo, MSLane.cpp:1608-1685)
     int ahead = c.veh_ahead[v];

@@ -205,7 +205,7 @@ struct Ctx {
     const int32_t* link_contpred;                    // derived: the entry link consulted by lastWasContMajor/State, or -1
     SUMOTime* link_last_change;                      // myLastStateChange
     uint8_t* link_last_green;                        // myLastGreenState
-    int32_t* link_app_head[2];                       // approach table heads (record = veh*MAX_DRIVE_ITEMS+item), per buffer
+    int32_t* link_app_head[2];                       // approach table heads (record = item*nV + work-list position), per buffer
     // ---- traffic lights ------------------------------------------------------------------
     const int32_t* tl_phase_begin; const SUMOTime* phase_dur; const int32_t* phase_state_begin; const uint8_t* phase_states;
     int32_t* tl_cur_phase; SUMOTime* tl_next_switch;
@@ -272,6 +272,7 @@ struct Ctx {
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
     // ---- E2 lane area detectors on one lane (MSE2Collector as a move reminder, sb2_e2.h); nE2 == 0: one dummy element each
+    int max_items;                   // drive items per vehicle (MAX_DRIVE_ITEMS unless the scenario asks for more)
     int nE2, e2_note_cap;
     const int32_t* lane_e2_begin;    // [nL+1] CSR like lane_e1_begin
     const int32_t* e2_of_lane;       // [nE2]
@@ -314,7 +315,7 @@ struct Ctx {
     // POSITION wp in that step's work list (record = item * nV + wp), so the plan kernel writes and the execute kernel reads the
     // records fully coalesced; veh_order[buf][wp] gives the vehicle back (approach tables of the previous step use buf = cur ^ 1).
     int32_t* veh_order[2];
-    // drive items, double buffered [2][MAX_DRIVE_ITEMS*nV], item-major (item i of the vehicle at work-list position wp at i*nV+wp);
+    // drive items, double buffered [2][max_items*nV], item-major (item i of the vehicle at work-list position wp at i*nV+wp);
     // veh_ndi[buf][wp] likewise
     int32_t* veh_ndi[2];
     int32_t* di_link[2]; uint8_t* di_request[2]; uint8_t* di_hadstopped[2];

@@ -323,6 +323,7 @@ int main(int argc, char** argv) {
     std::string traceOut, drawsIn, fcdOut, emisOut, tripOut, fcdXmlOut, summaryOut, tlsSetPhase, vehSetSpeed, e1Out, mdOut, e2Out;
     long long e1Period = 60000, mdPeriod = 60000, e2Period = 60000;
     long maxSteps = -1;
+    int driveItems = 0;
     std::string debugName, partFile;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
@@ -342,6 +343,8 @@ int main(int argc, char** argv) {
             mdOut = argv[++i];   // text, one line per non-internal lane and interval: the raw members of MSLaneMeanDataValues (sumob200_meandata_interval)
         } else if (a == "--md-period" && i + 1 < argc) {
             mdPeriod = atoll(argv[++i]);   // ms
+        } else if (a == "--drive-items" && i + 1 < argc) {
+            driveItems = atoi(argv[++i]);   // the scenario scalar drive_item_capacity (networks of very short lanes)
         } else if (a == "--e2-out" && i + 1 < argc) {
             e2Out = argv[++i];   // text, one line per detector and interval: the attributes of the reference's E2 output (sumob200_e2_interval)
         } else if (a == "--e2-period" && i + 1 < argc) {
@@ -378,6 +381,9 @@ int main(int argc, char** argv) {
     Model m;
     try {
         ff.load(argv[1]);
+        if (driveItems > 0) {
+            ff.putScalar<int32_t>("drive_item_capacity", driveItems);
+        }
         m.build(ff);
     } catch (const std::exception& e) {
         fprintf(stderr, "%s\n", e.what());

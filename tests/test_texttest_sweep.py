@@ -1,5 +1,5 @@
 """The reference's own texttest scenarios through the engine, in bulk (tools_dev/texttest_sweep.py; results of the full sweep over 4585
-test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 328 -- reproduces the reference's trajectories
+test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 329 -- reproduces the reference's trajectories
 bit for bit, everything else is refused with a message, rejected by the reference itself, or has no vehicles).
 
 This test re-runs every fourth of the accepted scenarios: the reference's loader flattens the scenario and records the reference's

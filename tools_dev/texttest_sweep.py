@@ -74,16 +74,21 @@ def run_one(rel):
                 return rel, "FLOWDIFF", "expanded flows change the reference's own run"
         if sum(len(s[1]) for s in ref) == 0:
             return rel, "EMPTY", ""
+        cmd = [EMUL, "x.flat", "--trace-out", "e.trace", "--draws", "x.draws", "--steps", str(len(ref))]
+        note = ""
         try:
-            e = subprocess.run([EMUL, "x.flat", "--trace-out", "e.trace", "--draws", "x.draws", "--steps", str(len(ref))], cwd=tmp, capture_output=True,
-                               text=True, timeout=300)
+            e = subprocess.run(cmd, cwd=tmp, capture_output=True, text=True, timeout=300)
+            if e.returncode == 0 and "err=" in e.stderr and int(e.stderr.strip().splitlines()[-1].rsplit("err=", 1)[-1], 16) & 1:
+                # more than 8 links inside the look-ahead (very short lanes): the scenario asks for more drive items per vehicle
+                e = subprocess.run(cmd + ["--drive-items", "32"], cwd=tmp, capture_output=True, text=True, timeout=300)
+                note = " (drive_item_capacity 32)"
         except subprocess.TimeoutExpired:
             return rel, "TIMEOUT", "emulation > 300 s"
         if e.returncode != 0:
             msg = (e.stderr.strip().splitlines() or [""])[-1]
             return rel, ("REFUSED" if "sumob200" in msg else "EMULFAIL"), msg[:160]
         if open(os.path.join(tmp, "x.trace"), "rb").read() == open(os.path.join(tmp, "e.trace"), "rb").read():
-            return rel, "SAME", "%d steps, %d vehicle-steps" % (len(ref), sum(len(s[1]) for s in ref))
+            return rel, "SAME", "%d steps, %d vehicle-steps%s" % (len(ref), sum(len(s[1]) for s in ref), note)
         flags = int(e.stderr.strip().splitlines()[-1].rsplit("err=", 1)[-1], 16) if "err=" in e.stderr else 0
         if flags & (1 | 2 | 4 | 512 | 8192):
             # a fixed capacity of the engine was exceeded (drive items, further lanes, partial occupators, link leaders, detector slots):
