@@ -26,7 +26,7 @@ def needs_build():
 
 
 # kernel sets: kernels.cu compiled once per feature selection (see its header); the engine picks one per scenario
-KERNEL_SETS = {"full": [], "krauss": ["-DSB2_NO_IDM"]}
+KERNEL_SETS = {"full": [], "krauss": ["-DSB2_NO_IDM"], "plain": ["-DSB2_NO_IDM", "-DSB2_NO_OBSERVERS"]}
 
 
 def build(force=False, verbose=False, extra_flags=(), out=None):

@@ -101,7 +101,8 @@ int finishCreate(sumob200_engine* e, const FlatFile& ff, int device, sumob200_en
     try {
         e->model.build(ff);
         // kernel set for this scenario (kernels.cu): code the fleet never executes is not compiled in
-        e->ks = e->model.anyIDM ? sb2_kernelset_full() : sb2_kernelset_krauss();
+        const bool observers = e->model.h.nE1 > 0 || e->model.h.nE2 > 0 || e->model.h.md_on != 0;
+        e->ks = e->model.anyIDM ? sb2_kernelset_full() : (observers ? sb2_kernelset_krauss() : sb2_kernelset_plain());
         if (e->ks->ctx_size != sizeof(Ctx)) {
             throw std::runtime_error("sumob200: kernel set was built with a different Ctx layout");
         }

@@ -6,6 +6,8 @@
  * (the IDM branches for a Krauss-only fleet) costs 10 % of its time just by being compiled in.
  *   full    every implemented feature
  *   krauss  -DSB2_NO_IDM : all vTypes use carFollowModel Krauss
+ *   plain   -DSB2_NO_IDM -DSB2_NO_OBSERVERS : Krauss fleet, no E1 / E2 detectors, no edgeData (the move-reminder hooks cost
+ *           k_execute 7 % when compiled in and unused)
  * Every set lives in its own namespace, so the inlined device functions of two sets never meet at link time.
  *
  * One simulation step = 8 launches on one stream (no host synchronisation in between).  Every kernel takes the Ctx by

@@ -64,7 +64,7 @@ SB2_HD void e1_count_entered(const Ctx& c, int det) {
 // MSVehicle::leaveLane(reason != NOTIFICATION_JUNCTION): notifyLeave of every reminder -> a vehicle on a detector leaves it early
 // (arrival, teleport, collision); no reminder survives
 SB2_HD void veh_e1_leave_net(const Ctx& c, int v) {
-    if (c.nE1 == 0) {
+    if (!SB2_OBSERVERS || c.nE1 == 0) {
         return;
     }
     for (int i = 0; i < MAX_E1_REMINDERS; i++) {
@@ -83,7 +83,7 @@ SB2_HD void veh_e1_leave_net(const Ctx& c, int v) {
 // the detectors of `lane` become reminders with offset 0 (addReminder); `enter`: notifyEnter with a reason other than
 // NOTIFICATION_JUNCTION (departure) -- dropped if the vehicle's back is beyond the detector, on the detector if its front is
 SB2_HD void veh_e1_add_lane(const Ctx& c, int v, int lane, bool enter, double pos, double backPos) {
-    if (c.nE1 == 0) {
+    if (!SB2_OBSERVERS || c.nE1 == 0) {
         return;
     }
     for (int k = c.lane_e1_begin[lane]; k < c.lane_e1_begin[lane + 1]; k++) {
@@ -117,7 +117,7 @@ SB2_HD void veh_e1_add_lane(const Ctx& c, int v, int lane, bool enter, double po
 
 // adaptLaneEntering2MoveReminder: rem.second += oldLaneLength, then the entered lane's reminders (notifyEnter(JUNCTION) keeps them)
 SB2_HD void veh_e1_enter_at_move(const Ctx& c, int v, int oldLane, int newLane) {
-    if (c.nE1 == 0) {
+    if (!SB2_OBSERVERS || c.nE1 == 0) {
         return;
     }
     const double oldLaneLength = c.lane_length[oldLane];
@@ -131,7 +131,7 @@ SB2_HD void veh_e1_enter_at_move(const Ctx& c, int v, int oldLane, int newLane) 
 
 // workOnMoveReminders(oldPos, newPos, newSpeed) -> MSInductLoop::notifyMove for every reminder
 SB2_HD void veh_e1_move(const Ctx& c, int v, double oldPos0, double newPos0, double newSpeed0) {
-    if (c.nE1 == 0) {
+    if (!SB2_OBSERVERS || c.nE1 == 0) {
         return;
     }
     const double newSpeed = MAX2(0., newSpeed0);

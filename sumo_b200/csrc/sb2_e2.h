@@ -45,7 +45,7 @@ SB2_HD void e2_push_note(const Ctx& c, int det, int v, double dist, double timeO
 
 // notifyLeave with a reason other than NOTIFICATION_JUNCTION (arrival, teleport): the VehicleInfo is erased at once
 SB2_HD void veh_e2_leave_net(const Ctx& c, int v) {
-    if (c.nE2 == 0) {
+    if (!SB2_OBSERVERS || c.nE2 == 0) {
         return;
     }
     for (int i = 0; i < MAX_E2_REMINDERS; i++) {
@@ -62,7 +62,7 @@ SB2_HD void veh_e2_leave_net(const Ctx& c, int v) {
 // notifyEnter for the detectors of `lane`; `enter`: reason other than NOTIFICATION_JUNCTION (departure, end of a teleport) -- no
 // subscription if the vehicle's back is already behind the detector's end
 SB2_HD void veh_e2_add_lane(const Ctx& c, int v, int lane, bool enter, double backPos) {
-    if (c.nE2 == 0) {
+    if (!SB2_OBSERVERS || c.nE2 == 0) {
         return;
     }
     for (int k = c.lane_e2_begin[lane]; k < c.lane_e2_begin[lane + 1]; k++) {
@@ -102,7 +102,7 @@ SB2_HD void veh_e2_add_lane(const Ctx& c, int v, int lane, bool enter, double ba
 
 // adaptLaneEntering2MoveReminder + the entered lane's reminders
 SB2_HD void veh_e2_enter_at_move(const Ctx& c, int v, int oldLane, int newLane) {
-    if (c.nE2 == 0) {
+    if (!SB2_OBSERVERS || c.nE2 == 0) {
         return;
     }
     const double oldLaneLength = c.lane_length[oldLane];
@@ -117,7 +117,7 @@ SB2_HD void veh_e2_enter_at_move(const Ctx& c, int v, int oldLane, int newLane) 
 // workOnMoveReminders(oldPos, newPos, newSpeed) -> MSE2Collector::notifyMove of every subscription; vmaxLane =
 // veh.getLane()->getVehicleMaxSpeed(&veh) of the lane the vehicle is on after the move
 SB2_HD void veh_e2_move(const Ctx& c, int v, double oldPos0, double newPos0, double speed, double vmaxLane) {
-    if (c.nE2 == 0) {
+    if (!SB2_OBSERVERS || c.nE2 == 0) {
         return;
     }
     const double TS = c.TS;

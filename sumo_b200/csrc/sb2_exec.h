@@ -386,10 +386,10 @@ SB2_HDN bool veh_executeMove(const Ctx& c, int v, int wp, double random, int liv
     }
     veh_emissions_notifyMove(c, v, speed, accelOut);   // workOnMoveReminders (MSVehicle.cpp:4902) -> MSDevice_Emissions::notifyMove
     veh_e1_move(c, v, pos - lastDist, pos, speed);     //                                          -> MSInductLoop::notifyMove
-    if (c.nE2 > 0) {
+    if (SB2_OBSERVERS && c.nE2 > 0) {
         veh_e2_move(c, v, pos - lastDist, pos, speed, lane_vehicle_max_speed(c, myLane, v));   //       -> MSE2Collector::notifyMove
     }
-    if (c.md_on) {
+    if (SB2_OBSERVERS && c.md_on) {
         // -> MeanDataValues::notifyMove of every lane the vehicle's body was on or entered; rem->second = lengths of the lanes left since
         const double vmaxNow = lane_vehicle_max_speed(c, myLane, v);
         const int nChain = np + (arrivalLaneEntered >= 0 ? 1 : 0);

@@ -42,3 +42,4 @@ struct sb2_kernelset {
 
 extern "C" const sb2_kernelset* sb2_kernelset_full(void);
 extern "C" const sb2_kernelset* sb2_kernelset_krauss(void);
+extern "C" const sb2_kernelset* sb2_kernelset_plain(void);

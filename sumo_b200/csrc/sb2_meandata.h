@@ -21,7 +21,7 @@ namespace sb2 {
 
 // (edge partition: a rank accumulates its OWN lanes only -- it executes every vehicle that touches them, own or ghost; the lanes of
 // its ghost column are the neighbour's to report)
-SB2_HD bool md_lane_measured(const Ctx& c, int lane) { return c.md_on != 0 && !lane_internal(c, lane) && lane_auth(c, lane); }
+SB2_HD bool md_lane_measured(const Ctx& c, int lane) { return SB2_OBSERVERS && c.md_on != 0 && !lane_internal(c, lane) && lane_auth(c, lane); }
 
 SB2_HD void md_add(const Ctx& c, int lane, int k, double x) {
     double* p = &c.md_sums[(size_t)k * c.nL + lane];

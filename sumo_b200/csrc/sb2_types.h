@@ -68,6 +68,12 @@ typedef int64_t SUMOTime;
 #define SB2_NO_INTERSECTION 10000.0              /* MSLink.cpp:76 */
 #define SB2_EMERGENCY_DECEL_AMPLIFIER 1.2        /* MSCFModel.h:35 */
 
+// kernel set without move reminders (-DSB2_NO_OBSERVERS, kernels.cu): E1 / E2 detectors and edgeData compiled out
+#if defined(SB2_NO_OBSERVERS)
+#define SB2_OBSERVERS 0
+#else
+#define SB2_OBSERVERS 1
+#endif
 enum { MAX_DRIVE_ITEMS = 8, MAX_FURTHER = 4, MAX_PARTIAL = 4, MAX_E1_REMINDERS = 4, MAX_E2_REMINDERS = 8 };
 // rows of Ctx::md_sums / md_counts (sb2_meandata.h)
 enum { MD_SAMPLE = 0, MD_DIST = 1, MD_WAIT = 2, MD_TIMELOSS = 3, MD_FRONT_SAMPLE = 4, MD_FRONT_DIST = 5, MD_LENGTH_SUM = 6, MD_OCCUPATION = 7, MD_NSUMS = 8 };
