@@ -155,6 +155,12 @@ int edgeFlags(const MSEdge* e) {
            | (e->isCrossing() || e->isWalkingArea() ? 16 : 0);
 }
 
+// Parity harness only (sumo_flatten --trajectories-only, used by tools_dev/texttest_sweep.py): features that OBSERVE the vehicles without
+// ever changing lane, position or speed -- output devices, detectors and mean data the engine has no counterpart for -- are left
+// out of the flat file instead of refusing the scenario; only the trajectories are compared then.  Never set by the hook: a run
+// that is asked for such an output and cannot write it is refused.
+bool gTrajectoriesOnly = false;
+
 void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     OptionsCont& oc = OptionsCont::getOptions();
     // ---------------- edges and lanes
@@ -473,7 +479,8 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             }
             for (const MSVehicleDevice* d : v->getDevices()) {
                 const std::string dev = d->deviceName();
-                if (dev != "emissions" && dev != "tripinfo" && dev != "fcd" && dev != "vehroute") {
+                const bool observer = dev == "ssm" || dev == "btreceiver" || dev == "btsender" || dev == "battery" || dev == "example";
+                if (dev != "emissions" && dev != "tripinfo" && dev != "fcd" && dev != "vehroute" && !(gTrajectoriesOnly && observer)) {
                     throw ProcessError(who + "device '" + dev + "' is not supported");
                 }
             }
@@ -730,7 +737,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     {
         MSDetectorControl& dc = net->getDetectorControl();
         for (const SumoXMLTag tag : dc.getAvailableTypes()) {
-            if (tag != SUMO_TAG_INDUCTION_LOOP && tag != SUMO_TAG_LANE_AREA_DETECTOR && dc.getTypedDetectors(tag).size() > 0) {
+            if (tag != SUMO_TAG_INDUCTION_LOOP && tag != SUMO_TAG_LANE_AREA_DETECTOR && dc.getTypedDetectors(tag).size() > 0 && !gTrajectoriesOnly) {
                 throw ProcessError("sumob200: detectors of type '" + toString(tag) + "' are not supported (only inductionLoop / e1Detector and laneAreaDetector / e2Detector)");
             }
         }
@@ -741,6 +748,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             const MSInductLoop* loop = dynamic_cast<const MSInductLoop*>(item.second);
             if (loop == nullptr) {
                 throw ProcessError("sumob200: unexpected detector object '" + item.first + "'");
+            }
+            if (gTrajectoriesOnly && (!loop->getVehicleTypes().empty() || loop->detectsPersons())) {
+                continue;
             }
             if (!loop->getVehicleTypes().empty() || loop->detectsPersons()) {
                 throw ProcessError("sumob200: detector '" + item.first + "': vTypes / detectPersons filters are not supported");
@@ -775,6 +785,10 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
                 throw ProcessError("sumob200: unexpected detector object '" + item.first + "'");
             }
             const std::string who = "sumob200: detector '" + item.first + "': ";
+            if (gTrajectoriesOnly && (det->myLanes.size() != 1 || !det->getVehicleTypes().empty() || det->detectsPersons() || !det->myNextEdges.empty()
+                                      || periodic.count(det) == 0)) {
+                continue;
+            }
             if (det->myLanes.size() != 1) {
                 throw ProcessError(who + "lane area detectors over several lanes are not supported");
             }
@@ -809,6 +823,10 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
         for (const auto& item : net->getDetectorControl().getMeanData()) {
             for (const MSMeanData* md : item.second) {
                 const MSMeanData_Net* mdn = dynamic_cast<const MSMeanData_Net*>(md);
+                if (gTrajectoriesOnly && (mdn == nullptr || md->*get(MdTrackTag()) || md->*get(MdInternalTag()) || mdn->*get(MdHaltRelTag()) > 0
+                                          || !md->getVehicleTypes().empty() || (any && mdn->*get(MdHaltTag()) != halt))) {
+                    continue;
+                }
                 if (mdn == nullptr) {
                     throw ProcessError("sumob200: mean data '" + item.first + "' is not of type edgeData / laneData (emissions, harmonoise, ... are not supported)");
                 }
@@ -1010,6 +1028,8 @@ main(int argc, char** argv) {
             flatOut = argv[++i];
         } else if (a == "--trace-out" && i + 1 < argc) {
             traceOut = argv[++i];
+        } else if (a == "--trajectories-only") {
+            gTrajectoriesOnly = true;
         } else if (a == "--draws-out" && i + 1 < argc) {
             drawsOut = argv[++i];
         } else if (a == "--tls-set-phase" && i + 1 < argc) {

@@ -2,6 +2,8 @@
 sub-trees of /root/reference/tests/sumo (a directory with an options.sumo and no sub-directories that have one): texttest's option
 inheritance, the reference's loader flattens the scenario and records the reference's trajectories (oracle/_ref/sumo_flatten
 --trace-out, --draws-out), tests/host_emul runs the same steps with the draws replayed, the two traces are compared byte by byte.
+The sweep compares trajectories only: sumo_flatten --trajectories-only leaves observers the engine has no counterpart for (SSM / bluetooth /
+battery devices, E3 and other detectors, emission / noise mean data) out of the flat file instead of refusing the scenario.
 Outcomes: SAME, DIFF (first differing step), REFUSED (the message), LOADFAIL (the reference itself rejects the options, e.g. tests of
 error messages), EMPTY (no vehicle ever on the road), FLAGGED (the engine raised one of its capacity flags during the run).
 FLOWDIFF would mean the harness's up-front <flow> expansion changed the reference's own trajectories (never seen).
@@ -55,7 +57,7 @@ def run_one(rel):
         if any(o.startswith("--remote-port") or o in ("-c", "--configuration-file") for o in options):
             return rel, "SKIP", "traci / config file"
         try:
-            r = subprocess.run([os.path.join(REF, "sumo_flatten"), "--flat-out", "x.flat", "--trace-out", "x.trace", "--draws-out", "x.draws"] + options,
+            r = subprocess.run([os.path.join(REF, "sumo_flatten"), "--trajectories-only", "--flat-out", "x.flat", "--trace-out", "x.trace", "--draws-out", "x.draws"] + options,
                                cwd=tmp, capture_output=True, text=True, timeout=120)
         except subprocess.TimeoutExpired:
             return rel, "TIMEOUT", "reference > 120 s"
