@@ -470,6 +470,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             if (p.arrivalLaneProcedure == ArrivalLaneDefinition::RANDOM) {
                 throw ProcessError(who + "arrivalLane is not supported");
             }
+            if (p.insertionChecks != (int)InsertionCheck::ALL) {
+                throw ProcessError(who + "insertionChecks other than 'all' are not supported");
+            }
             const SUMOVTypeParameter& tp = v->getVehicleType().getParameter();
             if (tp.actionStepLength != 0 && tp.actionStepLength != DELTA_T) {
                 throw ProcessError(who + "actionStepLength different from the step length is not supported");

@@ -472,15 +472,17 @@ public:
                     throw std::runtime_error("sumob200: departLane index out of range");
                 }
                 dl[v] = h.edge_lane_begin[e0] + idx;
-                // a vehicle inserted with its back behind the lane's start laps into the predecessor lanes
-                // (MSVehicle::computeFurtherLanes at insertion, MSVehicle.cpp:5823): not modelled
+                // a vehicle inserted with its back behind the lane's start laps into the predecessor lanes (MSVehicle::computeFurtherLanes
+                // at insertion, MSVehicle.cpp:5823) and MSLane::getFollowersOnConsecutive then asks the junction behind it for link
+                // leaders (MSLane.cpp:3951-3975): not modelled.  On a lane without a predecessor (network fringe) there is nothing
+                // behind: the back position is simply negative
                 if (h.veh_departpos_proc[v] == DPD_GIVEN) {
                     double pos = h.veh_departpos[v];
                     if (pos < 0.) {
                         pos += h.lane_length[dl[v]];
                     }
-                    if (pos < h.vt_length[h.veh_type[v]]) {
-                        throw std::runtime_error("sumob200: departPos closer to the lane's start than the vehicle is long is not supported");
+                    if (pos < h.vt_length[h.veh_type[v]] && h.lane_pred_logical[dl[v]] >= 0) {
+                        throw std::runtime_error("sumob200: departPos closer to the lane's start than the vehicle is long is not supported (on a lane with a predecessor)");
                     }
                 }
             }
