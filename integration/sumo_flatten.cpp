@@ -470,6 +470,9 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             if (p.arrivalLaneProcedure == ArrivalLaneDefinition::RANDOM) {
                 throw ProcessError(who + "arrivalLane is not supported");
             }
+            if (p.departEdgeProcedure != RouteIndexDefinition::DEFAULT || p.arrivalEdgeProcedure != RouteIndexDefinition::DEFAULT) {
+                throw ProcessError(who + "departEdge / arrivalEdge are not supported");
+            }
             if (p.insertionChecks != (int)InsertionCheck::ALL) {
                 throw ProcessError(who + "insertionChecks other than 'all' are not supported");
             }
@@ -640,6 +643,12 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
             if (TIME2STEPS(t->getParameter().getCFParam(SUMO_ATTR_SIGMA_STEP, TS)) > DELTA_T) {
                 // MSCFModel_Krauss::myDawdleStep: the dawdle draw is kept for several steps (MSCFModel_Krauss.cpp:51-60, 96-113)
                 throw ProcessError("sumob200: vType '" + t->getID() + "': sigmaStep longer than the step length is not supported");
+            }
+            if (!t->getCarFollowModel().getMaxAccelProfile().empty() || !t->getCarFollowModel().getDesAccelProfile().empty()) {
+                throw ProcessError("sumob200: vType '" + t->getID() + "': maxAccelProfile / desAccelProfile are not supported");
+            }
+            if (t->getParameter().getTimeToTeleport(-12345) != -12345 || t->getParameter().getTimeToTeleportBidi(-12345) != -12345) {
+                throw ProcessError("sumob200: vType '" + t->getID() + "': timeToTeleport per vType is not supported");
             }
             idmDelta.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_DELTA, 4.));
             idmStep.push_back(t->getParameter().getCFParam(SUMO_ATTR_CF_IDM_STEPPING, .25));
