@@ -71,7 +71,7 @@ typedef struct sumob200_step_result {
     int32_t halting;          /* on-road vehicles slower than 0.1 m/s     (MSVehicleControl::getHaltingVehicleNo, summary output) */
     int64_t vehicle_updates;  /* sum over the executed steps of vehicles on the road (numerator of SUMO's UPS, MSNet.cpp:959) */
     int32_t teleporting;      /* vehicles currently off the road in MSVehicleTransfer (part of `running`) */
-    int32_t reserved;
+    int32_t discarded_total;  /* vehicles removed before their departure: waited longer than --max-depart-delay (MSInsertionControl::tryInsert) */
 } sumob200_step_result;
 
 /* state mirror of one vehicle slot (slot = index in the veh_* arrays = load order); what libsumo::Vehicle getters read

@@ -721,7 +721,8 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     if (oc.getBool("ignore-route-errors")) {
         throw ProcessError("sumob200: --ignore-route-errors is not supported (insertion with impossible depart speeds)");
     }
-    if (string2time(oc.getString("max-depart-delay")) >= 0) {
+    if (string2time(oc.getString("max-depart-delay")) >= 0 && !gTrajectoriesOnly) {
+        // (the engine discards such vehicles, opt_max_depart_delay below; the hook does not delete them from MSVehicleControl yet)
         throw ProcessError("sumob200: --max-depart-delay is not supported");
     }
     for (const MSEdge* e : MSEdge::getAllEdges()) {
@@ -864,6 +865,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     ff.putScalar<int64_t>("opt_end", string2time(oc.getString("end")));
     ff.putScalar<int64_t>("opt_seed", (int64_t)oc.getInt("seed"));
     ff.putScalar<int64_t>("opt_time_to_teleport", MSGlobals::gTimeToGridlock);
+    ff.putScalar<int64_t>("opt_max_depart_delay", string2time(oc.getString("max-depart-delay")));
     ff.putScalar<int64_t>("opt_time_to_impatience", MSGlobals::gTimeToImpatience);
     ff.putScalar<int64_t>("opt_startup_wait_threshold", MSGlobals::gStartupWaitThreshold);
     ff.putScalar<int64_t>("opt_ignore_junction_blocker", MSGlobals::gIgnoreJunctionBlocker);

@@ -417,7 +417,7 @@ int sumob200_step(sumob200_engine* e, int n_steps, sumob200_step_result* out) {
         out->time_ms = c.t;
         out->running = counters[0] + counters[10] + counters[11];
         out->teleporting = counters[10] + counters[11];
-        out->reserved = 0;
+        out->discarded_total = counters[15];
         out->arrived_total = counters[1];
         out->departed_total = counters[2];
         out->collisions = counters[4];

@@ -199,6 +199,7 @@ public:
         h.timeToTeleport = ff.scalar<int64_t>("opt_time_to_teleport", 300000);
         h.startupWaitThreshold = ff.scalar<int64_t>("opt_startup_wait_threshold", 2000);
         h.ignoreJunctionBlocker = ff.scalar<int64_t>("opt_ignore_junction_blocker", -1);
+        h.maxDepartDelay = ff.scalar<int64_t>("opt_max_depart_delay", -1);
         h.tlsYellowMinDecel = ff.scalar<double>("opt_tls_yellow_min_decel", 3.);
         if (ff.scalar<int32_t>("opt_sublane", 0) != 0) {
             throw std::runtime_error("sumob200: the sublane model (--lateral-resolution) is not supported");

@@ -461,7 +461,28 @@ SB2_HDN void lane_insertVehicles(const Ctx& c, int l) {
         if (c.veh_depart[v] > c.t) {
             break;
         }
+        if (c.veh_lane[v] == -4) {
+            head++;   // discarded earlier while it was not at the head of the queue
+            continue;
+        }
         if (!lane_tryInsert(c, l, v)) {
+            if (c.maxDepartDelay >= 0) {
+                // MSInsertionControl::tryInsert (MSInsertionControl.cpp:170-173): every pending vehicle of this edge fails in this step
+                // (the edge remembers the failed attempt, MSEdge::insertVehicle); the ones that have waited too long are deleted
+                for (int k = head; k < end; k++) {
+                    const int w = c.dq_veh[k];
+                    if (c.veh_depart[w] > c.t) {
+                        break;
+                    }
+                    if (c.veh_lane[w] == -1 && c.t - c.veh_depart[w] > c.maxDepartDelay) {
+                        c.veh_lane[w] = -4;
+                        atomic_inc(&c.counters[15]);
+                    }
+                }
+                while (head < end && c.veh_lane[c.dq_veh[head]] == -4) {
+                    head++;
+                }
+            }
             break;
         }
         head++;

@@ -40,6 +40,9 @@ SB2_HD void summary_add(SummaryPart& a, const SummaryPart& b) {
 // contribution of vehicle slot v; tStep = time of the step that was executed last (the `time` attribute of the summary line)
 SB2_HD void summary_vehicle(const Ctx& c, int v, SUMOTime tStep, SummaryPart& p) {
     const int lane = c.veh_lane[v];
+    if (lane == -4) {
+        return;   // discarded before its departure (--max-depart-delay): not loaded any more for the reference
+    }
     if (lane >= 0) {
         const double speed = c.veh_speed[v];
         p.count++;

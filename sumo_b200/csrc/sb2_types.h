@@ -278,6 +278,7 @@ struct Ctx {
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
     // ---- E2 lane area detectors on one lane (MSE2Collector as a move reminder, sb2_e2.h); nE2 == 0: one dummy element each
+    SUMOTime maxDepartDelay;         // --max-depart-delay (ms), -1 = off: a vehicle that could not depart for longer is discarded (veh_lane -4)
     int max_items;                   // drive items per vehicle (MAX_DRIVE_ITEMS unless the scenario asks for more)
     int nE2, e2_note_cap;
     const int32_t* lane_e2_begin;    // [nL+1] CSR like lane_e1_begin
@@ -343,7 +344,7 @@ struct Ctx {
     int traci_speed_used; double* veh_traci_speed;
     // ---- step results --------------------------------------------------------------------
     int32_t* err_flags;        // [1] OR of ERR_*
-    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step, 12 length of e1_events, 13 / 14 notes in e2_notes[0] / [1]
+    int32_t* counters;         // [16]: 7 = length of the work list, 8 = halting vehicles of this step; 0 running, 1 arrived(total), 2 inserted(total), 3 halting, 4 collisions, 5 emergency stops, 6 teleports, 9 deferred vehicles of this step, 10 length of tp_list, 11 removals pending until the next step, 12 length of e1_events, 13 / 14 notes in e2_notes[0] / [1], 15 vehicles discarded before departure (total)
 };
 
 SB2_HD double MIN2(double a, double b) { return a < b ? a : b; }

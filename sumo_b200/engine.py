@@ -35,7 +35,7 @@ class StepResult(ctypes.Structure):
     _fields_ = [("time_ms", ctypes.c_int64), ("running", ctypes.c_int32), ("departed_total", ctypes.c_int32),
                 ("arrived_total", ctypes.c_int32), ("collisions", ctypes.c_int32), ("emergency_stops", ctypes.c_int32),
                 ("teleports", ctypes.c_int32), ("flags", ctypes.c_int32), ("halting", ctypes.c_int32),
-                ("vehicle_updates", ctypes.c_int64), ("teleporting", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("vehicle_updates", ctypes.c_int64), ("teleporting", ctypes.c_int32), ("discarded_total", ctypes.c_int32)]
 
 
 VEHICLE_STATE = np.dtype([("lane", np.int32), ("route_pos", np.int32), ("pos", np.float64), ("speed", np.float64)])

@@ -609,7 +609,7 @@ int main(int argc, char** argv) {
             lastErr = *c.err_flags;
         }
         // termination like MSNet::simulationState: no vehicles left and none pending
-        if (m.end < 0 && n == 0 && c.counters[2] == c.nV) {
+        if (m.end < 0 && n == 0 && c.counters[2] + c.counters[15] == c.nV) {
             break;
         }
     }

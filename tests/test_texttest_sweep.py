@@ -1,8 +1,8 @@
 """The reference's own texttest scenarios through the engine, in bulk (tools_dev/texttest_sweep.py; results of the full sweep over 4585
-test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 553 -- reproduces the reference's trajectories
+test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 554 -- reproduces the reference's trajectories
 bit for bit, everything else is refused with a message, rejected by the reference itself, or has no vehicles).
 
-This test re-runs every fourth of the accepted scenarios: the reference's loader flattens the scenario and records the reference's
+This test re-runs every eighth of the accepted scenarios: the reference's loader flattens the scenario and records the reference's
 own run (oracle/_ref/sumo_flatten), tests/host_emul (the device functions compiled for the host) must give byte-identical traces.
 It also checks that a handful of scenarios with features outside the engine's scope are still REFUSED (never simplified).
 Needs /root/reference (the build container); skipped where it is absent."""
@@ -22,7 +22,7 @@ REFUSED = {
     "extended/bidiEdge/1edge_2vehicles": "bidirectional lanes",
     "extended/state/load_remove": "--load-state is not supported",
     "cf_model/Krauss/sigma1_step0.1_sigmaStep1": "sigmaStep longer than the step length",
-    "output/duration_log/vehicles_exceeding_max_depart_delay": "--max-depart-delay is not supported",
+    "spec/departure/insertionChecks/none": "insertionChecks other than 'all'",
     "spec/departure/errors/slow_lane_ahead_ignore": "--ignore-route-errors is not supported",
     "opposite_direction_driving/bugs/ticket9721": "opposite-direction driving",
     "rail/slow_fast_slow": "only static programs are supported",
