@@ -694,7 +694,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     {
         static const std::set<std::string> honoured = {
             "route-steps", "scale", "scale-suffix",  // loader only (the hook loads everything at once; --scale has been applied to the loaded vehicles)
-            "default.speeddev", "default.departspeed", "default.departlane", "default.carfollowmodel", "default.emergencydecel",   // in the exported vTypes / scalars
+            "default.speeddev", "default.departspeed", "default.departlane", "default.carfollowmodel", "default.emergencydecel", "extrapolate-departpos",   // in the exported vTypes / scalars
             "collision.mingap-factor",               // MSVehicleType::getCollisionMinGapFactor, exported per vType
             "time-to-teleport", "time-to-impatience", "ignore-junction-blocker", "startup-wait-threshold", "tls.yellow.min-decel",
             "emergencydecel.warning-threshold",      // exported scalars
@@ -866,6 +866,7 @@ void flattenTo(MSNet* net, sb2::FlatFile& ff) {
     ff.putScalar<int64_t>("opt_seed", (int64_t)oc.getInt("seed"));
     ff.putScalar<int64_t>("opt_time_to_teleport", MSGlobals::gTimeToGridlock);
     ff.putScalar<int64_t>("opt_max_depart_delay", string2time(oc.getString("max-depart-delay")));
+    ff.putScalar<int32_t>("opt_extrapolate_departpos", oc.getBool("extrapolate-departpos") ? 1 : 0);
     ff.putScalar<int64_t>("opt_time_to_impatience", MSGlobals::gTimeToImpatience);
     ff.putScalar<int64_t>("opt_startup_wait_threshold", MSGlobals::gStartupWaitThreshold);
     ff.putScalar<int64_t>("opt_ignore_junction_blocker", MSGlobals::gIgnoreJunctionBlocker);

@@ -200,6 +200,11 @@ public:
         h.startupWaitThreshold = ff.scalar<int64_t>("opt_startup_wait_threshold", 2000);
         h.ignoreJunctionBlocker = ff.scalar<int64_t>("opt_ignore_junction_blocker", -1);
         h.maxDepartDelay = ff.scalar<int64_t>("opt_max_depart_delay", -1);
+        h.extrapolateDepartPos = ff.scalar<int32_t>("opt_extrapolate_departpos", 0) != 0 ? 1 : 0;
+        if (h.extrapolateDepartPos && (ff.has("e1_lane") || ff.has("e2_lane") || ff.scalar<int32_t>("md_enabled", 0) != 0)) {
+            // (the reference notifies the move reminders of the fractional move: MSVehicle::executeFractionalMove -> workOnMoveReminders)
+            throw std::runtime_error("sumob200: --extrapolate-departpos together with detectors / edgeData is not supported");
+        }
         h.tlsYellowMinDecel = ff.scalar<double>("opt_tls_yellow_min_decel", 3.);
         if (ff.scalar<int32_t>("opt_sublane", 0) != 0) {
             throw std::runtime_error("sumob200: the sublane model (--lateral-resolution) is not supported");

@@ -449,7 +449,43 @@ SB2_HD bool lane_tryInsert(const Ctx& c, int l, int v) {
     if (pos < 0 || pos > c.lane_length[l]) {
         pos = c.lane_length[l];
     }
-    return lane_isInsertionSuccess(c, l, v, speed, pos, patchSpeed, patchSpeed || dsd != DSD_GIVEN, false);
+    const bool success = lane_isInsertionSuccess(c, l, v, speed, pos, patchSpeed, patchSpeed || dsd != DSD_GIVEN, false);
+    if (success && c.extrapolateDepartPos && c.t - c.veh_depart_param[v] > 0) {   // (veh_depart is rounded up to the step)
+        // --extrapolate-departpos (MSLane::insertVehicle, MSLane.cpp:797-815): the part of the step the vehicle is late is made up for by
+        // moving it forward at once, as far as its leader allows (MSLane::getLeader, MSLane.cpp:2957-3025; MSVehicle::executeFractionalMove)
+        const SUMOTime relevantDelay = c.t - c.veh_depart_param[v] < c.DELTA_T ? c.t - c.veh_depart_param[v] : c.DELTA_T;
+        const double vpos = c.veh_pos[v];
+        const double vspeed = c.veh_speed[v];
+        double dist = vspeed * STEPS2TIME(relevantDelay);
+        int leader = -1;
+        {
+            AnyVehIter it = any_begin(c, l);
+            for (int veh = any_next(c, l, it); veh >= 0; veh = any_next(c, l, it)) {
+                if (veh != v && veh_pos_on_lane(c, veh, l) >= vpos) {
+                    leader = veh;
+                    break;
+                }
+            }
+        }
+        if (leader >= 0) {
+            const double gap = veh_back_pos_on_lane(c, leader, l) - cf.minGap() - vpos;
+            const CF lcf = make_cf(c, c.veh_type[leader]);
+            const double frontGapNeeded = cf_getSecureGap(cf, vspeed, c.veh_speed[leader], lcf.decel());
+            dist = MIN2(dist, gap - frontGapNeeded);
+        } else if (c.lane_length[l] - vpos <= cf_brakeGap(cf, vspeed) + cf.minGap()) {
+            raise(c, ERR_UNSUPPORTED_LINKSTATE);   // the leader would have to be searched beyond the lane's end (getLeaderOnConsecutive): not modelled
+        }
+        if (dist > 0) {
+            if (vpos + dist > c.lane_length[l]) {
+                raise(c, ERR_UNSUPPORTED_LINKSTATE);   // executeFractionalMove across a lane end: not modelled
+            } else {
+                c.veh_pos[v] = vpos + dist;
+                c.veh_lastdist[v] = dist;
+                c.veh_backpos[v] = vpos + dist - cf.length();
+            }
+        }
+    }
+    return success;
 }
 
 // all due candidates of departure lane l, in load order
@@ -474,7 +510,7 @@ SB2_HDN void lane_insertVehicles(const Ctx& c, int l) {
                     if (c.veh_depart[w] > c.t) {
                         break;
                     }
-                    if (c.veh_lane[w] == -1 && c.t - c.veh_depart[w] > c.maxDepartDelay) {
+                    if (c.veh_lane[w] == -1 && c.t - c.veh_depart_param[w] > c.maxDepartDelay) {
                         c.veh_lane[w] = -4;
                         atomic_inc(&c.counters[15]);
                     }

@@ -278,6 +278,7 @@ struct Ctx {
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
     // ---- E2 lane area detectors on one lane (MSE2Collector as a move reminder, sb2_e2.h); nE2 == 0: one dummy element each
+    int extrapolateDepartPos;        // --extrapolate-departpos
     SUMOTime maxDepartDelay;         // --max-depart-delay (ms), -1 = off: a vehicle that could not depart for longer is discarded (veh_lane -4)
     int max_items;                   // drive items per vehicle (MAX_DRIVE_ITEMS unless the scenario asks for more)
     int nE2, e2_note_cap;

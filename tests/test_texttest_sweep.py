@@ -1,5 +1,5 @@
 """The reference's own texttest scenarios through the engine, in bulk (tools_dev/texttest_sweep.py; results of the full sweep over 4585
-test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 554 -- reproduces the reference's trajectories
+test directories in profiles/r02_texttest_sweep.tsv: every scenario the engine accepts -- 561 -- reproduces the reference's trajectories
 bit for bit, everything else is refused with a message, rejected by the reference itself, or has no vehicles).
 
 This test re-runs every eighth of the accepted scenarios: the reference's loader flattens the scenario and records the reference's
@@ -55,4 +55,4 @@ def test_reference_texttest_scenario_outside_the_scope_is_refused(rel, host_emul
 
 def test_sweep_file_has_no_divergence():
     text = open(SWEEP).read()
-    assert "\nDIFF\t" not in text and "\nFLOWDIFF\t" not in text and len(SAME) >= 550
+    assert "\nDIFF\t" not in text and "\nFLOWDIFF\t" not in text and len(SAME) >= 560
