@@ -84,13 +84,6 @@ SB2_HD void veh_e2_add_lane(const Ctx& c, int v, int lane, bool enter, double ba
             continue;
         }
         if (slot < 0) {
-#if !defined(__CUDA_ARCH__) && defined(SB2_E2_DEBUG)
-            fprintf(stderr, "E2 overflow t=%lld veh %d lane %d pos %.2f det %d:", (long long)c.t, v, lane, c.veh_pos[v], det);
-            for (int i = 0; i < MAX_E2_REMINDERS; i++) {
-                fprintf(stderr, " [det %d lane %d start %.1f len %.1f off %.1f]", c.veh_e2_det[E2_AT(i)], c.e2_lane[c.veh_e2_det[E2_AT(i)]], c.e2_start[c.veh_e2_det[E2_AT(i)]], c.e2_length[c.veh_e2_det[E2_AT(i)]], c.veh_e2_off[E2_AT(i)]);
-            }
-            fprintf(stderr, "\n");
-#endif
             raise(c, ERR_DETECTOR_OVERFLOW);
             continue;
         }
