@@ -185,7 +185,8 @@ int sumob200_lane_stats_all(sumob200_engine* e, sumob200_lane_stats* out, int ca
  * sumob200_e1_interval = MSInductLoop::writeXMLOutput (MSInductLoop.cpp:456-493) for every detector at once: the aggregates of the
  * interval [begin_ms, end_ms) that ends NOW (end_ms must be the engine's time: call it after the step that completes the period,
  * where MSDetectorControl::writeOutput(step + DELTA_T) fires), written to out[detector]; then MSInductLoop::reset.  The XML line
- * stays with the reference's writer.  Not supported together with sumob200_set_partition (SUMOB200_EUNSUPPORTED). */
+ * stays with the reference's writer.  Under sumob200_set_partition every rank reports the detectors on its own lanes (the others' records
+ * stay empty): merge by owner. */
 typedef struct sumob200_e1_interval_t {
     int32_t n_veh_contrib;        /* nVehContrib: vehicles that passed completely */
     int32_t n_veh_entered;        /* nVehEntered */
@@ -220,7 +221,7 @@ int sumob200_e1_drain(sumob200_engine* e, sumob200_e1_event* events, int capacit
  * runs MSE2Collector::detectorUpdate on the device (notifications sorted by distance to the detector's end, sums added in that order,
  * halting durations, jams).  sumob200_e2_interval = MSE2Collector::writeXMLOutput for every detector (the attributes of one
  * <interval .../>, durations in seconds), then MSE2Collector::reset.  Call it after the step that completes the period.
- * Not supported together with sumob200_set_partition (SUMOB200_EUNSUPPORTED). */
+ * Under sumob200_set_partition every rank reports the detectors on its own lanes: merge by owner. */
 typedef struct sumob200_e2_interval_t {
     double sampled_seconds;
     int32_t n_veh_entered, n_veh_left, n_veh_seen, max_jam_length_in_vehicles;

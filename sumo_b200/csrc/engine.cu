@@ -575,10 +575,6 @@ int sumob200_set_partition(sumob200_engine* e, const uint8_t* lane_vis, const in
         gLastError = "sumob200_set_partition: bad argument (or called twice)";
         return SUMOB200_EINVAL;
     }
-    if (e->d.nE1 > 0 || e->d.nE2 > 0) {
-        gLastError = "sumob200_set_partition: E1 / E2 detectors are not carried across partitions yet";
-        return SUMOB200_EUNSUPPORTED;
-    }
     const int nL = e->d.nL;
     for (int side = 0; side < 2; side++) {
         for (int i = 0; i < n_exp[side]; i++) {

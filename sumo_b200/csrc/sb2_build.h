@@ -597,6 +597,7 @@ public:
             h.nE1 = nD;
             int32_t* lb = add<int32_t>("lane_e1_begin", SB2_OFF(lane_e1_begin), (size_t)nL + 1, false, 0);
             int32_t* of = add<int32_t>("e1_of_lane", SB2_OFF(e1_of_lane), (size_t)nD, false, 0);
+            int32_t* el = add<int32_t>("e1_lane", SB2_OFF(e1_lane), (size_t)(nD > 0 ? nD : 1), false, 0);
             double* dp = add<double>("e1_pos", SB2_OFF(e1_pos), (size_t)nD, false, 0.);
             double* de = add<double>("e1_end", SB2_OFF(e1_end), (size_t)nD, false, 0.);
             if (nD > 0) {
@@ -614,6 +615,7 @@ public:
                     if (pos < 0 || len < 0 || pos + len > h.lane_length[dl[d]]) {
                         throw std::invalid_argument("sumob200: an E1 detector does not lie on its lane");
                     }
+                    el[d] = dl[d];
                     dp[d] = pos;
                     de[d] = pos + len;
                     lb[dl[d] + 1]++;
@@ -629,6 +631,7 @@ public:
             const size_t nR = nD > 0 ? (size_t)nV * MAX_E1_REMINDERS : 1;
             SB2_DYN(int32_t, veh_e1_det, nR, -1); SB2_DYN(double, veh_e1_off, nR, 0.); SB2_DYN(double, veh_e1_entry, nR, E1_NOT_ON);
             SB2_DYN(int32_t, e1_entered, (size_t)nD, 0);
+            SB2_DYN(int64_t, veh_sim_seen, (nD > 0 || ff.has("e2_lane")) ? (size_t)nV : 1, (int64_t)-1);
             // room for the passages of one output interval: every vehicle over a few detectors, or every detector a few thousand times
             h.e1_event_cap = nD > 0 ? (int)std::min<size_t>((size_t)1 << 26, std::max<size_t>((size_t)4 * nV + 65536, (size_t)64 * nD))
                                     : 1;

@@ -36,7 +36,13 @@ SB2_HD double cf_passingTime(const Ctx& c, double lastPos, double passedPos, dou
 SB2_HD double e1_simtime(const Ctx& c) { return (double)c.t / 1000.; }   // SIMTIME = STEPS2TIME(getCurrentTimeStep())
 
 // myVehicleDataCont.push_back(VehicleData(veh, entryTime, leaveTime, leftEarly, ...))
+// (edge partition: a detector is reported by the rank that owns its lane; the vehicles of the ghost column are executed redundantly)
+SB2_HD bool e1_owned(const Ctx& c, int det) { return lane_auth(c, c.e1_lane[det]); }
+
 SB2_HD void e1_push_event(const Ctx& c, int det, int v, double entry, double leave, bool leftEarly) {
+    if (!e1_owned(c, det)) {
+        return;
+    }
 #if defined(__CUDA_ARCH__)
     const int at = atomicAdd(&c.counters[12], 1);
 #else
@@ -54,11 +60,26 @@ SB2_HD void e1_push_event(const Ctx& c, int det, int v, double entry, double lea
 }
 
 SB2_HD void e1_count_entered(const Ctx& c, int det) {
+    if (!e1_owned(c, det)) {
+        return;
+    }
 #if defined(__CUDA_ARCH__)
     atomicAdd(&c.e1_entered[det], 1);
 #else
     c.e1_entered[det]++;
 #endif
+}
+
+// edge partition: a vehicle record received for a lane this rank does not simulate -- whatever reminders the slot still holds are
+// from an earlier visit of the vehicle to this rank's strip
+SB2_HD void veh_e1_forget(const Ctx& c, int v) {
+    if (!SB2_OBSERVERS || c.nE1 == 0) {
+        return;
+    }
+    for (int i = 0; i < MAX_E1_REMINDERS; i++) {
+        c.veh_e1_det[E1_AT(i)] = -1;
+        c.veh_e1_entry[E1_AT(i)] = E1_NOT_ON;
+    }
 }
 
 // MSVehicle::leaveLane(reason != NOTIFICATION_JUNCTION): notifyLeave of every reminder -> a vehicle on a detector leaves it early

@@ -18,10 +18,20 @@ namespace sb2 {
 
 #define E2_AT(i) ((size_t)(i) * c.nV + v)
 
-SB2_HD void e2_count(const Ctx& c, int det, int k) { atomic_inc(&c.e2_cnt[(size_t)k * c.nE2 + det]); }
+// (edge partition: a detector is reported by the rank that owns its lane)
+SB2_HD bool e2_owned(const Ctx& c, int det) { return lane_auth(c, c.e2_lane[det]); }
+
+SB2_HD void e2_count(const Ctx& c, int det, int k) {
+    if (e2_owned(c, det)) {
+        atomic_inc(&c.e2_cnt[(size_t)k * c.nE2 + det]);
+    }
+}
 
 // myMoveNotifications.push_back(makeMoveNotification(...))
 SB2_HD void e2_push_note(const Ctx& c, int det, int v, double dist, double timeOn, double lenOn, double timeLoss, double speed) {
+    if (!e2_owned(c, det)) {
+        return;
+    }
     const int buf = c.cur;
 #if defined(__CUDA_ARCH__)
     const int at = atomicAdd(&c.counters[13 + buf], 1);
@@ -41,6 +51,16 @@ SB2_HD void e2_push_note(const Ctx& c, int det, int v, double dist, double timeO
     c.e2_head[buf][det] = at;
 #endif
     c.e2_notes[buf][at] = n;
+}
+
+// edge partition: see veh_e1_forget
+SB2_HD void veh_e2_forget(const Ctx& c, int v) {
+    if (!SB2_OBSERVERS || c.nE2 == 0) {
+        return;
+    }
+    for (int i = 0; i < MAX_E2_REMINDERS; i++) {
+        c.veh_e2_det[E2_AT(i)] = -1;
+    }
 }
 
 // notifyLeave with a reason other than NOTIFICATION_JUNCTION (arrival, teleport): the VehicleInfo is erased at once

@@ -25,6 +25,7 @@
 #pragma once
 #include "sb2_types.h"
 #include "sb2_veh.h"
+#include "sb2_e2.h"
 
 namespace sb2 {
 
@@ -173,6 +174,13 @@ SB2_HDN void halo_clear_lane(const Ctx& c, const HaloSide& h, int i) {
         const int next = c.veh_behind[v];
         if (c.veh_lane[v] == l) {
             c.veh_lane[v] = (c.veh_depart_time[v] == c.t - c.DELTA_T) ? -1 : -5;
+            if (SB2_OBSERVERS && (c.nE1 > 0 || c.nE2 > 0) && lane_simulated(c, l)) {
+                c.veh_sim_seen[v] = c.t;   // executed here in the step that just ended: its move reminders are up to date
+                if (c.veh_lane[v] == -1) {
+                    veh_e1_forget(c, v);   // (a departure of the ghost column: redone below if the owner made it too)
+                    veh_e2_forget(c, v);
+                }
+            }
         }
         v = next;
     }
@@ -231,6 +239,25 @@ SB2_HDN void halo_unpack_vehicle(const Ctx& c, const void* msg, int i) {
         }
     }
     c.veh_deferred[v] = 0;
+    // move reminders (E1 / E2 detectors) are not part of the record: a vehicle on a lane this rank simulates (ghost column) keeps the
+    // ones its redundant execution gave it; on a lane it only reads (halo column) it has none that concern this rank; a teleporting
+    // vehicle has exactly those of the lane it virtually sits on (veh_transfer_add / transfer_checkInsertions)
+    if (r.kind == HV_TRANSFER) {
+        veh_e1_forget(c, v);
+        veh_e2_forget(c, v);
+        const int vl = c.edge_lane_begin[veh_succ_edge(c, v, 0)];
+        veh_e1_add_lane(c, v, vl, true, 0., -veh_length(c, v));
+        veh_e2_add_lane(c, v, vl, true, -veh_length(c, v));
+    } else if (SB2_OBSERVERS && (c.nE1 > 0 || c.nE2 > 0) && (r.lane < 0 || !lane_simulated(c, r.lane) || c.veh_sim_seen[v] != c.t)) {
+        // only read here, or it appears on the ghost column without having been executed here in this step (it drove in from the
+        // halo column, or a teleport ended there): no reminder of it concerns this rank's detectors
+        veh_e1_forget(c, v);
+        veh_e2_forget(c, v);
+    } else if (SB2_OBSERVERS && (c.nE1 > 0 || c.nE2 > 0) && r.kind == HV_QUEUE && r.depart_time == c.t - c.DELTA_T) {
+        // departed on the ghost column in the step that just ended (here too, see halo_clear_lane): addReminder + activateReminders
+        veh_e1_add_lane(c, v, r.lane, true, r.pos, r.pos - veh_length(c, v));
+        veh_e2_add_lane(c, v, r.lane, true, r.pos - veh_length(c, v));
+    }
     if (r.kind == HV_TRANSFER) {
 #if defined(__CUDA_ARCH__)
         const int at = atomicAdd(&c.counters[10], 1);

@@ -270,11 +270,13 @@ struct Ctx {
     int nE1, e1_event_cap;
     const int32_t* lane_e1_begin;    // [nL+1] CSR: detectors of a lane = e1_of_lane[lane_e1_begin[l] .. lane_e1_begin[l+1])
     const int32_t* e1_of_lane;       // [nE1] detector indices sorted by lane (load order within a lane)
+    const int32_t* e1_lane;          // [nE1] the detector's lane
     const double* e1_pos;            // [nE1] myPosition
     const double* e1_end;            // [nE1] myEndPosition = position + length
     int32_t* veh_e1_det;             // [MAX_E1_REMINDERS][nV] the vehicle's active reminders (MSBaseVehicle::myMoveReminders): detector or -1
     double* veh_e1_off;              // [MAX_E1_REMINDERS][nV] rem->second: length of the lanes left since the detector's lane
     double* veh_e1_entry;            // [MAX_E1_REMINDERS][nV] myVehiclesOnDet[veh] (entry time in s), E1_NOT_ON if not on the detector
+    SUMOTime* veh_sim_seen;          // [nV] (detectors + edge partition) time at which halo_clear_lane found the vehicle on a lane this rank simulates
     int32_t* e1_entered;             // [nE1] myEnteredVehicleNumber of the running interval
     struct E1Event* e1_events;       // [e1_event_cap] myVehicleDataCont of all detectors; length = counters[12]
     // ---- E2 lane area detectors on one lane (MSE2Collector as a move reminder, sb2_e2.h); nE2 == 0: one dummy element each

@@ -151,7 +151,8 @@ struct EmulPart {
     std::vector<char> sendBuf[2];
 };
 
-static int runPartitioned(const char* flatPath, const std::string& partFile, long maxSteps, const std::string& traceOut) {
+static int runPartitioned(const char* flatPath, const std::string& partFile, long maxSteps, const std::string& traceOut,
+                          const std::string& e1Out, long long e1Period, const std::string& e2Out, long long e2Period) {
     FILE* pf = fopen(partFile.c_str(), "rb");
     if (pf == nullptr) {
         fprintf(stderr, "cannot read %s\n", partFile.c_str());
@@ -201,6 +202,50 @@ static int runPartitioned(const char* flatPath, const std::string& partFile, lon
     }
     FILE* f = traceOut.empty() ? nullptr : fopen(traceOut.c_str(), "wb");
     const Ctx& c0 = parts[0]->m.h;
+    // detectors: every detector is reported by the partition that owns its lane; the interval lines are those of the single run
+    FILE* fe1 = e1Out.empty() ? nullptr : fopen(e1Out.c_str(), "w");
+    FILE* fe2 = e2Out.empty() ? nullptr : fopen(e2Out.c_str(), "w");
+    auto flushE1 = [&](SUMOTime from, SUMOTime to) {
+        std::vector<E1Event> ev;
+        std::vector<int32_t> entered((size_t)c0.nE1, 0);
+        for (EmulPart* e : parts) {
+            Ctx& c = e->m.h;
+            for (int v = 0; v < c.nV; v++) {
+                veh_e1_collect_on_detector(c, v);
+            }
+            const int n = std::min(c.counters[12], c.e1_event_cap);
+            ev.insert(ev.end(), c.e1_events, c.e1_events + n);
+            c.counters[12] = 0;
+            for (int d = 0; d < c.nE1; d++) {
+                entered[d] += c.e1_entered[d];
+                c.e1_entered[d] = 0;
+            }
+        }
+        std::vector<E1Result> res((size_t)c0.nE1);
+        e1_reduce(ev, entered.data(), c0.nE1, c0.e1_pos, c0.e1_end, from, to, res.data());
+        for (int d = 0; d < c0.nE1; d++) {
+            fprintf(fe1, "%lld %lld %d %d %.17g %.17g %.17g %.17g %.17g %d\n", (long long)from, (long long)to, d,
+                    res[d].nVehContrib, res[d].flow, res[d].occupancy, res[d].speed, res[d].harmonicMeanSpeed, res[d].length, res[d].nVehEntered);
+        }
+    };
+    auto flushE2 = [&](SUMOTime from, SUMOTime to) {
+        std::vector<E2Result> res((size_t)c0.nE2), scratch((size_t)c0.nE2);
+        for (EmulPart* e : parts) {
+            Ctx& c = e->m.h;
+            for (int d = 0; d < c.nE2; d++) {
+                e2_detector_readout(c, d, c.cur, e2_owned(c, d) ? res.data() : scratch.data());
+            }
+        }
+        for (int d = 0; d < c0.nE2; d++) {
+            const E2Result& r = res[d];
+            fprintf(fe2, "%lld %lld %d %.17g %d %d %d %.17g %.17g %.17g %.17g %.17g %.17g %d %.17g %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g %d %.17g %d\n",
+                    (long long)from, (long long)to, d, r.sampledSeconds, r.nVehEntered, r.nVehLeft, r.nVehSeen, r.meanSpeed, r.meanTimeLoss, r.meanOccupancy,
+                    r.maxOccupancy, r.meanMaxJamLengthInVehicles, r.meanMaxJamLengthInMeters, r.maxJamLengthInVehicles, r.maxJamLengthInMeters,
+                    r.jamLengthInVehiclesSum, r.jamLengthInMetersSum, r.meanHaltingDuration, r.maxHaltingDuration, r.haltingDurationSum,
+                    r.meanIntervalHaltingDuration, r.maxIntervalHaltingDuration, r.intervalHaltingDurationSum, r.startedHalts, r.meanVehicleNumber,
+                    r.maxVehicleNumber);
+        }
+    };
     std::vector<int> order(c0.nV);
     for (int v = 0; v < c0.nV; v++) {
         order[v] = v;
@@ -266,6 +311,12 @@ static int runPartitioned(const char* flatPath, const std::string& partFile, lon
                 e->m.h.fleet_next[k] = agg[k];
             }
         }
+        if (fe1 != nullptr && c0.nE1 > 0 && (t + c0.DELTA_T) % e1Period == 0) {
+            flushE1(t + c0.DELTA_T - e1Period, t + c0.DELTA_T);
+        }
+        if (fe2 != nullptr && c0.nE2 > 0 && (t + c0.DELTA_T) % e2Period == 0) {
+            flushE2(t + c0.DELTA_T - e2Period, t + c0.DELTA_T);
+        }
         // merged trace
         std::vector<int> owner(c0.nV, -1);
         int n = 0;
@@ -304,6 +355,12 @@ static int runPartitioned(const char* flatPath, const std::string& partFile, lon
     }
     if (f != nullptr) {
         fclose(f);
+    }
+    if (fe1 != nullptr) {
+        fclose(fe1);
+    }
+    if (fe2 != nullptr) {
+        fclose(fe2);
     }
     int inserted = 0, arrived = 0, teleports = 0;
     for (EmulPart* e : parts) {
@@ -371,7 +428,7 @@ int main(int argc, char** argv) {
     }
     if (!partFile.empty()) {
         try {
-            return runPartitioned(argv[1], partFile, maxSteps, traceOut);
+            return runPartitioned(argv[1], partFile, maxSteps, traceOut, e1Out, e1Period, e2Out, e2Period);
         } catch (const std::exception& e) {
             fprintf(stderr, "%s\n", e.what());
             return 1;

@@ -55,6 +55,29 @@ def test_partitioned_emulation_matches_reference(case, world, host_emul, tmp_pat
     assert assert_traces_identical(ref, load_trace(out)) > 1000
 
 
+@pytest.mark.parametrize("case,world", [("c1_grid10", 2), ("c1_grid10", 3), ("grid5_dense", 2)])
+def test_partitioned_emulation_reports_the_detectors_of_the_single_run(case, world, host_emul, tmp_path):
+    """E1 and E2 detectors under the edge partition: a detector is reported by the partition that owns its lane (vehicles of the
+    ghost column are executed redundantly; reminders are forgotten when a vehicle is only read, rebuilt for a teleporting one).
+    The merged interval lines must be the single run's -- which tests/test_detectors.py / test_e2_detectors.py pin to the
+    reference's files -- character by character."""
+    from test_detectors import detector_case
+    from test_e2_detectors import e2_case
+    for kind, (flat, trace, _), flag in (("e1", detector_case(case), "--e1"), ("e2", e2_case(case), "--e2")):
+        n = len(load_trace(trace))
+        part = str(tmp_path / (kind + ".part"))
+        partition.write_partition_file(part, load_flat(flat), world)
+        one, many = str(tmp_path / (kind + ".one.txt")), str(tmp_path / (kind + ".many.txt"))
+        subprocess.run([host_emul, flat, flag + "-out", one, flag + "-period", "30000", "--steps", str(n)], check=True, timeout=900, stderr=subprocess.DEVNULL)
+        r = subprocess.run([host_emul, flat, "--partitions", part, flag + "-out", many, flag + "-period", "30000", "--steps", str(n)],
+                           capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0 and "errors=0" in r.stderr, r.stderr[-2000:]
+        a = open(one).read().splitlines()
+        b = open(many).read().splitlines()
+        # (the single run also writes the partial interval at the end of the simulation)
+        assert len(b) > 200 and a[:len(b)] == b, next((x, y) for x, y in zip(a, b) if x != y)
+
+
 def _worker(rank, world, port, out):
     import torch
     import torch.distributed as dist
@@ -148,6 +171,55 @@ def test_partitioned_edgedata_sums_to_the_single_engine(world):
     for k in ("sample_seconds", "travelled_distance", "wait_seconds", "time_loss", "front_sample_seconds", "front_travelled_distance",
               "veh_length_sum", "occupation_sum", "minimal_vehicle_length"):
         assert np.allclose(merged[k], want[k], rtol=1e-9, atol=1e-9), k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,world", [("c1_grid10", 3), ("grid5_dense", 2)])
+def test_partitioned_detectors_equal_the_single_engine(case, world):
+    """E1 and E2 detectors under the edge partition on the device: every rank reports the detectors on its OWN lanes; merged by
+    owner the interval records equal one engine over the whole network (the E2 sums bit for bit: they are added per detector in
+    sorted order; E1 means are reduced from the same events)."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs CUDA")
+    from test_detectors import detector_case
+    from test_e2_detectors import e2_case
+    from sumo_b200.engine import Engine
+    for kind, (flat, trace, _) in (("e1", detector_case(case)), ("e2", e2_case(case))):
+        g = load_flat(flat)
+        steps = (len(load_trace(trace)) // 30) * 30
+        det_lane = g[kind + "_lane"]
+
+        def read(eng):
+            return eng.e1_interval(eng.time_ms - 30000, eng.time_ms).copy() if kind == "e1" else eng.e2_interval().copy()
+        want = []
+        with Engine(flat) as one:
+            for _ in range(steps // 30):
+                one.step(30, result=False)
+                want.append(read(one))
+        run = partition.LocalPartitionedRun(g, world)
+        try:
+            got = []
+            for k in range(steps):
+                run.step()
+                if (k + 1) % 30 == 0:
+                    merged = np.zeros_like(want[0])
+                    seen = np.zeros(len(det_lane), int)
+                    for p in run.parts:
+                        rows = read(p["eng"])
+                        own = p["plan"]["lane_vis"][det_lane] == partition.LV_AUTH
+                        merged[own] = rows[own]
+                        seen[own] += 1
+                    assert (seen == 1).all()
+                    got.append(merged)
+        finally:
+            run.close()
+        busy = 0
+        for a, b in zip(want, got):
+            for name in a.dtype.names:
+                assert np.array_equal(a[name], b[name]), (kind, name)
+            busy += int((a["n_veh_entered"] > 0).sum())
+        assert busy > 200
 
 
 @pytest.mark.gpu
