@@ -284,6 +284,25 @@ class PartitionedEngine:
     def phase_times(self, reset=True):
         return self.eng.phase_times(reset)
 
+    def _merge_owned(self, rows, det_lane):
+        """detector records of all ranks merged: a detector is reported by the rank that owns its lane, the rows of the others are
+        zeroed and the byte-wise sum over the ranks (one all-reduce) is the owner's row"""
+        torch = self.torch
+        own = self.plan["lane_vis"][np.asarray(det_lane)] == LV_AUTH
+        raw = np.ascontiguousarray(rows).view(np.uint8).reshape(len(rows), rows.dtype.itemsize).copy()
+        raw[~own] = 0
+        buf = torch.from_numpy(raw).to(self.dev)
+        self.dist.all_reduce(buf)
+        return buf.cpu().numpy().reshape(-1).view(rows.dtype).copy()
+
+    def e1_interval(self, begin_ms, end_ms, det_lane):
+        """Engine.e1_interval for the whole network (det_lane = the scenario's e1_lane array); collective: every rank calls it"""
+        return self._merge_owned(self.eng.e1_interval(begin_ms, end_ms), det_lane)
+
+    def e2_interval(self, det_lane):
+        """Engine.e2_interval for the whole network (det_lane = the scenario's e2_lane array); collective: every rank calls it"""
+        return self._merge_owned(self.eng.e2_interval(), det_lane)
+
     @property
     def kernel_launches(self):
         return self.eng.kernel_launches

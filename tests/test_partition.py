@@ -229,9 +229,10 @@ def test_two_gpus_over_nccl_match_reference():
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
-    flat, trace = reference_case("c1_grid10")
+    from test_e2_detectors import e2_case
+    flat, trace, _ = e2_case("c1_grid10")      # (with E2 detectors: the tool also checks the collective interval read-out)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                         "--master-port", "29655", os.path.join(ROOT, "tools_dev", "partition_nccl_check.py"), flat, trace],
                        capture_output=True, text=True, timeout=1200)
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
-    assert "PARTITION-NCCL-OK" in r.stdout
+    assert "PARTITION-NCCL-OK" in r.stdout and "PARTITION-NCCL-E2 OK" in r.stdout

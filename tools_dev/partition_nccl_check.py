@@ -25,6 +25,13 @@ def main():
     order = np.argsort(numid, kind="stable")
     eng = PartitionedEngine(g, dist, rank, world, device=local)
     vis = eng.plan["lane_vis"]
+    # scenario with E2 detectors: rank 0 also runs ONE engine over the whole network; the merged interval records (a collective
+    # read-out every 30 steps) must be that engine's, field by field
+    one = None
+    det_ok, det_rows = True, 0
+    if "e2_lane" in g and rank == 0:
+        from sumo_b200.engine import Engine
+        one = Engine(g, device=local)
     compared = torch.zeros(2, dtype=torch.int64, device="cuda")
     ok = True
     for (t, ids, lanes, pos, speed) in ref:
@@ -40,7 +47,19 @@ def main():
             break
         compared[0] += int(on.sum())
         compared[1] += len(ids)
+        if one is not None:
+            one.step(1, result=False)
+        if "e2_lane" in g and eng.time_ms % 30000 == 0:
+            merged = eng.e2_interval(g["e2_lane"])
+            if one is not None:
+                want = one.e2_interval()
+                det_ok = det_ok and all(np.array_equal(want[k], merged[k]) for k in want.dtype.names)
+                det_rows += int((want["n_veh_entered"] > 0).sum())
     eng.close()
+    if one is not None:
+        one.close()
+        print("PARTITION-NCCL-E2 %s (%d busy interval records)" % ("OK" if det_ok and det_rows > 100 else "FAILED", det_rows), flush=True)
+        ok = ok and det_ok and det_rows > 100
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.all_reduce(compared[:1])
